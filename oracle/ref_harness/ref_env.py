@@ -143,6 +143,10 @@ class RefDcaEnv(object):
         self.episode = -1
         self.obs_counter = -1
         self._list_idx = 0
+        # class-level cache of the flat table size (collective_assault_env.py:181-204) is per-process state:
+        # clear it so envs of different N can live in one harness process
+        from MISSION.dca.collective_assault_env import collective_assaultEnvV1
+        collective_assaultEnvV1.raw_obs_size = -1
         np.random.seed(np_seed)  # planner's kmeans2 seeds still come from the global stream
         if autoreset:
             from UTIL.shm_env import EnvAutoReset
