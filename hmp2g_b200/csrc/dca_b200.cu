@@ -1,0 +1,211 @@
+// dca_b200.cu -- C-ABI (include/dca_b200.h) over the kernels in dca_kernels.cuh.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "dca_kernels.cuh"
+
+using namespace dca;
+
+struct DcaHandle {
+    Params P;
+    int device;
+    int threads;
+    int smem;
+    bool bound;
+    int64_t launches;
+    std::string err;
+};
+
+static thread_local std::string g_err;
+
+static int fail(DcaHandle *h, int code, const std::string &msg) {
+    if (h) h->err = msg;
+    g_err = msg;
+    return code;
+}
+
+#define CUDA_TRY(h, expr)                                                                      \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return fail(h, DCA_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));     \
+    } while (0)
+
+namespace {
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+}  // namespace
+
+extern "C" {
+
+int dca_abi_version(void) { return 1; }
+
+const char *dca_last_error(const DcaHandle *h) { return h ? h->err.c_str() : g_err.c_str(); }
+
+int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
+    if (!cfg || !out || n_env <= 0) return fail(nullptr, DCA_E_INVALID, "dca_create: null argument or n_env <= 0");
+    *out = nullptr;
+    const int G = cfg->num_guards, A = cfg->num_attackers;
+    // the reference observation needs >= 6 candidates per team (argsort()[:6], collective_assault_env.py:308-309)
+    if (G < kVisN || A < kVisN || G > 250 || A > 250 || G + A > kMaxN)
+        return fail(nullptr, DCA_E_INVALID, "dca_create: need 6 <= num_guards, num_attackers <= 250 and N <= 320");
+    if (cfg->enable_attacker_fluctuation && (cfg->attacker_fluctuation < 0 || cfg->attacker_fluctuation > A))
+        return fail(nullptr, DCA_E_INVALID, "dca_create: attacker_fluctuation out of range");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, DCA_E_NODEVICE, "dca_create: no CUDA device (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(nullptr, DCA_E_INVALID, "dca_create: bad device index");
+    DeviceGuard guard(device);
+    DcaHandle *h = new (std::nothrow) DcaHandle();
+    if (!h) return fail(nullptr, DCA_E_INVALID, "dca_create: out of host memory");
+    h->device = device;
+    h->bound = false;
+    h->launches = 0;
+    std::memset(&h->P, 0, sizeof(Params));
+    h->P.cfg = *cfg;
+    h->P.L = make_layout(G, A);
+    h->P.E = n_env;
+    h->threads = (G + A) <= 128 ? 128 : 256;
+    h->smem = smem_bytes(h->P.L);
+    const size_t bytes = (size_t)n_env * h->P.L.bytes;
+    cudaError_t e = cudaMalloc((void **)&h->P.blobs, bytes);
+    if (e == cudaSuccess) e = cudaMemset(h->P.blobs, 0, bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_reset, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_observe, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+    if (e == cudaSuccess) {
+        k_init_blobs<<<(n_env + 255) / 256, 256>>>(h->P);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        const int rc = fail(nullptr, DCA_E_CUDA, std::string("dca_create: ") + cudaGetErrorString(e));
+        if (h->P.blobs) cudaFree(h->P.blobs);
+        delete h;
+        return rc;
+    }
+    h->launches += 1;
+    *out = h;
+    return DCA_OK;
+}
+
+int dca_destroy(DcaHandle *h) {
+    if (!h) return DCA_E_INVALID;
+    DeviceGuard guard(h->device);
+    cudaFree(h->P.blobs);
+    delete h;
+    return DCA_OK;
+}
+
+int dca_bind_buffers(DcaHandle *h, const DcaBuffers *b) {
+    if (!h || !b) return fail(h, DCA_E_INVALID, "dca_bind_buffers: null argument");
+    if (!b->obs || !b->reward || !b->done || !b->win)
+        return fail(h, DCA_E_INVALID, "dca_bind_buffers: obs, reward, done and win are required");
+    if (((uintptr_t)b->obs & 15) || (b->tobs && ((uintptr_t)b->tobs & 15)))
+        return fail(h, DCA_E_INVALID, "dca_bind_buffers: obs/tobs must be 16-byte aligned");
+    h->P.out = *b;
+    h->bound = true;
+    return DCA_OK;
+}
+
+static int check_ready(DcaHandle *h, const char *who) {
+    if (!h) return fail(nullptr, DCA_E_INVALID, std::string(who) + ": null handle");
+    if (!h->bound) return fail(h, DCA_E_UNBOUND, std::string(who) + ": call dca_bind_buffers first");
+    return DCA_OK;
+}
+
+int dca_reset(DcaHandle *h, const uint8_t *env_mask, dca_stream_t stream) {
+    if (int rc = check_ready(h, "dca_reset")) return rc;
+    DeviceGuard guard(h->device);
+    k_reset<<<h->P.E, h->threads, h->smem, (cudaStream_t)stream>>>(h->P, env_mask);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 1;
+    return DCA_OK;
+}
+
+int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, const uint8_t *skip,
+             const uint32_t *rng_words, int autoreset, dca_stream_t stream) {
+    if (int rc = check_ready(h, "dca_step")) return rc;
+    if (!actions || !att_force) return fail(h, DCA_E_INVALID, "dca_step: actions and att_force are required");
+    if (((uintptr_t)att_force & 15) || (rng_words && ((uintptr_t)rng_words & 15)))
+        return fail(h, DCA_E_INVALID, "dca_step: att_force / rng_words must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    k_step<<<h->P.E, h->threads, h->smem, (cudaStream_t)stream>>>(h->P, actions, att_force, skip, rng_words, autoreset);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 1;
+    return DCA_OK;
+}
+
+int dca_observe(DcaHandle *h, const uint32_t *rng_words, dca_stream_t stream) {
+    if (int rc = check_ready(h, "dca_observe")) return rc;
+    DeviceGuard guard(h->device);
+    k_observe<<<h->P.E, h->threads, h->smem, (cudaStream_t)stream>>>(h->P, rng_words);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 1;
+    return DCA_OK;
+}
+
+int dca_plan_centroid(DcaHandle *h, double *att_force, dca_stream_t stream) {
+    if (!h || !att_force) return fail(h, DCA_E_INVALID, "dca_plan_centroid: null argument");
+    DeviceGuard guard(h->device);
+    const int threads = 128, warps_per_block = threads / 32;
+    k_plan_centroid<<<(h->P.E + warps_per_block - 1) / warps_per_block, threads, 0, (cudaStream_t)stream>>>(h->P, att_force);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 1;
+    return DCA_OK;
+}
+
+static int state_io(DcaHandle *h, const DcaState *st, int import, dca_stream_t stream) {
+    if (!h || !st) return fail(h, DCA_E_INVALID, "dca_state_io: null argument");
+    const void *ptrs[] = {st->pos, st->vel, st->atk_rad, st->terrain, st->alive, st->just_died, st->hit, st->was_hit,
+                          st->num_hit, st->num_was_hit, st->init_theta, st->time_step, st->n_alive_guards,
+                          st->n_alive_attackers, st->obs_counter, st->episode};
+    for (const void *p : ptrs)
+        if (!p) return fail(h, DCA_E_INVALID, "dca_state_io: every DcaState pointer is required");
+    DeviceGuard guard(h->device);
+    const size_t total = (size_t)h->P.E * h->P.L.N;
+    const int blocks = (int)((total + 255) / 256);
+    k_state_io<<<blocks, 256, 0, (cudaStream_t)stream>>>(h->P, *st, import);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 1;
+    return DCA_OK;
+}
+
+int dca_export_state(DcaHandle *h, const DcaState *dst, dca_stream_t stream) { return state_io(h, dst, 0, stream); }
+int dca_import_state(DcaHandle *h, const DcaState *src, dca_stream_t stream) { return state_io(h, src, 1, stream); }
+
+int dca_gae(const float *reward, const float *value, const uint8_t *dead, const int32_t *traj_len, float *ret,
+            float *threat, float *reward_pushed, int T, int E, int G, double gamma, double tau, int threat_limit,
+            dca_stream_t stream) {
+    if (!reward || !value || !dead || !ret || T <= 0 || E <= 0 || G <= 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_gae: null argument or empty shape");
+    const size_t S = (size_t)E * G;
+    const int threads = 128;
+    k_gae<<<(unsigned)((S + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+        reward, value, dead, traj_len, ret, threat, reward_pushed, T, E, G, gamma, tau, threat_limit);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_gae: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_kernel_launches(const DcaHandle *h, int64_t *count) {
+    if (!h || !count) return DCA_E_INVALID;
+    *count = h->launches;
+    return DCA_OK;
+}
+
+}  // extern "C"

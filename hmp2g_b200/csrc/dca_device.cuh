@@ -1,0 +1,162 @@
+// dca_device.cuh -- device-side building blocks of the DCA hot path (sm_100a).
+//
+// Data layout in HBM: one 128-byte aligned "env blob" per env holding the complete entity state as
+// structure-of-arrays (field arrays of length N inside the blob) followed by the env scalars.  A CTA owns one
+// env: the blob is fetched into shared memory with ONE 1-D TMA bulk copy (cp.async.bulk + mbarrier), every
+// phase of the step works on shared memory, and the blob goes back with one bulk store.  The observation
+// tile [G,12,16] f32 is written straight from the shared entity table with 128-bit coalesced stores.
+//
+// Arithmetic follows the reference rounding for rounding (compile with -fmad=false): fp64 state, fp32
+// entity table, fp32 distance = sqrt_rn(fl(dx*dx)+fl(dy*dy)) (collective_assault_env.py:276,286,361-368).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "../../include/dca_b200.h"
+
+namespace dca {
+
+constexpr int kVisN = 6;
+constexpr int kObsRows = DCA_OBS_ROWS;
+constexpr int kObsRow = DCA_OBS_ROW;
+constexpr int kObsLen = kObsRows * kObsRow;  // 192 f32 per guard
+constexpr int kMaxN = 320;                   // reference allows up to 150 + 150 (parallel_run.py:37-38)
+constexpr double kPi = 3.141592653589793;    // np.pi
+
+// flag bits of the per-agent state byte
+enum : uint8_t { F_ALIVE = 1, F_JUST_DIED = 2, F_HIT = 4, F_WAS_HIT = 8 };
+
+__host__ __device__ inline int align_up(int x, int a) { return (x + a - 1) / a * a; }
+
+// Byte offsets of the fields inside one env blob.
+struct BlobLayout {
+    int N, G, A;
+    int px, py, vx, vy, atk, terrain;  // f64[N]
+    int num_hit, num_was_hit;          // i32[N]
+    int flags;                         // u8[N]
+    int scalars;                       // EnvScalars
+    int bytes;                         // multiple of 128
+};
+
+struct EnvScalars {
+    double init_theta;
+    int32_t time_step, n_alive_guards, n_alive_attackers;
+    uint32_t obs_counter, episode;
+    uint32_t pad;
+};
+static_assert(sizeof(EnvScalars) == 32, "EnvScalars must stay 32 bytes");
+
+__host__ __device__ inline BlobLayout make_layout(int G, int A) {
+    BlobLayout L;
+    L.G = G; L.A = A; L.N = G + A;
+    int o = 0;
+    const int f64 = align_up(L.N * 8, 16), i32 = align_up(L.N * 4, 16), u8 = align_up(L.N, 16);
+    L.px = o; o += f64; L.py = o; o += f64; L.vx = o; o += f64; L.vy = o; o += f64;
+    L.atk = o; o += f64; L.terrain = o; o += f64;
+    L.num_hit = o; o += i32; L.num_was_hit = o; o += i32;
+    L.flags = o; o += u8;
+    L.scalars = o; o += (int)sizeof(EnvScalars);
+    L.bytes = align_up(o, 128);
+    return L;
+}
+
+// Kernel parameters shared by every kernel (passed by value: lands in constant bank).
+struct Params {
+    DcaConfig cfg;
+    BlobLayout L;
+    int E;
+    unsigned char *blobs;  // [E, L.bytes]
+    DcaBuffers out;
+};
+
+// ------------------------------------------------------------------ Philox4x32-10 (keyed RNG stream)
+enum : uint32_t { SITE_OBS = 1, SITE_RESET = 2 };
+
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                               uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+// ------------------------------------------------------------------ exact-semantics math helpers
+// Python / numpy floored float modulo (CPython float_rem, numpy npy_divmod).
+__device__ __forceinline__ double py_fmod(double a, double b) {
+    double m = fmod(a, b);
+    if (m != 0.0) {
+        if ((b < 0) != (m < 0)) m += b;
+    } else {
+        m = copysign(0.0, b);
+    }
+    return m;
+}
+// reg_angle core.py:284-285 == reg_rad cython_func.pyx:16-17
+__device__ __forceinline__ double reg_angle(double rad) { return py_fmod(rad + kPi, 2 * kPi) - kPi; }
+
+// np.logaddexp(0, y)
+__device__ __forceinline__ double logaddexp0(double y) {
+    if (y == 0.0) return 0.693147180559945309417232121458176568;
+    const double tmp = 0.0 - y;
+    if (tmp > 0) return 0.0 + log1p(exp(-tmp));
+    else if (tmp <= 0) return y + log1p(exp(tmp));
+    return tmp;
+}
+
+// float32 distance exactly as distance_matrix() evaluates it (collective_assault_env.py:361-368)
+__device__ __forceinline__ float f32_dist(float xi, float yi, float xj, float yj) {
+    const float dx = __fsub_rn(xj, xi), dy = __fsub_rn(yj, yi);
+    return __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+}
+
+// ------------------------------------------------------------------ TMA bulk copy (1-D) + mbarrier
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(phase)
+            : "memory");
+    } while (!ok);
+}
+// global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// shared -> global bulk store
+__device__ __forceinline__ void tma_store_1d(void *gdst, const void *smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit_wait() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+}  // namespace dca

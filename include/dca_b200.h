@@ -1,0 +1,132 @@
+/* dca_b200.h -- C-ABI of libdca_b200.so: the B200-native replacement of HMAP's DCA batched
+ * env step + observation + GAE hot path.
+ *
+ * Nothing comparable exists in the reference as a native interface: today's "ABI" is pickled Python
+ * tuples (name, 'step', args) pushed through POSIX shm to worker processes
+ * (/root/reference/UTIL/shm_pool.pyx:168-181, :307-376).  Each entry point below names the reference
+ * Python interface it replaces.  Binding stubs (ctypes, as a maintainer of the reference would add
+ * them in UTIL/shm_env.py) are in INTEGRATION.md.
+ *
+ * Conventions: return 0 = ok, negative = DCA_E_* ; never throws; kernels are enqueued on the given
+ * stream and NOT synchronised; no allocation after dca_create; the caller owns every buffer passed
+ * in DcaBuffers (normally torch CUDA tensors); the library owns only its private state store.
+ * A handle is not thread-safe (the reference caller is single-threaded, task_runner.py:59-72);
+ * distinct handles are independent.  All pointers are DEVICE pointers unless marked host.
+ */
+#ifndef DCA_B200_H
+#define DCA_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DCA_OK 0
+#define DCA_E_INVALID (-1)   /* bad argument / unsupported size */
+#define DCA_E_CUDA (-2)      /* CUDA runtime error, see dca_last_error */
+#define DCA_E_UNBOUND (-3)   /* dca_bind_buffers not called */
+#define DCA_E_NODEVICE (-4)  /* no CUDA device: there is NO CPU fallback */
+
+#define DCA_OBS_ROWS 12  /* 6 friend rows (row 0 = self) + 6 hostile rows, collective_assault_env.py:344 */
+#define DCA_OBS_ROW 16   /* entity record length, ScenarioConfig.obs_vec_length parallel_run.py:70 */
+#define DCA_RNG_WORDS 12 /* u32 words per (guard, list) in an injected observation stream */
+
+/* POD snapshot of ScenarioConfig, taken at env construction like the reference does
+ * (MISSION/dca/collective_assault_parallel_run.py:30-101; read at core.py:72-73,
+ * collective_assault_env.py:10-13). */
+typedef struct DcaConfig {
+    int32_t num_guards, num_attackers;
+    double agent_acc, agent_max_speed, agent_max_rot;
+    double agent_shoot_base_radius, agent_shoot_win;
+    double random_jam_prob;
+    int32_t introduce_terrain;
+    double terrain_A, terrain_B; /* terrain_parameters[0], [1] */
+    int32_t max_episode_step;
+    double init_distance;
+    int32_t enable_attacker_fluctuation, attacker_fluctuation;
+    double size;
+    int32_t half_death_reward, reward_debug;
+    double reward_debug_value;
+    int32_t disable_red_function; /* DISALBE_RED_FUNCTION (sic) */
+    uint64_t seed;                /* key of the counter-based RNG; replaces SmartPool's base_seed+index, shm_pool.pyx:186 */
+    int64_t env_gid0;             /* global id of local env 0 (multi-GPU sharding: rank r owns [gid0, gid0+E)) */
+} DcaConfig;
+
+/* Output buffers, bound once; written in place every step (zero-copy hand-off to the torch policy).
+ * Replaces the tuple (ob, reward, done, info) of EnvAutoReset.step UTIL/shm_env.py:33-74 and the
+ * np.stack in SuperpoolEnv.step UTIL/shm_env.py:145-153. */
+typedef struct DcaBuffers {
+    float *obs;       /* [E,G,12,16] post-step obs (post-RESET obs where done, shm_env.py:58) */
+    float *tobs;      /* [E,G,12,16] terminal obs = info['obs-echo'], written where done; may be NULL */
+    float *reward;    /* [E,G] */
+    uint8_t *done;    /* [E] */
+    uint8_t *win;     /* [E] info['win'], valid where done */
+    uint8_t *alive;   /* [E,N] alive mask after the step (after reset where done); may be NULL */
+    int16_t *slot_id; /* [E,G,12] entity id gathered into each obs row, -1 = zero row; may be NULL */
+    int32_t *nearest; /* [E,A] guard index each alive attacker aimed at (-1 dead); may be NULL */
+} DcaBuffers;
+
+/* Full env state in the oracle's SoA layout, for import/export (parity harness, checkpointing; the
+ * reference never checkpoints env state).  Device pointers. */
+typedef struct DcaState {
+    double *pos;     /* [E,N,2] */
+    double *vel;     /* [E,N,2] */
+    double *atk_rad; /* [E,N] */
+    double *terrain; /* [E,N] */
+    uint8_t *alive, *just_died, *hit, *was_hit; /* [E,N] */
+    int32_t *num_hit, *num_was_hit;             /* [E,N] */
+    double *init_theta;                         /* [E] */
+    int32_t *time_step, *n_alive_guards, *n_alive_attackers; /* [E] */
+    uint32_t *obs_counter, *episode;            /* [E] */
+} DcaState;
+
+typedef struct DcaHandle DcaHandle;
+typedef void *dca_stream_t; /* cudaStream_t */
+
+/* replaces: SuperpoolEnv.__init__ -> SmartPool.add_target('env', EnvAutoReset, ...) UTIL/shm_env.py:126-141,
+ * make_collective_assault_env parallel_run.py:103-117.  Allocates the state store for n_env envs on `device`. */
+int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out);
+int dca_destroy(DcaHandle *h);
+int dca_bind_buffers(DcaHandle *h, const DcaBuffers *bufs);
+
+/* replaces: SuperpoolEnv.reset UTIL/shm_env.py:155-164 / EnvAutoReset._real_reset :95-97 ->
+ * collective_assaultGlobalEnv.reset parallel_run.py:248-270.  env_mask: u8[E] (NULL = all envs). */
+int dca_reset(DcaHandle *h, const uint8_t *env_mask, dca_stream_t stream);
+
+/* replaces: SuperpoolEnv.step UTIL/shm_env.py:145-153 -> EnvAutoReset.step :33-74 ->
+ * collective_assaultGlobalEnv.step parallel_run.py:192-246 (World.step core.py:189-207).
+ *   actions   i32[E,G]   discrete 0..6 (parallel_run.py:337-343)
+ *   att_force f64[E,A,2] scripted-attacker planner output attacker.act[0:2] (cheat_script_ai.py:183-184)
+ *   skip      u8[E] or NULL: 1 = ENV-PAUSE (NaN action row, shm_env.py:37-41): env untouched, outputs keep last values
+ *   rng_words u32[E,G,2,12] or NULL: injected observation stream; NULL = in-kernel Philox4x32-10 (same words)
+ *   autoreset != 0: EnvAutoReset semantics (terminal obs -> tobs, reset, obs = reset obs) */
+int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, const uint8_t *skip,
+             const uint32_t *rng_words, int autoreset, dca_stream_t stream);
+
+/* Observation pass only (the k-nearest-neighbour gather kernel on the resident state):
+ * collective_assaultEnvV1.observation collective_assault_env.py:228-359 for every guard.
+ * Advances the per-env observation counter like any other pass. */
+int dca_observe(DcaHandle *h, const uint32_t *rng_words, dca_stream_t stream);
+
+/* Benchmark planner stand-in (NOT the reference planner): force = centroid(alive guards) - pos. */
+int dca_plan_centroid(DcaHandle *h, double *att_force, dca_stream_t stream);
+
+int dca_export_state(DcaHandle *h, const DcaState *dst, dca_stream_t stream);
+int dca_import_state(DcaHandle *h, const DcaState *src, dca_stream_t stream);
+
+/* replaces: trajectory.finalize / reward_push_forward / gae_finalize_return
+ * ALGORITHM/conc/trajectory.py:60-117 (= ALGORITHM/common/traj_gae.py:54-133), batched over a
+ * rollout buffer [T,E,G]; one trajectory per env column of length traj_len[e] (NULL = T).
+ * reward f32 in; ret/threat f32 out; reward_pushed (f32, may be NULL) = reward after push-forward. */
+int dca_gae(const float *reward, const float *value, const uint8_t *dead, const int32_t *traj_len,
+            float *ret, float *threat, float *reward_pushed, int T, int E, int G,
+            double gamma, double tau, int threat_limit, dca_stream_t stream);
+
+const char *dca_last_error(const DcaHandle *h); /* host string; h may be NULL for create/gae errors */
+int dca_kernel_launches(const DcaHandle *h, int64_t *count); /* kernels launched through this handle so far */
+int dca_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
