@@ -1,0 +1,303 @@
+"""bench.py -- DCA 50v50 step+obs throughput (agent-steps/s) on N B200s, with roofline and CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one batch: the planner stand-in kernel (attacker forces) + the fused
+step/observation/autoreset kernel for every env of this rank.  Workload (BASELINE.json configs[1]): DCA 50v50, 4096
+parallel envs per GPU, random guard actions injected from a pre-generated device pool, terrain on, jam 0.05.
+Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for every definition.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+import numpy as np  # noqa: E402
+
+WORKLOAD = dict(num_guards=50, num_attackers=50, size=5.0, random_jam_prob=0.05, introduce_terrain=True,
+                terrain_parameters=[0.05, 0.2], MaxEpisodeStep=180, half_death_reward=True, init_distance=4)
+ENVS_PER_GPU = 4096
+SEED = 20240
+# algorithmic bytes per env-step, 50v50 = obs 38400 + state r/w 12000 + actions 200 +
+# attacker force 800 + reward 200 + done/win/alive 102
+BYTES_PER_ENV_STEP = 38400 + 12000 + 200 + 800 + 200 + 102
+FALLBACK_HBM_GBS = 6650.0
+
+
+def measured_peak():
+    p = os.path.join(REPO, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, 'fallback (B200_PROFILING.md 6.65 TB/s)'
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.01):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.sm_max = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: 'hw_slowdown',
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: 'hw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: 'sw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonSwPowerCap: 'sw_power_cap',
+                 nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: 'hw_power_brake'}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {'sm_mhz': med, 'sm_max_mhz': self.sm_max, 'reasons': sorted(self.reasons), 'samples': len(self.samples)}
+
+
+def physical_gpu_index(local_index):
+    vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+    if vis:
+        try:
+            return int(vis.split(',')[local_index])
+        except Exception:
+            return local_index
+    return local_index
+
+
+# ------------------------------------------------------------------------------------------ CPU arm (oracle port)
+def cpu_port_run(n_env, steps, warmup, threads, seed=SEED):
+    """Times the CPU restatement of the reference path (oracle/dca_oracle.c, OpenMP over envs) on `threads` host
+    threads: planner stand-in + step + obs + autoreset, same workload.  Returns (agent_steps_per_s, seconds)."""
+    sys.path.insert(0, os.path.join(REPO, 'oracle'))
+    from dca_oracle import OracleVecEnv
+    env = OracleVecEnv(WORKLOAD, n_env, seed=seed, nthreads=threads)
+    env.reset()
+    rng = np.random.RandomState(1)
+    pool = [rng.randint(0, 7, size=(n_env, env.G)).astype(np.float64) for _ in range(8)]
+    for i in range(warmup):
+        env.step(pool[i % 8], env.plan_centroid())
+    t0 = time.perf_counter()
+    for i in range(steps):
+        env.step(pool[i % 8], env.plan_centroid())
+    dt = time.perf_counter() - t0
+    return n_env * env.N * steps / dt, dt
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores.  The reference
+    is Python (cannot travel to the GPU box; no oracle/_ref), so this is the oracle port with every host thread.
+    Each step is a bounded sample: 1024 envs instead of 4096 per GPU (throughput per env-step is size independent
+    on the CPU)."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_env = 1024
+    steps = max(1, min(args.steps, 200))
+    warm = max(3, min(args.warmup, 20))
+    value, dt = cpu_port_run(n_env, steps, warm, cores)
+    line = {
+        'impl': 'reference', 'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s',
+        'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': dt / steps * 1e3,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': {'workload': 'DCA 50v50 step+obs+autoreset, injected random guard actions, centroid planner stand-in',
+                   'envs_per_step_sample': n_env, 'scenario': WORKLOAD},
+        'cpu_baseline': {'value': value, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
+                         'sample': '%d envs x %d steps of the 50v50 workload, OpenMP over envs' % (n_env, steps)},
+        'e2e': {'value': value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.sharding import init_distributed
+    from hmp2g_b200.vec_env import DcaSuperpoolEnv, DcaVecEnv
+
+    assert torch.cuda.is_available(), 'bench.py needs a GPU: the product path has no CPU fallback'
+    rank, world, local_rank = init_distributed('nccl')
+    assert world == args.gpus, 'launch with torchrun --nproc-per-node %d (WORLD_SIZE=%d)' % (args.gpus, world)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    E, K, W = args.envs_per_gpu, args.steps, args.warmup
+    scfg = type('BenchScenarioConfig', (ScenarioConfig,), dict(WORKLOAD))
+    env = DcaVecEnv(E, scfg=scfg, device=dev, seed=SEED, env_gid0=rank * E)
+    G, A, N = env.G, env.A, env.N
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(SEED + rank)
+    n_pool = 16  # pre-generated guard action batches resident in HBM (RandomController, ALGORITHM/random/foundation.py:28)
+    act_pool = [torch.randint(0, 7, (E, G), generator=gen, device=dev, dtype=torch.int32) for _ in range(n_pool)]
+    force = torch.zeros((E, A, 2), dtype=torch.float64, device=dev)
+    lib, h = env.lib, env.handle
+    import ctypes as C
+    stream = torch.cuda.current_stream(dev)
+    sptr = C.c_void_p(stream.cuda_stream)
+    fptr = C.c_void_p(force.data_ptr())
+    aptrs = [C.c_void_p(a.data_ptr()) for a in act_pool]
+
+    def one_step(i):
+        rc = lib.dca_plan_centroid(h, fptr, sptr)
+        rc |= lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
+        return rc
+
+    env.reset()
+    launches0 = env.kernel_launches()
+    for i in range(W):
+        assert one_step(i) == 0
+    ev_s = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    ev_e = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(physical_gpu_index(local_rank)) if rank == 0 else None
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.start()
+    launches_before = env.kernel_launches()
+    t_begin.record(stream)
+    for i in range(K):
+        lib.dca_plan_centroid(h, fptr, sptr)
+        ev_s[i].record(stream)
+        lib.dca_step(h, aptrs[(W + i) % n_pool], fptr, None, None, 1, sptr)
+        ev_e[i].record(stream)
+    t_end.record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+    gpu_launches = env.kernel_launches() - launches_before
+    ms_total = t_begin.elapsed_time(t_end)
+    ms_step_kernel = sum(ev_s[i].elapsed_time(ev_e[i]) for i in range(K)) / K
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * E * N * K / (ms_total * 1e-3)
+    alive_frac = float(env.alive.float().mean().item())
+    done_frac = float(env.done.float().mean().item())
+
+    # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
+    del env
+    torch.cuda.empty_cache()
+    from hmp2g_b200.config import GlobalConfig
+    GlobalConfig.seed = SEED
+    host = DcaSuperpoolEnv(n_env=E, scfg=scfg, device=dev, env_gid0=rank * E)
+    host.reset()
+    rng = np.random.RandomState(rank)
+    host_pool = [rng.randint(0, 7, size=(E, G)).astype(np.float64) for _ in range(4)]
+    Ke = max(3, min(K, args.e2e_steps))
+    for i in range(3):
+        host.step(host_pool[i % 4])
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(Ke):
+        host.step(host_pool[i % 4])
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * E * N * Ke / float(te.item())
+    h2d, d2h = host.h2d_bytes, host.d2h_bytes
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peak()
+    algo_bytes = BYTES_PER_ENV_STEP * E
+    achieved = algo_bytes / (ms_step_kernel * 1e-3) / 1e9
+    line = {
+        'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s', 'n_gpus': world, 'steps': K,
+        'warmup': W, 'ms_per_step': ms_total / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'f64', 'data': 'synthetic',
+        'config': {'workload': 'DCA 50v50 step+obs+autoreset, %d envs/GPU, injected random guard actions, '
+                               'centroid planner stand-in (BASELINE.json configs[1])' % E,
+                   'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD,
+                   'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
+                         '> 126 MB L2' % ((E * (G * 768 + 2 * 5760)) / 1e6, E * G * 768 / 1e6, 2 * E * 5760 / 1e6),
+                   'policy_agent_steps_per_sec': value * G / N,
+                   'alive_fraction_at_end': alive_frac, 'done_fraction_last_step': done_frac},
+        'roofline': {'bound': 'hbm', 'kernel': 'k_step', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / peak, 'traffic': args.traffic, 'peak_source': peak_src,
+                     'algorithmic_bytes_per_launch': algo_bytes, 'kernel_ms': ms_step_kernel},
+        'e2e': {'value': e2e_value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy in, numpy obs/reward/done/info out)'},
+        'gpu_launches': gpu_launches,
+        'clocks': clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        n_cpu_env, cpu_steps = 1024, 60
+        v, dt = cpu_port_run(n_cpu_env, cpu_steps, 5, cores)
+        v1, dt1 = cpu_port_run(128, 40, 3, 1)
+        line['cpu_baseline'] = {'value': v, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
+                                'sample': '%d envs x %d steps of the same 50v50 workload (%.1f s)' % (n_cpu_env, cpu_steps, dt),
+                                'single_core_value': v1}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=int(os.environ.get('WORLD_SIZE', '1')))
+    ap.add_argument('--steps', type=int, default=1800)
+    ap.add_argument('--warmup', type=int, default=180)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--envs-per-gpu', type=int, default=ENVS_PER_GPU)
+    ap.add_argument('--e2e-steps', type=int, default=40)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--traffic', type=float, default=None,
+                    help='dram bytes per k_step launch from the committed ncu --set full capture (profiles/)')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == 'reference':
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -513,7 +513,7 @@ __global__ void __launch_bounds__(256) k_observe(const Params P, const uint32_t 
         ((EnvScalars *)(P.blobs + (size_t)e * P.L.bytes + P.L.scalars))->obs_counter = s.sc->obs_counter;
 }
 
-// ------------------------------------------------------------------ state import / export (oracle SoA <-> blobs)
+// ------------------------------------------------------------------ state import / export (plain SoA <-> blobs)
 __global__ void k_state_io(const Params P, const DcaState st, int import) {
     const BlobLayout &L = P.L;
     const size_t total = (size_t)P.E * L.N;

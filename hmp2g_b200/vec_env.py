@@ -1,0 +1,281 @@
+"""Vectorised DCA env on one B200: the drop-in for the reference's SuperpoolEnv / SmartPool / EnvAutoReset stack.
+
+Two facades over the C-ABI (include/dca_b200.h):
+
+* ``DcaVecEnv``       -- "fast": everything stays on the device; step() returns the bound torch CUDA tensors
+                         (zero copy) for a torch policy / rollout loop.
+* ``DcaSuperpoolEnv`` -- "compat": the exact host surface of /root/reference/UTIL/shm_env.py:126-168
+                         (numpy in, numpy + per-env info dicts out, NaN action row = ENV-PAUSE), so unmodified
+                         ALGORITHM modules (conc, conc_4hist, random) and task_runner.Runner can drive it.
+``make_parallel_envs`` mirrors /root/reference/MISSION/env_router.py:68-117.
+
+There is no CPU path: constructing either class without a CUDA device / without libdca_b200.so raises.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .config import GlobalConfig, ScenarioConfig
+
+OBS_ROWS, OBS_ROW = 12, 16
+
+
+def pod_config(scfg=ScenarioConfig, seed=0, env_gid0=0):
+    """POD snapshot of ScenarioConfig, taken at construction time (parallel_run.py:30-101)."""
+    tp = list(scfg.terrain_parameters)
+    return _lib.DcaConfig(
+        int(scfg.num_guards), int(scfg.num_attackers), float(scfg.agent_acc), float(scfg.agent_max_speed),
+        float(scfg.agent_max_rot), float(scfg.agent_shoot_base_radius), float(scfg.agent_shoot_win),
+        float(scfg.random_jam_prob), int(bool(scfg.introduce_terrain)), float(tp[0]), float(tp[1]),
+        int(scfg.MaxEpisodeStep), float(scfg.init_distance), int(bool(scfg.enable_attacker_fluctuation)),
+        int(scfg.attacker_fluctuation), float(scfg.size), int(bool(scfg.half_death_reward)),
+        int(bool(scfg.REWARD_DEBUG)), float(scfg.REWARD_DEBUG_Value), int(bool(scfg.DISALBE_RED_FUNCTION)),
+        int(seed) & 0xFFFFFFFFFFFFFFFF, int(env_gid0))
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class DcaVecEnv(object):
+    """n_env DCA envs resident on one GPU.  All tensors returned are views of buffers written in place."""
+
+    def __init__(self, n_env, scfg=ScenarioConfig, device=None, seed=0, env_gid0=0, debug_outputs=False):
+        if not torch.cuda.is_available():
+            raise _lib.DcaError('hmp2g_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
+        self.lib = _lib.load()
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        assert self.device.type == 'cuda'
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device('cuda', dev_index)
+        self.cfg = pod_config(scfg, seed, env_gid0)
+        self.E, self.G, self.A = int(n_env), self.cfg.num_guards, self.cfg.num_attackers
+        self.N = self.G + self.A
+        self.num_envs = self.E
+        self.handle = C.c_void_p()
+        _lib.check(self.lib.dca_create(C.byref(self.cfg), self.E, dev_index, C.byref(self.handle)))
+        E, G, A, N, dev = self.E, self.G, self.A, self.N, self.device
+        self.obs = torch.zeros((E, G, OBS_ROWS, OBS_ROW), dtype=torch.float32, device=dev)
+        self.tobs = torch.zeros((E, G, OBS_ROWS, OBS_ROW), dtype=torch.float32, device=dev)
+        self.reward = torch.zeros((E, G), dtype=torch.float32, device=dev)
+        self.done = torch.zeros((E,), dtype=torch.uint8, device=dev)
+        self.win = torch.zeros((E,), dtype=torch.uint8, device=dev)
+        self.alive = torch.zeros((E, N), dtype=torch.uint8, device=dev)
+        self.slot_id = torch.full((E, G, OBS_ROWS), -1, dtype=torch.int16, device=dev) if debug_outputs else None
+        self.nearest = torch.full((E, A), -1, dtype=torch.int32, device=dev) if debug_outputs else None
+        bufs = _lib.DcaBuffers(_ptr(self.obs), _ptr(self.tobs), _ptr(self.reward), _ptr(self.done), _ptr(self.win),
+                               _ptr(self.alive), _ptr(self.slot_id), _ptr(self.nearest))
+        _lib.check(self.lib.dca_bind_buffers(self.handle, C.byref(bufs)), self.handle)
+        self._force = torch.zeros((E, A, 2), dtype=torch.float64, device=dev)
+
+    # -- lifetime -----------------------------------------------------------------------
+    def close(self):
+        if getattr(self, 'handle', None) is not None and self.handle.value:
+            self.lib.dca_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _check_tensor(self, t, dtype, shape, name):
+        assert t.is_cuda and t.device == self.device, '%s must live on %s' % (name, self.device)
+        assert t.dtype == dtype and tuple(t.shape) == tuple(shape) and t.is_contiguous(), \
+            '%s must be contiguous %s%s, got %s%s' % (name, dtype, tuple(shape), t.dtype, tuple(t.shape))
+
+    # -- env surface --------------------------------------------------------------------
+    def reset(self, env_mask=None):
+        """collective_assaultGlobalEnv.reset (parallel_run.py:248-270) for all envs (or the masked ones)."""
+        if env_mask is not None:
+            self._check_tensor(env_mask, torch.uint8, (self.E,), 'env_mask')
+        _lib.check(self.lib.dca_reset(self.handle, _ptr(env_mask), self._stream()), self.handle)
+        return self.obs
+
+    def plan_centroid(self, out=None):
+        """Benchmark planner stand-in: fills (and returns) the attacker-force tensor f64 [E,A,2]."""
+        out = self._force if out is None else out
+        self._check_tensor(out, torch.float64, (self.E, self.A, 2), 'att_force')
+        _lib.check(self.lib.dca_plan_centroid(self.handle, _ptr(out), self._stream()), self.handle)
+        return out
+
+    def step(self, actions, att_force=None, skip=None, rng_words=None, autoreset=True):
+        """actions int32 [E,G]; att_force float64 [E,A,2] (None -> centroid stand-in planner);
+        skip uint8 [E]; rng_words int32/uint32-as-int32 [E,G,2,12].  Returns (obs, reward, done, win) views."""
+        self._check_tensor(actions, torch.int32, (self.E, self.G), 'actions')
+        if att_force is None:
+            att_force = self.plan_centroid()
+        else:
+            self._check_tensor(att_force, torch.float64, (self.E, self.A, 2), 'att_force')
+        if skip is not None:
+            self._check_tensor(skip, torch.uint8, (self.E,), 'skip')
+        if rng_words is not None:
+            self._check_tensor(rng_words, torch.int32, (self.E, self.G, 2, 12), 'rng_words')
+        _lib.check(self.lib.dca_step(self.handle, _ptr(actions), _ptr(att_force), _ptr(skip), _ptr(rng_words),
+                                     int(bool(autoreset)), self._stream()), self.handle)
+        return self.obs, self.reward, self.done, self.win
+
+    def observe(self, rng_words=None):
+        if rng_words is not None:
+            self._check_tensor(rng_words, torch.int32, (self.E, self.G, 2, 12), 'rng_words')
+        _lib.check(self.lib.dca_observe(self.handle, _ptr(rng_words), self._stream()), self.handle)
+        return self.obs
+
+    def kernel_launches(self):
+        n = C.c_int64()
+        _lib.check(self.lib.dca_kernel_launches(self.handle, C.byref(n)), self.handle)
+        return n.value
+
+    # -- state import / export (parity harness, checkpoints) ----------------------------------
+    _STATE_SPEC = (('pos', torch.float64, 2), ('vel', torch.float64, 2), ('atk_rad', torch.float64, 0),
+                   ('terrain', torch.float64, 0), ('alive', torch.uint8, 0), ('just_died', torch.uint8, 0),
+                   ('hit', torch.uint8, 0), ('was_hit', torch.uint8, 0), ('num_hit', torch.int32, 0),
+                   ('num_was_hit', torch.int32, 0))
+    _ENV_SPEC = (('init_theta', torch.float64), ('time_step', torch.int32), ('n_alive_guards', torch.int32),
+                 ('n_alive_attackers', torch.int32), ('obs_counter', torch.int32), ('episode', torch.int32))
+
+    def _alloc_state(self):
+        st = {}
+        for name, dt, k in self._STATE_SPEC:
+            st[name] = torch.zeros((self.E, self.N, k) if k else (self.E, self.N), dtype=dt, device=self.device)
+        for name, dt in self._ENV_SPEC:
+            st[name] = torch.zeros((self.E,), dtype=dt, device=self.device)
+        return st
+
+    def export_state(self):
+        """dict of numpy arrays in a plain SoA layout (counters as uint32)."""
+        st = self._alloc_state()
+        s = _lib.DcaState(*[_ptr(st[n]) for n in _lib.STATE_FIELDS])
+        _lib.check(self.lib.dca_export_state(self.handle, C.byref(s), self._stream()), self.handle)
+        torch.cuda.current_stream(self.device).synchronize()
+        out = {k: v.cpu().numpy() for k, v in st.items()}
+        out['obs_counter'] = out['obs_counter'].view(np.uint32)
+        out['episode'] = out['episode'].view(np.uint32)
+        return out
+
+    def import_state(self, state):
+        """state: dict of numpy arrays [E,...] (same keys as export_state)."""
+        st = self._alloc_state()
+        for k, t in st.items():
+            a = np.asarray(state[k])
+            if k in ('obs_counter', 'episode'):
+                a = a.astype(np.int64).astype(np.uint32).view(np.int32)
+            np_dt = {torch.float64: np.float64, torch.uint8: np.uint8, torch.int32: np.int32}[t.dtype]
+            t.copy_(torch.from_numpy(np.ascontiguousarray(a).astype(np_dt)).reshape(t.shape))
+        s = _lib.DcaState(*[_ptr(st[n]) for n in _lib.STATE_FIELDS])
+        _lib.check(self.lib.dca_import_state(self.handle, C.byref(s), self._stream()), self.handle)
+        torch.cuda.current_stream(self.device).synchronize()
+
+
+class DcaSuperpoolEnv(object):
+    """Host-facing drop-in for UTIL.shm_env.SuperpoolEnv (UTIL/shm_env.py:126-168) backed by DcaVecEnv.
+
+    step(actions float64 [E,G], NaN row => skip) -> (obs f32 [E,G,192], reward f64 [E,G], done bool [E],
+    info object[E] of dict).  info = {} | {'win': bool}; on done also 'obs-echo' (terminal obs [G,192]) and
+    'others' (reset info).  The returned obs of a done env is the post-reset obs (shm_env.py:51-66).
+    A skipped env returns its previous (ob, reward, done, info) (shm_env.py:37-41).
+    Attacker forces come from `planner` (callable(env) -> f64 cuda [E,A,2]) or the centroid stand-in.
+    """
+
+    def __init__(self, process_pool=None, env_args_dict_list=None, spaces=None, n_env=None, scfg=None,
+                 device=None, seed=None, planner=None, env_gid0=0):
+        scfg = scfg or GlobalConfig.ScenarioConfig
+        if n_env is None:
+            n_env = len(env_args_dict_list) if env_args_dict_list is not None else GlobalConfig.num_threads
+        self.SuperPool = process_pool  # unused: there are no worker processes
+        self.num_envs = n_env
+        self.env_name_marker = env_args_dict_list[0][0]['marker'] if env_args_dict_list else ''
+        seed = GlobalConfig.seed if seed is None else seed
+        self.env = DcaVecEnv(n_env, scfg=scfg, device=device, seed=seed, env_gid0=env_gid0)
+        self.planner = planner
+        self.observation_space, self.action_space = [], []  # parallel_run.py:170-171
+        E, G = self.env.E, self.env.G
+        pin = dict(pin_memory=True)
+        self._h_act = torch.zeros((E, G), dtype=torch.int32, **pin)
+        self._h_skip = torch.zeros((E,), dtype=torch.uint8, **pin)
+        self._d_act = torch.zeros((E, G), dtype=torch.int32, device=self.env.device)
+        self._d_skip = torch.zeros((E,), dtype=torch.uint8, device=self.env.device)
+        self._h_obs = torch.zeros((E, G, OBS_ROWS * OBS_ROW), dtype=torch.float32, **pin)
+        self._h_tobs = torch.zeros((E, G, OBS_ROWS * OBS_ROW), dtype=torch.float32, **pin)
+        self._h_rew = torch.zeros((E, G), dtype=torch.float32, **pin)
+        self._h_done = torch.zeros((E,), dtype=torch.uint8, **pin)
+        self._h_win = torch.zeros((E,), dtype=torch.uint8, **pin)
+        self._info = np.empty((E,), dtype=object)
+        for i in range(E):
+            self._info[i] = {}
+        self._cold_start = True
+        self._suffer_reset = np.zeros((E,), dtype=bool)
+        self.h2d_bytes = self._h_act.numel() * 4 + self._h_skip.numel()
+        self.d2h_bytes = (self._h_obs.numel() + self._h_rew.numel()) * 4 + 2 * E
+
+    def get_space(self):
+        return {'obs_space': self.observation_space, 'act_space': self.action_space}
+
+    def _fetch(self):
+        env = self.env
+        self._h_obs.copy_(env.obs.view(env.E, env.G, -1), non_blocking=True)
+        self._h_rew.copy_(env.reward, non_blocking=True)
+        self._h_done.copy_(env.done, non_blocking=True)
+        self._h_win.copy_(env.win, non_blocking=True)
+        torch.cuda.current_stream(env.device).synchronize()
+
+    def reset(self):
+        if self._cold_start:  # EnvAutoReset.reset shm_env.py:82-93
+            self._cold_start = False
+            self.env.reset()
+        elif not self._suffer_reset.all():
+            mask = torch.from_numpy((~self._suffer_reset).astype(np.uint8)).to(self.env.device)
+            self.env.reset(mask)
+        self._suffer_reset[:] = True
+        self._fetch()
+        info = np.empty((self.num_envs,), dtype=object)
+        for i in range(self.num_envs):
+            info[i] = {'others': None}
+        return self._h_obs.numpy().copy(), info
+
+    def step(self, actions):
+        env = self.env
+        actions = np.asarray(actions)
+        if actions.ndim == 3 and actions.shape[-1] == 1:  # RandomController layout (ALGORITHM/random/foundation.py:28)
+            actions = actions[..., 0]
+        skip = np.isnan(actions).any(axis=1)
+        assert not (skip & ~self._suffer_reset).any(), 'skip command on an env that was not just reset'
+        self._h_skip.numpy()[:] = skip
+        self._h_act.numpy()[:] = np.where(np.isnan(actions), 0, actions).astype(np.int32)
+        self._d_act.copy_(self._h_act, non_blocking=True)
+        self._d_skip.copy_(self._h_skip, non_blocking=True)
+        force = self.planner(env) if self.planner is not None else None
+        env.step(self._d_act, force, skip=self._d_skip)
+        self._fetch()
+        done = self._h_done.numpy().astype(bool)
+        win = self._h_win.numpy().astype(bool)
+        stepped = ~skip
+        info = self._info
+        idx_done = np.nonzero(stepped & done)[0]
+        for i in np.nonzero(stepped & ~done)[0]:
+            info[i] = {}
+        if len(idx_done):
+            sel = torch.from_numpy(idx_done).to(env.device)
+            tobs = env.tobs.view(env.E, env.G, -1)[sel].cpu().numpy()
+            for k, i in enumerate(idx_done):
+                info[i] = {'win': bool(win[i]), 'obs-echo': tobs[k], 'others': None}
+        self._suffer_reset[stepped] = done[stepped]
+        return (self._h_obs.numpy().copy(), self._h_rew.numpy().astype(np.float64), done, info.copy())
+
+    def sleep(self):
+        return None
+
+
+def make_parallel_envs(process_pool=None, marker=''):
+    """MISSION.env_router.make_parallel_envs (env_router.py:68-117) for env_name 'dca'."""
+    assert GlobalConfig.env_name in ('dca', 'collective_assault'), GlobalConfig.env_name
+    env_args_dict_list = [({'env_name': GlobalConfig.env_name,
+                            'proc_index': i if 'test' not in marker else -(i + 1),
+                            'marker': marker},) for i in range(GlobalConfig.num_threads)]
+    return DcaSuperpoolEnv(process_pool, env_args_dict_list)

@@ -66,7 +66,7 @@ typedef struct DcaBuffers {
     int32_t *nearest; /* [E,A] guard index each alive attacker aimed at (-1 dead); may be NULL */
 } DcaBuffers;
 
-/* Full env state in the oracle's SoA layout, for import/export (parity harness, checkpointing; the
+/* Full env state in a plain SoA layout, for import/export (parity harness, checkpointing; the
  * reference never checkpoints env state).  Device pointers. */
 typedef struct DcaState {
     double *pos;     /* [E,N,2] */

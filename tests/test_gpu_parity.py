@@ -1,0 +1,296 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the C-ABI
+(hmp2g_b200._lib -> libdca_b200.so), against (a) the golden trajectories produced by the reference itself and
+(b) the CPU oracle on the same seeded inputs.  Bar (BASELINE.json north_star): integer / index outputs bit-exact
+(alive masks, kill counts, done, win, kNN slot ids, nearest-guard index); floats within 1e-5 relative per step over
+a 100-step horizon.  /root/reference is NOT needed here.
+"""
+import numpy as np
+import pytest
+
+import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5  # north_star tolerance for float positions / rewards
+
+
+def _torch():
+    import torch
+    assert torch.cuda.is_available(), 'GPU tests need a CUDA device'
+    return torch
+
+
+class _Cfg(object):
+    pass
+
+
+def scenario_from_dict(d):
+    """A ScenarioConfig-like class carrying the case's parameters (what JSONC injection would produce)."""
+    from hmp2g_b200.config import ScenarioConfig
+    c = type('CaseScenarioConfig', (ScenarioConfig,), {})
+    for k, v in d.items():
+        assert hasattr(ScenarioConfig, k), k
+        setattr(c, k, v)
+    return c
+
+
+def make_gpu_env(cfg, n_env, seed, gid0, debug=True):
+    from hmp2g_b200.vec_env import DcaVecEnv
+    return DcaVecEnv(n_env, scfg=scenario_from_dict(cfg), seed=seed, env_gid0=gid0, debug_outputs=debug)
+
+
+def compare_state(gpu_state, ref_state, tag, e_gpu=slice(None), rtol=RTOL):
+    for k in gu.INT_KEYS:
+        a = gpu_state[k][e_gpu].astype(np.int64)
+        b = np.asarray(ref_state[k]).astype(np.int64)
+        if k in ('obs_counter', 'episode'):
+            a, b = a & 0xFFFFFFFF, b & 0xFFFFFFFF
+        assert np.array_equal(a, b), (tag, k)
+    for k in gu.FLOAT_KEYS:
+        gu.assert_close_rel(gpu_state[k][e_gpu], ref_state[k], rtol, '%s %s' % (tag, k), atol=1e-12)
+
+
+@pytest.mark.parametrize('name', gu.golden_cases())
+def test_cuda_matches_reference_golden(name):
+    """Replay the reference's recorded trajectory (state0, guard actions, planner forces) on the GPU."""
+    torch = _torch()
+    case = gu.load_case(name)
+    env = make_gpu_env(case['cfg'], 2, case['seed'], case['gid'])  # env 1 is a bystander with another global id
+    s0 = gu.state0(case)
+    env.import_state({k: np.stack([v, v]) for k, v in s0.items()})
+    T = case['actions'].shape[0]
+    dev = env.device
+    n_bits_equal = n_vals = 0
+    for t in range(T):
+        a = case['actions'][t]
+        skip = np.isnan(a).any()
+        act = torch.from_numpy(np.tile(np.where(np.isnan(a), 0, a).astype(np.int32), (2, 1))).to(dev)
+        frc = torch.from_numpy(np.tile(case['att_force'][t], (2, 1, 1))).to(dev)
+        skp = torch.full((2,), int(skip), dtype=torch.uint8, device=dev)
+        env.step(act, frc, skip=skp)
+        st = env.export_state()
+        tag = '%s t=%d' % (name, t)
+        compare_state(st, {k: case[k][t] for k in gu.STATE_KEYS}, tag, e_gpu=0)
+        assert int(env.done[0]) == int(case['done'][t]), tag
+        if case['done'][t]:
+            assert int(env.win[0]) == int(case['win'][t]), tag
+        assert np.array_equal(env.reward[0].cpu().numpy().astype(np.float64), case['reward'][t]), tag
+        obs = env.obs[0].reshape(env.G, 192).cpu().numpy()
+        ref_ids = gu.slot_ids_from_obs(case['obs'][t])
+        assert np.array_equal(env.slot_id[0].cpu().numpy().astype(np.int32), ref_ids), tag
+        assert np.array_equal(gu.slot_ids_from_obs(obs), ref_ids), tag
+        gu.assert_close_rel(obs, case['obs'][t], RTOL, tag + ' obs', atol=1e-12)
+        n_bits_equal += int((obs.view(np.uint32) == case['obs'][t].view(np.uint32)).sum())
+        n_vals += obs.size
+        if not skip:
+            assert np.array_equal(env.nearest[0].cpu().numpy(), case['nearest'][t]), tag
+        assert np.array_equal(env.alive[0].cpu().numpy(), case['alive'][t]), tag
+    for k, t in enumerate(case['tobs_steps']):
+        pass  # terminal obs is checked in test_cuda_terminal_obs (needs the value at the done step)
+    print('%s: obs float32 bit-identical to the reference in %.4f%% of %d values' % (name, 100.0 * n_bits_equal / n_vals, n_vals))
+
+
+@pytest.mark.parametrize('name', ['cfgA_50v50', 'small_8v10_fluct'])
+def test_cuda_terminal_obs(name):
+    torch = _torch()
+    case = gu.load_case(name)
+    env = make_gpu_env(case['cfg'], 1, case['seed'], case['gid'])
+    env.import_state({k: v[None] for k, v in gu.state0(case).items()})
+    want = {int(t): case['tobs'][k] for k, t in enumerate(case['tobs_steps'])}
+    assert want
+    for t in range(case['actions'].shape[0]):
+        a = case['actions'][t]
+        skip = np.isnan(a).any()
+        act = torch.from_numpy(np.where(np.isnan(a), 0, a).astype(np.int32)[None]).to(env.device)
+        frc = torch.from_numpy(case['att_force'][t][None]).to(env.device)
+        env.step(act, frc, skip=torch.full((1,), int(skip), dtype=torch.uint8, device=env.device))
+        if t in want:
+            tobs = env.tobs[0].reshape(env.G, 192).cpu().numpy()
+            assert np.array_equal(gu.slot_ids_from_obs(tobs), gu.slot_ids_from_obs(want[t])), (name, t)
+            gu.assert_close_rel(tobs, want[t], RTOL, 'tobs', atol=1e-12)
+
+
+@pytest.mark.parametrize('name', gu.golden_cases())
+def test_cuda_reset_matches_reference(name):
+    """In-kernel Philox + Box-Muller reset against the reference's reset under the same keyed draws."""
+    _torch()
+    case = gu.load_case(name)
+    env = make_gpu_env(case['cfg'], 1, case['seed'], case['gid'])
+    env.reset()
+    st = env.export_state()
+    for k in gu.INT_KEYS:
+        if k == 'just_died':
+            continue
+        assert np.array_equal(st[k][0].astype(np.int64) & 0xFFFFFFFF, case['s0_' + k].astype(np.int64) & 0xFFFFFFFF), k
+    for k in gu.FLOAT_KEYS:
+        gu.assert_close_rel(st[k][0], case['s0_' + k], 1e-9, 'reset ' + k, atol=1e-12)
+    obs = env.obs[0].reshape(env.G, 192).cpu().numpy()
+    assert np.array_equal(gu.slot_ids_from_obs(obs), gu.slot_ids_from_obs(case['obs0']))
+    gu.assert_close_rel(obs, case['obs0'], 1e-6, 'reset obs', atol=1e-7)
+
+
+def _run_against_oracle(cfg, E, steps, seed, gid0, nthreads=8, use_stream_every=0, resync=True):
+    """GPU and oracle step side by side on identical seeded inputs; returns summary counters."""
+    torch = _torch()
+    import dca_rng
+    from dca_oracle import OracleVecEnv
+    orc = OracleVecEnv(cfg, E, seed=seed, env_gid0=gid0, nthreads=nthreads)
+    env = make_gpu_env(cfg, E, seed, gid0)
+    orc.reset()
+    env.reset()
+    st = env.export_state()
+    compare_state(st, orc.state, 'reset', rtol=1e-9)
+    env.import_state(orc.state)  # start both from bit-identical states
+    rng = np.random.RandomState(seed + 17)
+    n_done = n_kill = 0
+    for t in range(steps):
+        act = rng.randint(0, 7, size=(E, orc.G)).astype(np.int32)
+        skip = np.zeros((E,), np.uint8)
+        if t % 7 == 3:
+            skip = ((orc.done != 0) & (rng.rand(E) < 0.5)).astype(np.uint8)  # pause some just-reset envs
+        force = orc.plan_centroid()
+        gforce = env.plan_centroid().cpu().numpy()
+        gu.assert_close_rel(gforce, force, 1e-12, 'centroid planner t=%d' % t, atol=1e-13)
+        words = None
+        if use_stream_every and t % use_stream_every == 0:
+            words = dca_rng.obs_words_all(seed, gid0 + np.arange(E),
+                                          (orc.state['obs_counter'].astype(np.int64) + 1) & 0xFFFFFFFF, orc.G)
+        act_f = act.astype(np.float64)
+        act_f[skip != 0] = np.nan
+        orc.step(act_f, force, rng_words=words)
+        env.step(torch.from_numpy(act).to(env.device), torch.from_numpy(force).to(env.device),
+                 skip=torch.from_numpy(skip).to(env.device),
+                 rng_words=None if words is None else torch.from_numpy(words.view(np.int32)).to(env.device))
+        tag = 't=%d' % t
+        st = env.export_state()
+        compare_state(st, orc.state, tag)
+        assert np.array_equal(env.done.cpu().numpy(), orc.done), tag
+        d = orc.done != 0
+        assert np.array_equal(env.win.cpu().numpy()[d], orc.win[d]), tag
+        assert np.array_equal(env.reward.cpu().numpy().astype(np.float64), orc.reward), tag
+        assert np.array_equal(env.slot_id.cpu().numpy(), orc.slot_id), tag
+        ns = skip == 0
+        assert np.array_equal(env.nearest.cpu().numpy()[ns], orc.nearest[ns]), tag
+        obs = env.obs.reshape(E, orc.G, 192).cpu().numpy()
+        gu.assert_close_rel(obs, orc.obs, RTOL, tag + ' obs', atol=1e-12)
+        if d.any():
+            tob = env.tobs.reshape(E, orc.G, 192).cpu().numpy()
+            dd = d & ns
+            assert np.array_equal(gu.slot_ids_from_obs(tob[dd]), gu.slot_ids_from_obs(orc.tobs[dd])), tag
+            gu.assert_close_rel(tob[dd], orc.tobs[dd], RTOL, tag + ' tobs', atol=1e-12)
+        n_done += int((d & ns).sum())
+        n_kill += int(orc.state['just_died'].sum())
+        if resync:
+            env.import_state(orc.state)  # keep ulp-level libm differences from accumulating into index flips
+    return dict(n_done=n_done, n_kill=n_kill)
+
+
+def test_cuda_vs_oracle_50v50_100_steps_no_resync():
+    """The north_star statement verbatim: identical initial states + action streams, 100 steps, no re-sync."""
+    cfg = dict(num_guards=50, num_attackers=50, random_jam_prob=0.05, introduce_terrain=True,
+               terrain_parameters=[0.05, 0.2], MaxEpisodeStep=180)
+    r = _run_against_oracle(cfg, 48, 100, seed=5, gid0=1000, resync=False)
+    assert r['n_kill'] > 100
+
+
+def test_cuda_vs_oracle_short_episodes_autoreset_skip_stream():
+    cfg = dict(num_guards=12, num_attackers=14, random_jam_prob=0.2, introduce_terrain=True,
+               terrain_parameters=[0.1, 0.3], MaxEpisodeStep=25, init_distance=2, size=3.0,
+               enable_attacker_fluctuation=True, attacker_fluctuation=5, REWARD_DEBUG=True, REWARD_DEBUG_Value=3)
+    r = _run_against_oracle(cfg, 96, 120, seed=11, gid0=2 ** 31 - 40, use_stream_every=3)
+    assert r['n_done'] > 96 * 3
+
+
+def test_cuda_vs_oracle_100v100():
+    cfg = dict(num_guards=100, num_attackers=100, random_jam_prob=0.05, introduce_terrain=True,
+               terrain_parameters=[0.05, 0.2], MaxEpisodeStep=60)
+    _run_against_oracle(cfg, 16, 70, seed=3, gid0=0)
+
+
+def test_cuda_vs_oracle_ragged_150v131():
+    """Largest sizes the reference admits (0..150 per side) with an odd N: blob padding / 256-thread path."""
+    cfg = dict(num_guards=150, num_attackers=131, random_jam_prob=0.5, introduce_terrain=False, MaxEpisodeStep=30)
+    _run_against_oracle(cfg, 6, 35, seed=8, gid0=77)
+
+
+def test_cuda_full_size_4096_envs_vs_oracle():
+    """BASELINE config 2 at full size: 4096 envs x 50v50; every env checked against the oracle for 40 steps."""
+    cfg = dict(num_guards=50, num_attackers=50, random_jam_prob=0.05, introduce_terrain=True,
+               terrain_parameters=[0.05, 0.2], MaxEpisodeStep=180)
+    r = _run_against_oracle(cfg, 4096, 40, seed=2024, gid0=0)
+    assert r['n_kill'] > 4096
+
+
+def test_cuda_full_size_invariants_long_run():
+    """Size-independent properties at 4096 envs over whole episodes (no oracle): every hit has a shooter and a
+    target (sum numHit == sum numWasHit), alive mask == 1 - ever-hit, obs rows equal the entity records they index,
+    dead guards observe zeros, done envs come back fully alive at time_step 0."""
+    torch = _torch()
+    cfg = dict(num_guards=50, num_attackers=50, random_jam_prob=0.05, introduce_terrain=True,
+               terrain_parameters=[0.05, 0.2], MaxEpisodeStep=60)
+    E = 4096
+    env = make_gpu_env(cfg, E, 9, 0)
+    env.reset()
+    g = torch.Generator(device=env.device)
+    g.manual_seed(1)
+    n_done = 0
+    for t in range(130):
+        act = torch.randint(0, 7, (E, env.G), generator=g, device=env.device, dtype=torch.int32)
+        env.step(act, None)
+        if t % 10 == 9 or t in (59, 60, 119, 120):
+            st = env.export_state()
+            assert (st['num_hit'].sum(1) == st['num_was_hit'].sum(1)).all()
+            assert np.array_equal(st['alive'] != 0, st['num_was_hit'] == 0) or cfg.get('enable_attacker_fluctuation')
+            assert (st['n_alive_guards'] == st['alive'][:, :env.G].sum(1)).all()
+            assert (st['n_alive_attackers'] == st['alive'][:, env.G:].sum(1)).all()
+            obs = env.obs.cpu().numpy()
+            sid = env.slot_id.cpu().numpy().astype(np.int64)
+            assert np.array_equal(gu.slot_ids_from_obs(obs.reshape(E, env.G, 192)), sid)
+            dead_g = st['alive'][:, :env.G] == 0
+            assert (obs[dead_g] == 0).all()
+            # gathered rows are exactly the float32 entity records
+            e_idx, g_idx, r_idx = np.nonzero(sid >= 0)
+            ent = sid[e_idx, g_idx, r_idx]
+            rows = obs[e_idx, g_idx, r_idx]
+            assert np.array_equal(rows[:, 1], st['pos'][e_idx, ent, 0].astype(np.float32))
+            assert np.array_equal(rows[:, 2], st['pos'][e_idx, ent, 1].astype(np.float32))
+            assert np.array_equal(rows[:, 7], st['terrain'][e_idx, ent].astype(np.float32))
+            assert (sid[:, :, 0][~dead_g] == np.broadcast_to(np.arange(env.G), (E, env.G))[~dead_g]).all()
+            d = env.done.cpu().numpy() != 0
+            n_done += int(d.sum())
+            if d.any():
+                assert (st['time_step'][d] == 0).all() and (st['alive'][d] == 1).all()
+    assert n_done >= E  # every env hit the 60-step limit at least once at t=59 / t=119
+
+
+def test_cuda_gae_matches_reference_and_oracle():
+    torch = _torch()
+    from dca_oracle import gae as orc_gae
+    from hmp2g_b200.gae import gae_return
+    z = np.load(gu.GOLDEN_DIR + '/gae_conc.npz')
+    n = len([k for k in z.files if k.endswith('_reward')])
+    for i in range(n):
+        r, v, d = z['c%d_reward' % i], z['c%d_value' % i], z['c%d_dead' % i]
+        dev = 'cuda'
+        ret, threat, pushed = gae_return(torch.from_numpy(r[:, None].astype(np.float32)).to(dev).contiguous(),
+                                         torch.from_numpy(v[:, None]).to(dev).contiguous(),
+                                         torch.from_numpy(d[:, None]).to(dev), want_pushed=True)
+        assert np.array_equal(pushed[:, 0].cpu().numpy().astype(np.float64), z['c%d_reward_pushed' % i])
+        assert np.array_equal(threat[:, 0].cpu().numpy(), z['c%d_threat' % i])
+        assert np.array_equal(ret[:, 0].cpu().numpy().view(np.uint32), z['c%d_return' % i].view(np.uint32)), i
+    # ragged trajectory lengths at rollout-buffer size, vs the oracle
+    rng = np.random.RandomState(0)
+    T, E, G = 180, 256, 50
+    r = rng.choice([0.0, 1.0, -0.5, 3.5], size=(T, E, G))
+    v = rng.randn(T, E, G).astype(np.float32)
+    death = rng.randint(1, T + 40, size=(E, G))
+    d = np.arange(T)[:, None, None] >= death[None]
+    tl = rng.randint(0, T + 1, size=E).astype(np.int32)
+    tl[:3] = (0, 1, T)
+    o_ret, o_thr, o_push = orc_gae(r, v, d, traj_len=tl, threat_limit=8)
+    ret, thr, push = gae_return(torch.from_numpy(r.astype(np.float32)).cuda(), torch.from_numpy(v).cuda(),
+                                torch.from_numpy(d).cuda(), traj_len=torch.from_numpy(tl).cuda(), threat_limit=8,
+                                want_pushed=True)
+    assert np.array_equal(ret.cpu().numpy().view(np.uint32), o_ret.view(np.uint32))
+    assert np.array_equal(thr.cpu().numpy(), o_thr)
+    assert np.array_equal(push.cpu().numpy().astype(np.float64), o_push)
