@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -50,6 +51,14 @@ struct DeviceGuard {
 };
 }  // namespace
 
+// largest float s with sqrtf(s) <= lim (sqrtf is correctly rounded, like __fsqrt_rn and numpy's float32 sqrt)
+static float sq_limit(float lim) {
+    float s = lim * lim;
+    while (sqrtf(s) > lim) s = nextafterf(s, 0.0f);
+    while (sqrtf(nextafterf(s, INFINITY)) <= lim) s = nextafterf(s, INFINITY);
+    return s;
+}
+
 extern "C" {
 
 int dca_abi_version(void) { return 1; }
@@ -79,6 +88,8 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     h->P.cfg = *cfg;
     h->P.L = make_layout(G, A);
     h->P.E = n_env;
+    h->P.smax_h = sq_limit(2.0f);  // obs_range collective_assault_env.py:284
+    h->P.smax_f = sq_limit(3.0f);  // obs_range * 1.5 :332
     h->threads = (G + A) <= 128 ? 128 : 256;
     h->smem = smem_bytes(h->P.L);
     const size_t bytes = (size_t)n_env * h->P.L.bytes;

@@ -68,6 +68,7 @@ struct Params {
     int E;
     unsigned char *blobs;  // [E, L.bytes]
     DcaBuffers out;
+    float smax_h, smax_f;  // largest f32 s with sqrt_rn(s) <= 2.0 (hostile range) / 3.0 (friend range)
 };
 
 // ------------------------------------------------------------------ Philox4x32-10 (keyed RNG stream)
@@ -89,7 +90,9 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 // ------------------------------------------------------------------ exact-semantics math helpers
 // Python / numpy floored float modulo (CPython float_rem, numpy npy_divmod).
 __device__ __forceinline__ double py_fmod(double a, double b) {
-    double m = fmod(a, b);
+    // fmod is exact; for |a| < 2|b| it is a or a -/+ b, and that subtraction is exact (Sterbenz) -- skip the slow loop
+    const double fa = fabs(a), fb = fabs(b);
+    double m = fa < fb ? a : (fa < 2 * fb ? copysign(fa - fb, a) : fmod(a, b));
     if (m != 0.0) {
         if ((b < 0) != (m < 0)) m += b;
     } else {

@@ -13,7 +13,7 @@ struct Smem {
     uint8_t *flags;
     EnvScalars *sc;
     double *fx, *fy, *ar;  // force (act[0:2]) and rotation (act[2]) of this step
-    float *x32, *y32;      // float32-rounded positions (distance matrix inputs)
+    float2 *xy;            // float32-rounded positions (distance matrix inputs); dead agents = (+inf, +inf)
     int32_t *hitcnt;       // times agent i was hit this step (also: exclusion keys during reset)
     uint8_t *canfire;
     float *table;          // [N,16] float32 entity records
@@ -25,7 +25,7 @@ struct Smem {
 __host__ __device__ inline int smem_bytes(const BlobLayout &L) {
     int o = L.bytes;
     o += 3 * align_up(L.N * 8, 16);   // fx fy ar
-    o += 2 * align_up(L.N * 4, 16);   // x32 y32
+    o += align_up(L.N * 8, 16);       // xy
     o += align_up(L.N * 4, 16);       // hitcnt
     o += align_up(L.N, 16);           // canfire
     o += L.N * kObsRow * 4;           // table
@@ -47,7 +47,7 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
     unsigned char *p = base + L.bytes;
     const int f64 = align_up(L.N * 8, 16), f32 = align_up(L.N * 4, 16);
     s.fx = (double *)p; p += f64; s.fy = (double *)p; p += f64; s.ar = (double *)p; p += f64;
-    s.x32 = (float *)p; p += f32; s.y32 = (float *)p; p += f32;
+    s.xy = (float2 *)p; p += f64;
     s.hitcnt = (int32_t *)p; p += f32;
     s.canfire = p; p += align_up(L.N, 16);
     s.table = (float *)p; p += L.N * kObsRow * 4;
@@ -111,8 +111,9 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
     for (int i = tid; i < L.N; i += nt) {
         float4 *row = (float4 *)(s.table + i * kObsRow);
         const float x = (float)s.px[i], y = (float)s.py[i];
-        s.x32[i] = x; s.y32[i] = y;
-        row[0] = make_float4((float)(s.flags[i] & F_ALIVE), x, y, (float)s.atk[i]);
+        const bool alive_i = s.flags[i] & F_ALIVE;
+        s.xy[i] = alive_i ? make_float2(x, y) : make_float2(CUDART_INF_F, CUDART_INF_F);
+        row[0] = make_float4(alive_i ? 1.f : 0.f, x, y, (float)s.atk[i]);
         row[1] = make_float4((float)s.vx[i], (float)s.vy[i], (float)i, (float)s.ter[i]);
         // get_binary_array :207-215 (float halving, int8 wrap, floored %); identical to plain bits for i < 256
         int v = i;
@@ -137,36 +138,45 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
             for (int r = 0; r < kObsRows; ++r) sid[r] = -1;
             continue;
         }
-        const float xg = s.x32[g], yg = s.y32[g];
+        const float2 pg = s.xy[g];
 #pragma unroll
         for (int lst = 0; lst < 2; ++lst) {  // 0 = hostile (:318-328), 1 = friend (:330-342)
             const int base = lst == 0 ? L.G : 0, cnt = lst == 0 ? L.A : L.G;
-            // stable top-6 by (distance, index): argsort()[:6] :308-309, dead = +inf :291-292
+            // argsort()[:6] then the range mask (:308-309, :320-322, :331-333) == the (up to) 6 nearest IN-RANGE
+            // candidates: anything farther than an out-of-range member of the top-6 is out of range too.  The range
+            // test runs on the squared distance (smax = largest f32 whose sqrt_rn is <= the range), so the sqrt and
+            // the sorted insert (stable: ties -> lower index) are paid by in-range candidates only.  Dead = +inf.
+            const float smax = lst == 0 ? P.smax_h : P.smax_f;
+            const float2 *cand = s.xy + base;
             float bd[kVisN];
             int bi[kVisN];
 #pragma unroll
             for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
+#pragma unroll 4
             for (int j = 0; j < cnt; ++j) {
-                if (!(s.flags[base + j] & F_ALIVE)) continue;
-                const float d = f32_dist(xg, yg, s.x32[base + j], s.y32[base + j]);
-                if (d < bd[kVisN - 1]) {
-                    bd[kVisN - 1] = d; bi[kVisN - 1] = j;
+                const float2 c = cand[j];
+                const float dx = __fsub_rn(c.x, pg.x), dy = __fsub_rn(c.y, pg.y);
+                const float sq = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+                if (sq <= smax) {
+                    const float d = __fsqrt_rn(sq);
+                    if (d < bd[kVisN - 1]) {
+                        bd[kVisN - 1] = d; bi[kVisN - 1] = j;
 #pragma unroll
-                    for (int k = kVisN - 1; k > 0; --k) {
-                        if (bd[k] < bd[k - 1]) {
-                            const float td = bd[k]; bd[k] = bd[k - 1]; bd[k - 1] = td;
-                            const int ti = bi[k]; bi[k] = bi[k - 1]; bi[k - 1] = ti;
+                        for (int k = kVisN - 1; k > 0; --k) {
+                            if (bd[k] < bd[k - 1]) {
+                                const float td = bd[k]; bd[k] = bd[k - 1]; bd[k - 1] = td;
+                                const int ti = bi[k]; bi[k] = bi[k - 1]; bi[k - 1] = ti;
+                            }
                         }
                     }
                 }
             }
             // visible list in sorted order, packed one byte per entry
-            const float lim = lst == 0 ? 2.0f : 3.0f;  // obs_range :284, 1.5*obs_range :332
             unsigned long long vis = 0;
             int n = 0;
 #pragma unroll
             for (int k = 0; k < kVisN; ++k) {
-                if (bi[k] >= 0 && bd[k] <= lim) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
+                if (bi[k] >= 0) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
             }
             int row = lst == 0 ? kVisN : 0;
             if (lst == 1) {  // :334-335 self = first visible friend, excluded from shuffle / jamming
@@ -359,7 +369,7 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         }
         s.fx[i] = fx; s.fy[i] = fy; s.ar[i] = ar; s.canfire[i] = cf;
         s.hitcnt[i] = 0;
-        s.x32[i] = (float)s.px[i]; s.y32[i] = (float)s.py[i];
+        s.xy[i] = alive ? make_float2((float)s.px[i], (float)s.py[i]) : make_float2(CUDART_INF_F, CUDART_INF_F);
         if (alive) {
             s.ter[i] = terrain_at(c, s.px[i], s.py[i], ct, sn);
             s.flags[i] = f & (uint8_t)~(F_HIT | F_WAS_HIT);
@@ -370,13 +380,31 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     for (int i = L.G + tid; i < L.N; i += nt) {
         int best = -1;
         if (s.flags[i] & F_ALIVE) {
+            // np.argmin of the float32 distance row (first minimum).  Pass 1 finds the minimum squared distance;
+            // pass 2 takes sqrt_rn only for candidates within 2^-20 of it (sqrt_rn is monotone, so every guard that
+            // ties with the minimum distance is among them) and keeps the lowest index.  Dead guards = +inf.
             best = 0;
-            float bd = CUDART_INF_F;
-            const float xi = s.x32[i], yi = s.y32[i];
+            const float2 pi = s.xy[i];
+            float smin = CUDART_INF_F;
+#pragma unroll 4
             for (int g = 0; g < L.G; ++g) {
-                if (!(s.flags[g] & F_ALIVE)) continue;
-                const float d = f32_dist(xi, yi, s.x32[g], s.y32[g]);
-                if (d < bd) { bd = d; best = g; }
+                const float2 c = s.xy[g];
+                const float dx = __fsub_rn(c.x, pi.x), dy = __fsub_rn(c.y, pi.y);
+                smin = fminf(smin, __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+            }
+            if (smin < CUDART_INF_F) {
+                const float shi = __fmul_ru(smin, 1.000001f);
+                float bd = CUDART_INF_F;
+#pragma unroll 4
+                for (int g = 0; g < L.G; ++g) {
+                    const float2 c = s.xy[g];
+                    const float dx = __fsub_rn(c.x, pi.x), dy = __fsub_rn(c.y, pi.y);
+                    const float sq = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+                    if (sq <= shi) {
+                        const float d = __fsqrt_rn(sq);
+                        if (d < bd) { bd = d; best = g; }
+                    }
+                }
             }
             double th = atan2(s.py[best] - s.py[i], s.px[best] - s.px[i]);
             if (th < 0) th += 2 * kPi;
@@ -396,8 +424,18 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         const double ox = s.px[i], oy = s.py[i];
         const int j0 = i < L.G ? L.G : 0, j1 = i < L.G ? L.N : L.G;
         int hits = 0;
+        // conservative float32 pre-filter (dead = +inf): pairs whose f32 squared distance exceeds r^2 by 1% + 1e-3
+        // cannot satisfy the exact fp64 test below (f32 rounding of |coord| <= 64 perturbs d^2 by < 1e-4 there).
+        const float2 po = s.xy[i];
+        const bool prefilter = fabs(ox) <= 64.0 && fabs(oy) <= 64.0 && r2 < 1.0e3;
+        const float r2f = prefilter ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
+#pragma unroll 4
         for (int j = j0; j < j1; ++j) {
-            if (!(s.flags[j] & F_ALIVE)) continue;
+            const float2 pj = s.xy[j];
+            const float fdx = pj.x - po.x, fdy = pj.y - po.y;
+            const float fs = fdx * fdx + fdy * fdy;
+            if (!(fs <= r2f)) continue;                                  // far away, or dead (+inf)
+            if (!prefilter && !(s.flags[j] & F_ALIVE)) continue;         // r2f = +inf lets dead targets through
             const double dx = s.px[j] - ox, dy = s.py[j] - oy;
             const double d2 = dx * dx + dy * dy;
             if (d2 > r2) continue;

@@ -201,7 +201,11 @@ class DcaSuperpoolEnv(object):
         self._h_skip = torch.zeros((E,), dtype=torch.uint8, **pin)
         self._d_act = torch.zeros((E, G), dtype=torch.int32, device=self.env.device)
         self._d_skip = torch.zeros((E,), dtype=torch.uint8, device=self.env.device)
-        self._h_obs = torch.zeros((E, G, OBS_ROWS * OBS_ROW), dtype=torch.float32, **pin)
+        # two pinned landing buffers, used alternately: the arrays handed out by step t stay valid while step t+1
+        # runs (the reference hands out fresh arrays; callers copy what they keep, task_runner.py:100)
+        self._h_obs_pair = [torch.zeros((E, G, OBS_ROWS * OBS_ROW), dtype=torch.float32, **pin) for _ in range(2)]
+        self._flip = 0
+        self._h_obs = self._h_obs_pair[0]
         self._h_tobs = torch.zeros((E, G, OBS_ROWS * OBS_ROW), dtype=torch.float32, **pin)
         self._h_rew = torch.zeros((E, G), dtype=torch.float32, **pin)
         self._h_done = torch.zeros((E,), dtype=torch.uint8, **pin)
@@ -209,6 +213,7 @@ class DcaSuperpoolEnv(object):
         self._info = np.empty((E,), dtype=object)
         for i in range(E):
             self._info[i] = {}
+        self._info_dirty = np.zeros((E,), dtype=bool)
         self._cold_start = True
         self._suffer_reset = np.zeros((E,), dtype=bool)
         self.h2d_bytes = self._h_act.numel() * 4 + self._h_skip.numel()
@@ -219,6 +224,8 @@ class DcaSuperpoolEnv(object):
 
     def _fetch(self):
         env = self.env
+        self._flip ^= 1
+        self._h_obs = self._h_obs_pair[self._flip]
         self._h_obs.copy_(env.obs.view(env.E, env.G, -1), non_blocking=True)
         self._h_rew.copy_(env.reward, non_blocking=True)
         self._h_done.copy_(env.done, non_blocking=True)
@@ -237,7 +244,7 @@ class DcaSuperpoolEnv(object):
         info = np.empty((self.num_envs,), dtype=object)
         for i in range(self.num_envs):
             info[i] = {'others': None}
-        return self._h_obs.numpy().copy(), info
+        return self._h_obs.numpy(), info
 
     def step(self, actions):
         env = self.env
@@ -258,15 +265,16 @@ class DcaSuperpoolEnv(object):
         stepped = ~skip
         info = self._info
         idx_done = np.nonzero(stepped & done)[0]
-        for i in np.nonzero(stepped & ~done)[0]:
+        for i in np.nonzero(stepped & ~done & self._info_dirty)[0]:
             info[i] = {}
+        self._info_dirty[stepped] = done[stepped]
         if len(idx_done):
             sel = torch.from_numpy(idx_done).to(env.device)
             tobs = env.tobs.view(env.E, env.G, -1)[sel].cpu().numpy()
             for k, i in enumerate(idx_done):
                 info[i] = {'win': bool(win[i]), 'obs-echo': tobs[k], 'others': None}
         self._suffer_reset[stepped] = done[stepped]
-        return (self._h_obs.numpy().copy(), self._h_rew.numpy().astype(np.float64), done, info.copy())
+        return (self._h_obs.numpy(), self._h_rew.numpy().astype(np.float64), done, info.copy())
 
     def sleep(self):
         return None
