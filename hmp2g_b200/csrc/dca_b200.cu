@@ -88,8 +88,10 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     h->P.cfg = *cfg;
     h->P.L = make_layout(G, A);
     h->P.E = n_env;
-    h->P.smax_h = sq_limit(2.0f);  // obs_range collective_assault_env.py:284
-    h->P.smax_f = sq_limit(3.0f);  // obs_range * 1.5 :332
+    for (int lvl = 0; lvl < 3; ++lvl) {
+        h->P.smax[0][lvl] = sq_limit(2.0f / (float)(1 << lvl));  // obs_range collective_assault_env.py:284
+        h->P.smax[1][lvl] = sq_limit(3.0f / (float)(1 << lvl));  // obs_range * 1.5 :332
+    }
     h->threads = (G + A) <= 128 ? 128 : 256;
     h->smem = smem_bytes(h->P.L);
     const size_t bytes = (size_t)n_env * h->P.L.bytes;

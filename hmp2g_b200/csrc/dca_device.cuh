@@ -68,7 +68,7 @@ struct Params {
     int E;
     unsigned char *blobs;  // [E, L.bytes]
     DcaBuffers out;
-    float smax_h, smax_f;  // largest f32 s with sqrt_rn(s) <= 2.0 (hostile range) / 3.0 (friend range)
+    float smax[2][3];  // [hostile, friend][level]: largest f32 s with sqrt_rn(s) <= range, range/2, range/4
 };
 
 // ------------------------------------------------------------------ Philox4x32-10 (keyed RNG stream)

@@ -13,7 +13,8 @@ struct Smem {
     uint8_t *flags;
     EnvScalars *sc;
     double *fx, *fy, *ar;  // force (act[0:2]) and rotation (act[2]) of this step
-    float2 *xy;            // float32-rounded positions (distance matrix inputs); dead agents = (+inf, +inf)
+    float2 *xyg, *xya;     // float32-rounded positions of guards / attackers (distance matrix inputs), each padded
+                           // to a multiple of 32 entries; dead agents and padding = (+inf, +inf)
     int32_t *hitcnt;       // times agent i was hit this step (also: exclusion keys during reset)
     uint8_t *canfire;
     float *table;          // [N,16] float32 entity records
@@ -25,7 +26,7 @@ struct Smem {
 __host__ __device__ inline int smem_bytes(const BlobLayout &L) {
     int o = L.bytes;
     o += 3 * align_up(L.N * 8, 16);   // fx fy ar
-    o += align_up(L.N * 8, 16);       // xy
+    o += (align_up(L.G, 32) + align_up(L.A, 32)) * 8;  // xyg xya
     o += align_up(L.N * 4, 16);       // hitcnt
     o += align_up(L.N, 16);           // canfire
     o += L.N * kObsRow * 4;           // table
@@ -47,7 +48,7 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
     unsigned char *p = base + L.bytes;
     const int f64 = align_up(L.N * 8, 16), f32 = align_up(L.N * 4, 16);
     s.fx = (double *)p; p += f64; s.fy = (double *)p; p += f64; s.ar = (double *)p; p += f64;
-    s.xy = (float2 *)p; p += f64;
+    s.xyg = (float2 *)p; p += align_up(L.G, 32) * 8; s.xya = (float2 *)p; p += align_up(L.A, 32) * 8;
     s.hitcnt = (int32_t *)p; p += f32;
     s.canfire = p; p += align_up(L.N, 16);
     s.table = (float *)p; p += L.N * kObsRow * 4;
@@ -94,6 +95,34 @@ __device__ __forceinline__ double terrain_at(const DcaConfig &c, double X, doubl
     return -Z;
 }
 
+// Refresh the padded float32 position arrays from the fp64 state (dead agents and padding slots = +inf).
+__device__ __forceinline__ void fill_xy(const Smem &s, const BlobLayout &L) {
+    const int Gp = align_up(L.G, 32), Ap = align_up(L.A, 32);
+    for (int k = threadIdx.x; k < Gp + Ap; k += blockDim.x) {
+        const bool isg = k < Gp;
+        const int a = isg ? k : k - Gp;
+        const int i = isg ? a : L.G + a;
+        float2 v = make_float2(CUDART_INF_F, CUDART_INF_F);
+        if ((isg ? a < L.G : a < L.A) && (s.flags[i] & F_ALIVE)) v = make_float2((float)s.px[i], (float)s.py[i]);
+        s.xyg[k] = v;  // xya follows xyg contiguously
+    }
+}
+
+// Branch-free stable insert of (d, j) into the ascending top-6 list: position = first k with d < bd[k]
+// (ties keep the earlier, lower-index entry in front), everything from there shifts down by one.
+__device__ __forceinline__ void top6_insert(float (&bd)[kVisN], int (&bi)[kVisN], float d, int j) {
+    bool p[kVisN];
+#pragma unroll
+    for (int k = 0; k < kVisN; ++k) p[k] = d < bd[k];
+#pragma unroll
+    for (int k = kVisN - 1; k >= 1; --k) {
+        bd[k] = p[k] ? (p[k - 1] ? bd[k - 1] : d) : bd[k];
+        bi[k] = p[k] ? (p[k - 1] ? bi[k - 1] : j) : bi[k];
+    }
+    bd[0] = p[0] ? d : bd[0];
+    bi[0] = p[0] ? j : bi[0];
+}
+
 // ------------------------------------------------------------------ observation pass
 // collective_assaultEnvV1.observation collective_assault_env.py:228-359 for every guard of the env.
 // dest == nullptr: the pass is only counted (keeps the keyed RNG stream aligned), nothing is computed.
@@ -107,12 +136,12 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
         __syncthreads();
         return;
     }
+    fill_xy(s, L);
     // entity table :237-276  [alive,x,y,atk_rad,vx,vy,iden,terrain,bit0..bit7] as float32
     for (int i = tid; i < L.N; i += nt) {
         float4 *row = (float4 *)(s.table + i * kObsRow);
         const float x = (float)s.px[i], y = (float)s.py[i];
         const bool alive_i = s.flags[i] & F_ALIVE;
-        s.xy[i] = alive_i ? make_float2(x, y) : make_float2(CUDART_INF_F, CUDART_INF_F);
         row[0] = make_float4(alive_i ? 1.f : 0.f, x, y, (float)s.atk[i]);
         row[1] = make_float4((float)s.vx[i], (float)s.vy[i], (float)i, (float)s.ter[i]);
         // get_binary_array :207-215 (float halving, int8 wrap, floored %); identical to plain bits for i < 256
@@ -138,37 +167,50 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
             for (int r = 0; r < kObsRows; ++r) sid[r] = -1;
             continue;
         }
-        const float2 pg = s.xy[g];
+        const float2 pg = s.xyg[g];
 #pragma unroll
         for (int lst = 0; lst < 2; ++lst) {  // 0 = hostile (:318-328), 1 = friend (:330-342)
-            const int base = lst == 0 ? L.G : 0, cnt = lst == 0 ? L.A : L.G;
+            const int base = lst == 0 ? L.G : 0;
             // argsort()[:6] then the range mask (:308-309, :320-322, :331-333) == the (up to) 6 nearest IN-RANGE
-            // candidates: anything farther than an out-of-range member of the top-6 is out of range too.  The range
-            // test runs on the squared distance (smax = largest f32 whose sqrt_rn is <= the range), so the sqrt and
-            // the sorted insert (stable: ties -> lower index) are paid by in-range candidates only.  Dead = +inf.
-            const float smax = lst == 0 ? P.smax_h : P.smax_f;
-            const float2 *cand = s.xy + base;
+            // candidates: anything farther than an out-of-range member of the top-6 is out of range too.
+            // Two phases per chunk of 32 candidates so that the warp never diverges on a per-candidate basis:
+            //  1. branch-free scan: squared distance (same roundings as distance_matrix :361-368) tested against
+            //     three nested radii -> three bit masks.  q[l] = largest f32 whose sqrt_rn is <= range, range/2,
+            //     range/4, so "in mask l" == "distance <= radius l" exactly; dead / padding = +inf never pass.
+            //  2. the smallest radius holding >= 6 candidates contains this chunk's 6 nearest; only those get the
+            //     sqrt_rn and the stable sorted insert (ties -> lower index, candidates visited in index order).
+            const float q0 = P.smax[lst][0], q1 = P.smax[lst][1], q2 = P.smax[lst][2];
+            const float2 *list = lst == 0 ? s.xya : s.xyg;
+            const int cntp = align_up(lst == 0 ? L.A : L.G, 32);
             float bd[kVisN];
             int bi[kVisN];
 #pragma unroll
             for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
-#pragma unroll 4
-            for (int j = 0; j < cnt; ++j) {
-                const float2 c = cand[j];
-                const float dx = __fsub_rn(c.x, pg.x), dy = __fsub_rn(c.y, pg.y);
-                const float sq = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-                if (sq <= smax) {
-                    const float d = __fsqrt_rn(sq);
-                    if (d < bd[kVisN - 1]) {
-                        bd[kVisN - 1] = d; bi[kVisN - 1] = j;
+            for (int c0 = 0; c0 < cntp; c0 += 32) {
+                const float4 *c4 = (const float4 *)(list + c0);
+                uint32_t m0 = 0, m1 = 0, m2 = 0;
 #pragma unroll
-                        for (int k = kVisN - 1; k > 0; --k) {
-                            if (bd[k] < bd[k - 1]) {
-                                const float td = bd[k]; bd[k] = bd[k - 1]; bd[k - 1] = td;
-                                const int ti = bi[k]; bi[k] = bi[k - 1]; bi[k - 1] = ti;
-                            }
-                        }
-                    }
+                for (int jj = 0; jj < 16; ++jj) {
+                    const float4 v = c4[jj];
+                    const float dx0 = __fsub_rn(v.x, pg.x), dy0 = __fsub_rn(v.y, pg.y);
+                    const float dx1 = __fsub_rn(v.z, pg.x), dy1 = __fsub_rn(v.w, pg.y);
+                    const float s0 = __fadd_rn(__fmul_rn(dx0, dx0), __fmul_rn(dy0, dy0));
+                    const float s1 = __fadd_rn(__fmul_rn(dx1, dx1), __fmul_rn(dy1, dy1));
+                    m0 |= (s0 <= q0) ? (1u << (2 * jj)) : 0u;
+                    m1 |= (s0 <= q1) ? (1u << (2 * jj)) : 0u;
+                    m2 |= (s0 <= q2) ? (1u << (2 * jj)) : 0u;
+                    m0 |= (s1 <= q0) ? (2u << (2 * jj)) : 0u;
+                    m1 |= (s1 <= q1) ? (2u << (2 * jj)) : 0u;
+                    m2 |= (s1 <= q2) ? (2u << (2 * jj)) : 0u;
+                }
+                uint32_t m = __popc(m2) >= kVisN ? m2 : (__popc(m1) >= kVisN ? m1 : m0);
+                while (m) {
+                    const int j = __ffs(m) - 1;
+                    m &= m - 1;
+                    const float2 cj = list[c0 + j];
+                    const float dx = __fsub_rn(cj.x, pg.x), dy = __fsub_rn(cj.y, pg.y);
+                    const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+                    top6_insert(bd, bi, d, c0 + j);
                 }
             }
             // visible list in sorted order, packed one byte per entry
@@ -345,6 +387,7 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     double sn, ct;
     sincos(s.sc->init_theta, &sn, &ct);
     if (tid < 2) s.misc[tid] = 0;
+    fill_xy(s, L);
     // phase A: guard action decode (_set_action parallel_run.py:326-374), terrain (core.py:224-234),
     // attacker act init (cheat_script_ai.py:31-34) + injected planner force (:183-184), clear hit flags (core.py:239-242)
     for (int i = tid; i < L.N; i += nt) {
@@ -369,7 +412,6 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         }
         s.fx[i] = fx; s.fy[i] = fy; s.ar[i] = ar; s.canfire[i] = cf;
         s.hitcnt[i] = 0;
-        s.xy[i] = alive ? make_float2((float)s.px[i], (float)s.py[i]) : make_float2(CUDART_INF_F, CUDART_INF_F);
         if (alive) {
             s.ter[i] = terrain_at(c, s.px[i], s.py[i], ct, sn);
             s.flags[i] = f & (uint8_t)~(F_HIT | F_WAS_HIT);
@@ -384,11 +426,11 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
             // pass 2 takes sqrt_rn only for candidates within 2^-20 of it (sqrt_rn is monotone, so every guard that
             // ties with the minimum distance is among them) and keeps the lowest index.  Dead guards = +inf.
             best = 0;
-            const float2 pi = s.xy[i];
+            const float2 pi = s.xya[i - L.G];
             float smin = CUDART_INF_F;
 #pragma unroll 4
             for (int g = 0; g < L.G; ++g) {
-                const float2 c = s.xy[g];
+                const float2 c = s.xyg[g];
                 const float dx = __fsub_rn(c.x, pi.x), dy = __fsub_rn(c.y, pi.y);
                 smin = fminf(smin, __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
             }
@@ -397,7 +439,7 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
                 float bd = CUDART_INF_F;
 #pragma unroll 4
                 for (int g = 0; g < L.G; ++g) {
-                    const float2 c = s.xy[g];
+                    const float2 c = s.xyg[g];
                     const float dx = __fsub_rn(c.x, pi.x), dy = __fsub_rn(c.y, pi.y);
                     const float sq = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
                     if (sq <= shi) {
@@ -426,12 +468,13 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         int hits = 0;
         // conservative float32 pre-filter (dead = +inf): pairs whose f32 squared distance exceeds r^2 by 1% + 1e-3
         // cannot satisfy the exact fp64 test below (f32 rounding of |coord| <= 64 perturbs d^2 by < 1e-4 there).
-        const float2 po = s.xy[i];
+        const float2 po = i < L.G ? s.xyg[i] : s.xya[i - L.G];
+        const float2 *opp = i < L.G ? s.xya - L.G : s.xyg;  // opp[j] = float32 position of opponent agent j
         const bool prefilter = fabs(ox) <= 64.0 && fabs(oy) <= 64.0 && r2 < 1.0e3;
         const float r2f = prefilter ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
 #pragma unroll 4
         for (int j = j0; j < j1; ++j) {
-            const float2 pj = s.xy[j];
+            const float2 pj = opp[j];
             const float fdx = pj.x - po.x, fdy = pj.y - po.y;
             const float fs = fdx * fdx + fdy * fdy;
             if (!(fs <= r2f)) continue;                                  // far away, or dead (+inf)

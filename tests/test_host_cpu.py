@@ -161,7 +161,7 @@ adv = normalized_advantage(ret[sl], val[sl])
 full = (ret - val); full = (full - full.mean()) / (full.std() + 1e-5)
 assert torch.allclose(adv, full[sl], atol=1e-5), (adv - full[sl]).abs().max()
 dist.barrier(); dist.destroy_process_group()
-sys.stdout.write('rank %d ok\n' % rank); sys.stdout.flush()
+sys.stdout.write('rank' + str(rank) + 'ok\n'); sys.stdout.flush()
 '''
 
 
