@@ -160,16 +160,21 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
 
     const uint32_t k0 = (uint32_t)P.cfg.seed, k1 = (uint32_t)(P.cfg.seed >> 32);
     const uint32_t gid = (uint32_t)(P.cfg.env_gid0 + e);
-    for (int g = tid; g < L.G; g += nt) {
-        int16_t *sid = s.sid + g * kObsRows;
+    // One task per (guard, list): 2G tasks dealt out evenly over the CTA's warps (a warp lives on one SM
+    // sub-partition; a plain thread-per-guard mapping would leave half of the sub-partitions idle here).
+    const int ntask = 2 * L.G, nwarp = nt >> 5, quota = (ntask + nwarp - 1) / nwarp;
+    for (int o = tid & 31; o < quota; o += 32) {
+        const int task = (tid >> 5) * quota + o;
+        if (task >= ntask) break;
+        const int g = task >> 1, lst = task & 1;  // 0 = hostile (:318-328), 1 = friend (:330-342)
+        int16_t *sid = s.sid + g * kObsRows + (lst == 0 ? kVisN : 0);  // friend rows 0..5, hostile rows 6..11 (:344)
         if (!(s.flags[g] & F_ALIVE)) {  // :313-316 dead guard: zeros, no RNG draws
 #pragma unroll
-            for (int r = 0; r < kObsRows; ++r) sid[r] = -1;
+            for (int r = 0; r < kVisN; ++r) sid[r] = -1;
             continue;
         }
         const float2 pg = s.xyg[g];
-#pragma unroll
-        for (int lst = 0; lst < 2; ++lst) {  // 0 = hostile (:318-328), 1 = friend (:330-342)
+        {
             const int base = lst == 0 ? L.G : 0;
             // argsort()[:6] then the range mask (:308-309, :320-322, :331-333) == the (up to) 6 nearest IN-RANGE
             // candidates: anything farther than an out-of-range member of the top-6 is out of range too.
@@ -220,7 +225,7 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
             for (int k = 0; k < kVisN; ++k) {
                 if (bi[k] >= 0) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
             }
-            int row = lst == 0 ? kVisN : 0;
+            int row = 0;
             if (lst == 1) {  // :334-335 self = first visible friend, excluded from shuffle / jamming
                 sid[row++] = (int16_t)(vis & 0xff);
                 vis >>= 8; --n;
@@ -263,10 +268,9 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
                 }
                 n -= n_mv;
             }
-            const int end = lst == 0 ? kObsRows : kVisN;
 #pragma unroll
             for (int k = 0; k < kVisN; ++k) {
-                if (row < end) {
+                if (row < kVisN) {
                     sid[row] = k < n ? (int16_t)(base + (int)((vis >> (8 * k)) & 0xff)) : (int16_t)-1;
                     ++row;
                 }
@@ -419,7 +423,10 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     }
     __syncthreads();
     // phase B: scripted aim cheat_script_ai.py:196-218 -- nearest alive guard by the float32 distance matrix
-    for (int i = L.G + tid; i < L.N; i += nt) {
+    const int aquota = (L.A + (nt >> 5) - 1) / (nt >> 5);  // attackers dealt out evenly over the warps
+    for (int o = tid & 31; o < aquota; o += 32) {
+        const int i = L.G + (tid >> 5) * aquota + o;
+        if (i >= L.N) break;
         int best = -1;
         if (s.flags[i] & F_ALIVE) {
             // np.argmin of the float32 distance row (first minimum).  Pass 1 finds the minimum squared distance;
