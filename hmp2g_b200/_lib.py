@@ -33,7 +33,7 @@ class DcaState(C.Structure):
 
 EXPORTS = ('dca_abi_version', 'dca_last_error', 'dca_create', 'dca_destroy', 'dca_bind_buffers', 'dca_reset',
            'dca_step', 'dca_observe', 'dca_plan_centroid', 'dca_export_state', 'dca_import_state', 'dca_gae',
-           'dca_kernel_launches')
+           'dca_kernel_launches', 'dca_debug_phase_clocks')
 
 _lib = None
 
@@ -68,6 +68,7 @@ def load(build_if_missing=False):
     lib.dca_import_state.argtypes = [_P, C.POINTER(DcaState), _P]
     lib.dca_gae.argtypes = [_P, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, _P]
     lib.dca_kernel_launches.argtypes = [_P, C.POINTER(C.c_int64)]
+    lib.dca_debug_phase_clocks.argtypes = [_P, _P]
     for name in EXPORTS:
         getattr(lib, name)  # AttributeError if the symbol is not exported
         if name != 'dca_last_error':

@@ -215,6 +215,12 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
     return DCA_OK;
 }
 
+int dca_debug_phase_clocks(DcaHandle *h, uint64_t *clocks) {
+    if (!h) return DCA_E_INVALID;
+    h->P.prof = (unsigned long long *)clocks;
+    return DCA_OK;
+}
+
 int dca_kernel_launches(const DcaHandle *h, int64_t *count) {
     if (!h || !count) return DCA_E_INVALID;
     *count = h->launches;

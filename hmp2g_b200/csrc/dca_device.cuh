@@ -68,6 +68,7 @@ struct Params {
     int E;
     unsigned char *blobs;  // [E, L.bytes]
     DcaBuffers out;
+    unsigned long long *prof;  // optional [E,16] phase clocks (diagnostics), nullptr = off
     float smax[2][3];  // [hostile, friend][level]: largest f32 s with sqrt_rn(s) <= range, range/2, range/4
 };
 

@@ -16,7 +16,6 @@ struct Smem {
     float2 *xyg, *xya;     // float32-rounded positions of guards / attackers (distance matrix inputs), each padded
                            // to a multiple of 32 entries; dead agents and padding = (+inf, +inf)
     int32_t *hitcnt;       // times agent i was hit this step (also: exclusion keys during reset)
-    uint8_t *canfire;
     float *table;          // [N,16] float32 entity records
     int16_t *sid;          // [G,12] entity id per obs row, -1 = zero row
     int32_t *misc;         // [0] guard deaths, [1] attacker deaths
@@ -28,7 +27,6 @@ __host__ __device__ inline int smem_bytes(const BlobLayout &L) {
     o += 3 * align_up(L.N * 8, 16);   // fx fy ar
     o += (align_up(L.G, 32) + align_up(L.A, 32)) * 8;  // xyg xya
     o += align_up(L.N * 4, 16);       // hitcnt
-    o += align_up(L.N, 16);           // canfire
     o += L.N * kObsRow * 4;           // table
     o += align_up(L.G * kObsRows * 2, 16);  // sid
     o += 32;                          // misc
@@ -50,7 +48,6 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
     s.fx = (double *)p; p += f64; s.fy = (double *)p; p += f64; s.ar = (double *)p; p += f64;
     s.xyg = (float2 *)p; p += align_up(L.G, 32) * 8; s.xya = (float2 *)p; p += align_up(L.A, 32) * 8;
     s.hitcnt = (int32_t *)p; p += f32;
-    s.canfire = p; p += align_up(L.N, 16);
     s.table = (float *)p; p += L.N * kObsRow * 4;
     s.sid = (int16_t *)p; p += align_up(L.G * kObsRows * 2, 16);
     s.misc = (int32_t *)p; p += 32;
@@ -81,6 +78,12 @@ __device__ __forceinline__ void store_blob(const Smem &s, const Params &P, int e
         tma_store_commit_wait();
     }
 }
+
+// Optional per-CTA phase clocks (diagnostics, dca_debug_phase_clocks): slot k of env e <- clock64() of thread 0.
+#define DCA_PROF(P, e, k)                                                                     \
+    do {                                                                                      \
+        if ((P).prof != nullptr && threadIdx.x == 0) (P).prof[(size_t)(e) * 16 + (k)] = clock64(); \
+    } while (0)
 
 // ------------------------------------------------------------------ terrain
 // World.set_terrain_adv core.py:224-234 + get_terrain core.py:306-314; alive agents only, dead keep old value.
@@ -126,7 +129,8 @@ __device__ __forceinline__ void top6_insert(float (&bd)[kVisN], int (&bi)[kVisN]
 // ------------------------------------------------------------------ observation pass
 // collective_assaultEnvV1.observation collective_assault_env.py:228-359 for every guard of the env.
 // dest == nullptr: the pass is only counted (keeps the keyed RNG stream aligned), nothing is computed.
-__device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, const uint32_t *rng_words) {
+__device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, const uint32_t *rng_words,
+                         int prof_slot = 12) {
     const BlobLayout &L = P.L;
     const int tid = threadIdx.x, nt = blockDim.x;
     const uint32_t counter = s.sc->obs_counter + 1;
@@ -156,6 +160,7 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
         row[3] = make_float4(b[4], b[5], b[6], b[7]);
     }
     __syncthreads();
+    DCA_PROF(P, e, prof_slot);
     if (tid == 0) s.sc->obs_counter = counter;
 
     const uint32_t k0 = (uint32_t)P.cfg.seed, k1 = (uint32_t)(P.cfg.seed >> 32);
@@ -278,6 +283,7 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
         }
     }
     __syncthreads();
+    DCA_PROF(P, e, prof_slot + 1);
     // gather: 48 x 128-bit per guard, consecutive threads write consecutive 16 B (coalesced)
     float4 *out4 = (float4 *)(dest + (size_t)e * L.G * kObsLen);
     const float4 *tab4 = (const float4 *)s.table;
@@ -291,6 +297,7 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
         for (int t = tid; t < L.G * kObsRows; t += nt) o[t] = s.sid[t];
     }
     __syncthreads();
+    DCA_PROF(P, e, prof_slot + 2);
 }
 
 // ------------------------------------------------------------------ reset
@@ -386,7 +393,9 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     const DcaConfig &c = P.cfg;
     const Smem s = carve(smem_raw, L);
     const int tid = threadIdx.x, nt = blockDim.x;
+    DCA_PROF(P, e, 0);
     load_blob(s, P, e);
+    DCA_PROF(P, e, 1);
 
     double sn, ct;
     sincos(s.sc->init_theta, &sn, &ct);
@@ -398,7 +407,6 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         uint8_t f = s.flags[i];
         const bool alive = f & F_ALIVE;
         double fx = 0, fy = 0, ar = 0;
-        uint8_t cf = 0;
         if (i < L.G) {
             const int a = actions[(size_t)e * L.G + i];
             double a0 = 0, a1 = 0;
@@ -409,12 +417,11 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
             if (a == 5) ar = +c.agent_max_rot;
             if (a == 6) ar = -c.agent_max_rot;
             fx = a0 * c.agent_acc; fy = a1 * c.agent_acc;
-            cf = 1;
         } else if (alive) {
             const double2 F = ((const double2 *)att_force)[(size_t)e * L.A + (i - L.G)];
             fx = F.x; fy = F.y;
         }
-        s.fx[i] = fx; s.fy[i] = fy; s.ar[i] = ar; s.canfire[i] = cf;
+        s.fx[i] = fx; s.fy[i] = fy; s.ar[i] = ar;
         s.hitcnt[i] = 0;
         if (alive) {
             s.ter[i] = terrain_at(c, s.px[i], s.py[i], ct, sn);
@@ -422,83 +429,105 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         }
     }
     __syncthreads();
-    // phase B: scripted aim cheat_script_ai.py:196-218 -- nearest alive guard by the float32 distance matrix
-    const int aquota = (L.A + (nt >> 5) - 1) / (nt >> 5);  // attackers dealt out evenly over the warps
-    for (int o = tid & 31; o < aquota; o += 32) {
-        const int i = L.G + (tid >> 5) * aquota + o;
-        if (i >= L.N) break;
-        int best = -1;
-        if (s.flags[i] & F_ALIVE) {
-            // np.argmin of the float32 distance row (first minimum).  Pass 1 finds the minimum squared distance;
-            // pass 2 takes sqrt_rn only for candidates within 2^-20 of it (sqrt_rn is monotone, so every guard that
-            // ties with the minimum distance is among them) and keeps the lowest index.  Dead guards = +inf.
-            best = 0;
-            const float2 pi = s.xya[i - L.G];
-            float smin = CUDART_INF_F;
+    DCA_PROF(P, e, 2);
+    DCA_PROF(P, e, 3);
+    // phase B+C: scripted aim (cheat_script_ai.py:196-218) and apply_laser_effect (core.py:244-263 with
+    // laser_hit_improve3 cython_func.pyx:22-46).  Warp roles: the first half of the CTA's warps own the attackers
+    // (aim, then fire), the second half the guards (fire), so no warp mixes the two code paths.
+    {
+        const int nwarp = nt >> 5, wa = nwarp >> 1;
+        const bool att_role = (tid >> 5) < wa;
+        const int role_threads = (att_role ? wa : nwarp - wa) * 32;
+        const int role_tid = att_role ? tid : tid - wa * 32;
+        const int role_cnt = att_role ? L.A : L.G;
+        const float2 *opp = att_role ? s.xyg : s.xya;       // float32 positions of the opposing team (+inf = dead)
+        const int opp_cnt = att_role ? L.G : L.A, opp_base = att_role ? 0 : L.G;
+        const int opp4 = (opp_cnt + 1) >> 1;                // float4 = 2 candidates; padding slots are +inf
+        const float4 *opp_v4 = (const float4 *)opp;
+        for (int t = role_tid; t < role_cnt; t += role_threads) {
+            const int i = att_role ? L.G + t : t;
+            const bool alive = s.flags[i] & F_ALIVE;
+            const float2 po = att_role ? s.xya[t] : s.xyg[t];
+            if (att_role) {
+                int best = -1;
+                if (alive) {
+                    // np.argmin over the float32 distance row (first minimum; dead guards +inf).  One branch-free pass
+                    // tracks the two smallest SQUARED distances and the first index of the smallest; sqrt_rn is
+                    // monotone, so only when the runner-up is within 2^-20 of the minimum can the rounded distances
+                    // tie -- then (rare) a second pass compares true sqrt_rn values, lowest index first.
+                    float s1 = CUDART_INF_F, s2 = CUDART_INF_F;
+                    best = 0;
 #pragma unroll 4
-            for (int g = 0; g < L.G; ++g) {
-                const float2 c = s.xyg[g];
-                const float dx = __fsub_rn(c.x, pi.x), dy = __fsub_rn(c.y, pi.y);
-                smin = fminf(smin, __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+                    for (int jj = 0; jj < opp4; ++jj) {
+                        const float4 v = opp_v4[jj];
+                        const float dx0 = __fsub_rn(v.x, po.x), dy0 = __fsub_rn(v.y, po.y);
+                        const float dx1 = __fsub_rn(v.z, po.x), dy1 = __fsub_rn(v.w, po.y);
+                        const float q0 = __fadd_rn(__fmul_rn(dx0, dx0), __fmul_rn(dy0, dy0));
+                        const float q1 = __fadd_rn(__fmul_rn(dx1, dx1), __fmul_rn(dy1, dy1));
+                        bool lt = q0 < s1;
+                        s2 = fminf(s2, lt ? s1 : q0); best = lt ? 2 * jj : best; s1 = fminf(s1, q0);
+                        lt = q1 < s1;
+                        s2 = fminf(s2, lt ? s1 : q1); best = lt ? 2 * jj + 1 : best; s1 = fminf(s1, q1);
+                    }
+                    if (s2 <= __fmul_ru(s1, 1.000001f) && s1 < CUDART_INF_F) {
+                        float bd = CUDART_INF_F;
+                        for (int g = 0; g < opp_cnt; ++g) {
+                            const float d = f32_dist(po.x, po.y, opp[g].x, opp[g].y);
+                            if (d < bd) { bd = d; best = g; }
+                        }
+                    }
+                    double th = atan2(s.py[best] - s.py[i], s.px[best] - s.px[i]);
+                    if (th < 0) th += 2 * kPi;
+                    s.atk[i] = th;
+                }
+                if (P.out.nearest) P.out.nearest[(size_t)e * L.A + t] = best;
+                if (c.disable_red_function) continue;  // can_fire = False (cheat_script_ai.py:216-217)
             }
-            if (smin < CUDART_INF_F) {
-                const float shi = __fmul_ru(smin, 1.000001f);
-                float bd = CUDART_INF_F;
+            if (!alive) continue;
+            const double radius = c.agent_shoot_base_radius * s.ter[i];
+            const double r2 = radius * radius;
+            const double dir = s.atk[i];
+            const double pos_r = dir + c.agent_shoot_win / 2, neg_r = dir - c.agent_shoot_win / 2;
+            const double ox = s.px[i], oy = s.py[i];
+            // conservative float32 pre-filter (dead = +inf): a pair whose f32 squared distance exceeds r^2 by
+            // 1% + 1e-3 cannot pass the exact fp64 test (f32 rounding of |coord| <= 64 perturbs d^2 by < 1e-4).
+            // Candidates are collected branch-free into a bit mask per 32 opponents; the exact fp64 test
+            // (atan2, two reg_angle) then runs once per set bit, all lanes of the warp in parallel.
+            const bool prefilter = fabs(ox) <= 64.0 && fabs(oy) <= 64.0 && r2 < 1.0e3;
+            const float r2f = prefilter ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
+            int hits = 0;
+            for (int c0 = 0; c0 < opp_cnt; c0 += 32) {
+                uint32_t m = 0;
+                const int n4 = min(16, opp4 - (c0 >> 1));
 #pragma unroll 4
-                for (int g = 0; g < L.G; ++g) {
-                    const float2 c = s.xyg[g];
-                    const float dx = __fsub_rn(c.x, pi.x), dy = __fsub_rn(c.y, pi.y);
-                    const float sq = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-                    if (sq <= shi) {
-                        const float d = __fsqrt_rn(sq);
-                        if (d < bd) { bd = d; best = g; }
+                for (int jj = 0; jj < n4; ++jj) {
+                    const float4 v = opp_v4[(c0 >> 1) + jj];
+                    const float dx0 = v.x - po.x, dy0 = v.y - po.y, dx1 = v.z - po.x, dy1 = v.w - po.y;
+                    const float f0 = dx0 * dx0 + dy0 * dy0, f1 = dx1 * dx1 + dy1 * dy1;
+                    m |= ((f0 <= r2f) ? 1u : 0u) << (2 * jj);
+                    m |= ((f1 <= r2f) ? 2u : 0u) << (2 * jj);
+                }
+                while (m) {
+                    const int j = opp_base + c0 + __ffs(m) - 1;
+                    m &= m - 1;
+                    if (j >= opp_base + opp_cnt) break;
+                    if (!prefilter && !(s.flags[j] & F_ALIVE)) continue;  // r2f = +inf lets dead targets through
+                    const double dx = s.px[j] - ox, dy = s.py[j] - oy;
+                    const double d2 = dx * dx + dy * dy;
+                    if (d2 > r2) continue;
+                    const double tt = atan2(dy, dx);
+                    const double d1 = fabs(reg_angle(pos_r - tt)), d2r = fabs(reg_angle(neg_r - tt));
+                    if (d1 <= c.agent_shoot_win && d2r <= c.agent_shoot_win) {
+                        ++hits;
+                        atomicAdd(&s.hitcnt[j], 1);
                     }
                 }
             }
-            double th = atan2(s.py[best] - s.py[i], s.px[best] - s.px[i]);
-            if (th < 0) th += 2 * kPi;
-            s.atk[i] = th;
-            s.canfire[i] = c.disable_red_function ? 0 : 1;
+            if (hits) { s.flags[i] |= F_HIT; s.nhit[i] += hits; }
         }
-        if (P.out.nearest) P.out.nearest[(size_t)e * L.A + (i - L.G)] = best;
     }
     __syncthreads();
-    // phase C: apply_laser_effect core.py:244-263 with laser_hit_improve3 cython_func.pyx:22-46
-    for (int i = tid; i < L.N; i += nt) {
-        if (!(s.flags[i] & F_ALIVE) || !s.canfire[i]) continue;
-        const double radius = c.agent_shoot_base_radius * s.ter[i];
-        const double r2 = radius * radius;
-        const double dir = s.atk[i];
-        const double pos_r = dir + c.agent_shoot_win / 2, neg_r = dir - c.agent_shoot_win / 2;
-        const double ox = s.px[i], oy = s.py[i];
-        const int j0 = i < L.G ? L.G : 0, j1 = i < L.G ? L.N : L.G;
-        int hits = 0;
-        // conservative float32 pre-filter (dead = +inf): pairs whose f32 squared distance exceeds r^2 by 1% + 1e-3
-        // cannot satisfy the exact fp64 test below (f32 rounding of |coord| <= 64 perturbs d^2 by < 1e-4 there).
-        const float2 po = i < L.G ? s.xyg[i] : s.xya[i - L.G];
-        const float2 *opp = i < L.G ? s.xya - L.G : s.xyg;  // opp[j] = float32 position of opponent agent j
-        const bool prefilter = fabs(ox) <= 64.0 && fabs(oy) <= 64.0 && r2 < 1.0e3;
-        const float r2f = prefilter ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
-#pragma unroll 4
-        for (int j = j0; j < j1; ++j) {
-            const float2 pj = opp[j];
-            const float fdx = pj.x - po.x, fdy = pj.y - po.y;
-            const float fs = fdx * fdx + fdy * fdy;
-            if (!(fs <= r2f)) continue;                                  // far away, or dead (+inf)
-            if (!prefilter && !(s.flags[j] & F_ALIVE)) continue;         // r2f = +inf lets dead targets through
-            const double dx = s.px[j] - ox, dy = s.py[j] - oy;
-            const double d2 = dx * dx + dy * dy;
-            if (d2 > r2) continue;
-            const double t = atan2(dy, dx);
-            const double d1 = fabs(reg_angle(pos_r - t)), d2r = fabs(reg_angle(neg_r - t));
-            if (d1 <= c.agent_shoot_win && d2r <= c.agent_shoot_win) {
-                ++hits;
-                atomicAdd(&s.hitcnt[j], 1);
-            }
-        }
-        if (hits) { s.flags[i] |= F_HIT; s.nhit[i] += hits; }
-    }
-    __syncthreads();
+    DCA_PROF(P, e, 4);
     // phase D: deaths core.py:266-279, forces :210-222,339-353, integrate_state :282-302 (survivors only)
     for (int i = tid; i < L.N; i += nt) {
         uint8_t f = s.flags[i];
@@ -535,6 +564,7 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         s.px[i] = x + vx * dt; s.py[i] = y + vy * dt;
     }
     __syncthreads();
+    DCA_PROF(P, e, 5);
     // phase E: done/win (_get_done parallel_run.py:286-316), reward (collective_assault_env.py:153-179, :228-231)
     const int nG = s.sc->n_alive_guards - s.misc[0], nA = s.sc->n_alive_attackers - s.misc[1];
     const int ts = s.sc->time_step;
@@ -560,9 +590,10 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
         P.out.win[e] = (uint8_t)win;
     }
     __syncthreads();
+    DCA_PROF(P, e, 6);
     // phase F: observation; on done the terminal obs goes to tobs, the env is reset and observed again
     const bool do_reset = done && autoreset;
-    obs_pass(s, P, e, do_reset ? P.out.tobs : P.out.obs, rng_words);
+    obs_pass(s, P, e, do_reset ? P.out.tobs : P.out.obs, rng_words, 7);
     if (do_reset) {
         reset_world(s, P, e);
         obs_pass(s, P, e, P.out.obs, nullptr);
@@ -570,7 +601,9 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     if (P.out.alive) {
         for (int i = tid; i < L.N; i += nt) P.out.alive[(size_t)e * L.N + i] = s.flags[i] & F_ALIVE;
     }
+    DCA_PROF(P, e, 10);
     store_blob(s, P, e);
+    DCA_PROF(P, e, 11);
 }
 
 // reset kernel: SuperpoolEnv.reset -> collective_assaultGlobalEnv.reset parallel_run.py:248-270

@@ -124,6 +124,10 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
 
 const char *dca_last_error(const DcaHandle *h); /* host string; h may be NULL for create/gae errors */
 int dca_kernel_launches(const DcaHandle *h, int64_t *count); /* kernels launched through this handle so far */
+/* Diagnostics: u64[E,16] device buffer receiving clock64() of thread 0 at the phase boundaries of the next
+ * dca_step launches (NULL switches it off).  Slots: 0 start, 1 blob loaded, 2 decode+terrain, 3 aim, 4 laser,
+ * 5 deaths+integrate, 6 reward/done, 7 entity table, 8 kNN+shuffle, 9 gather, 10 reset path done, 11 blob stored. */
+int dca_debug_phase_clocks(DcaHandle *h, uint64_t *clocks);
 int dca_abi_version(void);
 
 #ifdef __cplusplus
