@@ -1,0 +1,24 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, bench line, phase clocks, ncu launch list + one --set full capture of k_step.
+# usage: gpurun --timeout 1500 -- 'bash tools/gpu_check.sh <tag>'
+tag=${1:-run}
+out=gpurun_out/$tag
+mkdir -p $out
+nvidia-smi --query-gpu=index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active --format=csv -lms 500 > $out/clocks.csv &
+SMI=$!
+timeout 900 python -m pytest tests -m gpu -x -q > $out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $out/pytest_gpu.log
+tail -3 $out/pytest_gpu.log
+timeout 600 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench rc=$?"
+cat $out/bench.json
+timeout 300 python bench.py --impl reference --steps 60 --warmup 5 > $out/bench_ref.json 2>> $out/bench.err; echo "ref rc=$?"
+cat $out/bench_ref.json
+timeout 300 python tools/phase_clocks.py > $out/phase.log 2>&1; cat $out/phase.log
+kill $SMI
+SHORT="python bench.py --steps 12 --warmup 4 --no-cpu-baseline --e2e-steps 3"
+timeout 300 $SHORT > $out/plain.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $out/launches.csv $SHORT > $out/ncu_list.log 2>&1
+echo "ncu list rc=$?"
+timeout 300 $SHORT > $out/plain2.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_step -s 8 -c 2 -o $out/prof_step $SHORT > $out/ncu_full.log 2>&1
+echo "ncu full rc=$?"
+ls -la $out
