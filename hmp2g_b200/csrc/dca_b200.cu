@@ -59,6 +59,34 @@ static float sq_limit(float lim) {
     return s;
 }
 
+// Kernel instantiations: the BASELINE team sizes get compile-time layouts, everything else the generic build.
+#define DCA_DISPATCH(h, KERNEL, ...)                                                                        \
+    do {                                                                                                    \
+        const int G_ = (h)->P.L.G, A_ = (h)->P.L.A;                                                         \
+        const dim3 grid_((h)->P.E);                                                                         \
+        if ((h)->threads == 128) {                                                                          \
+            if (G_ == 50 && A_ == 50) KERNEL<128, 50, 50><<<grid_, 128, (h)->smem, st_>>>(__VA_ARGS__);      \
+            else if (G_ == 50 && A_ == 55) KERNEL<128, 50, 55><<<grid_, 128, (h)->smem, st_>>>(__VA_ARGS__); \
+            else KERNEL<128, 0, 0><<<grid_, 128, (h)->smem, st_>>>(__VA_ARGS__);                             \
+        } else {                                                                                            \
+            if (G_ == 100 && A_ == 100) KERNEL<256, 100, 100><<<grid_, 256, (h)->smem, st_>>>(__VA_ARGS__);  \
+            else KERNEL<256, 0, 0><<<grid_, 256, (h)->smem, st_>>>(__VA_ARGS__);                             \
+        }                                                                                                   \
+    } while (0)
+
+template <typename K>
+static cudaError_t allow_smem(K kernel, int bytes) {
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+#define DCA_ALLOW_SMEM(KERNEL, bytes)                                                                   \
+    do {                                                                                                \
+        if (e == cudaSuccess) e = allow_smem(KERNEL<128, 50, 50>, bytes);                               \
+        if (e == cudaSuccess) e = allow_smem(KERNEL<128, 50, 55>, bytes);                               \
+        if (e == cudaSuccess) e = allow_smem(KERNEL<128, 0, 0>, bytes);                                 \
+        if (e == cudaSuccess) e = allow_smem(KERNEL<256, 100, 100>, bytes);                             \
+        if (e == cudaSuccess) e = allow_smem(KERNEL<256, 0, 0>, bytes);                                 \
+    } while (0)
+
 extern "C" {
 
 int dca_abi_version(void) { return 1; }
@@ -88,18 +116,27 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     h->P.cfg = *cfg;
     h->P.L = make_layout(G, A);
     h->P.E = n_env;
-    for (int lvl = 0; lvl < 3; ++lvl) {
-        h->P.smax[0][lvl] = sq_limit(2.0f / (float)(1 << lvl));  // obs_range collective_assault_env.py:284
-        h->P.smax[1][lvl] = sq_limit(3.0f / (float)(1 << lvl));  // obs_range * 1.5 :332
+    h->P.smax[0] = sq_limit(2.0f);  // obs_range collective_assault_env.py:284
+    h->P.smax[1] = sq_limit(3.0f);  // obs_range * 1.5 :332
+    {
+        const int cap = (G > A ? G : A) + 1;  // candidate indices and the marker are <= cap - 1
+        int bits = 5;
+        while ((1 << bits) < cap) ++bits;
+        h->P.idx_bits = bits;  // 6 for teams of <= 63, 7 for <= 127, 8 for <= 255
+    }
+    {
+        // (double)w * 2^-32 < p  <=>  w < p * 2^32 (exact scaling)  <=>  w < ceil(p * 2^32) for integer w
+        const double t = std::ceil(cfg->random_jam_prob * 4294967296.0);
+        h->P.jam_thresh = t <= 0 ? 0ull : (t >= 4294967296.0 ? 4294967296ull : (unsigned long long)t);
     }
     h->threads = (G + A) <= 128 ? 128 : 256;
     h->smem = smem_bytes(h->P.L);
     const size_t bytes = (size_t)n_env * h->P.L.bytes;
     cudaError_t e = cudaMalloc((void **)&h->P.blobs, bytes);
     if (e == cudaSuccess) e = cudaMemset(h->P.blobs, 0, bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_reset, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_observe, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+    DCA_ALLOW_SMEM(k_step, h->smem);
+    DCA_ALLOW_SMEM(k_reset, h->smem);
+    DCA_ALLOW_SMEM(k_observe, h->smem);
     if (e == cudaSuccess) {
         k_init_blobs<<<(n_env + 255) / 256, 256>>>(h->P);
         e = cudaGetLastError();
@@ -144,7 +181,8 @@ static int check_ready(DcaHandle *h, const char *who) {
 int dca_reset(DcaHandle *h, const uint8_t *env_mask, dca_stream_t stream) {
     if (int rc = check_ready(h, "dca_reset")) return rc;
     DeviceGuard guard(h->device);
-    k_reset<<<h->P.E, h->threads, h->smem, (cudaStream_t)stream>>>(h->P, env_mask);
+    cudaStream_t st_ = (cudaStream_t)stream;
+    DCA_DISPATCH(h, k_reset, h->P, env_mask);
     CUDA_TRY(h, cudaGetLastError());
     h->launches += 1;
     return DCA_OK;
@@ -157,7 +195,8 @@ int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, cons
     if (((uintptr_t)att_force & 15) || (rng_words && ((uintptr_t)rng_words & 15)))
         return fail(h, DCA_E_INVALID, "dca_step: att_force / rng_words must be 16-byte aligned");
     DeviceGuard guard(h->device);
-    k_step<<<h->P.E, h->threads, h->smem, (cudaStream_t)stream>>>(h->P, actions, att_force, skip, rng_words, autoreset);
+    cudaStream_t st_ = (cudaStream_t)stream;
+    DCA_DISPATCH(h, k_step, h->P, actions, att_force, skip, rng_words, autoreset);
     CUDA_TRY(h, cudaGetLastError());
     h->launches += 1;
     return DCA_OK;
@@ -166,7 +205,8 @@ int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, cons
 int dca_observe(DcaHandle *h, const uint32_t *rng_words, dca_stream_t stream) {
     if (int rc = check_ready(h, "dca_observe")) return rc;
     DeviceGuard guard(h->device);
-    k_observe<<<h->P.E, h->threads, h->smem, (cudaStream_t)stream>>>(h->P, rng_words);
+    cudaStream_t st_ = (cudaStream_t)stream;
+    DCA_DISPATCH(h, k_observe, h->P, rng_words);
     CUDA_TRY(h, cudaGetLastError());
     h->launches += 1;
     return DCA_OK;

@@ -27,7 +27,7 @@ constexpr double kPi = 3.141592653589793;    // np.pi
 // flag bits of the per-agent state byte
 enum : uint8_t { F_ALIVE = 1, F_JUST_DIED = 2, F_HIT = 4, F_WAS_HIT = 8 };
 
-__host__ __device__ inline int align_up(int x, int a) { return (x + a - 1) / a * a; }
+__host__ __device__ constexpr int align_up(int x, int a) { return (x + a - 1) / a * a; }
 
 // Byte offsets of the fields inside one env blob.
 struct BlobLayout {
@@ -35,6 +35,9 @@ struct BlobLayout {
     int px, py, vx, vy, atk, terrain;  // f64[N]
     int num_hit, num_was_hit;          // i32[N]
     int flags;                         // u8[N]
+    int knn_ids;                       // u64[2G] perf hint: the 7 nearest of the last pass per (guard, list), one byte each
+                                       //         (marker = list length); bounds the next scan radius, never affects results
+    int hmin;                          // f32[G]  lower bound of the f32 squared distance guard -> nearest alive attacker
     int scalars;                       // EnvScalars
     int bytes;                         // multiple of 128
 };
@@ -44,11 +47,16 @@ struct EnvScalars {
     int32_t time_step, n_alive_guards, n_alive_attackers;
     uint32_t obs_counter, episode;
     uint32_t pad;
+    double cos_theta, sin_theta;  // cos / sin of init_theta (derived; refreshed by reset and state import)
 };
-static_assert(sizeof(EnvScalars) == 32, "EnvScalars must stay 32 bytes");
+static_assert(sizeof(EnvScalars) == 48, "EnvScalars must stay 48 bytes");
 
-__host__ __device__ inline BlobLayout make_layout(int G, int A) {
-    BlobLayout L;
+// list arrays (float32 positions per team) are padded with +inf to a multiple of 4 entries and always hold at least
+// one padding slot: index `cnt` is the "no entry" marker of the kNN hints
+__host__ __device__ constexpr int list_pad(int cnt) { return (cnt + 1 + 3) / 4 * 4; }
+
+__host__ __device__ constexpr BlobLayout make_layout(int G, int A) {
+    BlobLayout L{};
     L.G = G; L.A = A; L.N = G + A;
     int o = 0;
     const int f64 = align_up(L.N * 8, 16), i32 = align_up(L.N * 4, 16), u8 = align_up(L.N, 16);
@@ -56,6 +64,8 @@ __host__ __device__ inline BlobLayout make_layout(int G, int A) {
     L.atk = o; o += f64; L.terrain = o; o += f64;
     L.num_hit = o; o += i32; L.num_was_hit = o; o += i32;
     L.flags = o; o += u8;
+    L.knn_ids = o; o += align_up(2 * L.G * 8, 16);
+    L.hmin = o; o += align_up(L.G * 4, 16);
     L.scalars = o; o += (int)sizeof(EnvScalars);
     L.bytes = align_up(o, 128);
     return L;
@@ -69,7 +79,9 @@ struct Params {
     unsigned char *blobs;  // [E, L.bytes]
     DcaBuffers out;
     unsigned long long *prof;  // optional [E,16] phase clocks (diagnostics), nullptr = off
-    float smax[2][3];  // [hostile, friend][level]: largest f32 s with sqrt_rn(s) <= range, range/2, range/4
+    float smax[2];     // [hostile, friend]: largest f32 s with sqrt_rn(s) <= obs range (2.0 / 3.0)
+    int idx_bits;      // low bits of a kNN / aim key that hold the candidate index
+    unsigned long long jam_thresh;  // a jam draw w (u32) removes an item iff w < jam_thresh  (== w * 2^-32 < random_jam_prob)
 };
 
 // ------------------------------------------------------------------ Philox4x32-10 (keyed RNG stream)
@@ -117,6 +129,43 @@ __device__ __forceinline__ double logaddexp0(double y) {
 __device__ __forceinline__ float f32_dist(float xi, float yi, float xj, float yj) {
     const float dx = __fsub_rn(xj, xi), dy = __fsub_rn(yj, yi);
     return __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+}
+
+// ------------------------------------------------------------------ packed f32x2 arithmetic (sm_100 FADD2 / FMUL2 / FFMA2)
+// Two candidates per instruction.  ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2, so the packed squared
+// distance below may differ from the reference's fl(fl(dx*dx)+fl(dy*dy)) by one rounding: it is used ONLY for
+// conservative pre-filters (thresholds carry a margin); every value that decides an output is recomputed with the
+// scalar __fmul_rn/__fadd_rn sequence.
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+    return (u64)__float_as_uint(lo) | ((u64)__float_as_uint(hi) << 32);
+}
+__device__ __forceinline__ float lo2(u64 v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float hi2(u64 v) { return __uint_as_float((uint32_t)(v >> 32)); }
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) {
+    u64 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+// approximate squared distances of two candidates (x0,x1),(y0,y1) to (px,px),(py,py): within 2 ulp of the exact one
+__device__ __forceinline__ u64 sqdist2(u64 xs, u64 ys, u64 px2, u64 py2) {
+    const u64 dx = sub2(xs, px2), dy = sub2(ys, py2);
+    return fma2(dx, dx, mul2(dy, dy));
+}
+// exact float32 squared distance, same roundings as distance_matrix() before the sqrt (collective_assault_env.py:361-368)
+__device__ __forceinline__ float f32_sqdist(float xi, float yi, float xj, float yj) {
+    const float dx = __fsub_rn(xj, xi), dy = __fsub_rn(yj, yi);
+    return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
 }
 
 // ------------------------------------------------------------------ TMA bulk copy (1-D) + mbarrier

@@ -1,9 +1,16 @@
 // dca_kernels.cuh -- the DCA step / observation / reset kernels (one CTA per env, state in shared memory).
 // Reference semantics are cited per phase (paths relative to /root/reference).
+//
+// Every kernel is a template on <threads, G, A>: the common team sizes are compiled with the blob layout as
+// compile-time constants (all offsets, loop bounds and index arithmetic fold); <.., 0, 0> reads the layout from
+// the kernel parameters.
 #pragma once
 #include "dca_device.cuh"
 
 namespace dca {
+
+constexpr int kPairCap = 256;  // queued (shooter, target) laser candidates per env; overflow is tested in place
+constexpr int kHintN = kVisN + 1;  // neighbours remembered per (guard, list) for the next pass
 
 // Shared-memory view of one env: the blob (TMA destination) followed by per-step work arrays.
 struct Smem {
@@ -11,26 +18,33 @@ struct Smem {
     double *px, *py, *vx, *vy, *atk, *ter;
     int32_t *nhit, *nwas;
     uint8_t *flags;
+    u64 *knn_ids;
+    float *hmin;
     EnvScalars *sc;
     double *fx, *fy, *ar;  // force (act[0:2]) and rotation (act[2]) of this step
-    float2 *xyg, *xya;     // float32-rounded positions of guards / attackers (distance matrix inputs), each padded
-                           // to a multiple of 32 entries; dead agents and padding = (+inf, +inf)
+    float *xg, *yg, *xa, *ya;  // float32-rounded positions of guards / attackers (distance matrix inputs), SoA,
+                               // list_pad() entries each; dead agents and padding = +inf
     int32_t *hitcnt;       // times agent i was hit this step (also: exclusion keys during reset)
-    float *table;          // [N,16] float32 entity records
+    int32_t *shots;        // hits agent i scored this step
+    float *table;          // [N+1,16] float32 entity records; row N is all zero (invisible / jammed / empty slots)
     int16_t *sid;          // [G,12] entity id per obs row, -1 = zero row
-    int32_t *misc;         // [0] guard deaths, [1] attacker deaths
+    int16_t *shooters;     // [N] compacted list of agents that may hit something this step
+    uint32_t *pairs;       // [kPairCap] (shooter << 16 | target) candidates for the exact fp64 laser test
+    int32_t *misc;         // [0] guard deaths, [1] attacker deaths, [2] #shooters, [3] #pairs
     uint64_t *bar;
 };
 
-__host__ __device__ inline int smem_bytes(const BlobLayout &L) {
+__host__ __device__ constexpr int smem_bytes(const BlobLayout &L) {
     int o = L.bytes;
-    o += 3 * align_up(L.N * 8, 16);   // fx fy ar
-    o += (align_up(L.G, 32) + align_up(L.A, 32)) * 8;  // xyg xya
-    o += align_up(L.N * 4, 16);       // hitcnt
-    o += L.N * kObsRow * 4;           // table
-    o += align_up(L.G * kObsRows * 2, 16);  // sid
-    o += 32;                          // misc
-    o += 16;                          // mbarrier
+    o += 3 * align_up(L.N * 8, 16);                 // fx fy ar
+    o += (list_pad(L.G) + list_pad(L.A)) * 8;       // xg yg xa ya
+    o += 2 * align_up(L.N * 4, 16);                 // hitcnt shots
+    o += (L.N + 1) * kObsRow * 4;                   // table
+    o += align_up(L.G * kObsRows * 2, 16);          // sid
+    o += align_up(L.N * 2, 16);                     // shooters
+    o += kPairCap * 4;                              // pairs
+    o += 32;                                        // misc
+    o += 16;                                        // mbarrier
     return o;
 }
 
@@ -42,39 +56,44 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
     s.atk = (double *)(base + L.atk); s.ter = (double *)(base + L.terrain);
     s.nhit = (int32_t *)(base + L.num_hit); s.nwas = (int32_t *)(base + L.num_was_hit);
     s.flags = base + L.flags;
+    s.knn_ids = (u64 *)(base + L.knn_ids); s.hmin = (float *)(base + L.hmin);
     s.sc = (EnvScalars *)(base + L.scalars);
     unsigned char *p = base + L.bytes;
     const int f64 = align_up(L.N * 8, 16), f32 = align_up(L.N * 4, 16);
+    const int Gp = list_pad(L.G), Ap = list_pad(L.A);
     s.fx = (double *)p; p += f64; s.fy = (double *)p; p += f64; s.ar = (double *)p; p += f64;
-    s.xyg = (float2 *)p; p += align_up(L.G, 32) * 8; s.xya = (float2 *)p; p += align_up(L.A, 32) * 8;
-    s.hitcnt = (int32_t *)p; p += f32;
-    s.table = (float *)p; p += L.N * kObsRow * 4;
+    s.xg = (float *)p; p += Gp * 4; s.yg = (float *)p; p += Gp * 4;
+    s.xa = (float *)p; p += Ap * 4; s.ya = (float *)p; p += Ap * 4;
+    s.hitcnt = (int32_t *)p; p += f32; s.shots = (int32_t *)p; p += f32;
+    s.table = (float *)p; p += (L.N + 1) * kObsRow * 4;
     s.sid = (int16_t *)p; p += align_up(L.G * kObsRows * 2, 16);
+    s.shooters = (int16_t *)p; p += align_up(L.N * 2, 16);
+    s.pairs = (uint32_t *)p; p += kPairCap * 4;
     s.misc = (int32_t *)p; p += 32;
     s.bar = (uint64_t *)p;
     return s;
 }
 
 // Fetch the env blob with one TMA bulk copy; returns after the data has landed for every thread.
-__device__ __forceinline__ void load_blob(const Smem &s, const Params &P, int e) {
+__device__ __forceinline__ void load_blob(const Smem &s, const Params &P, const BlobLayout &L, int e) {
     if (threadIdx.x == 0) {
         mbar_init(s.bar, 1);
         fence_barrier_init();
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        mbar_expect_tx(s.bar, (uint32_t)P.L.bytes);
-        tma_load_1d(s.blob, P.blobs + (size_t)e * P.L.bytes, (uint32_t)P.L.bytes, s.bar);
+        mbar_expect_tx(s.bar, (uint32_t)L.bytes);
+        tma_load_1d(s.blob, P.blobs + (size_t)e * L.bytes, (uint32_t)L.bytes, s.bar);
     }
     mbar_wait(s.bar, 0);
 }
 
 // Write the blob back with one TMA bulk store.  Generic-proxy writes are fenced into the async proxy first.
-__device__ __forceinline__ void store_blob(const Smem &s, const Params &P, int e) {
+__device__ __forceinline__ void store_blob(const Smem &s, const Params &P, const BlobLayout &L, int e) {
     fence_proxy_async();
     __syncthreads();
     if (threadIdx.x == 0) {
-        tma_store_1d(P.blobs + (size_t)e * P.L.bytes, s.blob, (uint32_t)P.L.bytes);
+        tma_store_1d(P.blobs + (size_t)e * L.bytes, s.blob, (uint32_t)L.bytes);
         tma_store_commit_wait();
     }
 }
@@ -100,14 +119,15 @@ __device__ __forceinline__ double terrain_at(const DcaConfig &c, double X, doubl
 
 // Refresh the padded float32 position arrays from the fp64 state (dead agents and padding slots = +inf).
 __device__ __forceinline__ void fill_xy(const Smem &s, const BlobLayout &L) {
-    const int Gp = align_up(L.G, 32), Ap = align_up(L.A, 32);
+    const int Gp = list_pad(L.G), Ap = list_pad(L.A);
     for (int k = threadIdx.x; k < Gp + Ap; k += blockDim.x) {
         const bool isg = k < Gp;
         const int a = isg ? k : k - Gp;
         const int i = isg ? a : L.G + a;
-        float2 v = make_float2(CUDART_INF_F, CUDART_INF_F);
-        if ((isg ? a < L.G : a < L.A) && (s.flags[i] & F_ALIVE)) v = make_float2((float)s.px[i], (float)s.py[i]);
-        s.xyg[k] = v;  // xya follows xyg contiguously
+        float x = CUDART_INF_F, y = CUDART_INF_F;
+        if ((isg ? a < L.G : a < L.A) && (s.flags[i] & F_ALIVE)) { x = (float)s.px[i]; y = (float)s.py[i]; }
+        if (isg) { s.xg[a] = x; s.yg[a] = y; }
+        else { s.xa[a] = x; s.ya[a] = y; }
     }
 }
 
@@ -126,12 +146,127 @@ __device__ __forceinline__ void top6_insert(float (&bd)[kVisN], int (&bi)[kVisN]
     bi[0] = p[0] ? j : bi[0];
 }
 
+// Conservative candidate mask of list entries [c0, c0 + 4*nq), nq <= 8 quads: bit j set if the (approximate, packed)
+// squared distance of candidate c0+j is <= thr.  Warp-uniform addresses -> shared-memory broadcasts.
+__device__ __forceinline__ uint32_t scan_chunk(const float *lx, const float *ly, int c0, int nq, u64 px2, u64 py2,
+                                               float thr) {
+    const ulonglong2 *x4 = (const ulonglong2 *)(lx + c0), *y4 = (const ulonglong2 *)(ly + c0);
+    uint32_t m = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        if (q < nq) {
+            const ulonglong2 xs = x4[q], ys = y4[q];
+            const u64 s01 = sqdist2(xs.x, ys.x, px2, py2), s23 = sqdist2(xs.y, ys.y, px2, py2);
+            m |= (lo2(s01) <= thr) ? (1u << (4 * q)) : 0u;
+            m |= (hi2(s01) <= thr) ? (2u << (4 * q)) : 0u;
+            m |= (lo2(s23) <= thr) ? (4u << (4 * q)) : 0u;
+            m |= (hi2(s23) <= thr) ? (8u << (4 * q)) : 0u;
+        }
+    }
+    return m;
+}
+
+// Exact (rare) path of one kNN task: the candidates inside `thr` ordered by (sqrt_rn distance, index) exactly as
+// argsort()[:6] + range mask would (collective_assault_env.py:308-309,320-322,331-333); taken when two keys of the
+// fast path are too close to call.  Returns the visible ids packed one byte each, nearest first.
+__device__ __noinline__ unsigned long long knn_exact(const float *lx, const float *ly, int cnt, float pgx, float pgy,
+                                                      float thr, float q0, int *n_out) {
+    float bd[kVisN];
+    int bi[kVisN];
+#pragma unroll
+    for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
+    const u64 px2 = pack2(pgx, pgx), py2 = pack2(pgy, pgy);
+    const int nquad = (cnt + 3) >> 2;
+    for (int c0 = 0; c0 < cnt; c0 += 32) {
+        uint32_t m = scan_chunk(lx, ly, c0, min(8, nquad - (c0 >> 2)), px2, py2, thr);
+        while (m) {
+            const int j = c0 + __ffs(m) - 1;
+            m &= m - 1;
+            const float sq = f32_sqdist(pgx, pgy, lx[j], ly[j]);
+            if (sq <= q0) top6_insert(bd, bi, __fsqrt_rn(sq), j);
+        }
+    }
+    unsigned long long vis = 0;
+    int n = 0;
+#pragma unroll
+    for (int k = 0; k < kVisN; ++k)
+        if (bi[k] >= 0) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
+    *n_out = n;
+    return vis;
+}
+
+// One kNN task: the (up to) 6 nearest in-range candidates of a list, nearest first, ties -> lower index.
+//   argsort()[:6] then the range mask == the 6 nearest IN-RANGE candidates (anything farther than an out-of-range
+//   member of the top-6 is out of range too).  q0 = largest f32 s with sqrt_rn(s) <= range, so "s <= q0" is the
+//   reference's "d <= range" exactly.
+// (1) Scan radius: the 7 neighbours remembered from the last pass (blob field knn_ids) are re-measured; if all are
+//     still alive, the 6 nearest now lie within the farthest of them, so only that disc (or the obs range, if
+//     smaller) has to be searched.  A dead / missing neighbour measures +inf -> the full range is searched.  The hint
+//     only shrinks the search: any 7 live candidates bound the 6th nearest, whatever they are.
+// (2) Packed conservative scan of the list against that radius -> bit mask (typically 7-9 bits).
+// (3) The masked candidates get the exact squared distance and go through a 7-slot min/max insertion network on
+//     32-bit keys (s bits with the low idx_bits replaced by the index).  sqrt_rn is monotone, so key order ==
+//     (distance, index) order unless two of the 7 smallest keys are within one key step -- then knn_exact() decides.
+__device__ __forceinline__ unsigned long long knn_task(const float *lx, const float *ly, int cnt, float pgx, float pgy,
+                                                        u64 prev, float q0, int idx_bits, int *n_out, u64 *ids_out,
+                                                        float *near_out) {
+    const uint32_t im = (1u << idx_bits) - 1u;
+    const float q0c = __fmul_ru(q0, 1.000001f);  // conservative range for the approximate scan
+    float tub = 0.f;
+#pragma unroll
+    for (int k = 0; k < kHintN; ++k) {
+        const int id = (int)((prev >> (8 * k)) & 0xffu);
+        tub = fmaxf(tub, f32_sqdist(pgx, pgy, lx[id], ly[id]));
+    }
+    const float thr = fminf(__fmul_ru(tub, 1.000001f), q0c);
+    const u64 px2 = pack2(pgx, pgx), py2 = pack2(pgy, pgy);
+    uint32_t b[kHintN];
+#pragma unroll
+    for (int k = 0; k < kHintN; ++k) b[k] = 0x80000000u + ((uint32_t)k << 8);  // empty slots: distinct, ascending
+    const int nquad = (cnt + 3) >> 2;
+    for (int c0 = 0; c0 < cnt; c0 += 32) {
+        uint32_t m = scan_chunk(lx, ly, c0, min(8, nquad - (c0 >> 2)), px2, py2, thr);
+        while (m) {
+            const int j = c0 + __ffs(m) - 1;
+            m &= m - 1;
+            const float sq = f32_sqdist(pgx, pgy, lx[j], ly[j]);
+            uint32_t key = sq <= q0 ? ((__float_as_uint(sq) & ~im) | (uint32_t)j) : 0xFFFFFFFFu;
+#pragma unroll
+            for (int k = 0; k < kHintN; ++k) {
+                const uint32_t lo = min(b[k], key);
+                key = max(b[k], key);
+                b[k] = lo;
+            }
+        }
+    }
+    bool close_call = false;
+#pragma unroll
+    for (int k = 0; k < kVisN; ++k)
+        close_call |= ((int32_t)b[k + 1] >= 0) && ((b[k + 1] >> idx_bits) - (b[k] >> idx_bits) <= 1u);
+    unsigned long long vis = 0;
+    int n = 0;
+    if (close_call) {
+        vis = knn_exact(lx, ly, cnt, pgx, pgy, thr, q0, &n);
+    } else {
+#pragma unroll
+        for (int k = 0; k < kVisN; ++k)
+            if ((int32_t)b[k] >= 0) { vis |= (unsigned long long)(b[k] & im) << (8 * n); ++n; }
+    }
+    *n_out = n;
+    u64 ids = 0;
+#pragma unroll
+    for (int k = 0; k < kHintN; ++k)
+        ids |= (u64)((int32_t)b[k] >= 0 ? (b[k] & im) : (uint32_t)cnt) << (8 * k);
+    *ids_out = ids;
+    *near_out = (int32_t)b[0] >= 0 ? __uint_as_float(b[0] & ~im) : q0;  // lower bound of the nearest squared distance
+    return vis;
+}
+
 // ------------------------------------------------------------------ observation pass
 // collective_assaultEnvV1.observation collective_assault_env.py:228-359 for every guard of the env.
 // dest == nullptr: the pass is only counted (keeps the keyed RNG stream aligned), nothing is computed.
-__device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, const uint32_t *rng_words,
-                         int prof_slot = 12) {
-    const BlobLayout &L = P.L;
+__device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const BlobLayout &L, int e, float *dest,
+                                         const uint32_t *rng_words, int prof_slot = 12) {
     const int tid = threadIdx.x, nt = blockDim.x;
     const uint32_t counter = s.sc->obs_counter + 1;
     if (dest == nullptr) {
@@ -141,20 +276,29 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
         return;
     }
     fill_xy(s, L);
-    // entity table :237-276  [alive,x,y,atk_rad,vx,vy,iden,terrain,bit0..bit7] as float32
-    for (int i = tid; i < L.N; i += nt) {
+    // entity table :237-276  [alive,x,y,atk_rad,vx,vy,iden,terrain,bit0..bit7] as float32; row N = zeros
+    for (int i = tid; i <= L.N; i += nt) {
         float4 *row = (float4 *)(s.table + i * kObsRow);
+        if (i == L.N) {
+            row[0] = row[1] = row[2] = row[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+            continue;
+        }
         const float x = (float)s.px[i], y = (float)s.py[i];
         const bool alive_i = s.flags[i] & F_ALIVE;
         row[0] = make_float4(alive_i ? 1.f : 0.f, x, y, (float)s.atk[i]);
         row[1] = make_float4((float)s.vx[i], (float)s.vy[i], (float)i, (float)s.ter[i]);
-        // get_binary_array :207-215 (float halving, int8 wrap, floored %); identical to plain bits for i < 256
-        int v = i;
+        // get_binary_array :207-215 (float halving, int8 wrap, floored %) yields the plain bits for 0 <= i < 256
         float b[8];
+        if (i < 256) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            b[k] = (float)((((v % 2) + 2) % 2) == 1);
-            v = (int)(signed char)(int)((double)v / 2.0);
+            for (int k = 0; k < 8; ++k) b[k] = (float)((i >> k) & 1);
+        } else {
+            int v = i;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                b[k] = (float)((((v % 2) + 2) % 2) == 1);
+                v = (int)(signed char)(int)((double)v / 2.0);
+            }
         }
         row[2] = make_float4(b[0], b[1], b[2], b[3]);
         row[3] = make_float4(b[4], b[5], b[6], b[7]);
@@ -173,124 +317,87 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
         if (task >= ntask) break;
         const int g = task >> 1, lst = task & 1;  // 0 = hostile (:318-328), 1 = friend (:330-342)
         int16_t *sid = s.sid + g * kObsRows + (lst == 0 ? kVisN : 0);  // friend rows 0..5, hostile rows 6..11 (:344)
+        const int cnt = lst == 0 ? L.A : L.G;
         if (!(s.flags[g] & F_ALIVE)) {  // :313-316 dead guard: zeros, no RNG draws
 #pragma unroll
             for (int r = 0; r < kVisN; ++r) sid[r] = -1;
+            s.knn_ids[task] = 0x0101010101010101ull * (u64)cnt;
+            if (lst == 0) s.hmin[g] = 0.f;
             continue;
         }
-        const float2 pg = s.xyg[g];
-        {
-            const int base = lst == 0 ? L.G : 0;
-            // argsort()[:6] then the range mask (:308-309, :320-322, :331-333) == the (up to) 6 nearest IN-RANGE
-            // candidates: anything farther than an out-of-range member of the top-6 is out of range too.
-            // Two phases per chunk of 32 candidates so that the warp never diverges on a per-candidate basis:
-            //  1. branch-free scan: squared distance (same roundings as distance_matrix :361-368) tested against
-            //     three nested radii -> three bit masks.  q[l] = largest f32 whose sqrt_rn is <= range, range/2,
-            //     range/4, so "in mask l" == "distance <= radius l" exactly; dead / padding = +inf never pass.
-            //  2. the smallest radius holding >= 6 candidates contains this chunk's 6 nearest; only those get the
-            //     sqrt_rn and the stable sorted insert (ties -> lower index, candidates visited in index order).
-            const float q0 = P.smax[lst][0], q1 = P.smax[lst][1], q2 = P.smax[lst][2];
-            const float2 *list = lst == 0 ? s.xya : s.xyg;
-            const int cntp = align_up(lst == 0 ? L.A : L.G, 32);
-            float bd[kVisN];
-            int bi[kVisN];
+        const int base = lst == 0 ? L.G : 0;
+        int n = 0;
+        u64 ids;
+        float nearest;
+        unsigned long long vis = knn_task(lst == 0 ? s.xa : s.xg, lst == 0 ? s.ya : s.yg, cnt, s.xg[g], s.yg[g],
+                                          s.knn_ids[task], P.smax[lst], P.idx_bits, &n, &ids, &nearest);
+        s.knn_ids[task] = ids;
+        if (lst == 0) s.hmin[g] = nearest;
+        int row = 0;
+        if (lst == 1) {  // :334-335 self = first visible friend, excluded from shuffle / jamming
+            sid[row++] = (int16_t)(vis & 0xff);
+            vis >>= 8; --n;
+        }
+        // item_random_mv :217-226 with the keyed words (shuffle i = n-1..1, then jam draws)
+        if (n > 0) {
+            uint32_t w[DCA_RNG_WORDS];
+            if (rng_words) {
+                const uint4 *src = (const uint4 *)(rng_words + (((size_t)e * L.G + g) * 2 + lst) * DCA_RNG_WORDS);
 #pragma unroll
-            for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
-            for (int c0 = 0; c0 < cntp; c0 += 32) {
-                const float4 *c4 = (const float4 *)(list + c0);
-                uint32_t m0 = 0, m1 = 0, m2 = 0;
-#pragma unroll
-                for (int jj = 0; jj < 16; ++jj) {
-                    const float4 v = c4[jj];
-                    const float dx0 = __fsub_rn(v.x, pg.x), dy0 = __fsub_rn(v.y, pg.y);
-                    const float dx1 = __fsub_rn(v.z, pg.x), dy1 = __fsub_rn(v.w, pg.y);
-                    const float s0 = __fadd_rn(__fmul_rn(dx0, dx0), __fmul_rn(dy0, dy0));
-                    const float s1 = __fadd_rn(__fmul_rn(dx1, dx1), __fmul_rn(dy1, dy1));
-                    m0 |= (s0 <= q0) ? (1u << (2 * jj)) : 0u;
-                    m1 |= (s0 <= q1) ? (1u << (2 * jj)) : 0u;
-                    m2 |= (s0 <= q2) ? (1u << (2 * jj)) : 0u;
-                    m0 |= (s1 <= q0) ? (2u << (2 * jj)) : 0u;
-                    m1 |= (s1 <= q1) ? (2u << (2 * jj)) : 0u;
-                    m2 |= (s1 <= q2) ? (2u << (2 * jj)) : 0u;
+                for (int b = 0; b < 3; ++b) {
+                    const uint4 q = src[b];
+                    w[4 * b] = q.x; w[4 * b + 1] = q.y; w[4 * b + 2] = q.z; w[4 * b + 3] = q.w;
                 }
-                uint32_t m = __popc(m2) >= kVisN ? m2 : (__popc(m1) >= kVisN ? m1 : m0);
-                while (m) {
-                    const int j = __ffs(m) - 1;
-                    m &= m - 1;
-                    const float2 cj = list[c0 + j];
-                    const float dx = __fsub_rn(cj.x, pg.x), dy = __fsub_rn(cj.y, pg.y);
-                    const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-                    top6_insert(bd, bi, d, c0 + j);
-                }
-            }
-            // visible list in sorted order, packed one byte per entry
-            unsigned long long vis = 0;
-            int n = 0;
+            } else {
+                const int nblk = n <= 2 ? 1 : (n <= 4 ? 2 : 3);
 #pragma unroll
-            for (int k = 0; k < kVisN; ++k) {
-                if (bi[k] >= 0) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
-            }
-            int row = 0;
-            if (lst == 1) {  // :334-335 self = first visible friend, excluded from shuffle / jamming
-                sid[row++] = (int16_t)(vis & 0xff);
-                vis >>= 8; --n;
-            }
-            // item_random_mv :217-226 with the keyed words (shuffle i = n-1..1, then jam draws)
-            if (n > 0) {
-                uint32_t w[DCA_RNG_WORDS];
-                if (rng_words) {
-                    const uint4 *src = (const uint4 *)(rng_words + (((size_t)e * L.G + g) * 2 + lst) * DCA_RNG_WORDS);
-#pragma unroll
-                    for (int b = 0; b < 3; ++b) {
-                        const uint4 q = src[b];
+                for (int b = 0; b < 3; ++b) {
+                    if (b < nblk) {
+                        const uint4 q = philox4x32_10(gid, counter, (uint32_t)(g * 2 + lst), SITE_OBS | (b << 8), k0, k1);
                         w[4 * b] = q.x; w[4 * b + 1] = q.y; w[4 * b + 2] = q.z; w[4 * b + 3] = q.w;
-                    }
-                } else {
-                    const int nblk = n <= 2 ? 1 : (n <= 4 ? 2 : 3);
-#pragma unroll
-                    for (int b = 0; b < 3; ++b) {
-                        if (b < nblk) {
-                            const uint4 q = philox4x32_10(gid, counter, (uint32_t)(g * 2 + lst), SITE_OBS | (b << 8), k0, k1);
-                            w[4 * b] = q.x; w[4 * b + 1] = q.y; w[4 * b + 2] = q.z; w[4 * b + 3] = q.w;
-                        } else {
-                            w[4 * b] = w[4 * b + 1] = w[4 * b + 2] = w[4 * b + 3] = 0;
-                        }
+                    } else {
+                        w[4 * b] = w[4 * b + 1] = w[4 * b + 2] = w[4 * b + 3] = 0;
                     }
                 }
-#pragma unroll
-                for (int i = kVisN - 1; i >= 1; --i) {
-                    if (i < n) {
-                        const int j = (int)__umulhi(w[2 * i], (uint32_t)(i + 1));  // SHUF_W[i] = 2i
-                        const unsigned long long x = ((vis >> (8 * i)) ^ (vis >> (8 * j))) & 0xffull;
-                        vis ^= (x << (8 * i)) | (x << (8 * j));
-                    }
-                }
-                int n_mv = 0;
-#pragma unroll
-                for (int k = 0; k < kVisN; ++k) {
-                    const int wi = k == 0 ? 0 : 2 * k - 1;  // JAM_W = {0,1,3,5,7,9}
-                    if (k < n) n_mv += ((double)w[wi] * 0x1p-32 < P.cfg.random_jam_prob) ? 1 : 0;
-                }
-                n -= n_mv;
             }
 #pragma unroll
-            for (int k = 0; k < kVisN; ++k) {
-                if (row < kVisN) {
-                    sid[row] = k < n ? (int16_t)(base + (int)((vis >> (8 * k)) & 0xff)) : (int16_t)-1;
-                    ++row;
+            for (int i = kVisN - 1; i >= 1; --i) {
+                if (i < n) {
+                    const int j = (int)__umulhi(w[2 * i], (uint32_t)(i + 1));  // SHUF_W[i] = 2i
+                    const unsigned long long x = ((vis >> (8 * i)) ^ (vis >> (8 * j))) & 0xffull;
+                    vis ^= (x << (8 * i)) | (x << (8 * j));
                 }
+            }
+            int n_mv = 0;
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k) {
+                const int wi = k == 0 ? 0 : 2 * k - 1;  // JAM_W = {0,1,3,5,7,9}
+                // rand() < random_jam_prob with rand() = w * 2^-32, as an integer compare
+                if (k < n) n_mv += ((unsigned long long)w[wi] < P.jam_thresh) ? 1 : 0;
+            }
+            n -= n_mv;
+        }
+#pragma unroll
+        for (int k = 0; k < kVisN; ++k) {
+            if (row < kVisN) {
+                sid[row] = k < n ? (int16_t)(base + (int)((vis >> (8 * k)) & 0xff)) : (int16_t)-1;
+                ++row;
             }
         }
     }
     __syncthreads();
     DCA_PROF(P, e, prof_slot + 1);
-    // gather: 48 x 128-bit per guard, consecutive threads write consecutive 16 B (coalesced)
-    float4 *out4 = (float4 *)(dest + (size_t)e * L.G * kObsLen);
-    const float4 *tab4 = (const float4 *)s.table;
-    const int total = L.G * kObsRows * 4;
-    for (int t = tid; t < total; t += nt) {
-        const int id = s.sid[t >> 2];
-        out4[t] = id >= 0 ? tab4[id * 4 + (t & 3)] : make_float4(0.f, 0.f, 0.f, 0.f);
+    // gather: 48 x 128-bit per guard; a quad of threads copies one 64-byte record, consecutive threads write
+    // consecutive 16 B (coalesced); empty slots read the zero row
+    {
+        float4 *out4 = (float4 *)(dest + (size_t)e * L.G * kObsLen);
+        const float4 *tab4 = (const float4 *)s.table;
+        const int part = tid & 3, nrow = L.G * kObsRows, rstep = nt >> 2;
+#pragma unroll 4
+        for (int r = tid >> 2; r < nrow; r += rstep) {
+            const int id = min((int)(uint16_t)s.sid[r], L.N);
+            out4[r * 4 + part] = tab4[id * 4 + part];
+        }
     }
     if (P.out.slot_id) {
         int16_t *o = P.out.slot_id + (size_t)e * L.G * kObsRows;
@@ -303,8 +410,7 @@ __device__ void obs_pass(const Smem &s, const Params &P, int e, float *dest, con
 // ------------------------------------------------------------------ reset
 // collective_assaultEnvV1.reset_world collective_assault_env.py:55-136 with keyed draws, then the terrain pass
 // of collective_assaultGlobalEnv.reset parallel_run.py:258.  Caller runs obs_pass afterwards.
-__device__ void reset_world(const Smem &s, const Params &P, int e) {
-    const BlobLayout &L = P.L;
+__device__ __forceinline__ void reset_world(const Smem &s, const Params &P, const BlobLayout &L, int e) {
     const DcaConfig &c = P.cfg;
     const int tid = threadIdx.x, nt = blockDim.x;
     const uint32_t k0 = (uint32_t)c.seed, k1 = (uint32_t)(c.seed >> 32);
@@ -326,7 +432,11 @@ __device__ void reset_world(const Smem &s, const Params &P, int e) {
         s.sc->n_alive_attackers = L.A;  // :59-60 (not corrected for excluded attackers, as in the reference)
         s.sc->n_alive_guards = L.G;
         s.sc->init_theta = theta;
+        s.sc->cos_theta = ct;
+        s.sc->sin_theta = sn;
     }
+    // positions jump: no kNN hints (every remembered neighbour = the marker slot, which measures +inf)
+    for (int k = tid; k < 2 * L.G; k += nt) s.knn_ids[k] = 0x0101010101010101ull * (u64)((k & 1) ? L.G : L.A);
     for (int i = tid; i < L.N; i += nt) {
         const uint4 a = philox4x32_10(gid, ep, (uint32_t)(1 + i), SITE_RESET, k0, k1);
         const bool attacker = i >= L.G;
@@ -381,25 +491,69 @@ __device__ void reset_world(const Smem &s, const Params &P, int e) {
     __syncthreads();
 }
 
+// alive mask output [E,N] u8 (4 agents per 32-bit store when the row is 4-byte aligned)
+__device__ __forceinline__ void write_alive(const Smem &s, const Params &P, const BlobLayout &L, int e) {
+    if (!P.out.alive) return;
+    const int N = L.N;
+    uint8_t *dst = P.out.alive + (size_t)e * N;
+    if ((N & 3) == 0 && (((uintptr_t)dst) & 3) == 0) {
+        const uint32_t *f4 = (const uint32_t *)s.flags;  // flags sit at a 16-byte aligned blob offset
+        for (int k = threadIdx.x; k < N / 4; k += blockDim.x) ((uint32_t *)dst)[k] = f4[k] & 0x01010101u;
+    } else {
+        for (int i = threadIdx.x; i < N; i += blockDim.x) dst[i] = s.flags[i] & F_ALIVE;
+    }
+}
+
+// ------------------------------------------------------------------ laser: exact pair test
+// laser_hit_improve3 cython_func.pyx:22-46 for shooter i -> target j (both alive, opposite teams); records the hit.
+__device__ __forceinline__ void laser_pair(const Smem &s, const DcaConfig &c, int i, int j) {
+    const double radius = c.agent_shoot_base_radius * s.ter[i];
+    const double r2 = radius * radius;
+    const double dx = s.px[j] - s.px[i], dy = s.py[j] - s.py[i];
+    const double d2 = dx * dx + dy * dy;
+    if (d2 > r2) return;
+    const double dir = s.atk[i];
+    const double pos_r = dir + c.agent_shoot_win / 2, neg_r = dir - c.agent_shoot_win / 2;
+    const double tt = atan2(dy, dx);
+    const double d1 = fabs(reg_angle(pos_r - tt)), d2r = fabs(reg_angle(neg_r - tt));
+    if (d1 <= c.agent_shoot_win && d2r <= c.agent_shoot_win) {
+        atomicAdd(&s.shots[i], 1);
+        atomicAdd(&s.hitcnt[j], 1);
+    }
+}
+
+// Conservative float32 bound of shooter i's squared laser radius: a pair whose f32 squared distance exceeds r^2 by
+// 1% + 1e-3 cannot pass the exact fp64 test (f32 rounding of |coord| <= 64 perturbs d^2 by < 1e-4).  +inf = no bound.
+__device__ __forceinline__ float laser_r2f(const Smem &s, const DcaConfig &c, int i) {
+    const double radius = c.agent_shoot_base_radius * s.ter[i];
+    const double r2 = radius * radius;
+    const bool ok = fabs(s.px[i]) <= 64.0 && fabs(s.py[i]) <= 64.0 && r2 < 1.0e3;
+    return ok ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
+}
+
+__device__ __forceinline__ void push_shooter(const Smem &s, int i) {
+    s.shooters[atomicAdd(&s.misc[2], 1)] = (int16_t)i;
+}
+
 // ------------------------------------------------------------------ fused step kernel
 // collective_assaultGlobalEnv.step parallel_run.py:192-246 + EnvAutoReset.step UTIL/shm_env.py:33-74.
-__global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__restrict__ actions,
+template <int NT, int TG, int TA>
+__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, const int32_t *__restrict__ actions,
                                                const double *__restrict__ att_force, const uint8_t *__restrict__ skip,
                                                const uint32_t *__restrict__ rng_words, int autoreset) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
     if (skip != nullptr && skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay in place
-    const BlobLayout &L = P.L;
+    const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
     const DcaConfig &c = P.cfg;
     const Smem s = carve(smem_raw, L);
-    const int tid = threadIdx.x, nt = blockDim.x;
+    const int tid = threadIdx.x, nt = NT;
     DCA_PROF(P, e, 0);
-    load_blob(s, P, e);
+    load_blob(s, P, L, e);
     DCA_PROF(P, e, 1);
 
-    double sn, ct;
-    sincos(s.sc->init_theta, &sn, &ct);
-    if (tid < 2) s.misc[tid] = 0;
+    const double ct = s.sc->cos_theta, sn = s.sc->sin_theta;
+    if (tid < 4) s.misc[tid] = 0;
     fill_xy(s, L);
     // phase A: guard action decode (_set_action parallel_run.py:326-374), terrain (core.py:224-234),
     // attacker act init (cheat_script_ai.py:31-34) + injected planner force (:183-184), clear hit flags (core.py:239-242)
@@ -422,7 +576,7 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
             fx = F.x; fy = F.y;
         }
         s.fx[i] = fx; s.fy[i] = fy; s.ar[i] = ar;
-        s.hitcnt[i] = 0;
+        s.hitcnt[i] = 0; s.shots[i] = 0;
         if (alive) {
             s.ter[i] = terrain_at(c, s.px[i], s.py[i], ct, sn);
             s.flags[i] = f & (uint8_t)~(F_HIT | F_WAS_HIT);
@@ -430,100 +584,97 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     }
     __syncthreads();
     DCA_PROF(P, e, 2);
-    DCA_PROF(P, e, 3);
-    // phase B+C: scripted aim (cheat_script_ai.py:196-218) and apply_laser_effect (core.py:244-263 with
-    // laser_hit_improve3 cython_func.pyx:22-46).  Warp roles: the first half of the CTA's warps own the attackers
-    // (aim, then fire), the second half the guards (fire), so no warp mixes the two code paths.
+    // phase B: scripted aim (cheat_script_ai.py:196-218), and the list of agents that may hit anything this step.
+    // np.argmin over the float32 distance row (first minimum; dead guards +inf): one packed pass keeps the two
+    // smallest keys (approximate squared distance, low idx_bits = guard index).  sqrt_rn is monotone, so the smallest
+    // key names the argmin unless the runner-up is within one key step -- then (rare) an exact pass compares true
+    // sqrt_rn distances, lowest index first.
     {
-        const int nwarp = nt >> 5, wa = nwarp >> 1;
-        const bool att_role = (tid >> 5) < wa;
-        const int role_threads = (att_role ? wa : nwarp - wa) * 32;
-        const int role_tid = att_role ? tid : tid - wa * 32;
-        const int role_cnt = att_role ? L.A : L.G;
-        const float2 *opp = att_role ? s.xyg : s.xya;       // float32 positions of the opposing team (+inf = dead)
-        const int opp_cnt = att_role ? L.G : L.A, opp_base = att_role ? 0 : L.G;
-        const int opp4 = (opp_cnt + 1) >> 1;                // float4 = 2 candidates; padding slots are +inf
-        const float4 *opp_v4 = (const float4 *)opp;
-        for (int t = role_tid; t < role_cnt; t += role_threads) {
-            const int i = att_role ? L.G + t : t;
+        const uint32_t im = (1u << P.idx_bits) - 1u;
+        const int Gq = (L.G + 3) >> 2;
+        for (int t = tid; t < L.A; t += nt) {
+            const int i = L.G + t;
             const bool alive = s.flags[i] & F_ALIVE;
-            const float2 po = att_role ? s.xya[t] : s.xyg[t];
-            if (att_role) {
-                int best = -1;
-                if (alive) {
-                    // np.argmin over the float32 distance row (first minimum; dead guards +inf).  One branch-free pass
-                    // tracks the two smallest SQUARED distances and the first index of the smallest; sqrt_rn is
-                    // monotone, so only when the runner-up is within 2^-20 of the minimum can the rounded distances
-                    // tie -- then (rare) a second pass compares true sqrt_rn values, lowest index first.
-                    float s1 = CUDART_INF_F, s2 = CUDART_INF_F;
-                    best = 0;
+            int best = -1;
+            if (alive) {
+                const float pox = s.xa[t], poy = s.ya[t];
+                const u64 px2 = pack2(pox, pox), py2 = pack2(poy, poy);
+                const ulonglong2 *x4 = (const ulonglong2 *)s.xg, *y4 = (const ulonglong2 *)s.yg;
+                uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
 #pragma unroll 4
-                    for (int jj = 0; jj < opp4; ++jj) {
-                        const float4 v = opp_v4[jj];
-                        const float dx0 = __fsub_rn(v.x, po.x), dy0 = __fsub_rn(v.y, po.y);
-                        const float dx1 = __fsub_rn(v.z, po.x), dy1 = __fsub_rn(v.w, po.y);
-                        const float q0 = __fadd_rn(__fmul_rn(dx0, dx0), __fmul_rn(dy0, dy0));
-                        const float q1 = __fadd_rn(__fmul_rn(dx1, dx1), __fmul_rn(dy1, dy1));
-                        bool lt = q0 < s1;
-                        s2 = fminf(s2, lt ? s1 : q0); best = lt ? 2 * jj : best; s1 = fminf(s1, q0);
-                        lt = q1 < s1;
-                        s2 = fminf(s2, lt ? s1 : q1); best = lt ? 2 * jj + 1 : best; s1 = fminf(s1, q1);
-                    }
-                    if (s2 <= __fmul_ru(s1, 1.000001f) && s1 < CUDART_INF_F) {
-                        float bd = CUDART_INF_F;
-                        for (int g = 0; g < opp_cnt; ++g) {
-                            const float d = f32_dist(po.x, po.y, opp[g].x, opp[g].y);
-                            if (d < bd) { bd = d; best = g; }
-                        }
-                    }
-                    double th = atan2(s.py[best] - s.py[i], s.px[best] - s.px[i]);
-                    if (th < 0) th += 2 * kPi;
-                    s.atk[i] = th;
+                for (int q = 0; q < Gq; ++q) {
+                    const ulonglong2 xs = x4[q], ys = y4[q];
+                    const u64 s01 = sqdist2(xs.x, ys.x, px2, py2), s23 = sqdist2(xs.y, ys.y, px2, py2);
+                    const uint32_t ka = (__float_as_uint(lo2(s01)) & ~im) | (uint32_t)(4 * q);
+                    const uint32_t kb = (__float_as_uint(hi2(s01)) & ~im) | (uint32_t)(4 * q + 1);
+                    const uint32_t kc = (__float_as_uint(lo2(s23)) & ~im) | (uint32_t)(4 * q + 2);
+                    const uint32_t kd = (__float_as_uint(hi2(s23)) & ~im) | (uint32_t)(4 * q + 3);
+                    m2 = min(m2, max(m1, ka)); m1 = min(m1, ka);
+                    m2 = min(m2, max(m1, kb)); m1 = min(m1, kb);
+                    m2 = min(m2, max(m1, kc)); m1 = min(m1, kc);
+                    m2 = min(m2, max(m1, kd)); m1 = min(m1, kd);
                 }
-                if (P.out.nearest) P.out.nearest[(size_t)e * L.A + t] = best;
-                if (c.disable_red_function) continue;  // can_fire = False (cheat_script_ai.py:216-217)
+                best = (int)(m1 & im);
+                if ((m2 >> P.idx_bits) - (m1 >> P.idx_bits) <= 1u && m1 < 0x7F800000u) {
+                    float bd = CUDART_INF_F;
+                    best = 0;
+                    for (int g = 0; g < L.G; ++g) {
+                        const float d = f32_dist(pox, poy, s.xg[g], s.yg[g]);
+                        if (d < bd) { bd = d; best = g; }
+                    }
+                }
+                if (m1 >= 0x7F800000u) best = 0;  // no guard alive: argmin of an all-inf row is 0
+                double th = atan2(s.py[best] - s.py[i], s.px[best] - s.px[i]);
+                if (th < 0) th += 2 * kPi;
+                s.atk[i] = th;
+                // can_fire (cheat_script_ai.py:214-217): candidate shooter if the nearest guard may be inside the radius
+                if (!c.disable_red_function && __uint_as_float(m1 & ~im) <= laser_r2f(s, c, i)) push_shooter(s, i);
             }
-            if (!alive) continue;
-            const double radius = c.agent_shoot_base_radius * s.ter[i];
-            const double r2 = radius * radius;
-            const double dir = s.atk[i];
-            const double pos_r = dir + c.agent_shoot_win / 2, neg_r = dir - c.agent_shoot_win / 2;
-            const double ox = s.px[i], oy = s.py[i];
-            // conservative float32 pre-filter (dead = +inf): a pair whose f32 squared distance exceeds r^2 by
-            // 1% + 1e-3 cannot pass the exact fp64 test (f32 rounding of |coord| <= 64 perturbs d^2 by < 1e-4).
-            // Candidates are collected branch-free into a bit mask per 32 opponents; the exact fp64 test
-            // (atan2, two reg_angle) then runs once per set bit, all lanes of the warp in parallel.
-            const bool prefilter = fabs(ox) <= 64.0 && fabs(oy) <= 64.0 && r2 < 1.0e3;
-            const float r2f = prefilter ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
-            int hits = 0;
+            if (P.out.nearest) P.out.nearest[(size_t)e * L.A + t] = best;
+        }
+        // guards: hmin = lower bound of the squared distance to the nearest alive attacker, left by the last
+        // observation pass (same positions, same alive set)
+        for (int g = tid; g < L.G; g += nt)
+            if ((s.flags[g] & F_ALIVE) && s.hmin[g] <= laser_r2f(s, c, g)) push_shooter(s, g);
+    }
+    __syncthreads();
+    DCA_PROF(P, e, 3);
+    // phase C: apply_laser_effect core.py:244-263.  C1: every listed shooter scans the opposing team with the packed
+    // float32 pre-filter and queues the few (shooter, target) candidates; C2: one exact fp64 test per queued pair.
+    {
+        const int nsh = s.misc[2];
+        for (int q = tid; q < nsh; q += nt) {
+            const int i = s.shooters[q];
+            const bool att = i >= L.G;
+            const float *ox = att ? s.xg : s.xa, *oy = att ? s.yg : s.ya;
+            const int opp_cnt = att ? L.G : L.A, opp_base = att ? 0 : L.G;
+            const float pox = att ? s.xa[i - L.G] : s.xg[i], poy = att ? s.ya[i - L.G] : s.yg[i];
+            const u64 px2 = pack2(pox, pox), py2 = pack2(poy, poy);
+            const float r2f = laser_r2f(s, c, i);
+            const int nquad = (opp_cnt + 3) >> 2;
             for (int c0 = 0; c0 < opp_cnt; c0 += 32) {
-                uint32_t m = 0;
-                const int n4 = min(16, opp4 - (c0 >> 1));
-#pragma unroll 4
-                for (int jj = 0; jj < n4; ++jj) {
-                    const float4 v = opp_v4[(c0 >> 1) + jj];
-                    const float dx0 = v.x - po.x, dy0 = v.y - po.y, dx1 = v.z - po.x, dy1 = v.w - po.y;
-                    const float f0 = dx0 * dx0 + dy0 * dy0, f1 = dx1 * dx1 + dy1 * dy1;
-                    m |= ((f0 <= r2f) ? 1u : 0u) << (2 * jj);
-                    m |= ((f1 <= r2f) ? 2u : 0u) << (2 * jj);
+                uint32_t m = scan_chunk(ox, oy, c0, min(8, nquad - (c0 >> 2)), px2, py2, r2f);
+                if (r2f == CUDART_INF_F) {  // no bound: every alive opponent is a candidate (inf <= inf passes above)
+                    m = 0;
+                    for (int j = 0; j < 32 && c0 + j < opp_cnt; ++j)
+                        if (s.flags[opp_base + c0 + j] & F_ALIVE) m |= 1u << j;
                 }
                 while (m) {
                     const int j = opp_base + c0 + __ffs(m) - 1;
                     m &= m - 1;
-                    if (j >= opp_base + opp_cnt) break;
-                    if (!prefilter && !(s.flags[j] & F_ALIVE)) continue;  // r2f = +inf lets dead targets through
-                    const double dx = s.px[j] - ox, dy = s.py[j] - oy;
-                    const double d2 = dx * dx + dy * dy;
-                    if (d2 > r2) continue;
-                    const double tt = atan2(dy, dx);
-                    const double d1 = fabs(reg_angle(pos_r - tt)), d2r = fabs(reg_angle(neg_r - tt));
-                    if (d1 <= c.agent_shoot_win && d2r <= c.agent_shoot_win) {
-                        ++hits;
-                        atomicAdd(&s.hitcnt[j], 1);
-                    }
+                    const int slot = atomicAdd(&s.misc[3], 1);
+                    if (slot < kPairCap) s.pairs[slot] = ((uint32_t)i << 16) | (uint32_t)j;
+                    else laser_pair(s, c, i, j);
                 }
             }
-            if (hits) { s.flags[i] |= F_HIT; s.nhit[i] += hits; }
+        }
+    }
+    __syncthreads();
+    {
+        const int np = min(s.misc[3], kPairCap);
+        for (int q = tid; q < np; q += nt) {
+            const uint32_t pr = s.pairs[q];
+            laser_pair(s, c, (int)(pr >> 16), (int)(pr & 0xffffu));
         }
     }
     __syncthreads();
@@ -535,6 +686,8 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
             s.flags[i] = f & (uint8_t)~F_JUST_DIED;
             continue;
         }
+        const int sh = s.shots[i];
+        if (sh > 0) { f |= F_HIT; s.nhit[i] += sh; s.flags[i] = f; }
         const int hc = s.hitcnt[i];
         if (hc > 0) {
             s.nwas[i] += hc;
@@ -593,45 +746,46 @@ __global__ void __launch_bounds__(256) k_step(const Params P, const int32_t *__r
     DCA_PROF(P, e, 6);
     // phase F: observation; on done the terminal obs goes to tobs, the env is reset and observed again
     const bool do_reset = done && autoreset;
-    obs_pass(s, P, e, do_reset ? P.out.tobs : P.out.obs, rng_words, 7);
+    obs_pass(s, P, L, e, do_reset ? P.out.tobs : P.out.obs, rng_words, 7);
     if (do_reset) {
-        reset_world(s, P, e);
-        obs_pass(s, P, e, P.out.obs, nullptr);
+        reset_world(s, P, L, e);
+        obs_pass(s, P, L, e, P.out.obs, nullptr);
     }
-    if (P.out.alive) {
-        for (int i = tid; i < L.N; i += nt) P.out.alive[(size_t)e * L.N + i] = s.flags[i] & F_ALIVE;
-    }
+    write_alive(s, P, L, e);
     DCA_PROF(P, e, 10);
-    store_blob(s, P, e);
+    store_blob(s, P, L, e);
     DCA_PROF(P, e, 11);
 }
 
 // reset kernel: SuperpoolEnv.reset -> collective_assaultGlobalEnv.reset parallel_run.py:248-270
-__global__ void __launch_bounds__(256) k_reset(const Params P, const uint8_t *__restrict__ env_mask) {
+template <int NT, int TG, int TA>
+__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_reset(const Params P, const uint8_t *__restrict__ env_mask) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
     if (env_mask != nullptr && !env_mask[e]) return;
-    const Smem s = carve(smem_raw, P.L);
-    load_blob(s, P, e);
-    reset_world(s, P, e);
-    obs_pass(s, P, e, P.out.obs, nullptr);
+    const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
+    const Smem s = carve(smem_raw, L);
+    load_blob(s, P, L, e);
+    reset_world(s, P, L, e);
+    obs_pass(s, P, L, e, P.out.obs, nullptr);
     if (threadIdx.x == 0) { P.out.done[e] = 0; P.out.win[e] = 0; }
-    for (int g = threadIdx.x; g < P.L.G; g += blockDim.x) P.out.reward[(size_t)e * P.L.G + g] = 0.f;
-    if (P.out.alive)
-        for (int i = threadIdx.x; i < P.L.N; i += blockDim.x) P.out.alive[(size_t)e * P.L.N + i] = s.flags[i] & F_ALIVE;
-    store_blob(s, P, e);
+    for (int g = threadIdx.x; g < L.G; g += blockDim.x) P.out.reward[(size_t)e * L.G + g] = 0.f;
+    write_alive(s, P, L, e);
+    store_blob(s, P, L, e);
 }
 
 // observation-only kernel (the kNN gather kernel on the resident state)
-__global__ void __launch_bounds__(256) k_observe(const Params P, const uint32_t *__restrict__ rng_words) {
+template <int NT, int TG, int TA>
+__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_observe(const Params P, const uint32_t *__restrict__ rng_words) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
-    const Smem s = carve(smem_raw, P.L);
-    load_blob(s, P, e);
-    obs_pass(s, P, e, P.out.obs, rng_words);
+    const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
+    const Smem s = carve(smem_raw, L);
+    load_blob(s, P, L, e);
+    obs_pass(s, P, L, e, P.out.obs, rng_words);
     // only the observation counter changed: write the scalars back
     if (threadIdx.x == 0)
-        ((EnvScalars *)(P.blobs + (size_t)e * P.L.bytes + P.L.scalars))->obs_counter = s.sc->obs_counter;
+        ((EnvScalars *)(P.blobs + (size_t)e * L.bytes + L.scalars))->obs_counter = s.sc->obs_counter;
 }
 
 // ------------------------------------------------------------------ state import / export (plain SoA <-> blobs)
@@ -657,6 +811,15 @@ __global__ void k_state_io(const Params P, const DcaState st, int import) {
                 sc->init_theta = st.init_theta[e]; sc->time_step = st.time_step[e];
                 sc->n_alive_guards = st.n_alive_guards[e]; sc->n_alive_attackers = st.n_alive_attackers[e];
                 sc->obs_counter = st.obs_counter[e]; sc->episode = st.episode[e]; sc->pad = 0;
+                double sn_, ct_;
+                sincos(st.init_theta[e], &sn_, &ct_);
+                sc->cos_theta = ct_; sc->sin_theta = sn_;
+            }
+            // derived speed-up hints: none for a foreign state (full-range kNN scan, every guard a laser candidate)
+            if (i < L.G) {
+                u64 *ids = (u64 *)(b + L.knn_ids);
+                ids[2 * i] = 0x0101010101010101ull * (u64)L.A; ids[2 * i + 1] = 0x0101010101010101ull * (u64)L.G;
+                ((float *)(b + L.hmin))[i] = 0.f;
             }
         } else {
             st.pos[2 * t] = px[i]; st.pos[2 * t + 1] = py[i];
@@ -682,6 +845,10 @@ __global__ void k_init_blobs(const Params P) {
     EnvScalars *sc = (EnvScalars *)(P.blobs + (size_t)e * P.L.bytes + P.L.scalars);
     sc->obs_counter = 0xFFFFFFFFu;
     sc->episode = 0xFFFFFFFFu;
+    u64 *ids = (u64 *)(P.blobs + (size_t)e * P.L.bytes + P.L.knn_ids);
+    for (int g = 0; g < P.L.G; ++g) {  // no kNN hints yet (marker = list length)
+        ids[2 * g] = 0x0101010101010101ull * (u64)P.L.A; ids[2 * g + 1] = 0x0101010101010101ull * (u64)P.L.G;
+    }
 }
 
 // ------------------------------------------------------------------ benchmark planner stand-in (one warp per env)
