@@ -9,6 +9,9 @@
 
 namespace dca {
 
+#ifndef DCA_CTAS_128
+#define DCA_CTAS_128 8  // resident CTAs per SM the 128-thread kernels are register-budgeted for
+#endif
 constexpr int kPairCap = 256;  // queued (shooter, target) laser candidates per env; overflow is tested in place
 constexpr int kHintN = kVisN + 1;  // neighbours remembered per (guard, list) for the next pass
 
@@ -21,28 +24,27 @@ struct Smem {
     u64 *knn_ids;
     float *hmin;
     EnvScalars *sc;
-    double *fx, *fy, *ar;  // force (act[0:2]) and rotation (act[2]) of this step
     float *xg, *yg, *xa, *ya;  // float32-rounded positions of guards / attackers (distance matrix inputs), SoA,
                                // list_pad() entries each; dead agents and padding = +inf
     int32_t *hitcnt;       // times agent i was hit this step (also: exclusion keys during reset)
     int32_t *shots;        // hits agent i scored this step
-    float *table;          // [N+1,16] float32 entity records; row N is all zero (invisible / jammed / empty slots)
-    int16_t *sid;          // [G,12] entity id per obs row, -1 = zero row
-    int16_t *shooters;     // [N] compacted list of agents that may hit something this step
-    uint32_t *pairs;       // [kPairCap] (shooter << 16 | target) candidates for the exact fp64 laser test
+    float4 *table;         // [4][N+1] float32 entity records, one plane per 16-byte quarter of the 64-byte record (so that
+                           // consecutive agents are consecutive in a plane: conflict-free stores); record N is all zero
+                           // (invisible / jammed / empty slots)
+    int16_t *sid;          // [G,12] entity id per obs row, -1 = zero row          } the laser work lists are dead
+    int16_t *shooters;     // [N] agents that may hit something this step           } before the observation pass
+    uint32_t *pairs;       // [kPairCap] (shooter << 16 | target) laser candidates  } writes sid: same bytes
     int32_t *misc;         // [0] guard deaths, [1] attacker deaths, [2] #shooters, [3] #pairs
     uint64_t *bar;
 };
 
 __host__ __device__ constexpr int smem_bytes(const BlobLayout &L) {
     int o = L.bytes;
-    o += 3 * align_up(L.N * 8, 16);                 // fx fy ar
     o += (list_pad(L.G) + list_pad(L.A)) * 8;       // xg yg xa ya
     o += 2 * align_up(L.N * 4, 16);                 // hitcnt shots
     o += (L.N + 1) * kObsRow * 4;                   // table
-    o += align_up(L.G * kObsRows * 2, 16);          // sid
-    o += align_up(L.N * 2, 16);                     // shooters
-    o += kPairCap * 4;                              // pairs
+    const int a = align_up(L.G * kObsRows * 2, 16), b = align_up(L.N * 2, 16) + kPairCap * 4;
+    o += a > b ? a : b;                             // sid | shooters + pairs
     o += 32;                                        // misc
     o += 16;                                        // mbarrier
     return o;
@@ -59,16 +61,19 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
     s.knn_ids = (u64 *)(base + L.knn_ids); s.hmin = (float *)(base + L.hmin);
     s.sc = (EnvScalars *)(base + L.scalars);
     unsigned char *p = base + L.bytes;
-    const int f64 = align_up(L.N * 8, 16), f32 = align_up(L.N * 4, 16);
+    const int f32 = align_up(L.N * 4, 16);
     const int Gp = list_pad(L.G), Ap = list_pad(L.A);
-    s.fx = (double *)p; p += f64; s.fy = (double *)p; p += f64; s.ar = (double *)p; p += f64;
     s.xg = (float *)p; p += Gp * 4; s.yg = (float *)p; p += Gp * 4;
     s.xa = (float *)p; p += Ap * 4; s.ya = (float *)p; p += Ap * 4;
     s.hitcnt = (int32_t *)p; p += f32; s.shots = (int32_t *)p; p += f32;
-    s.table = (float *)p; p += (L.N + 1) * kObsRow * 4;
-    s.sid = (int16_t *)p; p += align_up(L.G * kObsRows * 2, 16);
-    s.shooters = (int16_t *)p; p += align_up(L.N * 2, 16);
-    s.pairs = (uint32_t *)p; p += kPairCap * 4;
+    s.table = (float4 *)p; p += (L.N + 1) * kObsRow * 4;
+    {
+        const int a = align_up(L.G * kObsRows * 2, 16), b = align_up(L.N * 2, 16) + kPairCap * 4;
+        s.sid = (int16_t *)p;
+        s.shooters = (int16_t *)p;
+        s.pairs = (uint32_t *)(p + align_up(L.N * 2, 16));
+        p += a > b ? a : b;
+    }
     s.misc = (int32_t *)p; p += 32;
     s.bar = (uint64_t *)p;
     return s;
@@ -106,29 +111,62 @@ __device__ __forceinline__ void store_blob(const Smem &s, const Params &P, const
 
 // ------------------------------------------------------------------ terrain
 // World.set_terrain_adv core.py:224-234 + get_terrain core.py:306-314; alive agents only, dead keep old value.
-__device__ __forceinline__ double terrain_at(const DcaConfig &c, double X, double Y, double ct, double st) {
-    if (!c.introduce_terrain) return 1.0;
+__device__ __forceinline__ double terrain_fn(double tA, double tB, double X, double Y, double ct, double st) {
     const double X_ = X * ct + Y * st;
     const double Y_ = -X * st + Y * ct;
     const double a = 0.1 * X_, b = 0.1 * Y_;
-    double Z = -1 + c.terrain_B * (a * a + b * b);
-    Z = Z - c.terrain_A * cos(2 * kPi * (0.3 * X_));
-    Z = Z - c.terrain_A * cos(2 * kPi * (0.5 * Y_));
+    double Z = -1 + tB * (a * a + b * b);
+    // cos(2 pi t) as cospi(2 t): same value to ~1e-16 (the reference rounds 2 pi t first), cheaper range reduction
+    Z = Z - tA * cospi(2 * (0.3 * X_));
+    Z = Z - tA * cospi(2 * (0.5 * Y_));
     return -Z;
 }
+__device__ __forceinline__ double terrain_at(const DcaConfig &c, double X, double Y, double ct, double st) {
+    if (!c.introduce_terrain) return 1.0;
+    return terrain_fn(c.terrain_A, c.terrain_B, X, Y, ct, st);
+}
 
-// Refresh the padded float32 position arrays from the fp64 state (dead agents and padding slots = +inf).
-__device__ __forceinline__ void fill_xy(const Smem &s, const BlobLayout &L) {
-    const int Gp = list_pad(L.G), Ap = list_pad(L.A);
-    for (int k = threadIdx.x; k < Gp + Ap; k += blockDim.x) {
-        const bool isg = k < Gp;
-        const int a = isg ? k : k - Gp;
-        const int i = isg ? a : L.G + a;
-        float x = CUDART_INF_F, y = CUDART_INF_F;
-        if ((isg ? a < L.G : a < L.A) && (s.flags[i] & F_ALIVE)) { x = (float)s.px[i]; y = (float)s.py[i]; }
-        if (isg) { s.xg[a] = x; s.yg[a] = y; }
-        else { s.xa[a] = x; s.ya[a] = y; }
+// Padding slots of the float32 position lists (+inf) and the all-zero table row; once per kernel.
+__device__ __forceinline__ void init_pads(const Smem &s, const BlobLayout &L) {
+    const int t = threadIdx.x;
+    const int ng = list_pad(L.G) - L.G, na = list_pad(L.A) - L.A;  // 1..4 each
+    if (t < ng) { s.xg[L.G + t] = CUDART_INF_F; s.yg[L.G + t] = CUDART_INF_F; }
+    else if (t < ng + na) { s.xa[L.A + t - ng] = CUDART_INF_F; s.ya[L.A + t - ng] = CUDART_INF_F; }
+    else if (t < ng + na + 4) s.table[(t - ng - na) * (L.N + 1) + L.N] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// float32 position of agent i in its team list (distance matrix input; dead = +inf)
+__device__ __forceinline__ void put_xy(const Smem &s, const BlobLayout &L, int i, bool alive, float x, float y) {
+    const float lx = alive ? x : CUDART_INF_F, ly = alive ? y : CUDART_INF_F;
+    if (i < L.G) { s.xg[i] = lx; s.yg[i] = ly; }
+    else { s.xa[i - L.G] = lx; s.ya[i - L.G] = ly; }
+}
+
+// Entity record of agent i, collective_assault_env.py:237-276: [alive,x,y,atk_rad,vx,vy,iden,terrain,bit0..bit7] as
+// float32, plus its list position.
+__device__ __forceinline__ void build_row(const Smem &s, const BlobLayout &L, int i) {
+    float4 *row = s.table + i;
+    const int ps = L.N + 1;  // plane stride
+    const float x = (float)s.px[i], y = (float)s.py[i];
+    const bool alive_i = s.flags[i] & F_ALIVE;
+    put_xy(s, L, i, alive_i, x, y);
+    row[0] = make_float4(alive_i ? 1.f : 0.f, x, y, (float)s.atk[i]);
+    row[ps] = make_float4((float)s.vx[i], (float)s.vy[i], (float)i, (float)s.ter[i]);
+    // get_binary_array :207-215 (float halving, int8 wrap, floored %) yields the plain bits for 0 <= i < 256
+    float b[8];
+    if (i < 256) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) b[k] = (float)((i >> k) & 1);
+    } else {
+        int v = i;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            b[k] = (float)((((v % 2) + 2) % 2) == 1);
+            v = (int)(signed char)(int)((double)v / 2.0);
+        }
     }
+    row[2 * ps] = make_float4(b[0], b[1], b[2], b[3]);
+    row[3 * ps] = make_float4(b[4], b[5], b[6], b[7]);
 }
 
 // Branch-free stable insert of (d, j) into the ascending top-6 list: position = first k with d < bd[k]
@@ -264,48 +302,24 @@ __device__ __forceinline__ unsigned long long knn_task(const float *lx, const fl
 
 // ------------------------------------------------------------------ observation pass
 // collective_assaultEnvV1.observation collective_assault_env.py:228-359 for every guard of the env.
+// `counter` = number of this pass in the env's keyed RNG stream (stored as the new obs_counter).
 // dest == nullptr: the pass is only counted (keeps the keyed RNG stream aligned), nothing is computed.
+// prebuilt: the entity table and the position lists already describe the current state and the CTA has synchronised
+// since they were written (k_step builds them while integrating).  No barrier at the end: the caller synchronises
+// before shared memory is written again.
 __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const BlobLayout &L, int e, float *dest,
-                                         const uint32_t *rng_words, int prof_slot = 12) {
+                                         const uint32_t *rng_words, uint32_t counter, bool prebuilt, int prof_slot) {
     const int tid = threadIdx.x, nt = blockDim.x;
-    const uint32_t counter = s.sc->obs_counter + 1;
     if (dest == nullptr) {
-        __syncthreads();
-        if (tid == 0) s.sc->obs_counter = counter;
-        __syncthreads();
+        if (tid == 0) s.sc->obs_counter = counter;  // callers have synchronised since every thread read the old value
         return;
     }
-    fill_xy(s, L);
-    // entity table :237-276  [alive,x,y,atk_rad,vx,vy,iden,terrain,bit0..bit7] as float32; row N = zeros
-    for (int i = tid; i <= L.N; i += nt) {
-        float4 *row = (float4 *)(s.table + i * kObsRow);
-        if (i == L.N) {
-            row[0] = row[1] = row[2] = row[3] = make_float4(0.f, 0.f, 0.f, 0.f);
-            continue;
-        }
-        const float x = (float)s.px[i], y = (float)s.py[i];
-        const bool alive_i = s.flags[i] & F_ALIVE;
-        row[0] = make_float4(alive_i ? 1.f : 0.f, x, y, (float)s.atk[i]);
-        row[1] = make_float4((float)s.vx[i], (float)s.vy[i], (float)i, (float)s.ter[i]);
-        // get_binary_array :207-215 (float halving, int8 wrap, floored %) yields the plain bits for 0 <= i < 256
-        float b[8];
-        if (i < 256) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) b[k] = (float)((i >> k) & 1);
-        } else {
-            int v = i;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                b[k] = (float)((((v % 2) + 2) % 2) == 1);
-                v = (int)(signed char)(int)((double)v / 2.0);
-            }
-        }
-        row[2] = make_float4(b[0], b[1], b[2], b[3]);
-        row[3] = make_float4(b[4], b[5], b[6], b[7]);
+    if (!prebuilt) {
+        init_pads(s, L);
+        for (int i = tid; i < L.N; i += nt) build_row(s, L, i);
+        __syncthreads();
     }
-    __syncthreads();
     DCA_PROF(P, e, prof_slot);
-    if (tid == 0) s.sc->obs_counter = counter;
 
     const uint32_t k0 = (uint32_t)P.cfg.seed, k1 = (uint32_t)(P.cfg.seed >> 32);
     const uint32_t gid = (uint32_t)(P.cfg.env_gid0 + e);
@@ -387,23 +401,28 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
     }
     __syncthreads();
     DCA_PROF(P, e, prof_slot + 1);
+    if (tid == 0) s.sc->obs_counter = counter;
     // gather: 48 x 128-bit per guard; a quad of threads copies one 64-byte record, consecutive threads write
-    // consecutive 16 B (coalesced); empty slots read the zero row
+    // consecutive 16 B (coalesced); empty slots read the zero row.  Float4 index of the k-th round = tid + k * nt.
     {
-        float4 *out4 = (float4 *)(dest + (size_t)e * L.G * kObsLen);
-        const float4 *tab4 = (const float4 *)s.table;
-        const int part = tid & 3, nrow = L.G * kObsRows, rstep = nt >> 2;
-#pragma unroll 4
-        for (int r = tid >> 2; r < nrow; r += rstep) {
-            const int id = min((int)(uint16_t)s.sid[r], L.N);
-            out4[r * 4 + part] = tab4[id * 4 + part];
+        float4 *op = (float4 *)(dest + (size_t)e * L.G * kObsLen) + tid;
+        const float4 *tp = s.table + (tid & 3) * (L.N + 1);
+        const int16_t *sp = s.sid + (tid >> 2);
+        const int total = L.G * kObsRows * 4, rstep = nt >> 2;
+        int k = 0;
+        for (; (k + 4) * nt <= total; k += 4) {  // 4 independent loads in flight before the stores
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = tp[min((int)(uint16_t)sp[(k + u) * rstep], L.N)];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) op[(k + u) * nt] = v[u];
         }
+        for (; k * nt + tid < total; ++k) op[k * nt] = tp[min((int)(uint16_t)sp[k * rstep], L.N)];
     }
     if (P.out.slot_id) {
         int16_t *o = P.out.slot_id + (size_t)e * L.G * kObsRows;
         for (int t = tid; t < L.G * kObsRows; t += nt) o[t] = s.sid[t];
     }
-    __syncthreads();
     DCA_PROF(P, e, prof_slot + 2);
 }
 
@@ -504,22 +523,32 @@ __device__ __forceinline__ void write_alive(const Smem &s, const Params &P, cons
     }
 }
 
+// soft wall, core.py:339-353: contact_force * softplus penetration (k = contact_margin); noinline: near-wall agents only
+__device__ __noinline__ double wall_push(double d) {
+    const double kk = 1e-10;
+    return 100.0 * (logaddexp0(-d / kk) * kk);
+}
+
 // ------------------------------------------------------------------ laser: exact pair test
 // laser_hit_improve3 cython_func.pyx:22-46 for shooter i -> target j (both alive, opposite teams); records the hit.
-__device__ __forceinline__ void laser_pair(const Smem &s, const DcaConfig &c, int i, int j) {
-    const double radius = c.agent_shoot_base_radius * s.ter[i];
+__device__ __noinline__ void laser_test(const double *px, const double *py, const double *atk, const double *ter,
+                                        int32_t *shots, int32_t *hitcnt, double base_radius, double win, int i, int j) {
+    const double radius = base_radius * ter[i];
     const double r2 = radius * radius;
-    const double dx = s.px[j] - s.px[i], dy = s.py[j] - s.py[i];
+    const double dx = px[j] - px[i], dy = py[j] - py[i];
     const double d2 = dx * dx + dy * dy;
     if (d2 > r2) return;
-    const double dir = s.atk[i];
-    const double pos_r = dir + c.agent_shoot_win / 2, neg_r = dir - c.agent_shoot_win / 2;
+    const double dir = atk[i];
+    const double pos_r = dir + win / 2, neg_r = dir - win / 2;
     const double tt = atan2(dy, dx);
     const double d1 = fabs(reg_angle(pos_r - tt)), d2r = fabs(reg_angle(neg_r - tt));
-    if (d1 <= c.agent_shoot_win && d2r <= c.agent_shoot_win) {
-        atomicAdd(&s.shots[i], 1);
-        atomicAdd(&s.hitcnt[j], 1);
+    if (d1 <= win && d2r <= win) {
+        atomicAdd(&shots[i], 1);
+        atomicAdd(&hitcnt[j], 1);
     }
+}
+__device__ __forceinline__ void laser_pair(const Smem &s, const DcaConfig &c, int i, int j) {
+    laser_test(s.px, s.py, s.atk, s.ter, s.shots, s.hitcnt, c.agent_shoot_base_radius, c.agent_shoot_win, i, j);
 }
 
 // Conservative float32 bound of shooter i's squared laser radius: a pair whose f32 squared distance exceeds r^2 by
@@ -538,9 +567,9 @@ __device__ __forceinline__ void push_shooter(const Smem &s, int i) {
 // ------------------------------------------------------------------ fused step kernel
 // collective_assaultGlobalEnv.step parallel_run.py:192-246 + EnvAutoReset.step UTIL/shm_env.py:33-74.
 template <int NT, int TG, int TA>
-__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, const int32_t *__restrict__ actions,
-                                               const double *__restrict__ att_force, const uint8_t *__restrict__ skip,
-                                               const uint32_t *__restrict__ rng_words, int autoreset) {
+__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
+    const Params P, const int32_t *__restrict__ actions, const double *__restrict__ att_force,
+    const uint8_t *__restrict__ skip, const uint32_t *__restrict__ rng_words, int autoreset) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
     if (skip != nullptr && skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay in place
@@ -552,33 +581,22 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, 
     load_blob(s, P, L, e);
     DCA_PROF(P, e, 1);
 
+    // env scalars into registers: nobody reads them from shared memory again, so thread 0 may update them freely
     const double ct = s.sc->cos_theta, sn = s.sc->sin_theta;
+    const int nG0 = s.sc->n_alive_guards, nA0 = s.sc->n_alive_attackers, ts = s.sc->time_step;
+    const uint32_t obs_counter = s.sc->obs_counter;
     if (tid < 4) s.misc[tid] = 0;
-    fill_xy(s, L);
-    // phase A: guard action decode (_set_action parallel_run.py:326-374), terrain (core.py:224-234),
-    // attacker act init (cheat_script_ai.py:31-34) + injected planner force (:183-184), clear hit flags (core.py:239-242)
+    init_pads(s, L);
+    // phase A: terrain (core.py:224-234), clear hit flags (core.py:239-242), float32 position lists of the pre-move
+    // state.  (Action decode and the injected planner force are read where they are used, in phase D.)
     for (int i = tid; i < L.N; i += nt) {
-        uint8_t f = s.flags[i];
+        const uint8_t f = s.flags[i];
         const bool alive = f & F_ALIVE;
-        double fx = 0, fy = 0, ar = 0;
-        if (i < L.G) {
-            const int a = actions[(size_t)e * L.G + i];
-            double a0 = 0, a1 = 0;
-            if (a == 1) a0 = +1.0;
-            if (a == 2) a0 = -1.0;
-            if (a == 3) a1 = +1.0;
-            if (a == 4) a1 = -1.0;
-            if (a == 5) ar = +c.agent_max_rot;
-            if (a == 6) ar = -c.agent_max_rot;
-            fx = a0 * c.agent_acc; fy = a1 * c.agent_acc;
-        } else if (alive) {
-            const double2 F = ((const double2 *)att_force)[(size_t)e * L.A + (i - L.G)];
-            fx = F.x; fy = F.y;
-        }
-        s.fx[i] = fx; s.fy[i] = fy; s.ar[i] = ar;
+        const double x = s.px[i], y = s.py[i];
+        put_xy(s, L, i, alive, (float)x, (float)y);
         s.hitcnt[i] = 0; s.shots[i] = 0;
         if (alive) {
-            s.ter[i] = terrain_at(c, s.px[i], s.py[i], ct, sn);
+            s.ter[i] = terrain_at(c, x, y, ct, sn);
             s.flags[i] = f & (uint8_t)~(F_HIT | F_WAS_HIT);
         }
     }
@@ -609,10 +627,11 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, 
                     const uint32_t kb = (__float_as_uint(hi2(s01)) & ~im) | (uint32_t)(4 * q + 1);
                     const uint32_t kc = (__float_as_uint(lo2(s23)) & ~im) | (uint32_t)(4 * q + 2);
                     const uint32_t kd = (__float_as_uint(hi2(s23)) & ~im) | (uint32_t)(4 * q + 3);
-                    m2 = min(m2, max(m1, ka)); m1 = min(m1, ka);
-                    m2 = min(m2, max(m1, kb)); m1 = min(m1, kb);
-                    m2 = min(m2, max(m1, kc)); m1 = min(m1, kc);
-                    m2 = min(m2, max(m1, kd)); m1 = min(m1, kd);
+                    // two smallest of {m1, m2, ka..kd}: pairwise tournaments keep the chains short
+                    const uint32_t lab = min(ka, kb), hab = max(ka, kb), lcd = min(kc, kd), hcd = max(kc, kd);
+                    const uint32_t lo4 = min(lab, lcd), se4 = min(max(lab, lcd), min(hab, hcd));
+                    m2 = min(min(m2, se4), max(m1, lo4));
+                    m1 = min(m1, lo4);
                 }
                 best = (int)(m1 & im);
                 if ((m2 >> P.idx_bits) - (m1 >> P.idx_bits) <= 1u && m1 < 0x7F800000u) {
@@ -641,8 +660,8 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, 
     DCA_PROF(P, e, 3);
     // phase C: apply_laser_effect core.py:244-263.  C1: every listed shooter scans the opposing team with the packed
     // float32 pre-filter and queues the few (shooter, target) candidates; C2: one exact fp64 test per queued pair.
-    {
-        const int nsh = s.misc[2];
+    const int nsh = s.misc[2];
+    if (nsh > 0) {  // uniform over the CTA
         for (int q = tid; q < nsh; q += nt) {
             const int i = s.shooters[q];
             const bool att = i >= L.G;
@@ -668,59 +687,73 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, 
                 }
             }
         }
-    }
-    __syncthreads();
-    {
+        __syncthreads();
         const int np = min(s.misc[3], kPairCap);
         for (int q = tid; q < np; q += nt) {
             const uint32_t pr = s.pairs[q];
             laser_pair(s, c, (int)(pr >> 16), (int)(pr & 0xffffu));
         }
+        __syncthreads();
     }
-    __syncthreads();
     DCA_PROF(P, e, 4);
-    // phase D: deaths core.py:266-279, forces :210-222,339-353, integrate_state :282-302 (survivors only)
+    // phase D: deaths core.py:266-279, _set_action parallel_run.py:326-374 / planner force cheat_script_ai.py:183-184,
+    // wall force core.py:210-222,339-353, integrate_state :282-302 (survivors only); then the agent's float32 entity
+    // record and list position for the observation pass.
     for (int i = tid; i < L.N; i += nt) {
         uint8_t f = s.flags[i];
         if (!(f & F_ALIVE)) {
             s.flags[i] = f & (uint8_t)~F_JUST_DIED;
-            continue;
+        } else {
+            const int sh = s.shots[i];
+            if (sh > 0) { f |= F_HIT; s.nhit[i] += sh; s.flags[i] = f; }
+            const int hc = s.hitcnt[i];
+            if (hc > 0) {
+                s.nwas[i] += hc;
+                s.flags[i] = (uint8_t)((f | F_WAS_HIT | F_JUST_DIED) & ~F_ALIVE);
+                atomicAdd(&s.misc[i < L.G ? 0 : 1], 1);
+            } else {
+                double fx = 0, fy = 0, ar = 0;
+                if (i < L.G) {
+                    const int a = actions[(size_t)e * L.G + i];
+                    double a0 = 0, a1 = 0;
+                    if (a == 1) a0 = +1.0;
+                    if (a == 2) a0 = -1.0;
+                    if (a == 3) a1 = +1.0;
+                    if (a == 4) a1 = -1.0;
+                    if (a == 5) ar = +c.agent_max_rot;
+                    if (a == 6) ar = -c.agent_max_rot;
+                    fx = a0 * c.agent_acc; fy = a1 * c.agent_acc;
+                } else {
+                    const double2 F = ((const double2 *)att_force)[(size_t)e * L.A + (i - L.G)];
+                    fx = F.x; fy = F.y;
+                }
+                const double x = s.px[i], y = s.py[i];
+                const double wall = c.size, esz = 0.05, dt = 0.1;
+                const double d0 = x - (esz + (-wall)), d1 = wall - x - esz, d2 = y - esz - (-wall), d3 = wall - y - esz;
+                double wx = 0, wy = 0;
+                if (!(d0 > 0 && d1 > 0 && d2 > 0 && d3 > 0)) {
+                    const double f1 = wall_push(d0), f2 = wall_push(d1), f3 = wall_push(d2), f4 = wall_push(d3);
+                    wx = f1 - f2; wy = f3 - f4;
+                }
+                const double Fx = wx + fx, Fy = wy + fy;
+                double vx = s.vx[i] * 0.75, vy = s.vy[i] * 0.75;
+                vx += (Fx / 1.0) * dt; vy += (Fy / 1.0) * dt;
+                const double speed = sqrt(vx * vx + vy * vy);
+                if (speed > c.agent_max_speed) {
+                    vx = vx / speed * c.agent_max_speed;
+                    vy = vy / speed * c.agent_max_speed;
+                }
+                s.atk[i] = reg_angle(s.atk[i] + ar);
+                s.vx[i] = vx; s.vy[i] = vy;
+                s.px[i] = x + vx * dt; s.py[i] = y + vy * dt;
+            }
         }
-        const int sh = s.shots[i];
-        if (sh > 0) { f |= F_HIT; s.nhit[i] += sh; s.flags[i] = f; }
-        const int hc = s.hitcnt[i];
-        if (hc > 0) {
-            s.nwas[i] += hc;
-            s.flags[i] = (uint8_t)((f | F_WAS_HIT | F_JUST_DIED) & ~F_ALIVE);
-            atomicAdd(&s.misc[i < L.G ? 0 : 1], 1);
-            continue;
-        }
-        const double x = s.px[i], y = s.py[i];
-        const double wall = c.size, esz = 0.05, kk = 1e-10, dt = 0.1;
-        const double d0 = x - (esz + (-wall)), d1 = wall - x - esz, d2 = y - esz - (-wall), d3 = wall - y - esz;
-        double wx = 0, wy = 0;
-        if (!(d0 > 0 && d1 > 0 && d2 > 0 && d3 > 0)) {
-            const double f1 = 100.0 * (logaddexp0(-d0 / kk) * kk), f2 = 100.0 * (logaddexp0(-d1 / kk) * kk);
-            const double f3 = 100.0 * (logaddexp0(-d2 / kk) * kk), f4 = 100.0 * (logaddexp0(-d3 / kk) * kk);
-            wx = f1 - f2; wy = f3 - f4;
-        }
-        const double Fx = wx + s.fx[i], Fy = wy + s.fy[i];
-        double vx = s.vx[i] * 0.75, vy = s.vy[i] * 0.75;
-        vx += (Fx / 1.0) * dt; vy += (Fy / 1.0) * dt;
-        const double speed = sqrt(vx * vx + vy * vy);
-        if (speed > c.agent_max_speed) {
-            vx = vx / speed * c.agent_max_speed;
-            vy = vy / speed * c.agent_max_speed;
-        }
-        s.atk[i] = reg_angle(s.atk[i] + s.ar[i]);
-        s.vx[i] = vx; s.vy[i] = vy;
-        s.px[i] = x + vx * dt; s.py[i] = y + vy * dt;
+        build_row(s, L, i);
     }
     __syncthreads();
     DCA_PROF(P, e, 5);
     // phase E: done/win (_get_done parallel_run.py:286-316), reward (collective_assault_env.py:153-179, :228-231)
-    const int nG = s.sc->n_alive_guards - s.misc[0], nA = s.sc->n_alive_attackers - s.misc[1];
-    const int ts = s.sc->time_step;
+    const int nG = nG0 - s.misc[0], nA = nA0 - s.misc[1];
     int done = 0, win = 0;
     if (nA == 0) { done = 1; win = 1; }
     else if (nG == 0) { done = 1; win = 0; }
@@ -735,21 +768,23 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, 
         if (c.reward_debug && done && win) r += (float)c.reward_debug_value;
         P.out.reward[(size_t)e * L.G + g] = r;
     }
-    __syncthreads();  // all threads have read the scalars
     if (tid == 0) {
         s.sc->n_alive_guards = nG; s.sc->n_alive_attackers = nA;
         s.sc->time_step = ts + 1;  // :238
         P.out.done[e] = (uint8_t)done;
         P.out.win[e] = (uint8_t)win;
     }
-    __syncthreads();
     DCA_PROF(P, e, 6);
     // phase F: observation; on done the terminal obs goes to tobs, the env is reset and observed again
     const bool do_reset = done && autoreset;
-    obs_pass(s, P, L, e, do_reset ? P.out.tobs : P.out.obs, rng_words, 7);
-    if (do_reset) {
+    float *dest = do_reset ? P.out.tobs : P.out.obs;
+    const uint32_t *words = rng_words;
+    for (int pass = 0;; ++pass) {
+        obs_pass(s, P, L, e, dest, words, obs_counter + 1 + pass, pass == 0, pass == 0 ? 7 : 12);
+        if (pass == 1 || !do_reset) break;
         reset_world(s, P, L, e);
-        obs_pass(s, P, L, e, P.out.obs, nullptr);
+        dest = P.out.obs;
+        words = nullptr;
     }
     write_alive(s, P, L, e);
     DCA_PROF(P, e, 10);
@@ -759,15 +794,17 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_step(const Params P, 
 
 // reset kernel: SuperpoolEnv.reset -> collective_assaultGlobalEnv.reset parallel_run.py:248-270
 template <int NT, int TG, int TA>
-__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_reset(const Params P, const uint8_t *__restrict__ env_mask) {
+__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_reset(const Params P,
+                                                                            const uint8_t *__restrict__ env_mask) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
     if (env_mask != nullptr && !env_mask[e]) return;
     const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
     const Smem s = carve(smem_raw, L);
     load_blob(s, P, L, e);
+    const uint32_t obs_counter = s.sc->obs_counter;
     reset_world(s, P, L, e);
-    obs_pass(s, P, L, e, P.out.obs, nullptr);
+    obs_pass(s, P, L, e, P.out.obs, nullptr, obs_counter + 1, false, 12);
     if (threadIdx.x == 0) { P.out.done[e] = 0; P.out.win[e] = 0; }
     for (int g = threadIdx.x; g < L.G; g += blockDim.x) P.out.reward[(size_t)e * L.G + g] = 0.f;
     write_alive(s, P, L, e);
@@ -776,16 +813,17 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_reset(const Params P,
 
 // observation-only kernel (the kNN gather kernel on the resident state)
 template <int NT, int TG, int TA>
-__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 3) k_observe(const Params P, const uint32_t *__restrict__ rng_words) {
+__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_observe(const Params P,
+                                                                              const uint32_t *__restrict__ rng_words) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
     const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
     const Smem s = carve(smem_raw, L);
     load_blob(s, P, L, e);
-    obs_pass(s, P, L, e, P.out.obs, rng_words);
-    // only the observation counter changed: write the scalars back
-    if (threadIdx.x == 0)
-        ((EnvScalars *)(P.blobs + (size_t)e * L.bytes + L.scalars))->obs_counter = s.sc->obs_counter;
+    const uint32_t counter = s.sc->obs_counter + 1;
+    obs_pass(s, P, L, e, P.out.obs, rng_words, counter, false, 12);
+    // only the observation counter changed: write the scalars back (hints stay valid: the state did not move)
+    if (threadIdx.x == 0) ((EnvScalars *)(P.blobs + (size_t)e * L.bytes + L.scalars))->obs_counter = counter;
 }
 
 // ------------------------------------------------------------------ state import / export (plain SoA <-> blobs)
