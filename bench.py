@@ -26,7 +26,18 @@ SEED = 20240
 # algorithmic bytes per env-step, 50v50 = obs 38400 + state r/w 12000 + actions 200 +
 # attacker force 800 + reward 200 + done/win/alive 102
 BYTES_PER_ENV_STEP = 38400 + 12000 + 200 + 800 + 200 + 102
+# SURVEY.md section 8(d), gather kernel (k_observe): obs G*768 + state read N*57
+GATHER_BYTES_PER_ENV = 50 * 768 + 100 * 57
 FALLBACK_HBM_GBS = 6650.0
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per k_step launch from the committed ncu --set full capture."""
+    p = os.path.join(REPO, 'profiles', 'latest_ncu.json')
+    try:
+        return json.load(open(p))
+    except Exception:
+        return {}
 
 
 def measured_peak():
@@ -213,6 +224,19 @@ def run_ours(args):
     alive_frac = float(env.alive.float().mean().item())
     done_frac = float(env.done.float().mean().item())
 
+    # ---- the gather kernel alone (k_observe: kNN + obs gather on the resident state), north_star's ">= 60 % of HBM
+    # roofline on the gather kernel" line
+    Kg = 200
+    for _ in range(5):
+        lib.dca_observe(h, None, sptr)
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record(stream)
+    for _ in range(Kg):
+        lib.dca_observe(h, None, sptr)
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_gather = g0.elapsed_time(g1) / Kg
+
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
     torch.cuda.empty_cache()
@@ -246,6 +270,9 @@ def run_ours(args):
         return
     peak, peak_src = measured_peak()
     algo_bytes = BYTES_PER_ENV_STEP * E
+    ncu = ncu_traffic()
+    traffic = args.traffic if args.traffic is not None else (
+        ncu.get('k_step_dram_bytes_per_launch') if E == ncu.get('envs_per_gpu') else None)
     achieved = algo_bytes / (ms_step_kernel * 1e-3) / 1e9
     line = {
         'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s', 'n_gpus': world, 'steps': K,
@@ -259,8 +286,14 @@ def run_ours(args):
                    'policy_agent_steps_per_sec': value * G / N,
                    'alive_fraction_at_end': alive_frac, 'done_fraction_last_step': done_frac},
         'roofline': {'bound': 'hbm', 'kernel': 'k_step', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': args.traffic, 'peak_source': peak_src,
-                     'algorithmic_bytes_per_launch': algo_bytes, 'kernel_ms': ms_step_kernel},
+                     'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
+                     'algorithmic_bytes_per_launch': algo_bytes, 'kernel_ms': ms_step_kernel,
+                     'traffic_source': ncu.get('source')},
+        'roofline_gather_kernel': {'bound': 'hbm', 'kernel': 'k_observe', 'unit': 'GB/s', 'peak': peak,
+                                   'achieved': GATHER_BYTES_PER_ENV * E / (ms_gather * 1e-3) / 1e9,
+                                   'frac': GATHER_BYTES_PER_ENV * E / (ms_gather * 1e-3) / 1e9 / peak,
+                                   'algorithmic_bytes_per_launch': GATHER_BYTES_PER_ENV * E, 'kernel_ms': ms_gather,
+                                   'traffic': ncu.get('k_observe_dram_bytes_per_launch')},
         'e2e': {'value': e2e_value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy in, numpy obs/reward/done/info out)'},
         'gpu_launches': gpu_launches,

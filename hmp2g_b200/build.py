@@ -37,4 +37,5 @@ def build(force=False, verbose=False):
 
 
 if __name__ == '__main__':
-    print(build(force=True, verbose=True))
+    import sys
+    print(build(force=True, verbose="-v" in sys.argv))

@@ -165,8 +165,8 @@ int dca_bind_buffers(DcaHandle *h, const DcaBuffers *b) {
     if (!h || !b) return fail(h, DCA_E_INVALID, "dca_bind_buffers: null argument");
     if (!b->obs || !b->reward || !b->done || !b->win)
         return fail(h, DCA_E_INVALID, "dca_bind_buffers: obs, reward, done and win are required");
-    if (((uintptr_t)b->obs & 15) || (b->tobs && ((uintptr_t)b->tobs & 15)))
-        return fail(h, DCA_E_INVALID, "dca_bind_buffers: obs/tobs must be 16-byte aligned");
+    if (((uintptr_t)b->obs & 31) || (b->tobs && ((uintptr_t)b->tobs & 31)))
+        return fail(h, DCA_E_INVALID, "dca_bind_buffers: obs/tobs must be 32-byte aligned");
     h->P.out = *b;
     h->bound = true;
     return DCA_OK;

@@ -168,6 +168,13 @@ __device__ __forceinline__ float f32_sqdist(float xi, float yi, float xj, float 
     return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
 }
 
+// 256-bit global store (sm_100: STG.E.ENL2.256); p must be 32-byte aligned
+__device__ __forceinline__ void st_global_256(float *p, float4 a, float4 b) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w),
+                 "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
+                 : "memory");
+}
+
 // ------------------------------------------------------------------ TMA bulk copy (1-D) + mbarrier
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

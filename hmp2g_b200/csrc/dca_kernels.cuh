@@ -402,22 +402,29 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
     __syncthreads();
     DCA_PROF(P, e, prof_slot + 1);
     if (tid == 0) s.sc->obs_counter = counter;
-    // gather: 48 x 128-bit per guard; a quad of threads copies one 64-byte record, consecutive threads write
-    // consecutive 16 B (coalesced); empty slots read the zero row.  Float4 index of the k-th round = tid + k * nt.
+    // gather: 12 records of 64 B per guard; a pair of threads copies one record, each thread its 32-byte half with
+    // one 256-bit store (STG.256), so a warp instruction writes 1 KB of contiguous obs.  Empty slots read the zero
+    // record.  Half-record index of the k-th round = tid + k * nt.
     {
-        float4 *op = (float4 *)(dest + (size_t)e * L.G * kObsLen) + tid;
-        const float4 *tp = s.table + (tid & 3) * (L.N + 1);
-        const int16_t *sp = s.sid + (tid >> 2);
-        const int total = L.G * kObsRows * 4, rstep = nt >> 2;
+        float *op = dest + (size_t)e * L.G * kObsLen + tid * 8;
+        const float4 *tp = s.table + (tid & 1) * 2 * (L.N + 1);  // planes 0,1 (first half) or 2,3 (second half)
+        const int16_t *sp = s.sid + (tid >> 1);
+        const int total = L.G * kObsRows * 2, rstep = nt >> 1, ps = L.N + 1;
         int k = 0;
-        for (; (k + 4) * nt <= total; k += 4) {  // 4 independent loads in flight before the stores
-            float4 v[4];
+        for (; (k + 4) * nt <= total; k += 4) {  // 8 independent shared loads in flight before the stores
+            float4 v[4][2];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = tp[min((int)(uint16_t)sp[(k + u) * rstep], L.N)];
+            for (int u = 0; u < 4; ++u) {
+                const int id = min((int)(uint16_t)sp[(k + u) * rstep], L.N);
+                v[u][0] = tp[id]; v[u][1] = tp[id + ps];
+            }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) op[(k + u) * nt] = v[u];
+            for (int u = 0; u < 4; ++u) st_global_256(op + (size_t)(k + u) * nt * 8, v[u][0], v[u][1]);
         }
-        for (; k * nt + tid < total; ++k) op[k * nt] = tp[min((int)(uint16_t)sp[k * rstep], L.N)];
+        for (; k * nt + tid < total; ++k) {
+            const int id = min((int)(uint16_t)sp[k * rstep], L.N);
+            st_global_256(op + (size_t)k * nt * 8, tp[id], tp[id + ps]);
+        }
     }
     if (P.out.slot_id) {
         int16_t *o = P.out.slot_id + (size_t)e * L.G * kObsRows;
