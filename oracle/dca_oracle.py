@@ -16,13 +16,13 @@ OBS_ROWS, OBS_ROW = 12, 16
 
 
 def build(force=False):
-    src = os.path.join(HERE, 'dca_oracle.c')
+    srcs = [os.path.join(HERE, 'dca_oracle.c'), os.path.join(HERE, 'dca_planner.c')]
     hdr = os.path.join(HERE, 'dca_oracle.h')
     if (not force and os.path.exists(LIB_PATH)
-            and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(src), os.path.getmtime(hdr))):
+            and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(f) for f in srcs + [hdr])):
         return LIB_PATH
     cmd = ['gcc', '-O2', '-std=c11', '-ffp-contract=off', '-fno-fast-math', '-fopenmp', '-fPIC', '-shared',
-           '-o', LIB_PATH, src, '-lm']
+           '-o', LIB_PATH] + srcs + ['-lm']
     subprocess.check_call(cmd)
     return LIB_PATH
 
@@ -85,6 +85,9 @@ def lib():
         _lib.orc_step.restype = C.c_int
         _lib.orc_gae.restype = C.c_int
         _lib.orc_plan_centroid.restype = C.c_int
+        _lib.orc_plan_core.restype = C.c_int
+        _lib.orc_kmeans.restype = C.c_int
+        _lib.orc_plan.restype = C.c_int
     return _lib
 
 
@@ -176,3 +179,54 @@ def gae(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=1
                        T, E, G, C.c_double(gamma), C.c_double(tau), int(threat_limit))
     assert rc == 0
     return ret, threat, pushed
+
+
+# ---------------------------------------------------------------------------------------------- planner (dca_planner.c)
+def plan_core(gpos, galive, apos, aalive, label, cent, disable_red=False):
+    """Deterministic part of attackers_policy_1 (cheat_script_ai.py:49-184) for ONE env, given the team labels [A]
+    and k-means centroids [K,2].  Returns attacker.act[0:2] as f64 [A,2]."""
+    gpos = np.ascontiguousarray(gpos, np.float64); apos = np.ascontiguousarray(apos, np.float64)
+    galive = np.ascontiguousarray(galive, np.uint8); aalive = np.ascontiguousarray(aalive, np.uint8)
+    label = np.ascontiguousarray(label, np.int32); cent = np.ascontiguousarray(cent, np.float64)
+    G, A, K = gpos.shape[0], apos.shape[0], cent.shape[0]
+    force = np.zeros((A, 2), np.float64)
+    rc = lib().orc_plan_core(G, A, _ptr(gpos), _ptr(galive), _ptr(apos), _ptr(aalive), _ptr(label), K, _ptr(cent),
+                             int(bool(disable_red)), _ptr(force))
+    assert rc == 0
+    return force
+
+
+def kmeans(pts, k, seed, gid, counter):
+    """get_groups' kmeans2(pts, k, iter=20, minit='++') under the keyed stream.  Returns (label[n], cent[k,2], raised)."""
+    pts = np.ascontiguousarray(pts, np.float64)
+    n = pts.shape[0]
+    label = np.zeros((n,), np.int32)
+    cent = np.zeros((k, 2), np.float64)
+    rc = lib().orc_kmeans(_ptr(pts), n, int(k), C.c_uint64(int(seed)), C.c_int64(int(gid)), C.c_uint32(int(counter)),
+                          _ptr(label), _ptr(cent))
+    assert rc >= 0
+    return label, cent, rc
+
+
+class OraclePlanner(object):
+    """attackers_policy_1 with its persistent team state (start_flag survives resets) for E envs."""
+
+    def __init__(self, env):
+        self.env = env
+        E, A = env.E, env.A
+        self.K = max(A // 5, 1)
+        self.start_flag = np.ones((E,), np.uint8)
+        self.small = np.zeros((E,), np.uint8)
+        self.counter = np.zeros((E,), np.uint32)
+        self.label1 = np.zeros((E, A), np.int32)
+        self.cent1 = np.zeros((E, self.K, 2), np.float64)
+
+    def plan(self):
+        env = self.env
+        force = np.zeros((env.E, env.A, 2), np.float64)
+        st, _ = env._structs()
+        rc = lib().orc_plan(C.byref(env.cfg), C.byref(st), env.E, C.c_int64(env.env_gid0), _ptr(self.start_flag),
+                            _ptr(self.small), _ptr(self.counter), _ptr(self.label1), _ptr(self.cent1), _ptr(force),
+                            env.nthreads)
+        assert rc == 0
+        return force
