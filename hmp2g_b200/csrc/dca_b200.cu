@@ -9,6 +9,7 @@
 #include <string>
 
 #include "dca_kernels.cuh"
+#include "dca_planner.cuh"
 
 using namespace dca;
 
@@ -19,6 +20,8 @@ struct DcaHandle {
     int smem;
     bool bound;
     int64_t launches;
+    PlanState plan;
+    int plan_smem;
     std::string err;
 };
 
@@ -134,6 +137,20 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     const size_t bytes = (size_t)n_env * h->P.L.bytes;
     cudaError_t e = cudaMalloc((void **)&h->P.blobs, bytes);
     if (e == cudaSuccess) e = cudaMemset(h->P.blobs, 0, bytes);
+    {   // persistent team state of the scripted attacker planner (zero = teams not formed yet)
+        const int K = A / 5 > 0 ? A / 5 : 1;
+        std::memset(&h->plan, 0, sizeof(PlanState));
+        h->plan_smem = plan_smem_bytes(G, A);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.flags, (size_t)n_env * 2);
+        if (e == cudaSuccess) e = cudaMemset(h->plan.flags, 0, (size_t)n_env * 2);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.counter, (size_t)n_env * 4);
+        if (e == cudaSuccess) e = cudaMemset(h->plan.counter, 0, (size_t)n_env * 4);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.label, (size_t)n_env * A);
+        if (e == cudaSuccess) e = cudaMemset(h->plan.label, 0, (size_t)n_env * A);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.cent, (size_t)n_env * K * 16);
+        if (e == cudaSuccess) e = cudaMemset(h->plan.cent, 0, (size_t)n_env * K * 16);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, h->plan_smem);
+    }
     DCA_ALLOW_SMEM(k_step, h->smem);
     DCA_ALLOW_SMEM(k_reset, h->smem);
     DCA_ALLOW_SMEM(k_observe, h->smem);
@@ -145,6 +162,7 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     if (e != cudaSuccess) {
         const int rc = fail(nullptr, DCA_E_CUDA, std::string("dca_create: ") + cudaGetErrorString(e));
         if (h->P.blobs) cudaFree(h->P.blobs);
+        cudaFree(h->plan.flags); cudaFree(h->plan.counter); cudaFree(h->plan.label); cudaFree(h->plan.cent);
         delete h;
         return rc;
     }
@@ -157,6 +175,7 @@ int dca_destroy(DcaHandle *h) {
     if (!h) return DCA_E_INVALID;
     DeviceGuard guard(h->device);
     cudaFree(h->P.blobs);
+    cudaFree(h->plan.flags); cudaFree(h->plan.counter); cudaFree(h->plan.label); cudaFree(h->plan.cent);
     delete h;
     return DCA_OK;
 }
@@ -217,6 +236,19 @@ int dca_plan_centroid(DcaHandle *h, double *att_force, dca_stream_t stream) {
     DeviceGuard guard(h->device);
     const int threads = 128, warps_per_block = threads / 32;
     k_plan_centroid<<<(h->P.E + warps_per_block - 1) / warps_per_block, threads, 0, (cudaStream_t)stream>>>(h->P, att_force);
+    CUDA_TRY(h, cudaGetLastError());
+    h->launches += 1;
+    return DCA_OK;
+}
+
+int dca_plan(DcaHandle *h, double *att_force, const int32_t *team_label, const double *team_centroid,
+             dca_stream_t stream) {
+    if (!h || !att_force) return fail(h, DCA_E_INVALID, "dca_plan: null argument");
+    if ((team_label == nullptr) != (team_centroid == nullptr))
+        return fail(h, DCA_E_INVALID, "dca_plan: team_label and team_centroid are injected together or not at all");
+    if ((uintptr_t)att_force & 15) return fail(h, DCA_E_INVALID, "dca_plan: att_force must be 16-byte aligned");
+    DeviceGuard guard(h->device);
+    k_plan<<<h->P.E, kPlanThreads, h->plan_smem, (cudaStream_t)stream>>>(h->P, h->plan, att_force, team_label, team_centroid);
     CUDA_TRY(h, cudaGetLastError());
     h->launches += 1;
     return DCA_OK;

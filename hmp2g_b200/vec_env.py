@@ -105,6 +105,20 @@ class DcaVecEnv(object):
         _lib.check(self.lib.dca_plan_centroid(self.handle, _ptr(out), self._stream()), self.handle)
         return out
 
+    def plan(self, out=None, team_label=None, team_centroid=None):
+        """The scripted attacker formation planner (cheat_script_ai.py:19-194) on the resident state: fills (and
+        returns) the attacker-force tensor f64 [E,A,2].  team_label int32 [E,A] + team_centroid f64 [E,A//5,2] inject
+        a k-means result (parity harness); by default the teams come from the keyed k-means++ in the kernel."""
+        out = self._force if out is None else out
+        self._check_tensor(out, torch.float64, (self.E, self.A, 2), 'att_force')
+        if team_label is not None:
+            K = max(self.A // 5, 1)
+            self._check_tensor(team_label, torch.int32, (self.E, self.A), 'team_label')
+            self._check_tensor(team_centroid, torch.float64, (self.E, K, 2), 'team_centroid')
+        _lib.check(self.lib.dca_plan(self.handle, _ptr(out), _ptr(team_label), _ptr(team_centroid), self._stream()),
+                   self.handle)
+        return out
+
     def step(self, actions, att_force=None, skip=None, rng_words=None, autoreset=True):
         """actions int32 [E,G]; att_force float64 [E,A,2] (None -> centroid stand-in planner);
         skip uint8 [E]; rng_words int32/uint32-as-int32 [E,G,2,12].  Returns (obs, reward, done, win) views."""

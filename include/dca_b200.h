@@ -108,6 +108,14 @@ int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, cons
  * Advances the per-env observation counter like any other pass. */
 int dca_observe(DcaHandle *h, const uint32_t *rng_words, dca_stream_t stream);
 
+/* replaces: CheatScriptAI.attackers_policy_1 formation planner MISSION/dca/cheat_script_ai.py:19-194 + get_groups
+ * :259-297 (DBSCAN targets, k-means teams, team->target and member->ring-slot assignments), which the reference runs
+ * inside World.step core.py:189-196.  Fills att_force f64[E,A,2] for dca_step.  The team state (World.start_flag,
+ * teams_result_step1) lives in the handle and survives resets like the reference's.  team_label i32[E,A] +
+ * team_centroid f64[E,A/5,2], both or neither: inject a k-means result (parity harness) instead of the keyed one. */
+int dca_plan(DcaHandle *h, double *att_force, const int32_t *team_label, const double *team_centroid,
+             dca_stream_t stream);
+
 /* Benchmark planner stand-in (NOT the reference planner): force = centroid(alive guards) - pos. */
 int dca_plan_centroid(DcaHandle *h, double *att_force, dca_stream_t stream);
 

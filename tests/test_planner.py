@@ -66,3 +66,75 @@ def test_keyed_kmeans_is_a_lloyd_fixed_point_and_statistically_scipy():
     l1, c1, _ = orc.kmeans(pts, 10, 77, 5, 9)
     l2, c2, _ = orc.kmeans(pts, 10, 77, 5, 9)
     assert np.array_equal(l1, l2) and np.array_equal(c1, c2)
+
+
+# ------------------------------------------------------------------------------------------------ GPU (run with -m gpu)
+def _blank_state(E, G, A, gpos, galive, apos, aalive):
+    N = G + A
+    st = dict(pos=np.concatenate([gpos, apos], 1), vel=np.zeros((E, N, 2)), atk_rad=np.zeros((E, N)),
+              terrain=np.ones((E, N)), alive=np.concatenate([galive, aalive], 1).astype(np.uint8),
+              just_died=np.zeros((E, N), np.uint8), hit=np.zeros((E, N), np.uint8), was_hit=np.zeros((E, N), np.uint8),
+              num_hit=np.zeros((E, N), np.int32), num_was_hit=np.zeros((E, N), np.int32), init_theta=np.zeros((E,)),
+              time_step=np.zeros((E,), np.int32), n_alive_guards=galive.sum(1).astype(np.int32),
+              n_alive_attackers=aalive.sum(1).astype(np.int32), obs_counter=np.zeros((E,), np.uint32),
+              episode=np.zeros((E,), np.uint32))
+    return st
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', PLANNER_CASES)
+def test_cuda_planner_core_matches_reference_and_oracle(name):
+    """k_plan with the reference's own k-means result injected: every recorded step of the fixture as one env of a
+    batch.  Forces vs the reference <= 1e-9 absolute, vs the C oracle <= 1e-12 (CUDA vs glibc cos/sin/sqrt)."""
+    import torch
+    from test_gpu_parity import make_gpu_env
+    d = load_planner_case(name)
+    G, A, E = int(d['G']), int(d['A']), len(d['label'])
+    cfg = dict(num_guards=G, num_attackers=A, DISALBE_RED_FUNCTION=bool(d['disable_red']))
+    env = make_gpu_env(cfg, E, seed=1, gid0=0, debug=False)
+    env.reset()
+    env.import_state(_blank_state(E, G, A, d['gpos'], d['galive'], d['apos'], d['aalive']))
+    lab = torch.from_numpy(d['label'].astype(np.int32)).to(env.device)
+    cen = torch.from_numpy(np.ascontiguousarray(d['cent'], np.float64)).to(env.device)
+    got = env.plan(team_label=lab, team_centroid=cen).cpu().numpy()
+    n_checked = 0
+    for t in range(E):
+        want_orc = orc.plan_core(d['gpos'][t], d['galive'][t], d['apos'][t], d['aalive'][t], d['label'][t], d['cent'][t],
+                                 bool(d['disable_red']))
+        np.testing.assert_allclose(got[t], want_orc, rtol=0, atol=1e-12, err_msg='%s step %d vs oracle' % (name, t))
+        if not np.isnan(d['force'][t]).any():
+            np.testing.assert_allclose(got[t], d['force'][t], rtol=0, atol=1e-9, err_msg='%s step %d vs reference' % (name, t))
+            n_checked += 1
+    assert n_checked >= 40
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('cfg,E,steps', [
+    (dict(num_guards=50, num_attackers=50, random_jam_prob=0.05, introduce_terrain=True, terrain_parameters=[0.05, 0.2],
+          MaxEpisodeStep=60, init_distance=2), 96, 80),
+    (dict(num_guards=20, num_attackers=33, introduce_terrain=False, MaxEpisodeStep=25, init_distance=1.5), 40, 60),
+])
+def test_cuda_planner_native_matches_oracle_in_a_rollout(cfg, E, steps):
+    """Full planner (keyed k-means++ teams with their persistent state) GPU vs C oracle on identical states over a
+    rollout with deaths and autoresets; the step itself is driven by the oracle's forces and re-synced, so any
+    difference is the planner's.  Forces <= 1e-12 absolute (a different team label would show as O(1))."""
+    import torch
+    from dca_oracle import OraclePlanner, OracleVecEnv
+    from test_gpu_parity import make_gpu_env
+    o = OracleVecEnv(cfg, E, seed=5, env_gid0=100, nthreads=8)
+    env = make_gpu_env(cfg, E, seed=5, gid0=100, debug=False)
+    o.reset(); env.reset()
+    env.import_state(o.state)
+    planner = OraclePlanner(o)
+    rng = np.random.RandomState(3)
+    n_done = 0
+    for t in range(steps):
+        want = planner.plan()
+        got = env.plan().cpu().numpy()
+        np.testing.assert_allclose(got, want, rtol=0, atol=1e-12, err_msg='t=%d' % t)
+        act = rng.randint(0, 7, size=(E, o.G))
+        o.step(act.astype(np.float64), want)
+        n_done += int((o.done != 0).sum())
+        env.import_state(o.state)
+    assert n_done > 0
+    assert np.abs(want).max() > 0.1
