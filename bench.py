@@ -107,20 +107,23 @@ def physical_gpu_index(local_index):
 
 
 # ------------------------------------------------------------------------------------------ CPU arm (oracle port)
-def cpu_port_run(n_env, steps, warmup, threads, seed=SEED):
-    """Times the CPU restatement of the reference path (oracle/dca_oracle.c, OpenMP over envs) on `threads` host
-    threads: planner stand-in + step + obs + autoreset, same workload.  Returns (agent_steps_per_s, seconds)."""
+def cpu_port_run(n_env, steps, warmup, threads, seed=SEED, full_planner=True):
+    """Times the CPU restatement of the reference path (oracle/dca_oracle.c + dca_planner.c, OpenMP over envs) on
+    `threads` host threads: scripted attacker planner + step + obs + autoreset, same workload (what one
+    SuperpoolEnv.step does in the reference).  Returns (agent_steps_per_s, seconds)."""
     sys.path.insert(0, os.path.join(REPO, 'oracle'))
-    from dca_oracle import OracleVecEnv
+    from dca_oracle import OraclePlanner, OracleVecEnv
     env = OracleVecEnv(WORKLOAD, n_env, seed=seed, nthreads=threads)
     env.reset()
+    planner = OraclePlanner(env)
+    plan = planner.plan if full_planner else env.plan_centroid
     rng = np.random.RandomState(1)
     pool = [rng.randint(0, 7, size=(n_env, env.G)).astype(np.float64) for _ in range(8)]
     for i in range(warmup):
-        env.step(pool[i % 8], env.plan_centroid())
+        env.step(pool[i % 8], plan())
     t0 = time.perf_counter()
     for i in range(steps):
-        env.step(pool[i % 8], env.plan_centroid())
+        env.step(pool[i % 8], plan())
     dt = time.perf_counter() - t0
     return n_env * env.N * steps / dt, dt
 
@@ -142,10 +145,11 @@ def run_reference_arm(args):
         'impl': 'reference', 'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s',
         'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': dt / steps * 1e3,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': 'DCA 50v50 step+obs+autoreset, injected random guard actions, centroid planner stand-in',
+        'config': {'workload': 'DCA 50v50 scripted-attacker planner + step + obs + autoreset, injected random guard actions',
                    'envs_per_step_sample': n_env, 'scenario': WORKLOAD},
         'cpu_baseline': {'value': value, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
-                         'sample': '%d envs x %d steps of the 50v50 workload, OpenMP over envs' % (n_env, steps)},
+                         'sample': '%d envs x %d steps of the 50v50 workload incl. the scripted attacker planner, C port, '
+                                   'OpenMP over envs' % (n_env, steps)},
         'e2e': {'value': value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
@@ -236,7 +240,6 @@ def run_ours(args):
     g1.record(stream)
     torch.cuda.synchronize()
     ms_gather = g0.elapsed_time(g1) / Kg
-
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
     torch.cuda.empty_cache()
@@ -262,6 +265,16 @@ def run_ours(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = world * E * N * Ke / float(te.item())
     h2d, d2h = host.h2d_bytes, host.d2h_bytes
+    # ---- the scripted attacker planner kernel (k_plan) on the state its own rollout produced; part of e2e, not of
+    # configs[1] ("injected actions")
+    pf = C.c_void_p(host.env._force.data_ptr())
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record(stream)
+    for _ in range(20):
+        host.env.lib.dca_plan(host.env.handle, pf, None, None, sptr)
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_plan = g0.elapsed_time(g1) / 20
 
     if rank != 0:
         if world > 1:
@@ -283,7 +296,7 @@ def run_ours(args):
                    'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD,
                    'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
                          '> 126 MB L2' % ((E * (G * 768 + 2 * 5760)) / 1e6, E * G * 768 / 1e6, 2 * E * 5760 / 1e6),
-                   'policy_agent_steps_per_sec': value * G / N,
+                   'policy_agent_steps_per_sec': value * G / N, 'planner_kernel_ms': ms_plan,
                    'alive_fraction_at_end': alive_frac, 'done_fraction_last_step': done_frac},
         'roofline': {'bound': 'hbm', 'kernel': 'k_step', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
@@ -295,7 +308,8 @@ def run_ours(args):
                                    'algorithmic_bytes_per_launch': GATHER_BYTES_PER_ENV * E, 'kernel_ms': ms_gather,
                                    'traffic': ncu.get('k_observe_dram_bytes_per_launch')},
         'e2e': {'value': e2e_value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy in, numpy obs/reward/done/info out)'},
+                'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy actions in; planner + step on device; numpy '
+                                    'obs/reward/done/info out)'},
         'gpu_launches': gpu_launches,
         'clocks': clocks,
     }
@@ -303,10 +317,12 @@ def run_ours(args):
         cores = os.cpu_count() or 1
         n_cpu_env, cpu_steps = 1024, 60
         v, dt = cpu_port_run(n_cpu_env, cpu_steps, 5, cores)
+        v0, _ = cpu_port_run(n_cpu_env, cpu_steps, 5, cores, full_planner=False)
         v1, dt1 = cpu_port_run(128, 40, 3, 1)
         line['cpu_baseline'] = {'value': v, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
-                                'sample': '%d envs x %d steps of the same 50v50 workload (%.1f s)' % (n_cpu_env, cpu_steps, dt),
-                                'single_core_value': v1}
+                                'sample': '%d envs x %d steps of the same 50v50 workload incl. the scripted attacker '
+                                          'planner (%.1f s)' % (n_cpu_env, cpu_steps, dt),
+                                'single_core_value': v1, 'value_without_planner': v0}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

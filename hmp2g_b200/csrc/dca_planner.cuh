@@ -15,7 +15,8 @@
 namespace dca {
 
 enum : uint32_t { SITE_PLAN = 3 };
-constexpr int kPlanThreads = 128;
+constexpr int kPlanThreads = 64;
+constexpr int kSerialTeam = 8;  // member <-> slot assignments up to this size run on a single thread
 
 // persistent team state of one env (World.start_flag / teams_result_step1 / team_centroid_step1 survive resets)
 struct PlanState {
@@ -30,48 +31,52 @@ struct PlanSmem {
     uint8_t *galive, *aalive;
     int16_t *gidx;                  // alive guards in index order
     unsigned long long *adj;        // [n][W] eps-graph rows
-    int16_t *comp;                  // [n] component of alive guard a
-    int16_t *csize;                 // [n] size of component k
-    int16_t *tsrc;                  // [K] target source: >= 0 cluster id, < 0 -> noise point ~value
+    int16_t *comp;                  // [n] lowest member of the component of alive guard a
+    int32_t *csize;                 // [n] size of the component rooted at a
+    int16_t *tsrc;                  // [K] target source: >= 0 cluster root, < 0 -> noise point ~value
     double *tx, *ty;                // [K] targets
-    double *cx, *cy, *nx, *ny;      // [K] centroids (code book) / new code book
+    double *cx, *cy;                // [K] centroids (code book)
     int32_t *cnt;                   // [K]
-    double *d2;                     // [A]
+    double *d2, *prob;              // [A]
     int16_t *lab;                   // [A] team label in use
+    uint32_t *lmask;                // [K][AW] members of team k as bit rows over the attackers
     int16_t *team_target;           // [K]
     int16_t *toff;                  // [K+1] member list offsets
-    int16_t *mem;                   // [A] members grouped by team
-    // per-warp assignment workspaces (4 warps)
-    double *hu, *hv, *hminv;        // [4][M+1]
-    int16_t *hp, *hway;             // [4][M+1]
-    uint8_t *hused;                 // [4][M+1]
-    int16_t *hcol;                  // [4][M]
-    double *sx, *sy;                // [4][A] ring slots
-    int32_t *misc;                  // [0] n alive guards, [1] n components, [2] n targets, [3] raised flag, [4] pick
+    int16_t *mem, *tof;             // [A] members grouped by team / team of that list position
+    double *c1;                     // [K*K] team-centroid <-> target distances
+    double *hu, *hv, *hminv;        // [A+K+2] assignment workspaces (team t owns [toff[t]+t, +n_t+1))
+    int16_t *hp, *hway;             // [A+K+2]
+    uint8_t *hused;                 // [A+K+2]
+    int16_t *hcol;                  // [A] slot of list position i
+    double *sx, *sy;                // [A] ring slots by list position
+    int32_t *misc;                  // [0] n alive guards, [2] n targets, [3] raised flag, [4] changed flag
 };
 
 __host__ __device__ inline int plan_smem_bytes(int G, int A) {
-    const int K = A / 5 > 0 ? A / 5 : 1, M = (A > K ? A : K) + 1, W = (G + 63) / 64;
+    const int K = A / 5 > 0 ? A / 5 : 1, H = A + K + 2, W = (G + 63) / 64, AW = (A + 31) / 32;
     int o = 0;
     o += 2 * G * 8 + 2 * A * 8;          // positions
     o += align_up(G + A, 16);            // alive
     o += align_up(G * 2, 16);            // gidx
     o += G * W * 8;                      // adj
-    o += 2 * align_up(G * 2, 16);        // comp csize
+    o += align_up(G * 2, 16) + align_up(G * 4, 16);  // comp csize
     o += align_up(K * 2, 16);            // tsrc
-    o += 6 * align_up(K * 8, 16);        // tx ty cx cy nx ny
+    o += 4 * align_up(K * 8, 16);        // tx ty cx cy
     o += align_up(K * 4, 16);            // cnt
-    o += align_up(A * 8, 16);            // d2
+    o += 2 * align_up(A * 8, 16);        // d2 prob
     o += align_up(A * 2, 16);            // lab
-    o += align_up(K * 2, 16) + align_up((K + 1) * 2, 16) + align_up(A * 2, 16);  // team_target toff mem
-    o += 4 * (3 * align_up(M * 8, 16) + 2 * align_up(M * 2, 16) + align_up(M, 16) + align_up(M * 2, 16));
-    o += 4 * 2 * align_up(A * 8, 16);    // sx sy
+    o += align_up(K * AW * 4, 16);       // lmask
+    o += align_up(K * 2, 16) + align_up((K + 1) * 2, 16) + 2 * align_up(A * 2, 16);  // team_target toff mem tof
+    o += align_up(K * K * 8, 16);        // c1
+    o += 3 * align_up(H * 8, 16) + 2 * align_up(H * 2, 16) + align_up(H, 16);  // hu hv hminv hp hway hused
+    o += align_up(A * 2, 16);            // hcol
+    o += 2 * align_up(A * 8, 16);        // sx sy
     o += 32;
     return o;
 }
 
 __device__ __forceinline__ PlanSmem plan_carve(unsigned char *p, int G, int A) {
-    const int K = A / 5 > 0 ? A / 5 : 1, M = (A > K ? A : K) + 1, W = (G + 63) / 64;
+    const int K = A / 5 > 0 ? A / 5 : 1, H = A + K + 2, W = (G + 63) / 64, AW = (A + 31) / 32;
     PlanSmem s;
     s.gx = (double *)p; p += G * 8; s.gy = (double *)p; p += G * 8;
     s.ax = (double *)p; p += A * 8; s.ay = (double *)p; p += A * 8;
@@ -79,24 +84,25 @@ __device__ __forceinline__ PlanSmem plan_carve(unsigned char *p, int G, int A) {
     s.gidx = (int16_t *)p; p += align_up(G * 2, 16);
     s.adj = (unsigned long long *)p; p += G * W * 8;
     s.comp = (int16_t *)p; p += align_up(G * 2, 16);
-    s.csize = (int16_t *)p; p += align_up(G * 2, 16);
+    s.csize = (int32_t *)p; p += align_up(G * 4, 16);
     s.tsrc = (int16_t *)p; p += align_up(K * 2, 16);
-    const int k8 = align_up(K * 8, 16);
+    const int k8 = align_up(K * 8, 16), a8 = align_up(A * 8, 16), a2 = align_up(A * 2, 16);
     s.tx = (double *)p; p += k8; s.ty = (double *)p; p += k8;
     s.cx = (double *)p; p += k8; s.cy = (double *)p; p += k8;
-    s.nx = (double *)p; p += k8; s.ny = (double *)p; p += k8;
     s.cnt = (int32_t *)p; p += align_up(K * 4, 16);
-    s.d2 = (double *)p; p += align_up(A * 8, 16);
-    s.lab = (int16_t *)p; p += align_up(A * 2, 16);
+    s.d2 = (double *)p; p += a8; s.prob = (double *)p; p += a8;
+    s.lab = (int16_t *)p; p += a2;
+    s.lmask = (uint32_t *)p; p += align_up(K * AW * 4, 16);
     s.team_target = (int16_t *)p; p += align_up(K * 2, 16);
     s.toff = (int16_t *)p; p += align_up((K + 1) * 2, 16);
-    s.mem = (int16_t *)p; p += align_up(A * 2, 16);
-    const int m8 = align_up(M * 8, 16), m2 = align_up(M * 2, 16), m1 = align_up(M, 16);
-    s.hu = (double *)p; p += 4 * m8; s.hv = (double *)p; p += 4 * m8; s.hminv = (double *)p; p += 4 * m8;
-    s.hp = (int16_t *)p; p += 4 * m2; s.hway = (int16_t *)p; p += 4 * m2;
-    s.hused = p; p += 4 * m1;
-    s.hcol = (int16_t *)p; p += 4 * m2;
-    s.sx = (double *)p; p += 4 * align_up(A * 8, 16); s.sy = (double *)p; p += 4 * align_up(A * 8, 16);
+    s.mem = (int16_t *)p; p += a2; s.tof = (int16_t *)p; p += a2;
+    s.c1 = (double *)p; p += align_up(K * K * 8, 16);
+    const int h8 = align_up(H * 8, 16), h2 = align_up(H * 2, 16);
+    s.hu = (double *)p; p += h8; s.hv = (double *)p; p += h8; s.hminv = (double *)p; p += h8;
+    s.hp = (int16_t *)p; p += h2; s.hway = (int16_t *)p; p += h2;
+    s.hused = p; p += align_up(H, 16);
+    s.hcol = (int16_t *)p; p += a2;
+    s.sx = (double *)p; p += a8; s.sy = (double *)p; p += a8;
     s.misc = (int32_t *)p;
     return s;
 }
@@ -177,17 +183,73 @@ __device__ __forceinline__ uint32_t plan_word(const DcaConfig &c, uint32_t gid, 
     return k == 0 ? q.x : (k == 1 ? q.y : (k == 2 ? q.z : q.w));
 }
 
+// The same assignment by ONE thread (small problems: a team's members <-> its ring slots); workspaces hold m+1 entries.
+template <typename CostFn>
+__device__ __forceinline__ void assign_serial(CostFn cost, int n, int m, double *u, double *v, double *minv, int16_t *p,
+                                              int16_t *way, uint8_t *used, int16_t *col_of_row) {
+    for (int j = 0; j <= m; ++j) { v[j] = 0; p[j] = 0; }
+    for (int i = 0; i <= n; ++i) u[i] = 0;
+    for (int i = 1; i <= n; ++i) {
+        p[0] = (int16_t)i;
+        int j0 = 0;
+        for (int j = 0; j <= m; ++j) { minv[j] = CUDART_INF; used[j] = 0; }
+        do {
+            used[j0] = 1;
+            const int i0 = p[j0];
+            const double ui0 = u[i0];
+            double delta = CUDART_INF;
+            int j1 = 0;
+            for (int j = 1; j <= m; ++j) {
+                if (used[j]) continue;
+                const double cur = (cost(i0 - 1, j - 1) - ui0) - v[j];
+                double mv = minv[j];
+                if (cur < mv) { mv = cur; minv[j] = cur; way[j] = (int16_t)j0; }
+                if (mv < delta) { delta = mv; j1 = j; }
+            }
+            for (int j = 0; j <= m; ++j) {
+                if (used[j]) { u[p[j]] += delta; v[j] -= delta; }
+                else minv[j] -= delta;
+            }
+            j0 = j1;
+        } while (p[j0] != 0);
+        do {
+            const int j1 = way[j0];
+            p[j0] = p[j1];
+            j0 = j1;
+        } while (j0);
+    }
+    for (int j = 1; j <= m; ++j)
+        if (p[j]) col_of_row[p[j] - 1] = (int16_t)(j - 1);
+}
+
+// Bit rows of the team labels: lmask[k][w] bit b <=> attacker 32 w + b is in team k (warp ballots).  CTA-wide, no sync.
+__device__ __forceinline__ void plan_label_masks(const PlanSmem &s, int A, int K) {
+    const int AW = (A + 31) / 32, tid = threadIdx.x, lane = tid & 31;
+    for (int j0 = (tid >> 5) * 32; j0 < A; j0 += blockDim.x) {  // warp-uniform
+        const int j = j0 + lane;
+        const int l = j < A ? (int)s.lab[j] : -1;
+        for (int k = 0; k < K; ++k) {
+            const uint32_t b = __ballot_sync(0xffffffffu, l == k);
+            if (lane == 0) s.lmask[k * AW + (j0 >> 5)] = b;
+        }
+    }
+}
+
 // get_groups' kmeans2(attacker positions, K, iter=20, minit='++', missing='raise') with up to 5 redraws, then
-// missing='warn' (cheat_script_ai.py:276-288), CTA-wide.  Result: s.lab[A], s.cx/s.cy[K].
-__device__ void plan_kmeans(const PlanSmem &s, const DcaConfig &c, int A, int K, uint32_t gid, uint32_t counter) {
-    const int tid = threadIdx.x, nt = blockDim.x;
+// missing='warn' (cheat_script_ai.py:276-288), CTA-wide.  Result: s.lab[A], s.lmask, s.cx/s.cy[K].
+// The means are sequential sums in index order (update_cluster_means); a Lloyd round that changes no label is a
+// fixed point, so the remaining rounds of the 20 are skipped without changing the result.
+__device__ __forceinline__ void plan_kmeans(const PlanSmem &s, const DcaConfig &c, int A, int K, uint32_t gid,
+                                            uint32_t counter) {
+    const int tid = threadIdx.x, nt = blockDim.x, AW = (A + 31) / 32;
     for (int attempt = 0;; ++attempt) {
         // _kpp seeding
         if (tid == 0) {
             const int pick = (int)__umulhi(plan_word(c, gid, counter, attempt, 0), (uint32_t)A);
             s.cx[0] = s.ax[pick]; s.cy[0] = s.ay[pick];
+            s.misc[3] = 0; s.misc[4] = 0;  // raised / changed flags
         }
-        for (int j = tid; j < A; j += nt) s.d2[j] = CUDART_INF;
+        for (int j = tid; j < A; j += nt) { s.d2[j] = CUDART_INF; s.lab[j] = -1; }
         __syncthreads();
         for (int i = 1; i < K; ++i) {
             for (int j = tid; j < A; j += nt) {
@@ -195,24 +257,27 @@ __device__ void plan_kmeans(const PlanSmem &s, const DcaConfig &c, int A, int K,
                 if (d < s.d2[j]) s.d2[j] = d;
             }
             __syncthreads();
-            if (tid == 0) {
+            {   // every thread forms the same sequential total, then its own probabilities
                 double tot = 0;
                 for (int j = 0; j < A; ++j) tot += s.d2[j];
+                for (int j = tid; j < A; j += nt) s.prob[j] = s.d2[j] / tot;
+            }
+            __syncthreads();
+            if (tid == 0) {
                 const double r = (double)plan_word(c, gid, counter, attempt, i) * 0x1p-32;
                 double cum = 0;
                 int pick = A - 1;
                 for (int j = 0; j < A; ++j) {
-                    cum += s.d2[j] / tot;
+                    cum += s.prob[j];
                     if (cum >= r) { pick = j; break; }
                 }
                 s.cx[i] = s.ax[pick]; s.cy[i] = s.ay[pick];
             }
             __syncthreads();
         }
-        // 20 Lloyd rounds
+        // Lloyd rounds
         bool raised = false;
         for (int it = 0; it < 20; ++it) {
-            if (tid == 0) s.misc[3] = 0;
             for (int j = tid; j < A; j += nt) {  // vq: nearest code, first minimum
                 double best = plan_sq2(s.ax[j], s.ay[j], s.cx[0], s.cy[0]);
                 int bl = 0;
@@ -220,23 +285,30 @@ __device__ void plan_kmeans(const PlanSmem &s, const DcaConfig &c, int A, int K,
                     const double d = plan_sq2(s.ax[j], s.ay[j], s.cx[k], s.cy[k]);
                     if (d < best) { best = d; bl = k; }
                 }
-                s.lab[j] = (int16_t)bl;
+                if (bl != s.lab[j]) { s.lab[j] = (int16_t)bl; s.misc[4] = 1; }
             }
             __syncthreads();
+            if (s.misc[4] == 0) break;  // same labels as last round: the code book already holds their means
+            plan_label_masks(s, A, K);
+            __syncthreads();
+            if (tid == 0) s.misc[4] = 0;  // everyone has read it; the next labelling pass may set it again
             for (int k = tid; k < K; k += nt) {  // update_cluster_means: sequential sums in index order
                 double sx = 0, sy = 0;
                 int n = 0;
-                for (int j = 0; j < A; ++j)
-                    if (s.lab[j] == k) { sx += s.ax[j]; sy += s.ay[j]; ++n; }
-                if (n) { s.nx[k] = sx / n; s.ny[k] = sy / n; }
-                else if (attempt < 5) s.misc[3] = 1;               // missing='raise'
-                else { s.nx[k] = s.cx[k]; s.ny[k] = s.cy[k]; }     // missing='warn'
+                for (int w = 0; w < AW; ++w) {
+                    uint32_t m = s.lmask[k * AW + w];
+                    while (m) {
+                        const int j = w * 32 + __ffs(m) - 1;
+                        m &= m - 1;
+                        sx += s.ax[j]; sy += s.ay[j]; ++n;
+                    }
+                }
+                if (n) { s.cx[k] = sx / n; s.cy[k] = sy / n; }
+                else if (attempt < 5) s.misc[3] = 1;  // missing='raise'; ('warn': the old centre stays)
             }
             __syncthreads();
             raised = s.misc[3] != 0;
             if (raised) break;
-            for (int k = tid; k < K; k += nt) { s.cx[k] = s.nx[k]; s.cy[k] = s.ny[k]; }
-            __syncthreads();
         }
         __syncthreads();
         if (!raised) return;
@@ -246,14 +318,15 @@ __device__ void plan_kmeans(const PlanSmem &s, const DcaConfig &c, int A, int K,
 // ------------------------------------------------------------------ planner kernel
 // inj_label (i32[E,A]) / inj_cent (f64[E,K,2]) != nullptr: use these teams (the parity harness injects the
 // reference's own k-means result) and leave the persistent state alone.
-__global__ void __launch_bounds__(kPlanThreads) k_plan(const Params P, const PlanState ps, double *__restrict__ att_force,
-                                                       const int32_t *__restrict__ inj_label,
-                                                       const double *__restrict__ inj_cent) {
+__global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const PlanState ps,
+                                                          double *__restrict__ att_force,
+                                                          const int32_t *__restrict__ inj_label,
+                                                          const double *__restrict__ inj_cent) {
     extern __shared__ __align__(16) unsigned char plan_raw[];
     const BlobLayout &L = P.L;
     const DcaConfig &c = P.cfg;
-    const int G = L.G, A = L.A, K = A / 5 > 0 ? A / 5 : 1, M = (A > K ? A : K) + 1, W = (G + 63) / 64;
-    const int e = blockIdx.x, tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+    const int G = L.G, A = L.A, K = A / 5 > 0 ? A / 5 : 1, W = (G + 63) / 64, AW = (A + 31) / 32;
+    const int e = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
     const PlanSmem s = plan_carve(plan_raw, G, A);
     const unsigned char *blob = P.blobs + (size_t)e * L.bytes;
     const double *bpx = (const double *)(blob + L.px), *bpy = (const double *)(blob + L.py);
@@ -271,23 +344,21 @@ __global__ void __launch_bounds__(kPlanThreads) k_plan(const Params P, const Pla
         for (int a = tid; a < A; a += nt) s.lab[a] = (int16_t)inj_label[(size_t)e * A + a];
         for (int k = tid; k < K; k += nt) { s.cx[k] = inj_cent[((size_t)e * K + k) * 2]; s.cy[k] = inj_cent[((size_t)e * K + k) * 2 + 1]; }
         __syncthreads();
+        plan_label_masks(s, A, K);
     } else {
         const uint32_t gid = (uint32_t)(c.env_gid0 + e);
         uint32_t counter = ps.counter[e];
         const bool start = ps.flags[2 * e] == 0;
         bool small = ps.flags[2 * e + 1] != 0;
-        __syncthreads();
         if (start) {
             plan_kmeans(s, c, A, K, gid, counter++);
             for (int a = tid; a < A; a += nt) ps.label[(size_t)e * A + a] = (uint8_t)s.lab[a];
-            for (int k = tid; k < K; k += nt) { ps.cent[((size_t)e * K + k) * 2] = s.cx[k]; ps.cent[((size_t)e * K + k) * 2 + 1] = s.cy[k]; }
-            for (int k = tid; k < K; k += nt) s.cnt[k] = 0;
-            if (tid == 0) s.misc[3] = 0;
-            __syncthreads();
-            for (int a = tid; a < A; a += nt) atomicAdd(&s.cnt[s.lab[a]], 1);
-            __syncthreads();
-            for (int k = tid; k < K; k += nt)
-                if (s.cnt[k] > 0 && s.cnt[k] <= 3) s.misc[3] = 1;  // a team of <= 3: regroup on every call from now on
+            for (int k = tid; k < K; k += nt) {
+                ps.cent[((size_t)e * K + k) * 2] = s.cx[k]; ps.cent[((size_t)e * K + k) * 2 + 1] = s.cy[k];
+                int n = 0;
+                for (int w = 0; w < AW; ++w) n += __popc(s.lmask[k * AW + w]);
+                if (n > 0 && n <= 3) s.misc[3] = 1;  // a team of <= 3: regroup on every call from now on (:112-117)
+            }
             __syncthreads();
             small = s.misc[3] != 0;
             __syncthreads();
@@ -295,12 +366,13 @@ __global__ void __launch_bounds__(kPlanThreads) k_plan(const Params P, const Pla
             for (int a = tid; a < A; a += nt) s.lab[a] = ps.label[(size_t)e * A + a];
             for (int k = tid; k < K; k += nt) { s.cx[k] = ps.cent[((size_t)e * K + k) * 2]; s.cy[k] = ps.cent[((size_t)e * K + k) * 2 + 1]; }
             __syncthreads();
+            plan_label_masks(s, A, K);
         }
         if (small) plan_kmeans(s, c, A, K, gid, counter++);
         if (tid == 0) { ps.counter[e] = counter; ps.flags[2 * e] = 1; ps.flags[2 * e + 1] = small ? 1 : 0; }
     }
 
-    // ---- targets: DBSCAN components of the alive guards (cheat_script_ai.py:49-101)
+    // ---- targets: DBSCAN(eps .5, min_samples 2) of the alive guards (cheat_script_ai.py:49-101)
     if (tid == 0) {
         int n = 0;
         for (int g = 0; g < G; ++g)
@@ -320,44 +392,43 @@ __global__ void __launch_bounds__(kPlanThreads) k_plan(const Params P, const Pla
             }
             s.adj[a * W + w] = m;
         }
+        s.comp[a] = (int16_t)a;
+        s.csize[a] = 0;
     }
     __syncthreads();
-    if (tid == 0) {  // components in order of their lowest member (serial flood fill over the bit rows)
-        unsigned long long unv[4] = {0, 0, 0, 0};
-        for (int a = 0; a < n; ++a) unv[a >> 6] |= 1ull << (a & 63);
-        int nc = 0;
-        for (int a = 0; a < n; ++a) {
-            if (!((unv[a >> 6] >> (a & 63)) & 1ull)) continue;
-            unsigned long long fr[4] = {0, 0, 0, 0};
-            fr[a >> 6] = 1ull << (a & 63);
-            unv[a >> 6] &= ~fr[a >> 6];
-            int size = 0;
-            for (;;) {
-                int b = -1;
-                for (int w = 0; w < W; ++w)
-                    if (fr[w]) { b = w * 64 + __ffsll((long long)fr[w]) - 1; break; }
-                if (b < 0) break;
-                fr[b >> 6] &= ~(1ull << (b & 63));
-                s.comp[b] = (int16_t)nc;
-                ++size;
-                for (int w = 0; w < W; ++w) {
-                    const unsigned long long nb = s.adj[b * W + w] & unv[w];
-                    unv[w] &= ~nb;
-                    fr[w] |= nb;
+    // connected components by min-label propagation with pointer jumping: comp[a] -> lowest member of a's component
+    for (;;) {
+        if (tid == 0) s.misc[4] = 0;
+        __syncthreads();
+        for (int a = tid; a < n; a += nt) {
+            int best = s.comp[a];
+            for (int w = 0; w < W; ++w) {
+                unsigned long long m = s.adj[a * W + w];
+                while (m) {
+                    const int b = w * 64 + __ffsll((long long)m) - 1;
+                    m &= m - 1;
+                    best = min(best, (int)s.comp[b]);
                 }
             }
-            s.csize[nc++] = (int16_t)size;
+            best = min(best, (int)s.comp[best]);
+            if (best < s.comp[a]) { s.comp[a] = (int16_t)best; s.misc[4] = 1; }
         }
-        // target list in the reference's order: labels by first appearance; the noise label expands to its points
+        __syncthreads();
+        const bool changed = s.misc[4] != 0;
+        __syncthreads();
+        if (!changed) break;
+    }
+    for (int a = tid; a < n; a += nt) atomicAdd(&s.csize[s.comp[a]], 1);
+    __syncthreads();
+    if (tid == 0) {
+        // target list in the reference's order: labels by first appearance (a cluster first appears at its lowest
+        // member); the noise label expands to all its points where it first appears
         int ntg = 0;
         bool noise_done = false;
-        unsigned long long seen[4] = {0, 0, 0, 0};
         for (int a = 0; a < n && ntg < K; ++a) {
-            const int k = s.comp[a];
-            if (s.csize[k] >= 2) {
-                if ((seen[k >> 6] >> (k & 63)) & 1ull) continue;
-                seen[k >> 6] |= 1ull << (k & 63);
-                s.tsrc[ntg++] = (int16_t)k;
+            const int r = s.comp[a];
+            if (s.csize[r] >= 2) {
+                if (r == a) s.tsrc[ntg++] = (int16_t)r;
             } else if (!noise_done) {
                 noise_done = true;
                 for (int b = a; b < n && ntg < K; ++b)
@@ -378,53 +449,90 @@ __global__ void __launch_bounds__(kPlanThreads) k_plan(const Params P, const Pla
         } else {
             s.tx[t] = s.gx[s.gidx[~src]]; s.ty[t] = s.gy[s.gidx[~src]];
         }
+        int cntk = 0;  // team sizes for the member lists
+        for (int w = 0; w < AW; ++w) cntk += __popc(s.lmask[t * AW + w]);
+        s.cnt[t] = cntk;
     }
-    // member lists per team (attacker index order)
+    __syncthreads();
+    // ---- team -> target (:153-157): distances centroid <-> target, then the assignment by warp 0
+    for (int q = tid; q < K * K; q += nt) {
+        const int r = q / K, cc = q - r * K;
+        const double dx = s.tx[cc] - s.cx[r], dy = s.ty[cc] - s.cy[r];
+        s.c1[q] = sqrt(dx * dx + dy * dy);
+    }
     if (tid == 0) {
         int o = 0;
-        for (int k = 0; k < K; ++k) {
-            s.toff[k] = (int16_t)o;
-            for (int a = 0; a < A; ++a)
-                if (s.lab[a] == k) s.mem[o++] = (int16_t)a;
-        }
+        for (int k = 0; k < K; ++k) { s.toff[k] = (int16_t)o; o += s.cnt[k]; }
         s.toff[K] = (int16_t)o;
     }
     __syncthreads();
-    const int m8 = align_up(M * 8, 16) / 8, m2 = align_up(M * 2, 16) / 2, m1 = align_up(M, 16), a8 = align_up(A * 8, 16) / 8;
-    double *u = s.hu + warp * m8, *v = s.hv + warp * m8, *minv = s.hminv + warp * m8;
-    int16_t *hp = s.hp + warp * m2, *hway = s.hway + warp * m2, *hcol = s.hcol + warp * m2;
-    uint8_t *used = s.hused + warp * m1;
-    // ---- team -> target (:153-157): assignment on the euclidean distances centroid <-> target
-    if (warp == 0) {
-        auto cost1 = [&](int r, int cc) {
-            const double dx = s.tx[cc] - s.cx[r], dy = s.ty[cc] - s.cy[r];
-            return sqrt(dx * dx + dy * dy);
-        };
-        assign_warp(cost1, K, K, u, v, minv, hp, hway, used, s.team_target);
+    if ((tid >> 5) == 0) {
+        const double *c1 = s.c1;
+        auto cost1 = [c1, K](int r, int cc) { return c1[r * K + cc]; };
+        assign_warp(cost1, K, K, s.hu, s.hv, s.hminv, s.hp, s.hway, s.hused, s.team_target);
+    } else {
+        // meanwhile the other warps lay out the member lists (attacker index order inside a team)
+        for (int k = tid - 32; k < K; k += nt - 32) {
+            int o = s.toff[k];
+            for (int w = 0; w < AW; ++w) {
+                uint32_t m = s.lmask[k * AW + w];
+                while (m) {
+                    const int a = w * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    s.mem[o] = (int16_t)a; s.tof[o] = (int16_t)k; ++o;
+                }
+            }
+        }
     }
     __syncthreads();
-    // ---- member -> ring slot (:160-184): one warp per team
-    double *sx = s.sx + warp * a8, *sy = s.sy + warp * a8;
-    for (int key = warp; key < K; key += (nt >> 5)) {
-        const int off = s.toff[key], nm = s.toff[key + 1] - off;
-        if (nm == 0) continue;
-        const double delta = kPi / nm - 1;
-        const double lx = s.tx[s.team_target[key]], ly = s.ty[s.team_target[key]];
-        for (int j = lane; j < nm; j += 32) { sx[j] = lx + 0.8 * cos(delta * j); sy[j] = ly + 0.8 * sin(delta * j); }
-        __syncwarp();
-        auto cost2 = [&](int i, int j) {
-            const double dx = s.ax[s.mem[off + i]] - sx[j], dy = s.ay[s.mem[off + i]] - sy[j];
-            return sqrt(dx * dx + dy * dy);
-        };
-        assign_warp(cost2, nm, nm, u, v, minv, hp, hway, used, hcol);
-        for (int i = lane; i < nm; i += 32) {
-            const int a = s.mem[off + i];
-            if (!s.aalive[a]) continue;
-            double fx = -s.ax[a] + sx[hcol[i]], fy = -s.ay[a] + sy[hcol[i]];
-            if (c.disable_red_function) { fx = -fx; fy = -fy; }
-            out[a] = make_double2(fx, fy);
+    // ---- ring slots (:160-170), by list position
+    for (int i = tid; i < A; i += nt) {
+        const int k = s.tof[i], nm = s.cnt[k], j = i - s.toff[k];
+        const double delta = kPi / nm - 1;  // (float)(np.pi / len(team_agents) - 1) :163
+        const int tg = s.team_target[k];
+        s.sx[i] = s.tx[tg] + 0.8 * cos(delta * j);
+        s.sy[i] = s.ty[tg] + 0.8 * sin(delta * j);
+    }
+    __syncthreads();
+    // ---- member -> slot (:171-173): teams of up to kSerialTeam members get one thread each (spread over the warps),
+    // larger ones a whole warp
+    {
+        const int nw = nt >> 5, k = (tid & 31) * nw + (tid >> 5);
+        const double *ax = s.ax, *ay = s.ay;
+        if ((tid & 31) * nw < K && k < K && s.cnt[k] > 0 && s.cnt[k] <= kSerialTeam) {
+            const int off = s.toff[k], nm = s.cnt[k], ho = off + k;
+            const double *sx = s.sx + off, *sy = s.sy + off;
+            const int16_t *mem = s.mem + off;
+            auto cost2 = [=](int i, int j) {
+                const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];
+                return sqrt(dx * dx + dy * dy);
+            };
+            assign_serial(cost2, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
+                          s.hcol + off);
         }
         __syncwarp();
+        for (int kk = tid >> 5; kk < K; kk += nw) {  // warp-uniform
+            if (s.cnt[kk] <= kSerialTeam) continue;
+            const int off = s.toff[kk], nm = s.cnt[kk], ho = off + kk;
+            const double *sx = s.sx + off, *sy = s.sy + off;
+            const int16_t *mem = s.mem + off;
+            auto cost2 = [=](int i, int j) {
+                const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];
+                return sqrt(dx * dx + dy * dy);
+            };
+            assign_warp(cost2, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
+                        s.hcol + off);
+        }
+    }
+    __syncthreads();
+    // ---- forces (:175-188)
+    for (int i = tid; i < A; i += nt) {
+        const int a = s.mem[i];
+        if (!s.aalive[a]) continue;
+        const int slot = s.toff[s.tof[i]] + s.hcol[i];
+        double fx = -s.ax[a] + s.sx[slot], fy = -s.ay[a] + s.sy[slot];
+        if (c.disable_red_function) { fx = -fx; fy = -fy; }
+        out[a] = make_double2(fx, fy);
     }
 }
 

@@ -120,11 +120,11 @@ class DcaVecEnv(object):
         return out
 
     def step(self, actions, att_force=None, skip=None, rng_words=None, autoreset=True):
-        """actions int32 [E,G]; att_force float64 [E,A,2] (None -> centroid stand-in planner);
+        """actions int32 [E,G]; att_force float64 [E,A,2] (None -> the scripted attacker planner, plan());
         skip uint8 [E]; rng_words int32/uint32-as-int32 [E,G,2,12].  Returns (obs, reward, done, win) views."""
         self._check_tensor(actions, torch.int32, (self.E, self.G), 'actions')
         if att_force is None:
-            att_force = self.plan_centroid()
+            att_force = self.plan()
         else:
             self._check_tensor(att_force, torch.float64, (self.E, self.A, 2), 'att_force')
         if skip is not None:
@@ -194,7 +194,8 @@ class DcaSuperpoolEnv(object):
     info object[E] of dict).  info = {} | {'win': bool}; on done also 'obs-echo' (terminal obs [G,192]) and
     'others' (reset info).  The returned obs of a done env is the post-reset obs (shm_env.py:51-66).
     A skipped env returns its previous (ob, reward, done, info) (shm_env.py:37-41).
-    Attacker forces come from `planner` (callable(env) -> f64 cuda [E,A,2]) or the centroid stand-in.
+    Attacker forces come from the scripted planner kernel (DcaVecEnv.plan, cheat_script_ai.py:19-194), as in the
+    reference where World.step runs it (core.py:189-196), or from `planner` (callable(env) -> f64 cuda [E,A,2]).
     """
 
     def __init__(self, process_pool=None, env_args_dict_list=None, spaces=None, n_env=None, scfg=None,

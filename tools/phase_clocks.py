@@ -28,7 +28,7 @@ def main(steps=120, E=4096):
         act = torch.randint(0, 7, (E, env.G), generator=g, device=env.device, dtype=torch.int32)
         on = t >= steps - 20
         env.lib.dca_debug_phase_clocks(env.handle, C.c_void_p(prof.data_ptr()) if on else None)
-        env.step(act, None)
+        env.step(act, env.plan_centroid())
         if on:
             c = prof.cpu().numpy().astype(np.float64)
             acc += np.diff(c[:, :12], axis=1).mean(0)
