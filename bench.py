@@ -26,6 +26,18 @@ SEED = 20240
 # algorithmic bytes per env-step, 50v50 = obs 38400 + state r/w 12000 + actions 200 +
 # attacker force 800 + reward 200 + done/win/alive 102
 BYTES_PER_ENV_STEP = 38400 + 12000 + 200 + 800 + 200 + 102
+SCENARIOS = {  # BASELINE.json configs: [1] 50v50 (default, the headline), [2] 100v100, [3] 50 RL vs 55 scripted
+    '50v50': {},
+    '100v100': dict(num_guards=100, num_attackers=100),
+    '50v55': dict(num_guards=50, num_attackers=55, terrain_parameters=[0.15, 0.2], REWARD_DEBUG=True, REWARD_DEBUG_Value=3),
+}
+
+
+def bytes_per_env_step(G, A):
+    """obs G*768 + state r/w 2*N*60 + actions G*4 + attacker force A*16 + reward G*4 +
+    done/win 2 + alive N."""
+    N = G + A
+    return G * 768 + 2 * N * 60 + G * 4 + A * 16 + G * 4 + 2 + N
 # SURVEY.md section 8(d), gather kernel (k_observe): obs G*768 + state read N*57
 GATHER_BYTES_PER_ENV = 50 * 768 + 100 * 57
 FALLBACK_HBM_GBS = 6650.0
@@ -240,6 +252,23 @@ def run_ours(args):
     g1.record(stream)
     torch.cuda.synchronize()
     ms_gather = g0.elapsed_time(g1) / Kg
+    # ---- GAE / return kernel over a rollout buffer [T,E,G] (21 B per (t, env, guard))
+    from hmp2g_b200.gae import gae_return
+    T = 180 if E * G * 180 * 21 < 8e9 else 45
+    r_buf = torch.rand((T, E, G), device=dev)
+    v_buf = torch.rand((T, E, G), device=dev)
+    d_buf = (torch.rand((T, E, G), device=dev) < 0.2).to(torch.uint8)
+    for _ in range(2):
+        gae_return(r_buf, v_buf, d_buf)
+    g0.record(stream)
+    for _ in range(5):
+        gae_return(r_buf, v_buf, d_buf)
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_gae = g0.elapsed_time(g1) / 5
+    gae_bytes = T * E * G * (4 + 4 + 1 + 4 + 4)  # reward, value, dead in; return, threat out
+    del r_buf, v_buf, d_buf
+
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
     torch.cuda.empty_cache()
@@ -282,17 +311,19 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     peak, peak_src = measured_peak()
-    algo_bytes = BYTES_PER_ENV_STEP * E
+    algo_bytes = bytes_per_env_step(G, A) * E
+    gather_bytes = (G * 768 + N * 57) * E
     ncu = ncu_traffic()
     traffic = args.traffic if args.traffic is not None else (
-        ncu.get('k_step_dram_bytes_per_launch') if E == ncu.get('envs_per_gpu') else None)
+        ncu.get('k_step_dram_bytes_per_launch') if (E == ncu.get('envs_per_gpu') and args.scenario == '50v50') else None)
     achieved = algo_bytes / (ms_step_kernel * 1e-3) / 1e9
     line = {
         'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s', 'n_gpus': world, 'steps': K,
         'warmup': W, 'ms_per_step': ms_total / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': 'DCA 50v50 step+obs+autoreset, %d envs/GPU, injected random guard actions, '
-                               'centroid planner stand-in (BASELINE.json configs[1])' % E,
+        'config': {'workload': 'DCA %dv%d step+obs+autoreset, %d envs/GPU, injected random guard actions, '
+                               'centroid planner stand-in (BASELINE.json configs[1]%s)'
+                               % (G, A, E, '' if args.scenario == '50v50' else ' at another team size'),
                    'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD,
                    'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
                          '> 126 MB L2' % ((E * (G * 768 + 2 * 5760)) / 1e6, E * G * 768 / 1e6, 2 * E * 5760 / 1e6),
@@ -303,10 +334,13 @@ def run_ours(args):
                      'algorithmic_bytes_per_launch': algo_bytes, 'kernel_ms': ms_step_kernel,
                      'traffic_source': ncu.get('source')},
         'roofline_gather_kernel': {'bound': 'hbm', 'kernel': 'k_observe', 'unit': 'GB/s', 'peak': peak,
-                                   'achieved': GATHER_BYTES_PER_ENV * E / (ms_gather * 1e-3) / 1e9,
-                                   'frac': GATHER_BYTES_PER_ENV * E / (ms_gather * 1e-3) / 1e9 / peak,
-                                   'algorithmic_bytes_per_launch': GATHER_BYTES_PER_ENV * E, 'kernel_ms': ms_gather,
+                                   'achieved': gather_bytes / (ms_gather * 1e-3) / 1e9,
+                                   'frac': gather_bytes / (ms_gather * 1e-3) / 1e9 / peak,
+                                   'algorithmic_bytes_per_launch': gather_bytes, 'kernel_ms': ms_gather,
                                    'traffic': ncu.get('k_observe_dram_bytes_per_launch')},
+        'gae_kernel': {'bound': 'hbm', 'kernel': 'k_gae', 'unit': 'GB/s',
+                       'shape_TEG': [T, E, G], 'kernel_ms': ms_gae, 'achieved': gae_bytes / (ms_gae * 1e-3) / 1e9,
+                       'peak': peak, 'frac': gae_bytes / (ms_gae * 1e-3) / 1e9 / peak},
         'e2e': {'value': e2e_value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy actions in; planner + step on device; numpy '
                                     'obs/reward/done/info out)'},
@@ -330,6 +364,7 @@ def run_ours(args):
 
 
 def main():
+    global WORKLOAD
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=int(os.environ.get('WORLD_SIZE', '1')))
     ap.add_argument('--steps', type=int, default=1800)
@@ -340,7 +375,10 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--traffic', type=float, default=None,
                     help='dram bytes per k_step launch from the committed ncu --set full capture (profiles/)')
+    ap.add_argument('--scenario', default='50v50', choices=sorted(SCENARIOS),
+                    help='50v50 = BASELINE.json configs[1] (the headline); the others are extra report lines')
     args = ap.parse_args()
+    WORKLOAD = dict(WORKLOAD, **SCENARIOS[args.scenario])
     args.warmup = max(args.warmup, 3)
     if args.impl == 'reference':
         run_reference_arm(args)

@@ -7,7 +7,7 @@ reference's Python interfaces.  No CPU fallback exists.
 from .config import ChainVar, GlobalConfig, ScenarioConfig, inject, load_jsonc  # noqa: F401
 
 __all__ = ['ChainVar', 'GlobalConfig', 'ScenarioConfig', 'inject', 'load_jsonc', 'DcaVecEnv', 'DcaSuperpoolEnv',
-           'make_parallel_envs', 'gae_return']
+           'make_parallel_envs', 'gae_return', 'DeviceRollout']
 
 
 def __getattr__(name):  # torch is imported lazily so that config-only users do not pay for it
@@ -17,4 +17,7 @@ def __getattr__(name):  # torch is imported lazily so that config-only users do 
     if name in ('gae_return', 'normalized_advantage'):
         from . import gae
         return getattr(gae, name)
+    if name == 'DeviceRollout':
+        from . import rollout
+        return rollout.DeviceRollout
     raise AttributeError(name)

@@ -33,7 +33,7 @@ class DcaState(C.Structure):
 
 EXPORTS = ('dca_abi_version', 'dca_last_error', 'dca_create', 'dca_destroy', 'dca_bind_buffers', 'dca_reset',
            'dca_step', 'dca_observe', 'dca_plan', 'dca_plan_centroid', 'dca_export_state', 'dca_import_state', 'dca_gae',
-           'dca_kernel_launches', 'dca_debug_phase_clocks')
+           'dca_kernel_launches', 'dca_debug_phase_clocks', 'dca_set_option')
 
 _lib = None
 
@@ -65,6 +65,7 @@ def load(build_if_missing=False):
     lib.dca_observe.argtypes = [_P, _P, _P]
     lib.dca_plan_centroid.argtypes = [_P, _P, _P]
     lib.dca_plan.argtypes = [_P, _P, _P, _P, _P]
+    lib.dca_set_option.argtypes = [_P, C.c_int, C.c_int]
     lib.dca_export_state.argtypes = [_P, C.POINTER(DcaState), _P]
     lib.dca_import_state.argtypes = [_P, C.POINTER(DcaState), _P]
     lib.dca_gae.argtypes = [_P, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, _P]

@@ -287,6 +287,12 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
     return DCA_OK;
 }
 
+int dca_set_option(DcaHandle *h, int option, int value) {
+    if (!h) return DCA_E_INVALID;
+    if (option == DCA_OPT_EMPTY_ROWS_NAN) { h->P.empty_nan = value != 0; return DCA_OK; }
+    return fail(h, DCA_E_INVALID, "dca_set_option: unknown option");
+}
+
 int dca_debug_phase_clocks(DcaHandle *h, uint64_t *clocks) {
     if (!h) return DCA_E_INVALID;
     h->P.prof = (unsigned long long *)clocks;

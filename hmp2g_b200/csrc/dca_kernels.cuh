@@ -127,12 +127,17 @@ __device__ __forceinline__ double terrain_at(const DcaConfig &c, double X, doubl
 }
 
 // Padding slots of the float32 position lists (+inf) and the all-zero table row; once per kernel.
-__device__ __forceinline__ void init_pads(const Smem &s, const BlobLayout &L) {
+__device__ __forceinline__ void init_pads(const Smem &s, const BlobLayout &L, const Params &P) {
     const int t = threadIdx.x;
     const int ng = list_pad(L.G) - L.G, na = list_pad(L.A) - L.A;  // 1..4 each
     if (t < ng) { s.xg[L.G + t] = CUDART_INF_F; s.yg[L.G + t] = CUDART_INF_F; }
     else if (t < ng + na) { s.xa[L.A + t - ng] = CUDART_INF_F; s.ya[L.A + t - ng] = CUDART_INF_F; }
-    else if (t < ng + na + 4) s.table[(t - ng - na) * (L.N + 1) + L.N] = make_float4(0.f, 0.f, 0.f, 0.f);
+    else if (t < ng + na + 4) {
+        // the conc / conc_4hist policies turn all-zero rows into NaN first thing (ALGORITHM/conc/shell_env.py:72-75):
+        // with DCA_OPT_EMPTY_ROWS_NAN the kernel hands them over that way
+        const float z = P.empty_nan ? __int_as_float(0x7fc00000) : 0.f;
+        s.table[(t - ng - na) * (L.N + 1) + L.N] = make_float4(z, z, z, z);
+    }
 }
 
 // float32 position of agent i in its team list (distance matrix input; dead = +inf)
@@ -315,7 +320,7 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
         return;
     }
     if (!prebuilt) {
-        init_pads(s, L);
+        init_pads(s, L, P);
         for (int i = tid; i < L.N; i += nt) build_row(s, L, i);
         __syncthreads();
     }
@@ -593,7 +598,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     const int nG0 = s.sc->n_alive_guards, nA0 = s.sc->n_alive_attackers, ts = s.sc->time_step;
     const uint32_t obs_counter = s.sc->obs_counter;
     if (tid < 4) s.misc[tid] = 0;
-    init_pads(s, L);
+    init_pads(s, L, P);
     // phase A: terrain (core.py:224-234), clear hit flags (core.py:239-242), float32 position lists of the pre-move
     // state.  (Action decode and the injected planner force are read where they are used, in phase D.)
     for (int i = tid; i < L.N; i += nt) {
@@ -942,11 +947,10 @@ __global__ void k_gae(const float *__restrict__ reward, const float *__restrict_
     double carry = 0, gae = 0, th = -1;
     float v_next = 0.f;
     int d_next = 0;
-    for (int i = Lc - 1; i >= 0; --i) {
+    // one backward step of the scan (numpy's dtype walk: gamma*V[t+1] in f32, delta / gae in f64, f32 stores)
+    auto step = [&](int i, float rw, float vf, int d) {
         const size_t k = (size_t)i * S + c;
-        const int d = dead[k] != 0;
-        const float vf = value[k];
-        double r = (double)reward[k] + carry;
+        double r = (double)rw + carry;
         if (i > 0) {
             carry = r * (double)d;
             r = r * (double)(!d);
@@ -965,6 +969,24 @@ __global__ void k_gae(const float *__restrict__ reward, const float *__restrict_
         }
         ret[k] = (float)(gae + v);
         v_next = vf; d_next = d;
+    };
+    // the recurrence is serial in time but its inputs are not: fetch kU time steps ahead of the dependent chain
+    constexpr int kU = 8;
+    int i = Lc - 1;
+    for (; i >= kU - 1; i -= kU) {
+        float rw[kU], vf[kU];
+        int dd[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const size_t k = (size_t)(i - u) * S + c;
+            rw[u] = reward[k]; vf[u] = value[k]; dd[u] = dead[k] != 0;
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) step(i - u, rw[u], vf[u], dd[u]);
+    }
+    for (; i >= 0; --i) {
+        const size_t k = (size_t)i * S + c;
+        step(i, reward[k], value[k], dead[k] != 0);
     }
 }
 

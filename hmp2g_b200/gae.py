@@ -23,9 +23,11 @@ def gae_return(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_
     assert dead.shape == reward.shape
     if traj_len is not None:
         assert traj_len.dtype == torch.int32 and traj_len.shape == (E,) and traj_len.is_cuda
-    ret = torch.zeros_like(reward)
-    threat = torch.zeros_like(reward)
-    pushed = torch.zeros_like(reward) if want_pushed else None
+    # full-length trajectories overwrite every element; ragged ones leave rows >= traj_len at zero
+    alloc = torch.empty_like if traj_len is None else torch.zeros_like
+    ret = alloc(reward)
+    threat = alloc(reward)
+    pushed = alloc(reward) if want_pushed else None
     stream = C.c_void_p(torch.cuda.current_stream(reward.device).cuda_stream)
     with torch.cuda.device(reward.device):
         _lib.check(lib.dca_gae(_ptr(reward), _ptr(value), _ptr(dead), _ptr(traj_len), _ptr(ret), _ptr(threat),

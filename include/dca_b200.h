@@ -130,6 +130,12 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
             float *ret, float *threat, float *reward_pushed, int T, int E, int G,
             double gamma, double tau, int threat_limit, dca_stream_t stream);
 
+/* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a
+ * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
+ * it (ALGORITHM/conc/shell_env.py:72-75); default 0 = the env's own zeros (collective_assault_env.py:313-316,340-343). */
+#define DCA_OPT_EMPTY_ROWS_NAN 1
+int dca_set_option(DcaHandle *h, int option, int value);
+
 const char *dca_last_error(const DcaHandle *h); /* host string; h may be NULL for create/gae errors */
 int dca_kernel_launches(const DcaHandle *h, int64_t *count); /* kernels launched through this handle so far */
 /* Diagnostics: u64[E,16] device buffer receiving clock64() of thread 0 at the phase boundaries of the next

@@ -294,3 +294,52 @@ def test_cuda_gae_matches_reference_and_oracle():
     assert np.array_equal(ret.cpu().numpy().view(np.uint32), o_ret.view(np.uint32))
     assert np.array_equal(thr.cpu().numpy(), o_thr)
     assert np.array_equal(push.cpu().numpy().astype(np.float64), o_push)
+
+
+def test_cuda_empty_rows_nan_option_and_device_rollout():
+    """(1) DCA_OPT_EMPTY_ROWS_NAN hands over exactly what ShellEnvWrapper makes of the env's observation
+    (ALGORITHM/conc/shell_env.py:72-75: all-zero rows -> NaN).  (2) DeviceRollout + dca_gae reproduce
+    trajectory.finalize (restated by the oracle's gae()) on the rewards / dead masks of a rollout with the native planner."""
+    torch = _torch()
+    from dca_oracle import gae as oracle_gae
+    from hmp2g_b200.rollout import DeviceRollout
+    from hmp2g_b200.vec_env import DcaVecEnv
+    cfg = dict(num_guards=50, num_attackers=50, random_jam_prob=0.05, introduce_terrain=True,
+               terrain_parameters=[0.05, 0.2], MaxEpisodeStep=50, init_distance=2)
+    E, T = 64, 50
+    plain = make_gpu_env(cfg, E, seed=9, gid0=0, debug=False)
+    nan_env = DcaVecEnv(E, scfg=scenario_from_dict(cfg), seed=9, env_gid0=0, empty_rows_nan=True)
+    plain.reset(); nan_env.reset()
+    roll = DeviceRollout(nan_env, horizon=T)
+    gen = torch.Generator(device=plain.device); gen.manual_seed(4)
+    rec_r, rec_v, rec_d = [], [], []
+    finished_any = torch.zeros((E,), dtype=torch.bool, device=plain.device)
+    for t in range(T):
+        act = torch.randint(0, 7, (E, 50), generator=gen, device=plain.device, dtype=torch.int32)
+        alive_before = roll.alive_guards().clone()
+        value = torch.rand((E, 50), generator=gen, device=plain.device)
+        force = plain.plan().clone()
+        plain.step(act, force)
+        nan_env.step(act, force)
+        o0, o1 = plain.obs.view(E, 50, 12, 16), nan_env.obs.view(E, 50, 12, 16)
+        want = torch.where((o0 == 0).all(-1, keepdim=True), torch.full_like(o0, float('nan')), o0)
+        assert torch.equal(torch.isnan(o1), torch.isnan(want)) and torch.equal(torch.nan_to_num(o1), torch.nan_to_num(want)), t
+        assert torch.equal(plain.reward, nan_env.reward) and torch.equal(plain.done, nan_env.done)
+        if t == 0 or finished_any.any():
+            pass
+        finished_any |= roll.add(alive_before, value, nan_env.reward, nan_env.done)
+        rec_r.append(nan_env.reward.cpu().numpy().copy()); rec_v.append(value.cpu().numpy().copy())
+        rec_d.append((alive_before == 0).cpu().numpy().copy())
+        if bool(nan_env.done.any()):
+            break
+    # every env finalized as a (possibly truncated) trajectory of the steps collected so far
+    n = len(rec_r)
+    ret, threat, adv, valid = roll.finalize()
+    r = np.stack(rec_r).astype(np.float64); v = np.stack(rec_v); d = np.stack(rec_d)
+    want_ret, want_thr, _ = oracle_gae(r, v, d, traj_len=None)
+    np.testing.assert_allclose(ret[:n].cpu().numpy(), want_ret, rtol=1e-6, atol=1e-6)
+    assert np.array_equal(threat[:n].cpu().numpy(), want_thr)
+    assert bool(valid[:n].all()) and not bool(valid[n:].any())
+    a = adv[:n].cpu().numpy()
+    assert abs(a.mean()) < 1e-3 and abs(a.std() - 1) < 1e-2
+    assert int(roll.length.sum()) == 0
