@@ -34,7 +34,10 @@ struct Smem {
     int16_t *sid;          // [G,12] entity id per obs row, -1 = zero row          } the laser work lists are dead
     int16_t *shooters;     // [N] agents that may hit something this step           } before the observation pass
     uint32_t *pairs;       // [kPairCap] (shooter << 16 | target) laser candidates  } writes sid: same bytes
-    int32_t *misc;         // [0] guard deaths, [1] attacker deaths, [2] #shooters, [3] #pairs
+    int16_t *alist;        // [N] agents alive at the start of the step, index order (guards first)
+    int16_t *glist;        // [G] guards alive for the observation pass (any order)
+    int32_t *misc;         // [0] guard deaths, [1] attacker deaths, [2] #shooters, [3] #pairs, [4] #alist, [5] alive
+                           // guards in alist, [6] #glist, [8..15] per-warp counts of the compaction
     uint64_t *bar;
 };
 
@@ -45,7 +48,8 @@ __host__ __device__ constexpr int smem_bytes(const BlobLayout &L) {
     o += (L.N + 1) * kObsRow * 4;                   // table
     const int a = align_up(L.G * kObsRows * 2, 16), b = align_up(L.N * 2, 16) + kPairCap * 4;
     o += a > b ? a : b;                             // sid | shooters + pairs
-    o += 32;                                        // misc
+    o += align_up(L.N * 2, 16) + align_up(L.G * 2, 16);  // alist glist
+    o += 64;                                        // misc
     o += 16;                                        // mbarrier
     return o;
 }
@@ -74,7 +78,9 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
         s.pairs = (uint32_t *)(p + align_up(L.N * 2, 16));
         p += a > b ? a : b;
     }
-    s.misc = (int32_t *)p; p += 32;
+    s.alist = (int16_t *)p; p += align_up(L.N * 2, 16);
+    s.glist = (int16_t *)p; p += align_up(L.G * 2, 16);
+    s.misc = (int32_t *)p; p += 64;
     s.bar = (uint64_t *)p;
     return s;
 }
@@ -145,6 +151,33 @@ __device__ __forceinline__ void put_xy(const Smem &s, const BlobLayout &L, int i
     const float lx = alive ? x : CUDART_INF_F, ly = alive ? y : CUDART_INF_F;
     if (i < L.G) { s.xg[i] = lx; s.yg[i] = ly; }
     else { s.xa[i - L.G] = lx; s.ya[i - L.G] = ly; }
+}
+
+
+// Index-ordered list of the alive agents in [lo, hi): list[0..n), returns n (to every thread).
+// Warps that hold no alive agent then issue nothing in the loops over the list -- dead agents cost no issue slots.
+// CTA-wide; ends with a barrier (the list is visible to everyone on return).
+__device__ __forceinline__ int compact_alive(const Smem &s, int lo, int hi, int16_t *list) {
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
+    int base = 0;
+    for (int r0 = lo; r0 < hi; r0 += nt) {  // uniform
+        const int i = r0 + tid;
+        const bool alive = i < hi && (s.flags[i] & F_ALIVE);
+        const uint32_t b = __ballot_sync(0xffffffffu, alive);
+        if (r0 != lo) __syncthreads();  // the previous round's counts have been read
+        if (lane == 0) s.misc[8 + warp] = __popc(b);
+        __syncthreads();
+        int off = base, tot = 0;
+        for (int w = 0; w < nw; ++w) {
+            const int cw = s.misc[8 + w];
+            off += w < warp ? cw : 0;
+            tot += cw;
+        }
+        if (alive) list[off + __popc(b & ((1u << lane) - 1u))] = (int16_t)i;
+        base += tot;
+    }
+    __syncthreads();
+    return base;
 }
 
 // Entity record of agent i, collective_assault_env.py:237-276: [alive,x,y,atk_rad,vx,vy,iden,terrain,bit0..bit7] as
@@ -319,38 +352,32 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
         if (tid == 0) s.sc->obs_counter = counter;  // callers have synchronised since every thread read the old value
         return;
     }
+    int n_obs_guards = s.misc[6];  // prebuilt: the caller's list of guards alive now
     if (!prebuilt) {
         init_pads(s, L, P);
         for (int i = tid; i < L.N; i += nt) build_row(s, L, i);
+        for (int t = tid; t < L.G * kObsRows; t += nt) s.sid[t] = -1;  // dead guards: zeros (:313-316), no RNG draws
         __syncthreads();
+        n_obs_guards = compact_alive(s, 0, L.G, s.glist);
     }
     DCA_PROF(P, e, prof_slot);
 
     const uint32_t k0 = (uint32_t)P.cfg.seed, k1 = (uint32_t)(P.cfg.seed >> 32);
     const uint32_t gid = (uint32_t)(P.cfg.env_gid0 + e);
-    // One task per (guard, list): 2G tasks dealt out evenly over the CTA's warps (a warp lives on one SM
-    // sub-partition; a plain thread-per-guard mapping would leave half of the sub-partitions idle here).
-    const int ntask = 2 * L.G, nwarp = nt >> 5, quota = (ntask + nwarp - 1) / nwarp;
-    for (int o = tid & 31; o < quota; o += 32) {
-        const int task = (tid >> 5) * quota + o;
-        if (task >= ntask) break;
-        const int g = task >> 1, lst = task & 1;  // 0 = hostile (:318-328), 1 = friend (:330-342)
+    // One task per (alive guard, list), packed densely over the threads: warps beyond the last task issue nothing.
+    // (Dead guards' rows were preset to "empty"; their hints are not needed before the next reset rewrites them.)
+    for (int task = tid; task < 2 * n_obs_guards; task += nt) {
+        const int g = s.glist[task >> 1], lst = task & 1;  // 0 = hostile (:318-328), 1 = friend (:330-342)
         int16_t *sid = s.sid + g * kObsRows + (lst == 0 ? kVisN : 0);  // friend rows 0..5, hostile rows 6..11 (:344)
         const int cnt = lst == 0 ? L.A : L.G;
-        if (!(s.flags[g] & F_ALIVE)) {  // :313-316 dead guard: zeros, no RNG draws
-#pragma unroll
-            for (int r = 0; r < kVisN; ++r) sid[r] = -1;
-            s.knn_ids[task] = 0x0101010101010101ull * (u64)cnt;
-            if (lst == 0) s.hmin[g] = 0.f;
-            continue;
-        }
+        const int hint_slot = 2 * g + lst;
         const int base = lst == 0 ? L.G : 0;
         int n = 0;
         u64 ids;
         float nearest;
         unsigned long long vis = knn_task(lst == 0 ? s.xa : s.xg, lst == 0 ? s.ya : s.yg, cnt, s.xg[g], s.yg[g],
-                                          s.knn_ids[task], P.smax[lst], P.idx_bits, &n, &ids, &nearest);
-        s.knn_ids[task] = ids;
+                                          s.knn_ids[hint_slot], P.smax[lst], P.idx_bits, &n, &ids, &nearest);
+        s.knn_ids[hint_slot] = ids;
         if (lst == 0) s.hmin[g] = nearest;
         int row = 0;
         if (lst == 1) {  // :334-335 self = first visible friend, excluded from shuffle / jamming
@@ -590,6 +617,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     const Smem s = carve(smem_raw, L);
     const int tid = threadIdx.x, nt = NT;
     DCA_PROF(P, e, 0);
+    if (tid < 16) s.misc[tid] = 0;  // ordered before any use by the barrier inside load_blob
     load_blob(s, P, L, e);
     DCA_PROF(P, e, 1);
 
@@ -597,20 +625,37 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     const double ct = s.sc->cos_theta, sn = s.sc->sin_theta;
     const int nG0 = s.sc->n_alive_guards, nA0 = s.sc->n_alive_attackers, ts = s.sc->time_step;
     const uint32_t obs_counter = s.sc->obs_counter;
-    if (tid < 4) s.misc[tid] = 0;
     init_pads(s, L, P);
-    // phase A: terrain (core.py:224-234), clear hit flags (core.py:239-242), float32 position lists of the pre-move
-    // state.  (Action decode and the injected planner force are read where they are used, in phase D.)
+    // phase A0: dead agents are settled here once (no position in the distance lists; justDied cleared, core.py:266-268
+    // -- nothing reads it before the reward, where a long-dead agent must show False); everything after this works on
+    // the compact index-ordered list of the agents alive at the start of the step (guards first).
     for (int i = tid; i < L.N; i += nt) {
         const uint8_t f = s.flags[i];
-        const bool alive = f & F_ALIVE;
-        const double x = s.px[i], y = s.py[i];
-        put_xy(s, L, i, alive, (float)x, (float)y);
         s.hitcnt[i] = 0; s.shots[i] = 0;
-        if (alive) {
-            s.ter[i] = terrain_at(c, x, y, ct, sn);
-            s.flags[i] = f & (uint8_t)~(F_HIT | F_WAS_HIT);
+        if (!(f & F_ALIVE)) {
+            put_xy(s, L, i, false, 0.f, 0.f);
+            s.flags[i] = f & (uint8_t)~F_JUST_DIED;
+            if (i >= L.G && P.out.nearest) P.out.nearest[(size_t)e * L.A + (i - L.G)] = -1;
         }
+    }
+    const int n_alive = compact_alive(s, 0, L.N, s.alist);
+    int n_alive_g = 0;  // alive guards = entries of alist below G (index order)
+    {
+        int lo = 0, hi = n_alive;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (s.alist[mid] < L.G) lo = mid + 1; else hi = mid;
+        }
+        n_alive_g = lo;
+    }
+    // phase A: terrain (core.py:224-234), clear hit flags (core.py:239-242), float32 position lists of the pre-move
+    // state.  (Action decode and the injected planner force are read where they are used, in phase D.)
+    for (int q = tid; q < n_alive; q += nt) {
+        const int i = s.alist[q];
+        const double x = s.px[i], y = s.py[i];
+        put_xy(s, L, i, true, (float)x, (float)y);
+        s.ter[i] = terrain_at(c, x, y, ct, sn);
+        s.flags[i] &= (uint8_t)~(F_HIT | F_WAS_HIT);
     }
     __syncthreads();
     DCA_PROF(P, e, 2);
@@ -622,11 +667,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     {
         const uint32_t im = (1u << P.idx_bits) - 1u;
         const int Gq = (L.G + 3) >> 2;
-        for (int t = tid; t < L.A; t += nt) {
-            const int i = L.G + t;
-            const bool alive = s.flags[i] & F_ALIVE;
+        for (int q = n_alive_g + tid; q < n_alive; q += nt) {
+            const int i = s.alist[q], t = i - L.G;
             int best = -1;
-            if (alive) {
+            {
                 const float pox = s.xa[t], poy = s.ya[t];
                 const u64 px2 = pack2(pox, pox), py2 = pack2(poy, poy);
                 const ulonglong2 *x4 = (const ulonglong2 *)s.xg, *y4 = (const ulonglong2 *)s.yg;
@@ -665,8 +709,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
         }
         // guards: hmin = lower bound of the squared distance to the nearest alive attacker, left by the last
         // observation pass (same positions, same alive set)
-        for (int g = tid; g < L.G; g += nt)
-            if ((s.flags[g] & F_ALIVE) && s.hmin[g] <= laser_r2f(s, c, g)) push_shooter(s, g);
+        for (int q = tid; q < n_alive_g; q += nt) {
+            const int g = s.alist[q];
+            if (s.hmin[g] <= laser_r2f(s, c, g)) push_shooter(s, g);
+        }
     }
     __syncthreads();
     DCA_PROF(P, e, 3);
@@ -711,11 +757,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     // phase D: deaths core.py:266-279, _set_action parallel_run.py:326-374 / planner force cheat_script_ai.py:183-184,
     // wall force core.py:210-222,339-353, integrate_state :282-302 (survivors only); then the agent's float32 entity
     // record and list position for the observation pass.
-    for (int i = tid; i < L.N; i += nt) {
-        uint8_t f = s.flags[i];
-        if (!(f & F_ALIVE)) {
-            s.flags[i] = f & (uint8_t)~F_JUST_DIED;
-        } else {
+    for (int q = tid; q < n_alive; q += nt) {
+        const int i = s.alist[q];
+        {
+            uint8_t f = s.flags[i];
             const int sh = s.shots[i];
             if (sh > 0) { f |= F_HIT; s.nhit[i] += sh; s.flags[i] = f; }
             const int hc = s.hitcnt[i];
@@ -723,6 +768,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
                 s.nwas[i] += hc;
                 s.flags[i] = (uint8_t)((f | F_WAS_HIT | F_JUST_DIED) & ~F_ALIVE);
                 atomicAdd(&s.misc[i < L.G ? 0 : 1], 1);
+                put_xy(s, L, i, false, 0.f, 0.f);  // gone from the distance lists of the observation pass
             } else {
                 double fx = 0, fy = 0, ar = 0;
                 if (i < L.G) {
@@ -758,9 +804,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
                 s.atk[i] = reg_angle(s.atk[i] + ar);
                 s.vx[i] = vx; s.vy[i] = vy;
                 s.px[i] = x + vx * dt; s.py[i] = y + vy * dt;
+                build_row(s, L, i);  // only alive entities are ever gathered into an observation
+                if (i < L.G) s.glist[atomicAdd(&s.misc[6], 1)] = (int16_t)i;
             }
         }
-        build_row(s, L, i);
     }
     __syncthreads();
     DCA_PROF(P, e, 5);
@@ -779,6 +826,11 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
         }
         if (c.reward_debug && done && win) r += (float)c.reward_debug_value;
         P.out.reward[(size_t)e * L.G + g] = r;
+        if (!(f & F_ALIVE)) {  // :313-316 dead guard: an observation of zeros (no RNG draws)
+            uint32_t *row = (uint32_t *)(s.sid + g * kObsRows);
+#pragma unroll
+            for (int k = 0; k < kObsRows / 2; ++k) row[k] = 0xFFFFFFFFu;
+        }
     }
     if (tid == 0) {
         s.sc->n_alive_guards = nG; s.sc->n_alive_attackers = nA;
