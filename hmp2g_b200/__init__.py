@@ -7,7 +7,7 @@ reference's Python interfaces.  No CPU fallback exists.
 from .config import ChainVar, GlobalConfig, ScenarioConfig, inject, load_jsonc  # noqa: F401
 
 __all__ = ['ChainVar', 'GlobalConfig', 'ScenarioConfig', 'inject', 'load_jsonc', 'DcaVecEnv', 'DcaSuperpoolEnv',
-           'make_parallel_envs', 'gae_return', 'DeviceRollout']
+           'make_parallel_envs', 'gae_return', 'DeviceRollout', 'DeviceRunner']
 
 
 def __getattr__(name):  # torch is imported lazily so that config-only users do not pay for it
@@ -20,4 +20,7 @@ def __getattr__(name):  # torch is imported lazily so that config-only users do 
     if name == 'DeviceRollout':
         from . import rollout
         return rollout.DeviceRollout
+    if name == 'DeviceRunner':
+        from . import runner
+        return runner.DeviceRunner
     raise AttributeError(name)

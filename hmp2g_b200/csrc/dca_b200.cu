@@ -10,6 +10,7 @@
 
 #include "dca_kernels.cuh"
 #include "dca_planner.cuh"
+#include "dca_runner.cuh"
 
 using namespace dca;
 
@@ -284,6 +285,49 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
         reward, value, dead, traj_len, ret, threat, reward_pushed, T, E, G, gamma, tau, threat_limit);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_gae: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_runner_init(const DcaRunnerState *s, int n_env, int n_agent, dca_stream_t stream) {
+    if (!s || !s->pause || !s->suffered || !s->cur_step || !s->ep_cnt || !s->reward_sum || !s->counters || !s->fin_slot ||
+        !s->log_meta || !s->log_reward || n_env <= 0 || n_agent <= 0 || s->log_capacity < n_env)
+        return fail(nullptr, DCA_E_INVALID, "dca_runner_init: null buffer, empty shape or log_capacity < n_env");
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaMemsetAsync(s->pause, 0, n_env, st);
+    cudaMemsetAsync(s->suffered, 1, n_env, st);
+    cudaMemsetAsync(s->cur_step, 0, sizeof(int32_t) * n_env, st);
+    cudaMemsetAsync(s->ep_cnt, 0, sizeof(int32_t) * n_env, st);
+    cudaMemsetAsync(s->reward_sum, 0, sizeof(double) * n_env * n_agent, st);
+    cudaMemsetAsync(s->counters, 0, sizeof(int64_t) * 8, st);
+    cudaMemsetAsync(s->fin_slot, 0, sizeof(int32_t) * n_env, st);
+    cudaMemsetAsync(s->log_meta, 0, sizeof(int64_t) * 4 * s->log_capacity, st);
+    cudaError_t e = cudaMemsetAsync(s->log_reward, 0, sizeof(double) * (size_t)s->log_capacity * n_agent, st);
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_runner_init: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_runner_update(const DcaRunnerState *s, int n_env, int n_agent, int align_episode, const uint8_t *done,
+                      const uint8_t *win, const float *reward, dca_stream_t stream) {
+    if (!s || !done || !win || !reward || n_env <= 0 || n_agent <= 0 || s->log_capacity < n_env)
+        return fail(nullptr, DCA_E_INVALID, "dca_runner_update: null argument, empty shape or log_capacity < n_env");
+    cudaStream_t st = (cudaStream_t)stream;
+    k_runner_scan<<<1, kRunnerThreads, 0, st>>>(*s, n_env, align_episode != 0, done, win);
+    const size_t n = (size_t)n_env * n_agent;
+    k_runner_rewards<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(*s, n_env, n_agent, reward);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_runner_update: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_runner_report(const DcaRunnerState *s, int n_agent, int64_t first_episode, int n_episodes,
+                      const int32_t *team_of_agent, int n_team, double *out, dca_stream_t stream) {
+    if (!s || !team_of_agent || !out || n_agent <= 0 || n_team <= 0 || first_episode < 1 || n_episodes <= 0 ||
+        n_episodes > s->log_capacity)
+        return fail(nullptr, DCA_E_INVALID, "dca_runner_report: bad window (1-based first episode, at most log_capacity)");
+    k_runner_report<<<1, 256, 0, (cudaStream_t)stream>>>(*s, n_agent, (long long)first_episode, n_episodes,
+                                                         team_of_agent, n_team, out);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_runner_report: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
 

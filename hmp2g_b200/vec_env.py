@@ -234,11 +234,33 @@ class DcaSuperpoolEnv(object):
         self._info_dirty = np.zeros((E,), dtype=bool)
         self._cold_start = True
         self._suffer_reset = np.zeros((E,), dtype=bool)
+        # the planner reads only the resident state, so the plan for step t+1 is computed right after step t on a
+        # second stream, under the device->host copy of step t's observations
+        self._plan_stream = torch.cuda.Stream(device=self.env.device)
+        self._plan_ready = None
         self.h2d_bytes = self._h_act.numel() * 4 + self._h_skip.numel()
         self.d2h_bytes = (self._h_obs.numel() + self._h_rew.numel()) * 4 + 2 * E
 
     def get_space(self):
         return {'obs_space': self.observation_space, 'act_space': self.action_space}
+
+    def _plan_ahead(self):
+        if self.planner is not None:
+            return
+        env = self.env
+        self._plan_stream.wait_stream(torch.cuda.current_stream(env.device))
+        with torch.cuda.stream(self._plan_stream):
+            env.plan()
+            self._plan_ready = torch.cuda.Event()
+            self._plan_ready.record(self._plan_stream)
+
+    def _take_plan(self):
+        """The force tensor planned ahead for the current state (None: nothing valid is in flight)."""
+        if self._plan_ready is None:
+            return None
+        torch.cuda.current_stream(self.env.device).wait_event(self._plan_ready)
+        self._plan_ready = None
+        return self.env._force
 
     def _fetch(self):
         env = self.env
@@ -253,10 +275,14 @@ class DcaSuperpoolEnv(object):
     def reset(self):
         if self._cold_start:  # EnvAutoReset.reset shm_env.py:82-93
             self._cold_start = False
+            self._take_plan()
             self.env.reset()
+            self._plan_ahead()
         elif not self._suffer_reset.all():
+            self._take_plan()  # the state changes under it: wait for the plan in flight, then drop it
             mask = torch.from_numpy((~self._suffer_reset).astype(np.uint8)).to(self.env.device)
             self.env.reset(mask)
+            self._plan_ahead()
         self._suffer_reset[:] = True
         self._fetch()
         info = np.empty((self.num_envs,), dtype=object)
@@ -275,8 +301,9 @@ class DcaSuperpoolEnv(object):
         self._h_act.numpy()[:] = np.where(np.isnan(actions), 0, actions).astype(np.int32)
         self._d_act.copy_(self._h_act, non_blocking=True)
         self._d_skip.copy_(self._h_skip, non_blocking=True)
-        force = self.planner(env) if self.planner is not None else None
+        force = self.planner(env) if self.planner is not None else self._take_plan()
         env.step(self._d_act, force, skip=self._d_skip)
+        self._plan_ahead()
         self._fetch()
         done = self._h_done.numpy().astype(bool)
         win = self._h_win.numpy().astype(bool)

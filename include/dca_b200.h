@@ -130,6 +130,35 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
             float *ret, float *threat, float *reward_pushed, int T, int E, int G,
             double gamma, double tau, int threat_limit, dca_stream_t stream);
 
+/* ---- runner bookkeeping on the device -----------------------------------------------------------------------------
+ * replaces: the per-env Python loop of task_runner.Runner.update_runner task_runner.py:95-138 (and its test-run twin
+ * update_test_runner :191-217): ENV-PAUSE / Env-Suffered-Reset / Current-Obs-Step / Latest-Reward-Sum /
+ * Thread-Episode-Cnt per env, current_n_frame / current_n_episode, and the Recent-Reward-Sum / Recent-Win lists,
+ * kept as an episode log indexed by global episode number (episodes are numbered in env-index order within a step, as
+ * the reference's loop appends them).  `pause` is the skip mask of the next dca_step (= the NaN action rows
+ * MMPlatform.act writes for paused envs, multi_team.py:62-66).  All arrays are caller-owned device buffers. */
+typedef struct DcaRunnerState {
+    uint8_t *pause;       /* [E] ENV-PAUSE */
+    uint8_t *suffered;    /* [E] Env-Suffered-Reset */
+    int32_t *cur_step;    /* [E] Current-Obs-Step */
+    int32_t *ep_cnt;      /* [E] Thread-Episode-Cnt */
+    double *reward_sum;   /* [E,G] Latest-Reward-Sum */
+    int64_t *counters;    /* [8]: 0 current_n_frame, 1 current_n_episode, 2 aligned restarts */
+    int32_t *fin_slot;    /* [E] scratch: -1 paused, 0 running, slot+1 = finished an episode logged at `slot` */
+    int64_t *log_meta;    /* [log_capacity,4]: env, win, steps, episode number (1-based) */
+    double *log_reward;   /* [log_capacity,G] reward sums of the logged episodes */
+    int32_t log_capacity; /* ring size: >= E + the longest window that is read back */
+} DcaRunnerState;
+/* init_runner (task_runner.py:77-93): zero everything, Env-Suffered-Reset = 1. */
+int dca_runner_init(const DcaRunnerState *s, int n_env, int n_agent, dca_stream_t stream);
+/* update_runner: done u8[E], win u8[E] (read where done), reward f32[E,G] of the step just taken. */
+int dca_runner_update(const DcaRunnerState *s, int n_env, int n_agent, int align_episode, const uint8_t *done,
+                      const uint8_t *win, const float *reward, dca_stream_t stream);
+/* _checkout_interested_agents (task_runner.py:231-275) over episodes first_episode .. first_episode+n_episodes-1:
+ * out f64[n_team+1] = mean episode reward of each team's agents (team_of_agent i32[G]), then the win rate. */
+int dca_runner_report(const DcaRunnerState *s, int n_agent, int64_t first_episode, int n_episodes,
+                      const int32_t *team_of_agent, int n_team, double *out, dca_stream_t stream);
+
 /* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a
  * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
  * it (ALGORITHM/conc/shell_env.py:72-75); default 0 = the env's own zeros (collective_assault_env.py:313-316,340-343). */

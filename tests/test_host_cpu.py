@@ -96,12 +96,13 @@ def test_c_abi_library_exports_every_declared_symbol():
 def test_abi_struct_layout_matches_header():
     """ctypes mirrors vs the sizes the C compiler gives include/dca_b200.h."""
     from hmp2g_b200 import _lib
-    src = '#include <stdio.h>\n#include "dca_b200.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(DcaConfig), sizeof(DcaBuffers), sizeof(DcaState));return 0;}'
+    src = '#include <stdio.h>\n#include "dca_b200.h"\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(DcaConfig), sizeof(DcaBuffers), sizeof(DcaState), sizeof(DcaRunnerState));return 0;}'
     exe = os.path.join(REPO, 'build', 'abi_sizes')
     os.makedirs(os.path.dirname(exe), exist_ok=True)
     subprocess.run(['gcc', '-x', 'c', '-', '-I', os.path.join(REPO, 'include'), '-o', exe], input=src.encode(), check=True)
     sizes = [int(x) for x in subprocess.check_output([exe]).split()]
-    assert sizes == [ctypes.sizeof(_lib.DcaConfig), ctypes.sizeof(_lib.DcaBuffers), ctypes.sizeof(_lib.DcaState)]
+    assert sizes == [ctypes.sizeof(_lib.DcaConfig), ctypes.sizeof(_lib.DcaBuffers), ctypes.sizeof(_lib.DcaState),
+                     ctypes.sizeof(_lib.DcaRunnerState)]
 
 
 def test_no_gpu_means_loud_failure_not_fallback():
