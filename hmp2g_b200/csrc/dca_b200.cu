@@ -11,6 +11,7 @@
 #include "dca_kernels.cuh"
 #include "dca_planner.cuh"
 #include "dca_runner.cuh"
+#include "dca_histpool.cuh"
 
 using namespace dca;
 
@@ -328,6 +329,20 @@ int dca_runner_report(const DcaRunnerState *s, int n_agent, int64_t first_episod
                                                          team_of_agent, n_team, out);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_runner_report: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_histpool_roll(const float *obs, float *his_pool, const uint8_t *pause, const uint8_t *suffered_reset,
+                      float *obs_feed, int n_env, int n_agent, dca_stream_t stream) {
+    if (!obs || !his_pool || !obs_feed || n_env <= 0 || n_agent <= 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_histpool_roll: null buffer or empty shape");
+    if (((uintptr_t)obs | (uintptr_t)his_pool | (uintptr_t)obs_feed) & 15)
+        return fail(nullptr, DCA_E_INVALID, "dca_histpool_roll: buffers must be 16-byte aligned");
+    const size_t n = (size_t)n_env * n_agent;  // one warp each
+    k_histpool<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+        (const float4 *)obs, (float4 *)his_pool, pause, suffered_reset, (float4 *)obs_feed, n_env, n_agent);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_histpool_roll: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
 

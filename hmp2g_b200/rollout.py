@@ -7,9 +7,41 @@ One trajectory per env per episode, as in the reference: when an env finishes an
 `dead[t, e, g]` = "the observation guard g acted on at step t was all-NaN" (trajectory.py:72), i.e. the guard was not
 alive when the step began.
 """
+import ctypes as C
+
 import torch
 
+from . import _lib
 from .gae import gae_return, normalized_advantage
+
+
+class HistoryPool(object):
+    """The conc_4hist history pool on the device: ShellEnvWrapper's '_Histpool_Obs_' state and solve_duplicate
+    (/root/reference/ALGORITHM/conc_4hist/shell_env.py:25-99, roll_hisory cython_func.pyx:32-53).  roll() takes the
+    env's observation tensor [E,G,12,16] (zero-copy from DcaVecEnv.obs) and returns obs_feed [E,G,24,16]: the new rows
+    followed by the remembered ones, empty rows NaN, everything NaN for a dead agent or a paused env."""
+
+    def __init__(self, n_env, n_agent, device=None):
+        self.lib = _lib.load()
+        if not torch.cuda.is_available():
+            raise _lib.DcaError('hmp2g_b200 needs a CUDA device; there is no CPU fallback')
+        self.device = torch.device(device if device is not None else 'cuda:%d' % torch.cuda.current_device())
+        self.E, self.G = int(n_env), int(n_agent)
+        self.his_pool = torch.zeros((self.E, self.G, 12, 16), dtype=torch.float32, device=self.device)
+        self.obs_feed = torch.zeros((self.E, self.G, 24, 16), dtype=torch.float32, device=self.device)
+
+    def roll(self, obs, pause=None, suffered_reset=None):
+        if obs.dtype != torch.float32 or obs.numel() != self.his_pool.numel() or not obs.is_cuda \
+                or not obs.is_contiguous():
+            raise _lib.DcaError('roll: obs must be a contiguous cuda float32 [E,G,12,16]')
+        for m in (pause, suffered_reset):
+            if m is not None and (m.dtype != torch.uint8 or tuple(m.shape) != (self.E,) or not m.is_cuda):
+                raise _lib.DcaError('roll: masks must be cuda uint8 [E]')
+        p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+        _lib.check(self.lib.dca_histpool_roll(p(obs), p(self.his_pool), p(pause), p(suffered_reset), p(self.obs_feed),
+                                              self.E, self.G,
+                                              C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return self.obs_feed
 
 
 class DeviceRollout(object):

@@ -159,6 +159,17 @@ int dca_runner_update(const DcaRunnerState *s, int n_env, int n_agent, int align
 int dca_runner_report(const DcaRunnerState *s, int n_agent, int64_t first_episode, int n_episodes,
                       const int32_t *team_of_agent, int n_team, double *out, dca_stream_t stream);
 
+/* ---- conc_4hist history pool -------------------------------------------------------------------------------------
+ * replaces: ShellEnvWrapper.interact_with_env's '_Histpool_Obs_' handling + solve_duplicate
+ * ALGORITHM/conc_4hist/shell_env.py:25-99 and roll_hisory ALGORITHM/conc_4hist/cython_func.pyx:32-53.
+ * obs f32 [E,G,12,16] (the env's observation, empty rows 0 or NaN); his_pool f32 [E,G,12,16] in/out (the
+ * '_Histpool_Obs_' state, zeros at start); pause / suffered_reset u8 [E] (ENV-PAUSE / Env-Suffered-Reset, NULL = all 0);
+ * obs_feed f32 [E,G,24,16] out = what the policy net is fed (new rows ++ history rows, empty rows NaN, everything NaN
+ * for a dead agent).  Envs are not compacted: a paused env keeps its slot, its obs_feed is NaN and its history is
+ * cleared (shell_env.py:44). */
+int dca_histpool_roll(const float *obs, float *his_pool, const uint8_t *pause, const uint8_t *suffered_reset,
+                      float *obs_feed, int n_env, int n_agent, dca_stream_t stream);
+
 /* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a
  * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
  * it (ALGORITHM/conc/shell_env.py:72-75); default 0 = the env's own zeros (collective_assault_env.py:313-316,340-343). */
