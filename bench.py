@@ -268,6 +268,28 @@ def run_ours(args):
     ms_gae = g0.elapsed_time(g1) / 5
     gae_bytes = T * E * G * (4 + 4 + 1 + 4 + 4)  # reward, value, dead in; return, threat out
     del r_buf, v_buf, d_buf
+    # ---- conc_4hist history pool (k_histpool) on the env's observations + runner bookkeeping (k_runner_*)
+    from hmp2g_b200.rollout import HistoryPool
+    from hmp2g_b200.runner import DeviceRunner
+    hp = HistoryPool(E, G, device=dev)
+    run = DeviceRunner(E, G, align_episode=False, report_interval=64, device=dev)
+    for _ in range(5):
+        hp.roll(env.obs)
+        run.update(env.done, env.win, env.reward)
+    g0.record(stream)
+    for _ in range(50):
+        hp.roll(env.obs)
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_hist = g0.elapsed_time(g1) / 50
+    g0.record(stream)
+    for _ in range(50):
+        run.update(env.done, env.win, env.reward)
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_runner = g0.elapsed_time(g1) / 50
+    hist_bytes = E * G * 12 * 16 * 4 * 5  # obs + history in, obs_feed (2x) + history out
+    del hp, run
 
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
@@ -338,6 +360,10 @@ def run_ours(args):
                                    'frac': gather_bytes / (ms_gather * 1e-3) / 1e9 / peak,
                                    'algorithmic_bytes_per_launch': gather_bytes, 'kernel_ms': ms_gather,
                                    'traffic': ncu.get('k_observe_dram_bytes_per_launch')},
+        'histpool_kernel': {'bound': 'hbm', 'kernel': 'k_histpool', 'unit': 'GB/s', 'kernel_ms': ms_hist,
+                            'achieved': hist_bytes / (ms_hist * 1e-3) / 1e9, 'peak': peak,
+                            'frac': hist_bytes / (ms_hist * 1e-3) / 1e9 / peak},
+        'runner_update_ms': ms_runner,
         'gae_kernel': {'bound': 'hbm', 'kernel': 'k_gae', 'unit': 'GB/s',
                        'shape_TEG': [T, E, G], 'kernel_ms': ms_gae, 'achieved': gae_bytes / (ms_gae * 1e-3) / 1e9,
                        'peak': peak, 'frac': gae_bytes / (ms_gae * 1e-3) / 1e9 / peak},

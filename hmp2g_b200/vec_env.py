@@ -295,10 +295,12 @@ class DcaSuperpoolEnv(object):
         actions = np.asarray(actions)
         if actions.ndim == 3 and actions.shape[-1] == 1:  # RandomController layout (ALGORITHM/random/foundation.py:28)
             actions = actions[..., 0]
-        skip = np.isnan(actions).any(axis=1)
-        assert not (skip & ~self._suffer_reset).any(), 'skip command on an env that was not just reset'
+        skip = np.isnan(actions.sum(axis=1))  # a NaN anywhere in the row (ENV-PAUSE, shm_env.py:37)
+        if skip.any():
+            assert not (skip & ~self._suffer_reset).any(), 'skip command on an env that was not just reset'
+            actions = np.where(np.isnan(actions), 0, actions)
         self._h_skip.numpy()[:] = skip
-        self._h_act.numpy()[:] = np.where(np.isnan(actions), 0, actions).astype(np.int32)
+        np.copyto(self._h_act.numpy(), actions, casting='unsafe')  # float64 holding ints -> int32, into pinned memory
         self._d_act.copy_(self._h_act, non_blocking=True)
         self._d_skip.copy_(self._h_skip, non_blocking=True)
         force = self.planner(env) if self.planner is not None else self._take_plan()

@@ -18,7 +18,11 @@ SHORT="python bench.py --steps 12 --warmup 4 --no-cpu-baseline --e2e-steps 3"
 timeout 300 $SHORT > $out/plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $out/launches.csv $SHORT > $out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
-timeout 300 $SHORT > $out/plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_step -s 8 -c 2 -o $out/prof_step $SHORT > $out/ncu_full.log 2>&1
-echo "ncu full rc=$?"
+LONG="python bench.py --steps 80 --warmup 4 --no-cpu-baseline --e2e-steps 3"
+timeout 300 $LONG > $out/plain2.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_step -s 60 -c 1 -o $out/prof_step $LONG > $out/ncu_full.log 2>&1
+echo "ncu full k_step rc=$?"
+timeout 300 $SHORT > $out/plain3.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_observe -s 20 -c 1 -o $out/prof_observe $SHORT > $out/ncu_full_obs.log 2>&1
+echo "ncu full k_observe rc=$?"
 ls -la $out
