@@ -119,6 +119,9 @@ __device__ __forceinline__ double reg_angle(double rad) { return py_fmod(rad + k
 
 // np.logaddexp(0, y)
 __device__ __forceinline__ double logaddexp0(double y) {
+    // exp(-800) is 0 in double, so log1p(exp(-|y|)) is exactly 0 beyond it: the result is max(0, y) bit for bit
+    if (y < -800.0) return 0.0;
+    if (y > 800.0) return y;
     if (y == 0.0) return 0.693147180559945309417232121458176568;
     const double tmp = 0.0 - y;
     if (tmp > 0) return 0.0 + log1p(exp(-tmp));
