@@ -565,6 +565,7 @@ __device__ __forceinline__ void write_alive(const Smem &s, const Params &P, cons
 // soft wall, core.py:339-353: contact_force * softplus penetration (k = contact_margin); noinline: near-wall agents only
 __device__ __noinline__ double wall_push(double d) {
     const double kk = 1e-10;
+    if (d > 1e-7) return 0.0;  // -d/kk < -1000: softplus is exactly 0 (dca_device.cuh logaddexp0); skips the fp64 divide
     return 100.0 * (logaddexp0(-d / kk) * kk);
 }
 
