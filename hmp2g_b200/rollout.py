@@ -61,15 +61,25 @@ class DeviceRollout(object):
         """uint8 [E,G]: who is alive in the observation the policy is about to act on."""
         return self.env.alive[:, :self.env.G]
 
-    def add(self, alive_before, value, reward, done):
+    def add(self, alive_before, value, reward, done, active=None):
         """Record one env step.  alive_before: alive_guards() taken BEFORE env.step; value f32 [E,G] = critic output on
-        that observation; reward f32 [E,G], done u8 [E] = outputs of env.step.  Returns the mask of finished envs."""
+        that observation; reward f32 [E,G], done u8 [E] = outputs of env.step; active (bool / u8 [E], None = all):
+        the envs that really stepped (~ENV-PAUSE) -- paused envs record nothing, like the reference, which feeds
+        only obs[~P] to the algorithm (ALGORITHM/conc/shell_env.py:44-50).  Returns the mask of finished envs."""
         t = self.length.long().clamp_max(self.T - 1)
-        self.reward[t, self._rows] = reward
-        self.value[t, self._rows] = value
-        self.dead[t, self._rows] = (alive_before == 0).to(torch.uint8)
-        self.length += 1
-        return done != 0
+        if active is None:
+            self.reward[t, self._rows] = reward
+            self.value[t, self._rows] = value
+            self.dead[t, self._rows] = (alive_before == 0).to(torch.uint8)
+            self.length += 1
+            return done != 0
+        act = active != 0
+        rows, tt = self._rows[act], t[act]
+        self.reward[tt, rows] = reward[act]
+        self.value[tt, rows] = value[act]
+        self.dead[tt, rows] = (alive_before[act] == 0).to(torch.uint8)
+        self.length += act.to(self.length.dtype)
+        return (done != 0) & act
 
     def finalize(self, finished=None, group=None):
         """trajectory.finalize for the envs in `finished` (bool [E]; None = all, e.g. a truncated rollout): returns

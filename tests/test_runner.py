@@ -113,3 +113,53 @@ def test_cuda_runner_4096_envs_vs_oracle(align):
     assert np.array_equal(i['Thread-Episode-Cnt'].cpu().numpy(), orc.ep_cnt)
     assert orc.n_episode > 2 * E and len(orc.reports) == orc.n_episode // ri
     assert np.array_equal(np.array(seen, np.float64), np.array(orc.reports, np.float64))
+
+
+@pytest.mark.gpu
+def test_cuda_device_resident_loop_runner_histpool_rollout_gae():
+    """The loop of INTEGRATION.md §3: env kernel + planner + DeviceRunner (align_episode) + HistoryPool + DeviceRollout
+    + GAE, all on device tensors.  Checks the pieces against each other: frames counted by the runner == steps
+    finalized by the rollout buffer, paused envs record nothing, returns are finite where valid."""
+    import torch
+    import hmp2g_b200
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.rollout import HistoryPool
+    E = 256
+    scfg = type('S', (ScenarioConfig,), dict(num_guards=20, num_attackers=25, MaxEpisodeStep=14, init_distance=1.5))
+    env = hmp2g_b200.DcaVecEnv(E, scfg=scfg, seed=9, empty_rows_nan=True)
+    run = hmp2g_b200.DeviceRunner(E, env.G, align_episode=True, report_interval=32, test_interval=100)
+    hist = HistoryPool(E, env.G)
+    buf = hmp2g_b200.DeviceRollout(env)
+    env.reset()
+    g = torch.Generator(device=env.device)
+    g.manual_seed(1)
+    steps_finalized = episodes = tests_due = n_reports = paused_steps = 0
+    for t in range(70):
+        feed = hist.roll(env.obs, pause=run.pause, suffered_reset=run.info['Env-Suffered-Reset'])
+        running = run.pause == 0
+        paused_steps += int((~running).sum())
+        # a stand-in policy: random actions, value = number of visible rows (NaN-aware, like the reference's masks)
+        act = torch.randint(0, 7, (E, env.G), generator=g, device=env.device, dtype=torch.int32)
+        value = (~torch.isnan(feed[..., 0])).sum(-1).float()
+        alive = buf.alive_guards().clone()
+        # hold a random half back during the first steps so that the envs do not finish in lockstep
+        hold = (torch.rand((E,), generator=g, device=env.device) < (0.5 if t < 5 else 0.0)).to(torch.uint8)
+        env.step(act, skip=run.pause | hold)
+        stepped = running & (hold == 0)
+        finished = buf.add(alive, value, env.reward, env.done, active=stepped)
+        # the runner only knows its own pauses: give it done = 0 for the envs held back by the test
+        done_seen = env.done * (hold == 0).to(torch.uint8)
+        run.update(done_seen, env.win, env.reward)
+        st = run.poll()
+        tests_due += st['tests_due']
+        n_reports += len(st['reports'])
+        if bool(finished.any()):
+            lens = buf.length.clone()
+            ret, threat, adv, valid = buf.finalize(finished)
+            assert torch.isfinite(ret[valid]).all() and torch.isfinite(adv[valid]).all()
+            steps_finalized += int(lens[finished].sum())
+            episodes += int(finished.sum())
+    assert episodes == run.current_n_episode >= 2 * E
+    # the runner also counts the steps an env was held back by the test (it believes they ran)
+    assert run.current_n_frame >= steps_finalized and paused_steps > 0
+    assert tests_due == run.current_n_episode // 100 and n_reports == run.current_n_episode // 32
