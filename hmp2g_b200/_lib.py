@@ -39,7 +39,7 @@ class DcaRunnerState(C.Structure):
 EXPORTS = ('dca_abi_version', 'dca_last_error', 'dca_create', 'dca_destroy', 'dca_bind_buffers', 'dca_reset',
            'dca_step', 'dca_observe', 'dca_plan', 'dca_plan_centroid', 'dca_export_state', 'dca_import_state', 'dca_gae',
            'dca_kernel_launches', 'dca_debug_phase_clocks', 'dca_set_option', 'dca_runner_init', 'dca_runner_update',
-           'dca_runner_report', 'dca_histpool_roll')
+           'dca_runner_report', 'dca_histpool_roll', 'dca_adv_moments', 'dca_adv_normalize')
 
 _lib = None
 
@@ -79,6 +79,8 @@ def load(build_if_missing=False):
     lib.dca_runner_update.argtypes = [C.POINTER(DcaRunnerState), C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]
     lib.dca_runner_report.argtypes = [C.POINTER(DcaRunnerState), C.c_int, C.c_int64, C.c_int, _P, C.c_int, _P, _P]
     lib.dca_histpool_roll.argtypes = [_P, _P, _P, _P, _P, C.c_int, C.c_int, _P]
+    lib.dca_adv_moments.argtypes = [_P, _P, _P, C.c_int, C.c_uint64, _P, _P, _P]
+    lib.dca_adv_normalize.argtypes = [_P, _P, _P, C.c_int, C.c_uint64, _P, _P, _P]
     lib.dca_kernel_launches.argtypes = [_P, C.POINTER(C.c_int64)]
     lib.dca_debug_phase_clocks.argtypes = [_P, _P]
     for name in EXPORTS:

@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -343,6 +344,30 @@ int dca_histpool_roll(const float *obs, float *his_pool, const uint8_t *pause, c
         (const float4 *)obs, (float4 *)his_pool, pause, suffered_reset, (float4 *)obs_feed, n_env, n_agent);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_histpool_roll: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_adv_moments(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
+                    double *scratch, double *stats, dca_stream_t stream) {
+    if (!ret || !value || !scratch || !stats || n == 0 || (valid && valid_group <= 0))
+        return fail(nullptr, DCA_E_INVALID, "dca_adv_moments: null buffer, empty batch or bad valid_group");
+    cudaStream_t st = (cudaStream_t)stream;
+    k_adv_partial<<<kAdvBlocks, kAdvThreads, 0, st>>>(ret, value, valid, valid ? valid_group : 1, (size_t)n, scratch);
+    k_adv_final<<<1, kAdvThreads, 0, st>>>(scratch, stats);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_moments: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
+                      const double *stats, float *adv, dca_stream_t stream) {
+    if (!ret || !value || !stats || !adv || n == 0 || (valid && valid_group <= 0))
+        return fail(nullptr, DCA_E_INVALID, "dca_adv_normalize: null buffer, empty batch or bad valid_group");
+    const size_t blocks = std::min<size_t>((n + kAdvThreads - 1) / kAdvThreads, 148 * 16);
+    k_adv_normalize<<<(unsigned)blocks, kAdvThreads, 0, (cudaStream_t)stream>>>(ret, value, valid, valid ? valid_group : 1,
+                                                                             (size_t)n, stats, adv);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_normalize: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
 

@@ -133,4 +133,58 @@ __global__ void __launch_bounds__(256) k_runner_report(DcaRunnerState S, int G, 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Advantage normalisation over the pooled batch (ALGORITHM/conc/ppo.py:53-55, ALGORITHM/common/ppo_sampler.py:67-77):
+// adv = ret - value; adv = (adv - adv.mean()) / (adv.std() + 1e-5), numpy std = population std (ddof 0).
+// Moments are accumulated in fp64 in a fixed order (per-CTA partials, then one CTA): bit-reproducible run to run.
+// stats = (sum adv, sum adv^2, count); across GPUs the caller all-reduces the three doubles before normalising.
+constexpr int kAdvBlocks = 592, kAdvThreads = 256;  // 4 CTAs per SM on 148 SMs
+
+__device__ __forceinline__ void adv_block_reduce(double (&v)[3], double *sh) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    if (lane == 0) { sh[warp * 3] = v[0]; sh[warp * 3 + 1] = v[1]; sh[warp * 3 + 2] = v[2]; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < kAdvThreads / 32; ++w) { v[0] += sh[w * 3]; v[1] += sh[w * 3 + 1]; v[2] += sh[w * 3 + 2]; }
+    }
+}
+
+__global__ void __launch_bounds__(kAdvThreads) k_adv_partial(const float *__restrict__ ret, const float *__restrict__ value,
+                                                             const uint8_t *__restrict__ valid, int valid_group, size_t n,
+                                                             double *__restrict__ partial) {
+    __shared__ double sh[3 * kAdvThreads / 32];
+    double v[3] = {0.0, 0.0, 0.0};
+    for (size_t i = (size_t)blockIdx.x * kAdvThreads + threadIdx.x; i < n; i += (size_t)kAdvBlocks * kAdvThreads) {
+        if (valid && !valid[i / valid_group]) continue;
+        const double a = (double)__fsub_rn(ret[i], value[i]);  // the f32 difference the reference forms first
+        v[0] += a; v[1] += a * a; v[2] += 1.0;
+    }
+    adv_block_reduce(v, sh);
+    if (threadIdx.x == 0) { partial[blockIdx.x * 3] = v[0]; partial[blockIdx.x * 3 + 1] = v[1]; partial[blockIdx.x * 3 + 2] = v[2]; }
+}
+
+__global__ void __launch_bounds__(kAdvThreads) k_adv_final(const double *__restrict__ partial, double *__restrict__ stats) {
+    __shared__ double sh[3 * kAdvThreads / 32];
+    double v[3] = {0.0, 0.0, 0.0};
+    for (int b = threadIdx.x; b < kAdvBlocks; b += kAdvThreads) { v[0] += partial[b * 3]; v[1] += partial[b * 3 + 1]; v[2] += partial[b * 3 + 2]; }
+    adv_block_reduce(v, sh);
+    if (threadIdx.x == 0) { stats[0] = v[0]; stats[1] = v[1]; stats[2] = v[2]; }
+}
+
+__global__ void __launch_bounds__(kAdvThreads) k_adv_normalize(const float *__restrict__ ret, const float *__restrict__ value,
+                                                               const uint8_t *__restrict__ valid, int valid_group, size_t n,
+                                                               const double *__restrict__ stats, float *__restrict__ adv) {
+    const double cnt = stats[2] > 0.0 ? stats[2] : 1.0;
+    const double mean = stats[0] / cnt;
+    const double var = fmax(stats[1] / cnt - mean * mean, 0.0);
+    const float m = (float)mean, sd = __fadd_rn((float)sqrt(var), 1e-5f);
+    for (size_t i = (size_t)blockIdx.x * kAdvThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kAdvThreads) {
+        const bool ok = !valid || valid[i / valid_group];
+        adv[i] = ok ? __fdiv_rn(__fsub_rn(__fsub_rn(ret[i], value[i]), m), sd) : 0.f;
+    }
+}
+
 }  // namespace dca

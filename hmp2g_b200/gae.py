@@ -35,18 +35,46 @@ def gae_return(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_
     return (ret, threat, pushed) if want_pushed else (ret, threat)
 
 
-def normalized_advantage(ret, value, valid=None, group=None):
-    """adv = ret - value; adv = (adv - mean) / (std + 1e-5) over the pooled batch (ppo.py:53-55).
-    With `group` (a torch.distributed process group) the moments are all-reduced over ranks (NCCL): the only
-    collective on the rollout path besides the gradient all-reduce."""
-    adv = ret - value
-    if valid is None:
-        valid = torch.ones_like(adv, dtype=torch.bool)
-    m = valid.to(adv.dtype)
-    stats = torch.stack([(adv * m).sum(), (adv * adv * m).sum(), m.sum()]).to(torch.float64)
+def allreduce_moments(stats, group=None):
+    """stats f64[3] = (sum, sum of squares, count) of this rank's advantages -> the same over all ranks (in place)."""
     if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
         torch.distributed.all_reduce(stats, group=group)
-    n = stats[2]
+    return stats
+
+
+def moments_mean_std(stats):
+    """(mean, population std) from (sum, sum of squares, count) -- what k_adv_normalize derives on the device."""
+    n = stats[2].clamp_min(1)
     mean = stats[0] / n
-    var = (stats[1] / n - mean * mean).clamp_min(0) * (n / (n - 1).clamp_min(1))  # torch.std default: unbiased
-    return ((adv - mean.to(adv.dtype)) / (var.sqrt().to(adv.dtype) + 1e-5)) * m
+    return mean, (stats[1] / n - mean * mean).clamp_min(0).sqrt()
+
+
+def normalized_advantage(ret, value, valid=None, group=None):
+    """adv = ret - value; adv = (adv - mean) / (std + 1e-5) over the pooled batch (ppo.py:53-55; numpy std, ddof 0),
+    by dca_adv_moments / dca_adv_normalize.  valid: bool / uint8 mask, either elementwise (ret.shape) or one flag per
+    leading index (ret.shape[:-1], e.g. [T,E] for ret [T,E,G]); invalid elements get 0.  If torch.distributed is
+    initialised (or `group` is given) the three moments are all-reduced over the ranks (NCCL): the only collective on
+    the rollout path besides the gradient all-reduce."""
+    lib = _lib.load()
+    assert ret.is_cuda and ret.dtype == torch.float32 and ret.is_contiguous()
+    assert value.shape == ret.shape and value.dtype == torch.float32 and value.is_contiguous()
+    n = ret.numel()
+    vgroup = 1
+    if valid is not None:
+        if tuple(valid.shape) == tuple(ret.shape[:-1]):
+            vgroup = ret.shape[-1]
+        else:
+            assert valid.shape == ret.shape, 'valid must match ret or ret.shape[:-1]'
+        valid = valid.to(torch.uint8).contiguous()
+    dev = ret.device
+    scratch = torch.empty((592 * 3,), dtype=torch.float64, device=dev)
+    stats = torch.empty((3,), dtype=torch.float64, device=dev)
+    adv = torch.empty_like(ret)
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    with torch.cuda.device(dev):
+        _lib.check(lib.dca_adv_moments(_ptr(ret), _ptr(value), _ptr(valid), vgroup, n, _ptr(scratch), _ptr(stats),
+                                       stream))
+        allreduce_moments(stats, group)
+        _lib.check(lib.dca_adv_normalize(_ptr(ret), _ptr(value), _ptr(valid), vgroup, n, _ptr(stats), _ptr(adv),
+                                         stream))
+    return adv

@@ -91,7 +91,8 @@ class DeviceRollout(object):
         lens = torch.where(finished, self.length, torch.zeros_like(self.length)).clamp_max(self.T)
         ret, threat = gae_return(self.reward, self.value, self.dead, traj_len=lens, gamma=self.gamma, tau=self.tau,
                                  threat_limit=self.threat_limit)
-        valid = (torch.arange(self.T, device=lens.device)[:, None] < lens[None, :])[:, :, None].expand_as(ret)
-        adv = normalized_advantage(ret, self.value, valid=valid, group=group)
+        valid_te = torch.arange(self.T, device=lens.device)[:, None] < lens[None, :]
+        adv = normalized_advantage(ret, self.value, valid=valid_te, group=group)
+        valid = valid_te[:, :, None].expand_as(ret)
         self.length = torch.where(finished, torch.zeros_like(self.length), self.length)
         return ret, threat, adv, valid

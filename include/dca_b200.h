@@ -170,6 +170,17 @@ int dca_runner_report(const DcaRunnerState *s, int n_agent, int64_t first_episod
 int dca_histpool_roll(const float *obs, float *his_pool, const uint8_t *pause, const uint8_t *suffered_reset,
                       float *obs_feed, int n_env, int n_agent, dca_stream_t stream);
 
+/* ---- advantage normalisation -------------------------------------------------------------------------------------
+ * replaces: adv = ret - value; adv = (adv - adv.mean()) / (adv.std() + 1e-5) over the pooled batch,
+ * ALGORITHM/conc/ppo.py:53-55 (= ALGORITHM/common/ppo_sampler.py:67-77; numpy std, ddof 0).
+ * dca_adv_moments: stats f64[3] = (sum adv, sum adv^2, count) over the n elements whose valid[i / valid_group] != 0
+ * (valid NULL = all); scratch f64[1776] (device).  Across GPUs: all-reduce `stats` (3 doubles), then normalise.
+ * dca_adv_normalize: adv f32[n] out (0 where not valid). */
+int dca_adv_moments(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
+                    double *scratch, double *stats, dca_stream_t stream);
+int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
+                      const double *stats, float *adv, dca_stream_t stream);
+
 /* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a
  * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
  * it (ALGORITHM/conc/shell_env.py:72-75); default 0 = the env's own zeros (collective_assault_env.py:313-316,340-343). */

@@ -425,3 +425,31 @@ def test_cuda_superpool_plan_ahead_equals_plan_in_step():
         assert np.array_equal(d_h, env.done.cpu().numpy().astype(bool)), t
         n_done += int(d_h.sum())
     assert n_done >= E
+
+
+def test_cuda_advantage_normalisation_matches_numpy_formula():
+    """adv = ret - value; (adv - adv.mean()) / (adv.std() + 1e-5) as ALGORITHM/conc/ppo.py:53-55 evaluates it on the
+    pooled float32 numpy batch (population std); tolerance 1e-5 (the reference sums in float32, the kernel in fp64)."""
+    torch = _torch()
+    from hmp2g_b200.gae import normalized_advantage
+    rng = np.random.RandomState(3)
+    for shape in [(180, 64, 50), (7, 3, 5), (1, 1, 2)]:
+        ret = (rng.randn(*shape) * 3 + 1).astype(np.float32)
+        val = rng.randn(*shape).astype(np.float32)
+        adv = ret - val
+        want = (adv - adv.mean()) / (adv.std() + 1e-5)
+        tr, tv = torch.from_numpy(ret).cuda(), torch.from_numpy(val).cuda()
+        got = normalized_advantage(tr, tv)
+        assert np.allclose(got.cpu().numpy(), want, rtol=1e-5, atol=1e-5), shape
+        again = normalized_advantage(tr, tv)
+        assert torch.equal(got, again)  # fixed summation order: bit-reproducible
+        # ragged batch: one flag per (t, env) row, and the same mask given elementwise
+        rows = rng.rand(*shape[:2]) < 0.6
+        rows[0, 0] = True
+        sel = adv[rows]
+        want_m = (sel - sel.mean()) / (sel.std() + 1e-5)
+        got_rows = normalized_advantage(tr, tv, valid=torch.from_numpy(rows).cuda())
+        got_elem = normalized_advantage(tr, tv, valid=torch.from_numpy(np.broadcast_to(rows[..., None], shape).copy()).cuda())
+        assert torch.equal(got_rows, got_elem)
+        g = got_rows.cpu().numpy()
+        assert np.allclose(g[rows], want_m, rtol=1e-5, atol=1e-5) and (g[~rows] == 0).all()

@@ -145,7 +145,7 @@ import os, sys, torch
 sys.path.insert(0, %r)
 import torch.distributed as dist
 from hmp2g_b200.sharding import init_distributed, shard_envs, RolloutStats
-from hmp2g_b200.gae import normalized_advantage
+from hmp2g_b200.gae import allreduce_moments, moments_mean_std
 rank, world, _ = init_distributed('gloo')
 gid0, n = shard_envs(10, rank, world)
 g = torch.Generator().manual_seed(0)
@@ -158,9 +158,11 @@ tot = st.reduce()
 ref = RolloutStats('cpu'); ref.update(reward, done, win)
 for k, v in zip(ref.FIELDS, ref.buf.tolist()):
     assert abs(v - tot[k]) < 1e-9, (k, v, tot[k])
-adv = normalized_advantage(ret[sl], val[sl])
-full = (ret - val); full = (full - full.mean()) / (full.std() + 1e-5)
-assert torch.allclose(adv, full[sl], atol=1e-5), (adv - full[sl]).abs().max()
+a = (ret[sl] - val[sl]).double()     # what dca_adv_moments accumulates on each rank's shard
+stats = allreduce_moments(torch.stack([a.sum(), (a * a).sum(), torch.tensor(float(a.numel()), dtype=torch.float64)]))
+mean, std = moments_mean_std(stats)
+full = (ret - val).double()          # ppo.py:53-55 over the pooled batch (numpy std: ddof 0)
+assert abs(float(mean) - float(full.mean())) < 1e-12 and abs(float(std) - float(full.std(unbiased=False))) < 1e-12
 dist.barrier(); dist.destroy_process_group()
 sys.stdout.write('rank' + str(rank) + 'ok\n'); sys.stdout.flush()
 '''
