@@ -16,10 +16,10 @@ OBS_ROWS, OBS_ROW = 12, 16
 
 
 def build(force=False):
-    srcs = [os.path.join(HERE, 'dca_oracle.c'), os.path.join(HERE, 'dca_planner.c')]
+    srcs = [os.path.join(HERE, 'dca_oracle.c'), os.path.join(HERE, 'dca_planner.c'), os.path.join(HERE, 'mt_oracle.c')]
     hdr = os.path.join(HERE, 'dca_oracle.h')
     if (not force and os.path.exists(LIB_PATH)
-            and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(f) for f in srcs + [hdr])):
+            and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(f) for f in srcs + [hdr, os.path.join(HERE, 'mt_oracle.h')])):
         return LIB_PATH
     cmd = ['gcc', '-O2', '-std=c11', '-ffp-contract=off', '-fno-fast-math', '-fopenmp', '-fPIC', '-shared',
            '-o', LIB_PATH] + srcs + ['-lm']
