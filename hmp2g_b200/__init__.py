@@ -7,7 +7,8 @@ reference's Python interfaces.  No CPU fallback exists.
 from .config import ChainVar, GlobalConfig, ScenarioConfig, inject, load_jsonc  # noqa: F401
 
 __all__ = ['ChainVar', 'GlobalConfig', 'ScenarioConfig', 'inject', 'load_jsonc', 'DcaVecEnv', 'DcaSuperpoolEnv',
-           'make_parallel_envs', 'gae_return', 'DeviceRollout', 'DeviceRunner']
+           'make_parallel_envs', 'gae_return', 'DeviceRollout', 'DeviceRunner', 'MtScenarioConfig', 'DcaMultiTeamVecEnv',
+           'DcaMultiTeamSuperpoolEnv']
 
 
 def __getattr__(name):  # torch is imported lazily so that config-only users do not pay for it
@@ -20,6 +21,9 @@ def __getattr__(name):  # torch is imported lazily so that config-only users do 
     if name == 'DeviceRollout':
         from . import rollout
         return rollout.DeviceRollout
+    if name in ('MtScenarioConfig', 'DcaMultiTeamVecEnv', 'DcaMultiTeamSuperpoolEnv'):
+        from . import multiteam
+        return getattr(multiteam, name)
     if name == 'DeviceRunner':
         from . import runner
         return runner.DeviceRunner

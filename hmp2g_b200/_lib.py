@@ -36,10 +36,31 @@ class DcaRunnerState(C.Structure):
                                   'log_meta', 'log_reward')] + [('log_capacity', C.c_int32)]
 
 
+class DcaMtConfig(C.Structure):
+    _fields_ = [('n_team', C.c_int32), ('team_size', C.c_int32 * 8), ('size', C.c_double),
+                ('random_jam_prob', C.c_double), ('introduce_terrain', C.c_int32), ('terrain_A', C.c_double),
+                ('terrain_B', C.c_double), ('max_episode_step', C.c_int32), ('steps_to_narrow', C.c_int32),
+                ('init_distance', C.c_double), ('half_death_reward', C.c_int32), ('seed', C.c_uint64),
+                ('env_gid0', C.c_int64)]
+
+
+class DcaMtBuffers(C.Structure):
+    _fields_ = [(n, _P) for n in ('obs', 'tobs', 'reward', 'done', 'ranking', 'alive', 'slot_id')]
+
+
+MT_STATE_FIELDS = ('pos', 'vel', 'atk_rad', 'terrain', 'alive', 'just_died', 'hit', 'was_hit', 'bsa', 'init_theta',
+                   'time_step', 'obs_counter', 'episode')
+
+
+class DcaMtState(C.Structure):
+    _fields_ = [(n, _P) for n in MT_STATE_FIELDS]
+
+
 EXPORTS = ('dca_abi_version', 'dca_last_error', 'dca_create', 'dca_destroy', 'dca_bind_buffers', 'dca_reset',
            'dca_step', 'dca_observe', 'dca_plan', 'dca_plan_centroid', 'dca_export_state', 'dca_import_state', 'dca_gae',
            'dca_kernel_launches', 'dca_debug_phase_clocks', 'dca_set_option', 'dca_runner_init', 'dca_runner_update',
-           'dca_runner_report', 'dca_histpool_roll', 'dca_adv_moments', 'dca_adv_normalize')
+           'dca_runner_report', 'dca_histpool_roll', 'dca_adv_moments', 'dca_adv_normalize', 'dca_mt_create', 'dca_mt_destroy',
+           'dca_mt_bind_buffers', 'dca_mt_reset', 'dca_mt_step', 'dca_mt_export_state', 'dca_mt_import_state')
 
 _lib = None
 
@@ -81,6 +102,13 @@ def load(build_if_missing=False):
     lib.dca_histpool_roll.argtypes = [_P, _P, _P, _P, _P, C.c_int, C.c_int, _P]
     lib.dca_adv_moments.argtypes = [_P, _P, _P, C.c_int, C.c_uint64, _P, _P, _P]
     lib.dca_adv_normalize.argtypes = [_P, _P, _P, C.c_int, C.c_uint64, _P, _P, _P]
+    lib.dca_mt_create.argtypes = [C.POINTER(DcaMtConfig), C.c_int, C.c_int, C.POINTER(_P)]
+    lib.dca_mt_destroy.argtypes = [_P]
+    lib.dca_mt_bind_buffers.argtypes = [_P, C.POINTER(DcaMtBuffers)]
+    lib.dca_mt_reset.argtypes = [_P, _P, _P]
+    lib.dca_mt_step.argtypes = [_P, _P, _P, C.c_int, _P]
+    lib.dca_mt_export_state.argtypes = [_P, C.POINTER(DcaMtState), _P]
+    lib.dca_mt_import_state.argtypes = [_P, C.POINTER(DcaMtState), _P]
     lib.dca_kernel_launches.argtypes = [_P, C.POINTER(C.c_int64)]
     lib.dca_debug_phase_clocks.argtypes = [_P, _P]
     for name in EXPORTS:

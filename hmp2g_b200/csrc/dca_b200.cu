@@ -13,6 +13,7 @@
 #include "dca_planner.cuh"
 #include "dca_runner.cuh"
 #include "dca_histpool.cuh"
+#include "dca_multiteam.cuh"
 
 using namespace dca;
 
@@ -26,6 +27,14 @@ struct DcaHandle {
     PlanState plan;
     int plan_smem;
     std::string err;
+};
+
+struct DcaMtHandle {
+    dca::MtParams P;
+    int device;
+    int smem;
+    bool bound;
+    void *slab;  // one allocation holding every state array
 };
 
 static thread_local std::string g_err;
@@ -370,6 +379,136 @@ int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_normalize: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ dca_multiteam
+namespace {
+struct MtField { size_t offset, bytes; };
+// carve the SoA state out of one slab; returns total bytes
+size_t mt_carve_state(DcaMtState *st, char *base, int E, int N) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off += (bytes + 255) & ~(size_t)255; return (void *)p; };
+    const size_t EN = (size_t)E * N;
+    st->pos = (double *)take(EN * 16); st->vel = (double *)take(EN * 16);
+    st->atk_rad = (double *)take(EN * 8); st->terrain = (double *)take(EN * 8);
+    st->alive = (uint8_t *)take(EN); st->just_died = (uint8_t *)take(EN); st->hit = (uint8_t *)take(EN);
+    st->was_hit = (uint8_t *)take(EN); st->bsa = (uint8_t *)take(EN);
+    st->init_theta = (double *)take((size_t)E * 8); st->time_step = (int32_t *)take((size_t)E * 4);
+    st->obs_counter = (uint32_t *)take((size_t)E * 4); st->episode = (uint32_t *)take((size_t)E * 4);
+    return off;
+}
+}  // namespace
+
+int dca_mt_create(const DcaMtConfig *cfg, int n_env, int device, DcaMtHandle **out) {
+    if (!cfg || !out || n_env <= 0) return fail(nullptr, DCA_E_INVALID, "dca_mt_create: null argument or n_env <= 0");
+    *out = nullptr;
+    if (cfg->n_team < 2 || cfg->n_team > DCA_MT_MAX_TEAMS)
+        return fail(nullptr, DCA_E_INVALID, "dca_mt_create: need 2 <= n_team <= 8");
+    int N = 0;
+    for (int t = 0; t < cfg->n_team; ++t) {
+        // the reference observation takes argsort()[:6] of the ally list and of the foe list: teams of >= 6
+        if (cfg->team_size[t] < kVisN) return fail(nullptr, DCA_E_INVALID, "dca_mt_create: every team needs >= 6 agents");
+        N += cfg->team_size[t];
+    }
+    if (N > 252 || (N * kMtLen) % 4 != 0) return fail(nullptr, DCA_E_INVALID, "dca_mt_create: at most 252 agents");
+    if (cfg->steps_to_narrow <= 0 || cfg->max_episode_step <= 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_mt_create: StepsToNarrowCircle and MaxEpisodeStep must be positive");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, DCA_E_NODEVICE, "dca_mt_create: no CUDA device (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(nullptr, DCA_E_INVALID, "dca_mt_create: bad device index");
+    DeviceGuard guard(device);
+    DcaMtHandle *h = new (std::nothrow) DcaMtHandle();
+    if (!h) return fail(nullptr, DCA_E_INVALID, "dca_mt_create: out of host memory");
+    std::memset(&h->P, 0, sizeof(h->P));
+    h->device = device;
+    h->bound = false;
+    h->P.cfg = *cfg;
+    h->P.E = n_env;
+    h->P.N = N;
+    {
+        const double t = std::ceil(cfg->random_jam_prob * 4294967296.0);
+        h->P.jam_thresh = t <= 0 ? 0ull : (t >= 4294967296.0 ? 4294967296ull : (unsigned long long)t);
+    }
+    h->smem = (int)mt_smem_bytes(N);
+    DcaMtState probe;
+    const size_t bytes = mt_carve_state(&probe, nullptr, n_env, N);
+    cudaError_t e = cudaMalloc(&h->slab, bytes);
+    if (e != cudaSuccess) { delete h; return fail(nullptr, DCA_E_CUDA, std::string("dca_mt_create: cudaMalloc: ") + cudaGetErrorString(e)); }
+    cudaMemset(h->slab, 0, bytes);
+    mt_carve_state(&h->P.st, (char *)h->slab, n_env, N);
+    if (h->smem > 48 * 1024) {
+        cudaFuncSetAttribute(k_mt_step, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+        cudaFuncSetAttribute(k_mt_reset, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+    }
+    k_mt_init<<<(n_env + 127) / 128, 128>>>(h->P);
+    e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { cudaFree(h->slab); delete h; return fail(nullptr, DCA_E_CUDA, std::string("dca_mt_create: ") + cudaGetErrorString(e)); }
+    *out = h;
+    return DCA_OK;
+}
+
+int dca_mt_destroy(DcaMtHandle *h) {
+    if (!h) return DCA_E_INVALID;
+    DeviceGuard guard(h->device);
+    cudaFree(h->slab);
+    delete h;
+    return DCA_OK;
+}
+
+int dca_mt_bind_buffers(DcaMtHandle *h, const DcaMtBuffers *b) {
+    if (!h || !b) return DCA_E_INVALID;
+    if (!b->obs || !b->reward || !b->done || !b->ranking) {
+        g_err = "dca_mt_bind_buffers: obs, reward, done and ranking are required";
+        return DCA_E_INVALID;
+    }
+    if (((uintptr_t)b->obs | (uintptr_t)b->tobs) & 15) { g_err = "dca_mt_bind_buffers: obs / tobs must be 16-byte aligned"; return DCA_E_INVALID; }
+    h->P.out = *b;
+    h->bound = true;
+    return DCA_OK;
+}
+
+static int mt_launch_check(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_mt_reset(DcaMtHandle *h, const uint8_t *env_mask, dca_stream_t stream) {
+    if (!h) return DCA_E_INVALID;
+    if (!h->bound) return fail(nullptr, DCA_E_UNBOUND, "dca_mt_reset: call dca_mt_bind_buffers first");
+    DeviceGuard guard(h->device);
+    k_mt_reset<<<h->P.E, kMtThreads, h->smem, (cudaStream_t)stream>>>(h->P, env_mask);
+    return mt_launch_check("dca_mt_reset");
+}
+
+int dca_mt_step(DcaMtHandle *h, const int32_t *actions, const uint8_t *skip, int autoreset, dca_stream_t stream) {
+    if (!h || !actions) return fail(nullptr, DCA_E_INVALID, "dca_mt_step: null argument");
+    if (!h->bound) return fail(nullptr, DCA_E_UNBOUND, "dca_mt_step: call dca_mt_bind_buffers first");
+    DeviceGuard guard(h->device);
+    k_mt_step<<<h->P.E, kMtThreads, h->smem, (cudaStream_t)stream>>>(h->P, actions, skip, autoreset);
+    return mt_launch_check("dca_mt_step");
+}
+
+static int mt_state_io(DcaMtHandle *h, const DcaMtState *u, bool import, dca_stream_t stream) {
+    if (!h || !u) return DCA_E_INVALID;
+    DeviceGuard guard(h->device);
+    const size_t EN = (size_t)h->P.E * h->P.N, E = (size_t)h->P.E;
+    const DcaMtState &m = h->P.st;
+    struct { void *mine; void *theirs; size_t bytes; } f[] = {
+        {m.pos, u->pos, EN * 16}, {m.vel, u->vel, EN * 16}, {m.atk_rad, u->atk_rad, EN * 8}, {m.terrain, u->terrain, EN * 8},
+        {m.alive, u->alive, EN}, {m.just_died, u->just_died, EN}, {m.hit, u->hit, EN}, {m.was_hit, u->was_hit, EN},
+        {m.bsa, u->bsa, EN}, {m.init_theta, u->init_theta, E * 8}, {m.time_step, u->time_step, E * 4},
+        {m.obs_counter, u->obs_counter, E * 4}, {m.episode, u->episode, E * 4}};
+    for (auto &x : f) {
+        if (!x.theirs) return fail(nullptr, DCA_E_INVALID, "dca_mt state io: every DcaMtState field is required");
+        cudaError_t e = cudaMemcpyAsync(import ? x.mine : x.theirs, import ? x.theirs : x.mine, x.bytes,
+                                        cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+        if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_mt state io: ") + cudaGetErrorString(e));
+    }
+    return DCA_OK;
+}
+int dca_mt_export_state(DcaMtHandle *h, const DcaMtState *dst, dca_stream_t stream) { return mt_state_io(h, dst, false, stream); }
+int dca_mt_import_state(DcaMtHandle *h, const DcaMtState *src, dca_stream_t stream) { return mt_state_io(h, src, true, stream); }
 
 int dca_set_option(DcaHandle *h, int option, int value) {
     if (!h) return DCA_E_INVALID;

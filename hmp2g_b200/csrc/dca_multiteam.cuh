@@ -1,0 +1,403 @@
+// dca_multiteam on the device: the sibling env of DCA with N teams, every agent policy-controlled,
+// a per-hit success draw, a shrinking kill circle and a team ranking instead of win/lose.
+//   MISSION/dca_multiteam/collective_assault_parallel_run.py:156-323  step / reset / _get_done / get_rank / _set_action
+//   MISSION/dca_multiteam/core.py:100-240                             World.step, laser, integrate, kill circle, terrain
+//   MISSION/dca_multiteam/envs/collective_assault_env.py:42-226      reset_world, reward, observation (12 x 17 floats)
+//   UTIL/shm_env.py:33-97                                            EnvAutoReset (skip mask, terminal obs, reset obs)
+// One CTA per env, state in SoA arrays [E,N] (loaded into shared memory per step), same keyed Philox stream as DCA plus
+// one site for the laser draws: hit draw of (shooter i, target j) = word 0 of Philox(gid, obs_counter, i*N+j, site 4).
+// Equal float32 distances are ordered by index (the reference's np.argsort leaves that order to its sort kernel).
+#pragma once
+#include "dca_device.cuh"
+
+namespace dca {
+
+constexpr int kMtRow = DCA_MT_OBS_ROW;          // 17 floats per entity record
+constexpr int kMtLen = kObsRows * kMtRow;       // 204 floats per agent
+constexpr int kMtThreads = 128;
+enum : uint32_t { SITE_MT_LASER = 4 };
+enum : uint8_t { MT_ALIVE = 1, MT_JUST_DIED = 2, MT_HIT = 4, MT_WAS_HIT = 8, MT_BSA = 16 };
+
+struct MtParams {
+    DcaMtConfig cfg;
+    int E, N;
+    DcaMtState st;     // library-owned SoA state
+    DcaMtBuffers out;  // caller-owned outputs
+    unsigned long long jam_thresh;
+};
+
+struct MtSmem {
+    double *px, *py, *vx, *vy, *atk, *ter;
+    float *xs, *ys, *table;  // table: [(N+1)][17], record N = zeros
+    int *hitf;               // per agent: bit 0 = hit someone, bit 1 = was hit (this step)
+    int16_t *sid;            // [N,12]
+    uint8_t *flags, *team, *tid;
+    int *misc;               // [0..7] alive count per team, 8 done, 9.. ranking
+};
+
+__host__ __device__ inline size_t mt_smem_bytes(int N) {
+    size_t b = 6 * sizeof(double) * N;
+    b += 2 * sizeof(float) * N + sizeof(float) * (size_t)(N + 1) * kMtRow;
+    b += sizeof(int) * N + sizeof(int16_t) * (size_t)N * kObsRows + 3 * (size_t)N + sizeof(int) * 32;
+    return (b + 63) & ~(size_t)15;
+}
+
+__device__ __forceinline__ MtSmem mt_carve(unsigned char *p, int N) {
+    MtSmem s;
+    s.px = (double *)p; p += sizeof(double) * N;
+    s.py = (double *)p; p += sizeof(double) * N;
+    s.vx = (double *)p; p += sizeof(double) * N;
+    s.vy = (double *)p; p += sizeof(double) * N;
+    s.atk = (double *)p; p += sizeof(double) * N;
+    s.ter = (double *)p; p += sizeof(double) * N;
+    s.xs = (float *)p; p += sizeof(float) * N;
+    s.ys = (float *)p; p += sizeof(float) * N;
+    s.table = (float *)p; p += sizeof(float) * (size_t)(N + 1) * kMtRow;
+    s.hitf = (int *)p; p += sizeof(int) * N;
+    s.misc = (int *)p; p += sizeof(int) * 32;
+    s.sid = (int16_t *)p; p += sizeof(int16_t) * (size_t)N * kObsRows;
+    s.flags = p; p += N;
+    s.team = p; p += N;
+    s.tid = p;
+    return s;
+}
+
+// entity record envs/collective_assault_env.py:116-128: [alive, x, y, atk_rad, vx, vy, iden, terrain, bi_hot(tid) x8, team]
+__device__ __forceinline__ void mt_build_row(const MtSmem &s, int i) {
+    float *r = s.table + (size_t)i * kMtRow;
+    const bool alive = s.flags[i] & MT_ALIVE;
+    const float x = (float)s.px[i], y = (float)s.py[i];
+    r[0] = alive ? 1.f : 0.f; r[1] = x; r[2] = y; r[3] = (float)s.atk[i];
+    r[4] = (float)s.vx[i]; r[5] = (float)s.vy[i]; r[6] = (float)i; r[7] = (float)s.ter[i];
+    int v = s.tid[i];  // get_binary_n_rows: n_int / 2 as float, then .astype(np.int8)
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        r[8 + b] = (float)((((v % 2) + 2) % 2) == 1);
+        v = (int)(signed char)(int)((double)v / 2.0);
+    }
+    r[16] = (float)s.team[i];
+    s.xs[i] = alive ? x : CUDART_INF_F;
+    s.ys[i] = alive ? y : CUDART_INF_F;
+}
+
+// observation of every agent (envs/collective_assault_env.py:131-226) + coalesced gather into dest [N,12,17]
+__device__ __forceinline__ void mt_obs_pass(const MtSmem &s, const MtParams &P, int e, float *dest, uint32_t counter,
+                                            const int *first) {
+    const int tid = threadIdx.x, N = P.N;
+    const uint32_t k0 = (uint32_t)P.cfg.seed, k1 = (uint32_t)(P.cfg.seed >> 32);
+    const uint32_t gid = (uint32_t)(P.cfg.env_gid0 + e);
+    if (dest != nullptr) {
+        for (int task = tid; task < 2 * N; task += kMtThreads) {
+            const int g = task >> 1, lst = task & 1;  // 0 = hostile (rows 6..11), 1 = friend (rows 0..5, row 0 = self)
+            int16_t *sid = s.sid + g * kObsRows + (lst == 0 ? kVisN : 0);
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k) sid[k] = -1;
+            if (!(s.flags[g] & MT_ALIVE)) continue;  // :176-179 zeros, no draws
+            const int tm = s.team[g];
+            const int own0 = first[tm], own1 = first[tm + 1];
+            const float lim = lst == 0 ? 2.0f : 3.0f;  // obs_range, obs_range * 1.5
+            const float gx = s.xs[g], gy = s.ys[g];
+            float bd[kVisN];
+            int bi[kVisN];
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
+            // candidates in uid order (ally list = own team, foe list = the other teams in team order, :162-170);
+            // argsort()[:6] + range mask == the 6 nearest in range, ties by list position
+            const int j0 = lst == 1 ? own0 : 0, j1 = lst == 1 ? own1 : N;
+            for (int j = j0; j < j1; ++j) {
+                if (lst == 0 && j >= own0 && j < own1) { j = own1 - 1; continue; }
+                const float d = f32_dist(gx, gy, s.xs[j], s.ys[j]);  // dead = +inf
+                if (d <= lim) {
+                    bool p[kVisN];
+#pragma unroll
+                    for (int k = 0; k < kVisN; ++k) p[k] = d < bd[k];
+#pragma unroll
+                    for (int k = kVisN - 1; k >= 1; --k) {
+                        bd[k] = p[k] ? (p[k - 1] ? bd[k - 1] : d) : bd[k];
+                        bi[k] = p[k] ? (p[k - 1] ? bi[k - 1] : j) : bi[k];
+                    }
+                    bd[0] = p[0] ? d : bd[0];
+                    bi[0] = p[0] ? j : bi[0];
+                }
+            }
+            int n = 0;
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k) n += bi[k] >= 0;
+            int row = 0, firstv = 0;
+            if (lst == 1) { sid[row++] = (int16_t)bi[0]; firstv = 1; }  // self = first visible friend (:207-208)
+            const int m = n - firstv;
+            int keep = m;
+            if (m > 0) {
+                uint32_t w[DCA_RNG_WORDS];
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    const uint4 q = philox4x32_10(gid, counter, (uint32_t)(g * 2 + lst), SITE_OBS | (b << 8), k0, k1);
+                    w[4 * b] = q.x; w[4 * b + 1] = q.y; w[4 * b + 2] = q.z; w[4 * b + 3] = q.w;
+                }
+                // item_random_mv :103-113 on positions firstv .. firstv+m-1
+#pragma unroll
+                for (int i = kVisN - 1; i >= 1; --i) {
+                    if (i < m) {
+                        const int j = (int)__umulhi(w[2 * i], (uint32_t)(i + 1));
+                        // swap entries firstv+i and firstv+j (register array: resolved by unrolled selects)
+                        int vi = 0, vj = 0;
+#pragma unroll
+                        for (int k = 0; k < kVisN; ++k) { vi = (k == firstv + i) ? bi[k] : vi; vj = (k == firstv + j) ? bi[k] : vj; }
+#pragma unroll
+                        for (int k = 0; k < kVisN; ++k) bi[k] = (k == firstv + i) ? vj : ((k == firstv + j) ? vi : bi[k]);
+                    }
+                }
+                int n_mv = 0;
+#pragma unroll
+                for (int k = 0; k < kVisN; ++k) {
+                    const int wi = k == 0 ? 0 : 2 * k - 1;
+                    if (k < m) n_mv += ((unsigned long long)w[wi] < P.jam_thresh) ? 1 : 0;
+                }
+                keep = m - n_mv;
+            }
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k)
+                if (k >= firstv && k < firstv + keep) sid[row++] = (int16_t)bi[k];
+        }
+    }
+    __syncthreads();
+    if (dest != nullptr) {
+        // gather: float4 stores over the env's contiguous [N*204] floats; a float4 may straddle two records
+        float4 *o4 = (float4 *)(dest + (size_t)e * N * kMtLen);
+        const int total4 = N * kMtLen / 4;  // 204 = 4 * 51
+        for (int q = tid; q < total4; q += kMtThreads) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int f = 4 * q + u;
+                const int slot = f / kMtRow, c = f - slot * kMtRow;  // slot = agent * 12 + row
+                const int id = s.sid[slot];
+                v[u] = s.table[(size_t)(id < 0 ? N : id) * kMtRow + c];
+            }
+            o4[q] = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        if (P.out.slot_id) {
+            int16_t *o = P.out.slot_id + (size_t)e * N * kObsRows;
+            for (int t = tid; t < N * kObsRows; t += kMtThreads) o[t] = s.sid[t];
+        }
+    }
+}
+
+// reset_world envs/collective_assault_env.py:42-82 (keyed draws), then reset(): BSA = all, terrain (parallel_run.py:197-203)
+__device__ __forceinline__ void mt_reset_world(const MtSmem &s, const MtParams &P, int e, uint32_t episode,
+                                               double *theta_out) {
+    const int tid = threadIdx.x, N = P.N;
+    const DcaMtConfig &c = P.cfg;
+    const uint32_t k0 = (uint32_t)c.seed, k1 = (uint32_t)(c.seed >> 32);
+    const uint32_t gid = (uint32_t)(c.env_gid0 + e);
+    const uint4 ww = philox4x32_10(gid, episode, 0u, SITE_RESET, k0, k1);
+    const double theta = (2 * ((double)ww.x * 0x1p-32) - 1) * kPi;
+    const double random_theta = (2 * ((double)ww.y * 0x1p-32) - 1) * kPi;
+    *theta_out = theta;
+    const double ct = cos(theta), st = sin(theta);
+    for (int i = tid; i < N; i += kMtThreads) {
+        const int tm = s.team[i], t = s.tid[i];
+        const double team_pos_dir = (2 * kPi / c.n_team) * tm + random_theta;
+        const double cs = cos(team_pos_dir), sn = sin(team_pos_dir);
+        const double x_ = 0.0 + c.init_distance / 2 + 0.1 * (t % 5);
+        const double y_ = 0.0 + ((double)(t / 5) / ((double)c.team_size[tm] / 5) - 0.5) * 10.0 * 0.25;
+        const double x = x_ * cs + y_ * (-sn), y = x_ * sn + y_ * cs;
+        const uint4 wa = philox4x32_10(gid, episode, (uint32_t)(1 + i), SITE_RESET, k0, k1);
+        s.px[i] = x; s.py[i] = y; s.vx[i] = 0.0; s.vy[i] = 0.0;
+        s.atk[i] = (team_pos_dir + kPi) + (((double)wa.x * 0x1p-32) - 0.5) / 12;
+        s.flags[i] = (uint8_t)((s.flags[i] & MT_JUST_DIED) | MT_ALIVE | MT_BSA);  // hit / wasHit cleared, justDied kept
+        s.ter[i] = c.introduce_terrain ? terrain_fn(c.terrain_A, c.terrain_B, x, y, ct, st) : 1.0;
+        mt_build_row(s, i);
+    }
+}
+
+__device__ __forceinline__ void mt_load(const MtSmem &s, const MtParams &P, int e, int *first) {
+    const int N = P.N;
+    int k = 0;
+    for (int t = 0; t < P.cfg.n_team; ++t) { first[t] = k; k += P.cfg.team_size[t]; }
+    for (int t = P.cfg.n_team; t <= DCA_MT_MAX_TEAMS; ++t) first[t] = k;
+    for (int i = threadIdx.x; i < N; i += kMtThreads) {
+        const size_t g = (size_t)e * N + i;
+        const double2 p = ((const double2 *)P.st.pos)[g], v = ((const double2 *)P.st.vel)[g];
+        s.px[i] = p.x; s.py[i] = p.y; s.vx[i] = v.x; s.vy[i] = v.y;
+        s.atk[i] = P.st.atk_rad[g]; s.ter[i] = P.st.terrain[g];
+        s.flags[i] = (uint8_t)((P.st.alive[g] ? MT_ALIVE : 0) | (P.st.just_died[g] ? MT_JUST_DIED : 0) |
+                               (P.st.hit[g] ? MT_HIT : 0) | (P.st.was_hit[g] ? MT_WAS_HIT : 0) | (P.st.bsa[g] ? MT_BSA : 0));
+        int tm = 0;
+        while (i >= first[tm + 1]) ++tm;
+        s.team[i] = (uint8_t)tm; s.tid[i] = (uint8_t)(i - first[tm]);
+    }
+    for (int c = threadIdx.x; c < kMtRow; c += kMtThreads) s.table[(size_t)N * kMtRow + c] = 0.f;
+    if (threadIdx.x < 32) s.misc[threadIdx.x] = 0;
+}
+
+__device__ __forceinline__ void mt_store(const MtSmem &s, const MtParams &P, int e) {
+    const int N = P.N;
+    for (int i = threadIdx.x; i < N; i += kMtThreads) {
+        const size_t g = (size_t)e * N + i;
+        ((double2 *)P.st.pos)[g] = make_double2(s.px[i], s.py[i]);
+        ((double2 *)P.st.vel)[g] = make_double2(s.vx[i], s.vy[i]);
+        P.st.atk_rad[g] = s.atk[i]; P.st.terrain[g] = s.ter[i];
+        const uint8_t f = s.flags[i];
+        P.st.alive[g] = (f & MT_ALIVE) != 0; P.st.just_died[g] = (f & MT_JUST_DIED) != 0;
+        P.st.hit[g] = (f & MT_HIT) != 0; P.st.was_hit[g] = (f & MT_WAS_HIT) != 0; P.st.bsa[g] = (f & MT_BSA) != 0;
+        if (P.out.alive) P.out.alive[g] = (f & MT_ALIVE) != 0;
+    }
+}
+
+__global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const int32_t *__restrict__ actions,
+                                                         const uint8_t *__restrict__ skip, int autoreset) {
+    extern __shared__ __align__(16) unsigned char mt_raw[];
+    const int e = blockIdx.x, tid = threadIdx.x, N = P.N;
+    if (skip != nullptr && skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay
+    const MtSmem s = mt_carve(mt_raw, N);
+    const DcaMtConfig &c = P.cfg;
+    int first[DCA_MT_MAX_TEAMS + 1];
+    mt_load(s, P, e, first);
+    double theta = P.st.init_theta[e];
+    const int time_step = P.st.time_step[e];
+    uint32_t counter = P.st.obs_counter[e], episode = P.st.episode[e];
+    const uint32_t k0 = (uint32_t)c.seed, k1 = (uint32_t)(c.seed >> 32);
+    const uint32_t gid = (uint32_t)(c.env_gid0 + e);
+    __syncthreads();
+    // ---- set_terrain_adv (parallel_run.py:164) for the agents of the previous step's list; then World.step's new list,
+    // hit flags cleared for its members (core.py:101, :161-165)
+    {
+        const double ct = cos(theta), st = sin(theta);
+        for (int i = tid; i < N; i += kMtThreads) {
+            uint8_t f = s.flags[i];
+            if (f & MT_BSA) s.ter[i] = c.introduce_terrain ? terrain_fn(c.terrain_A, c.terrain_B, s.px[i], s.py[i], ct, st) : 1.0;
+            f = (uint8_t)(f & ~MT_BSA);
+            if (f & MT_ALIVE) f = (uint8_t)((f | MT_BSA) & ~(MT_HIT | MT_WAS_HIT));
+            s.flags[i] = f;
+            s.hitf[i] = 0;
+        }
+    }
+    __syncthreads();
+    // ---- laser core.py:167-190: every alive shooter against every alive agent of another team
+    for (int i = tid; i < N; i += kMtThreads) {
+        if (!(s.flags[i] & MT_BSA)) continue;
+        const double radius = 0.4 * s.ter[i], r2 = radius * radius, win = kPi / 4;
+        const double xi = s.px[i], yi = s.py[i], dir = s.atk[i];
+        const int tm = s.team[i];
+        for (int j = 0; j < N; ++j) {
+            if (!(s.flags[j] & MT_BSA) || s.team[j] == tm) continue;
+            const double dx = s.px[j] - xi, dy = s.py[j] - yi;
+            if (dx * dx + dy * dy > r2) continue;
+            const double tt = atan2(dy, dx);
+            const double d1 = fabs(reg_angle((dir + win / 2) - tt)), d2 = fabs(reg_angle((dir - win / 2) - tt));
+            if (!(d1 <= win && d2 <= win)) continue;
+            const double adv = fmax(fmin(s.ter[i] - s.ter[j], 0.1), -0.1);
+            const double prob = 0.8 + adv;
+            const uint4 w = philox4x32_10(gid, counter, (uint32_t)(i * N + j), SITE_MT_LASER, k0, k1);
+            if (((double)w.x * 0x1p-32) < prob) { atomicOr(&s.hitf[i], 1); atomicOr(&s.hitf[j], 2); }
+        }
+    }
+    __syncthreads();
+    // ---- deaths (:193-201), integrate (:204-222, just-killed agents still move), kill circle (:115-132), records
+    {
+        const double frac = fmin((double)time_step / (double)c.steps_to_narrow, 1.0);
+        const double cur = c.size + (c.size / 3.5 - c.size) * frac, cur2 = cur * cur;
+        for (int i = tid; i < N; i += kMtThreads) {
+            uint8_t f = s.flags[i];
+            if (!(f & MT_ALIVE)) f = (uint8_t)(f & ~MT_JUST_DIED);
+            if (f & MT_BSA) {
+                const int h = s.hitf[i];
+                if (h & 1) f |= MT_HIT;
+                if (h & 2) { f |= MT_WAS_HIT; f = (uint8_t)((f & ~MT_ALIVE) | MT_JUST_DIED); }
+                const int a = actions[(size_t)e * N + i];
+                double a0 = 0, a1 = 0, ar = 0;
+                if (a == 1) a0 = +1.0;
+                if (a == 2) a0 = -1.0;
+                if (a == 3) a1 = +1.0;
+                if (a == 4) a1 = -1.0;
+                if (a == 5) ar = +0.17;
+                if (a == 6) ar = -0.17;
+                double vx = s.vx[i] * (1 - 0.25), vy = s.vy[i] * (1 - 0.25);
+                vx += ((a0 * 3) / 1.0) * 0.1; vy += ((a1 * 3) / 1.0) * 0.1;
+                const double speed = sqrt(vx * vx + vy * vy);
+                if (speed > 1.0) { vx = vx / speed * 1.0; vy = vy / speed * 1.0; }
+                s.vx[i] = vx; s.vy[i] = vy;
+                if (f & MT_ALIVE) s.atk[i] = reg_angle(s.atk[i] + ar);
+                const double x = s.px[i] + vx * 0.1, y = s.py[i] + vy * 0.1;
+                s.px[i] = x; s.py[i] = y;
+                if ((f & MT_ALIVE) && x * x + y * y > cur2) f = (uint8_t)((f & ~MT_ALIVE) | MT_WAS_HIT | MT_JUST_DIED);
+            }
+            s.flags[i] = f;
+            mt_build_row(s, i);
+            if (f & MT_ALIVE) atomicAdd(&s.misc[s.team[i]], 1);
+            // reward envs/collective_assault_env.py:87-95
+            float r = 0.f;
+            if (f & (MT_ALIVE | MT_JUST_DIED)) {
+                if (f & MT_HIT) r += 1.f;
+                if (f & MT_WAS_HIT) r = c.half_death_reward ? -0.5f : -1.f;
+            }
+            P.out.reward[(size_t)e * N + i] = r;
+        }
+    }
+    __syncthreads();
+    // ---- done / ranking parallel_run.py:219-245 (every thread computes the same flags)
+    int teams_alive = 0;
+    for (int t = 0; t < c.n_team; ++t) teams_alive += s.misc[t] > 0;
+    const bool done = teams_alive <= 1 || time_step == c.max_episode_step - 1;
+    if (tid == 0) {
+        P.out.done[e] = done;
+        if (done) {
+            bool all0 = true;
+            int rk[DCA_MT_MAX_TEAMS];
+            for (int t = 0; t < c.n_team; ++t) {
+                int r = 0;
+                for (int u = 0; u < c.n_team; ++u) r += s.misc[u] > s.misc[t];
+                rk[t] = r;
+                all0 &= r == 0;
+            }
+            for (int t = 0; t < c.n_team; ++t) P.out.ranking[(size_t)e * c.n_team + t] = all0 ? -1 : rk[t];
+        }
+    }
+    int new_time = time_step + 1;
+    counter += 1;
+    if (done && autoreset) {
+        mt_obs_pass(s, P, e, P.out.tobs, counter, first);  // terminal obs = info['obs-echo'] (tobs may be NULL)
+        __syncthreads();
+        episode += 1;
+        mt_reset_world(s, P, e, episode, &theta);
+        new_time = 0;
+        counter += 1;
+        __syncthreads();
+    }
+    mt_obs_pass(s, P, e, P.out.obs, counter, first);
+    mt_store(s, P, e);
+    if (tid == 0) {
+        P.st.init_theta[e] = theta; P.st.time_step[e] = new_time;
+        P.st.obs_counter[e] = counter; P.st.episode[e] = episode;
+    }
+}
+
+// reset(): masked envs get a fresh episode + observation (EnvAutoReset.reset / first manual reset)
+__global__ void __launch_bounds__(kMtThreads) k_mt_reset(const MtParams P, const uint8_t *__restrict__ mask) {
+    extern __shared__ __align__(16) unsigned char mt_raw[];
+    const int e = blockIdx.x;
+    if (mask != nullptr && !mask[e]) return;
+    const MtSmem s = mt_carve(mt_raw, P.N);
+    int first[DCA_MT_MAX_TEAMS + 1];
+    mt_load(s, P, e, first);
+    const uint32_t episode = P.st.episode[e] + 1, counter = P.st.obs_counter[e] + 1;
+    double theta;
+    __syncthreads();
+    mt_reset_world(s, P, e, episode, &theta);
+    __syncthreads();
+    mt_obs_pass(s, P, e, P.out.obs, counter, first);
+    mt_store(s, P, e);
+    if (threadIdx.x == 0) {
+        P.st.init_theta[e] = theta; P.st.time_step[e] = 0;
+        P.st.obs_counter[e] = counter; P.st.episode[e] = episode;
+        if (P.out.done) P.out.done[e] = 0;
+    }
+}
+
+__global__ void k_mt_init(MtParams P) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < P.E) { P.st.episode[e] = 0xFFFFFFFFu; P.st.obs_counter[e] = 0xFFFFFFFFu; }
+}
+
+}  // namespace dca

@@ -181,6 +181,56 @@ int dca_adv_moments(const float *ret, const float *value, const uint8_t *valid, 
 int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
                       const double *stats, float *adv, dca_stream_t stream);
 
+/* ---- dca_multiteam -------------------------------------------------------------------------------------------------
+ * The sibling env MISSION/dca_multiteam (N teams, every agent policy-controlled, per-hit success draw, shrinking kill
+ * circle, team ranking).  Same conventions as the dca_* calls above. */
+#define DCA_MT_MAX_TEAMS 8
+#define DCA_MT_OBS_ROW 17 /* ScenarioConfig.obs_vec_length, MISSION/dca_multiteam/collective_assault_parallel_run.py:62 */
+/* POD snapshot of MISSION/dca_multiteam ScenarioConfig (collective_assault_parallel_run.py:27-77) */
+typedef struct DcaMtConfig {
+    int32_t n_team;
+    int32_t team_size[DCA_MT_MAX_TEAMS]; /* N_AGENT_EACH_TEAM; uids are contiguous per team (arrange_id) */
+    double size, random_jam_prob;
+    int32_t introduce_terrain;
+    double terrain_A, terrain_B;
+    int32_t max_episode_step, steps_to_narrow; /* MaxEpisodeStep, StepsToNarrowCircle */
+    double init_distance;
+    int32_t half_death_reward;
+    uint64_t seed;
+    int64_t env_gid0;
+} DcaMtConfig;
+/* Output buffers (caller-owned, written in place).  replaces: the (ob, reward, done, info) tuple of EnvAutoReset.step
+ * UTIL/shm_env.py:33-74 around collective_assaultGlobalEnv.step dca_multiteam/collective_assault_parallel_run.py:156-191 */
+typedef struct DcaMtBuffers {
+    float *obs;       /* [E,N,12,17] post-step obs (post-RESET obs where done) */
+    float *tobs;      /* [E,N,12,17] terminal obs = info['obs-echo'], written where done; may be NULL */
+    float *reward;    /* [E,N] */
+    uint8_t *done;    /* [E] */
+    int32_t *ranking; /* [E,n_team] info['team_ranking'] (0 = first, -1 = all teams draw), written where done */
+    uint8_t *alive;   /* [E,N]; may be NULL */
+    int16_t *slot_id; /* [E,N,12] uid gathered into each obs row, -1 = zero row; may be NULL */
+} DcaMtBuffers;
+/* SoA view of the env state for export / import (device pointers, all required) */
+typedef struct DcaMtState {
+    double *pos, *vel, *atk_rad, *terrain;              /* [E,N,2] [E,N,2] [E,N] [E,N] */
+    uint8_t *alive, *just_died, *hit, *was_hit, *bsa;   /* [E,N]; bsa = member of World.before_step_alive_agents */
+    double *init_theta;                                 /* [E] */
+    int32_t *time_step;                                 /* [E] */
+    uint32_t *obs_counter, *episode;                    /* [E] keyed-RNG counters */
+} DcaMtState;
+typedef struct DcaMtHandle DcaMtHandle;
+/* replaces: make_collective_assault_env dca_multiteam/collective_assault_parallel_run.py:80-89 x n_env */
+int dca_mt_create(const DcaMtConfig *cfg, int n_env, int device, DcaMtHandle **out);
+int dca_mt_destroy(DcaMtHandle *h);
+int dca_mt_bind_buffers(DcaMtHandle *h, const DcaMtBuffers *b);
+/* replaces: collective_assaultGlobalEnv.reset :193-209 (env_mask u8[E], NULL = all) */
+int dca_mt_reset(DcaMtHandle *h, const uint8_t *env_mask, dca_stream_t stream);
+/* replaces: EnvAutoReset.step UTIL/shm_env.py:33-74 -> collective_assaultGlobalEnv.step :156-191.
+ * actions i32[E,N] in 0..6 (one per agent, all teams); skip u8[E] (NULL = none) = NaN action rows. */
+int dca_mt_step(DcaMtHandle *h, const int32_t *actions, const uint8_t *skip, int autoreset, dca_stream_t stream);
+int dca_mt_export_state(DcaMtHandle *h, const DcaMtState *dst, dca_stream_t stream);
+int dca_mt_import_state(DcaMtHandle *h, const DcaMtState *src, dca_stream_t stream);
+
 /* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a
  * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
  * it (ALGORITHM/conc/shell_env.py:72-75); default 0 = the env's own zeros (collective_assault_env.py:313-316,340-343). */

@@ -117,3 +117,155 @@ def test_mt_oracle_reset_matches_reference(name):
     for k in FLOAT_KEYS:
         gu.assert_close_rel(env.state[k][0], case['s0_' + k], 1e-12, 'reset ' + k, atol=1e-14)
     compare_obs('reset obs', obs[0], case['obs0'], case['s0_pos'])
+
+
+# ------------------------------------------------------------------------------------------------ CUDA path
+def _mt_scfg(cfg):
+    from hmp2g_b200.multiteam import MtScenarioConfig
+    c = type('CaseMtScenarioConfig', (MtScenarioConfig,), {})
+    for k, v in cfg.items():
+        assert hasattr(MtScenarioConfig, k), k
+        setattr(c, k, v)
+    return c
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', CASES)
+def test_cuda_mt_matches_reference_golden(name):
+    import torch
+    assert torch.cuda.is_available()
+    from hmp2g_b200.multiteam import DcaMultiTeamVecEnv
+    case = load_case(name)
+    env = DcaMultiTeamVecEnv(2, scfg=_mt_scfg(case['cfg']), seed=case['seed'], env_gid0=case['gid'], debug_outputs=True)
+    s0 = {k: case['s0_' + k] for k in STATE_KEYS}
+    env.import_state({k: np.stack([v, v]) for k, v in s0.items()})  # env 1: a bystander with another global id
+    want_tobs = {int(t): case['tobs'][k] for k, t in enumerate(case['tobs_steps'])}
+    dev = env.device
+    n_tie = n_rows = 0
+    for t in range(case['actions'].shape[0]):
+        a = case['actions'][t]
+        skip = bool(np.isnan(a).any())
+        act = torch.from_numpy(np.tile(np.where(np.isnan(a), 0, a).astype(np.int32), (2, 1))).to(dev)
+        env.step(act, skip=torch.full((2,), int(skip), dtype=torch.uint8, device=dev))
+        st = {k: v[0] for k, v in env.export_state().items()}
+        obs = env.obs[0].reshape(env.N, 204).cpu().numpy()
+        tag = '%s t=%d' % (name, t)
+        n_tie += check_step(tag, st, obs, env.reward[0].cpu().numpy(), int(env.done[0]), env.ranking[0].cpu().numpy(),
+                            case, t)
+        n_rows += obs.size // 17
+        assert np.array_equal(slot_ids(obs), env.slot_id[0].cpu().numpy().astype(np.int32)), tag
+        assert np.array_equal(env.alive[0].cpu().numpy(), case['alive'][t]), tag
+        if t in want_tobs:
+            tobs = env.tobs[0].reshape(env.N, 204).cpu().numpy()
+            ta, tb = slot_ids(tobs), slot_ids(want_tobs[t])
+            assert np.array_equal(ta >= 0, tb >= 0), tag
+            same = (ta == tb)[..., None] & np.ones((1, 1, 17), bool)
+            gu.assert_close_rel(np.where(same, tobs.reshape(-1, 12, 17), 0),
+                                np.where(same, want_tobs[t].reshape(-1, 12, 17), 0), RTOL, 'tobs', atol=1e-12)
+    assert n_tie < 0.02 * n_rows
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', CASES)
+def test_cuda_mt_reset_matches_reference(name):
+    import torch
+    from hmp2g_b200.multiteam import DcaMultiTeamVecEnv
+    case = load_case(name)
+    env = DcaMultiTeamVecEnv(1, scfg=_mt_scfg(case['cfg']), seed=case['seed'], env_gid0=case['gid'])
+    env.reset()
+    st = env.export_state()
+    for k in INT_KEYS:
+        if k == 'just_died':
+            continue
+        assert np.array_equal(np.asarray(st[k][0]).astype(np.int64) & 0xFFFFFFFF,
+                              np.asarray(case['s0_' + k]).astype(np.int64) & 0xFFFFFFFF), k
+    for k in FLOAT_KEYS:
+        gu.assert_close_rel(st[k][0], case['s0_' + k], 1e-9, 'reset ' + k, atol=1e-12)
+    compare_obs('reset obs', env.obs[0].reshape(env.N, 204).cpu().numpy(), case['obs0'], case['s0_pos'])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('cfg,E,steps', [
+    (dict(N_AGENT_EACH_TEAM=[25, 25], random_jam_prob=0.05, introduce_terrain=True, terrain_parameters=[0.05, 0.2],
+          MaxEpisodeStep=40, StepsToNarrowCircle=25, init_distance=1.5), 256, 100),
+    (dict(N_AGENT_EACH_TEAM=[6, 30, 11, 8], random_jam_prob=0.3, MaxEpisodeStep=25, StepsToNarrowCircle=10, size=3.0,
+          init_distance=1.0, half_death_reward=False), 64, 80),
+    (dict(N_AGENT_EACH_TEAM=[100, 100], introduce_terrain=True, terrain_parameters=[0.15, 0.2], MaxEpisodeStep=30,
+          StepsToNarrowCircle=20, init_distance=2.0), 16, 45),
+])
+def test_cuda_mt_vs_oracle_fresh_rollouts(cfg, E, steps):
+    """GPU and oracle side by side from their own resets, no resync: integer outputs bit-exact (alive, flags, done,
+    ranking, rewards), floats within 1e-5, observation rows equal up to exactly tied distances."""
+    import torch
+    from hmp2g_b200.multiteam import DcaMultiTeamVecEnv
+    from mt_oracle import OracleMtEnv
+    seed, gid0 = 77, 1000
+    gpu = DcaMultiTeamVecEnv(E, scfg=_mt_scfg(cfg), seed=seed, env_gid0=gid0, debug_outputs=True)
+    orc = OracleMtEnv(cfg, E, seed=seed, env_gid0=gid0)
+    gpu.reset()
+    orc.reset()
+    N = gpu.N
+    rng = np.random.RandomState(5)
+    n_done = n_tie = 0
+    for t in range(steps):
+        a = rng.randint(0, 7, size=(E, N))
+        gpu.step(torch.from_numpy(a.astype(np.int32)).to(gpu.device))
+        obs_o, rew_o, done_o, rank_o = orc.step(a.astype(np.float64))
+        st = gpu.export_state()
+        for k in INT_KEYS:
+            assert np.array_equal(st[k].astype(np.int64) & 0xFFFFFFFF, orc.state[k].astype(np.int64) & 0xFFFFFFFF), (t, k)
+        for k in FLOAT_KEYS:
+            gu.assert_close_rel(st[k], orc.state[k], RTOL, 't=%d %s' % (t, k), atol=1e-12)
+        done_g = gpu.done.cpu().numpy()
+        assert np.array_equal(done_g, done_o), t
+        d = done_o.astype(bool)
+        assert np.array_equal(gpu.ranking.cpu().numpy()[d], rank_o[d]), t
+        assert np.array_equal(gpu.reward.cpu().numpy().astype(np.float64), rew_o), t
+        n_done += int(d.sum())
+        obs_g = gpu.obs.cpu().numpy().reshape(E, N, 204)
+        tobs_g = gpu.tobs.cpu().numpy().reshape(E, N, 204)
+        for e in range(E):
+            n_tie += compare_obs('t=%d e=%d' % (t, e), obs_g[e], obs_o[e], orc.state['pos'][e])
+            if d[e]:
+                same = (slot_ids(tobs_g[e]) == slot_ids(orc.tobs[e]))[..., None] & np.ones((1, 1, 17), bool)
+                gu.assert_close_rel(np.where(same, tobs_g[e].reshape(-1, 12, 17), 0),
+                                    np.where(same, orc.tobs[e].reshape(-1, 12, 17), 0), RTOL, 'tobs', atol=1e-12)
+    assert n_done >= E
+    assert n_tie <= 1e-4 * E * N * 12 * steps  # same tie rule on both sides: only f32-rounding flips of ~1e-16 offsets
+
+
+@pytest.mark.gpu
+def test_cuda_mt_superpool_facade_matches_reference_autoreset():
+    import torch
+    from hmp2g_b200.multiteam import DcaMultiTeamSuperpoolEnv
+    name = '3teams'
+    case = load_case(name)
+    host = DcaMultiTeamSuperpoolEnv(n_env=1, scfg=_mt_scfg(case['cfg']), seed=case['seed'], env_gid0=case['gid'])
+    N = host.env.N
+    obs0, info0 = host.reset()
+    assert obs0.shape == (1, N, 204) and obs0.dtype == np.float32 and info0[0] == {}
+    compare_obs('obs0', obs0[0], case['obs0'], case['s0_pos'])
+    host.env.import_state({k: case['s0_' + k][None] for k in STATE_KEYS})
+    want_tobs = {int(t): case['tobs'][k] for k, t in enumerate(case['tobs_steps'])}
+    last_info = None
+    n_done = n_skip = 0
+    for t in range(case['actions'].shape[0]):
+        a = case['actions'][t]
+        obs, rew, done, info = host.step(a[None])
+        tag = '%s t=%d' % (name, t)
+        assert rew.dtype == np.float64 and done.dtype == bool and info.dtype == object
+        assert bool(done[0]) == bool(case['done'][t]), tag
+        assert np.array_equal(rew[0], case['reward'][t]), tag
+        compare_obs(tag, obs[0], case['obs'][t], case['pos'][t])
+        if np.isnan(a).any():
+            n_skip += 1
+            assert set(info[0]) == set(last_info), tag
+        elif done[0]:
+            n_done += 1
+            assert set(info[0]) == {'team_ranking', 'end_reason', 'obs-echo'}, tag
+            assert np.array_equal(info[0]['team_ranking'], case['ranking'][t]) and info[0]['end_reason'] == 'EndGame'
+            assert np.array_equal(slot_ids(info[0]['obs-echo']) >= 0, slot_ids(want_tobs[t]) >= 0), tag
+        else:
+            assert info[0] == {}, tag
+        last_info = info[0]
+    assert n_done >= 2 and n_skip >= 2
