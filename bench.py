@@ -290,6 +290,27 @@ def run_ours(args):
     ms_runner = g0.elapsed_time(g1) / 50
     hist_bytes = E * G * 12 * 16 * 4 * 5  # obs + history in, obs_feed (2x) + history out
     del hp, run
+    # ---- dca_multiteam (k_mt_step): 2 teams x 25, every agent observed and acting, same env count
+    from hmp2g_b200.multiteam import DcaMultiTeamVecEnv, MtScenarioConfig
+    mt_cfg = type('S', (MtScenarioConfig,), dict(N_AGENT_EACH_TEAM=[25, 25], random_jam_prob=0.05, introduce_terrain=True,
+                                                 terrain_parameters=[0.05, 0.2]))
+    mt = DcaMultiTeamVecEnv(E, scfg=mt_cfg, device=dev, seed=SEED, env_gid0=rank * E)
+    mt.reset()
+    mt_pool = [torch.randint(0, 7, (E, mt.N), device=dev, dtype=torch.int32) for _ in range(8)]
+    for i in range(20):
+        mt.step(mt_pool[i % 8])
+    Km = 300
+    g0.record(stream)
+    for i in range(Km):
+        mt.step(mt_pool[i % 8])
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_mt = g0.elapsed_time(g1) / Km
+    # obs N*816 out; state (pos, vel, atk_rad, terrain f64 + 5 flag bytes) read + written; actions in; reward + alive out
+    mt_bytes = E * mt.N * (12 * 17 * 4 + 2 * (6 * 8 + 5) + 4 + 4 + 1)
+    mt_alive = float(mt.alive.float().mean().item())
+    mt_N = mt.N
+    del mt, mt_pool
 
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
@@ -364,6 +385,10 @@ def run_ours(args):
                             'achieved': hist_bytes / (ms_hist * 1e-3) / 1e9, 'peak': peak,
                             'frac': hist_bytes / (ms_hist * 1e-3) / 1e9 / peak},
         'runner_update_ms': ms_runner,
+        'multiteam_kernel': {'bound': 'hbm', 'kernel': 'k_mt_step', 'workload': 'dca_multiteam 25v25, terrain on, jam 0.05, %d envs' % E,
+                             'kernel_ms': ms_mt, 'agent_steps_per_sec': E * mt_N / (ms_mt * 1e-3), 'unit': 'GB/s',
+                             'achieved': mt_bytes / (ms_mt * 1e-3) / 1e9, 'peak': peak,
+                             'frac': mt_bytes / (ms_mt * 1e-3) / 1e9 / peak, 'alive_fraction_at_end': mt_alive},
         'gae_kernel': {'bound': 'hbm', 'kernel': 'k_gae', 'unit': 'GB/s',
                        'shape_TEG': [T, E, G], 'kernel_ms': ms_gae, 'achieved': gae_bytes / (ms_gae * 1e-3) / 1e9,
                        'peak': peak, 'frac': gae_bytes / (ms_gae * 1e-3) / 1e9 / peak},
