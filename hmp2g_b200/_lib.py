@@ -60,7 +60,7 @@ EXPORTS = ('dca_abi_version', 'dca_last_error', 'dca_create', 'dca_destroy', 'dc
            'dca_step', 'dca_observe', 'dca_plan', 'dca_plan_centroid', 'dca_export_state', 'dca_import_state', 'dca_gae',
            'dca_kernel_launches', 'dca_debug_phase_clocks', 'dca_set_option', 'dca_runner_init', 'dca_runner_update',
            'dca_runner_report', 'dca_histpool_roll', 'dca_adv_moments', 'dca_adv_normalize', 'dca_mt_create', 'dca_mt_destroy',
-           'dca_mt_bind_buffers', 'dca_mt_reset', 'dca_mt_step', 'dca_mt_export_state', 'dca_mt_import_state')
+           'dca_mt_bind_buffers', 'dca_mt_reset', 'dca_mt_step', 'dca_mt_export_state', 'dca_mt_import_state', 'dca_mt_debug_phase_clocks')
 
 _lib = None
 
@@ -109,6 +109,7 @@ def load(build_if_missing=False):
     lib.dca_mt_step.argtypes = [_P, _P, _P, C.c_int, _P]
     lib.dca_mt_export_state.argtypes = [_P, C.POINTER(DcaMtState), _P]
     lib.dca_mt_import_state.argtypes = [_P, C.POINTER(DcaMtState), _P]
+    lib.dca_mt_debug_phase_clocks.argtypes = [_P, _P]
     lib.dca_kernel_launches.argtypes = [_P, C.POINTER(C.c_int64)]
     lib.dca_debug_phase_clocks.argtypes = [_P, _P]
     for name in EXPORTS:

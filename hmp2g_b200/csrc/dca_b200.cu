@@ -429,6 +429,19 @@ int dca_mt_create(const DcaMtConfig *cfg, int n_env, int device, DcaMtHandle **o
         const double t = std::ceil(cfg->random_jam_prob * 4294967296.0);
         h->P.jam_thresh = t <= 0 ? 0ull : (t >= 4294967296.0 ? 4294967296ull : (unsigned long long)t);
     }
+    h->P.smax[0] = sq_limit(2.0f);  // obs_range envs/collective_assault_env.py:148
+    h->P.smax[1] = sq_limit(3.0f);  // obs_range * 1.5 :204
+    {
+        int longest = 0, smallest = N;
+        for (int t = 0; t < cfg->n_team; ++t) {
+            longest = cfg->team_size[t] > longest ? cfg->team_size[t] : longest;
+            smallest = cfg->team_size[t] < smallest ? cfg->team_size[t] : smallest;
+        }
+        longest = (N - smallest) > longest ? (N - smallest) : longest;  // ally list / foe list
+        int bits = 3;
+        while ((1 << bits) < longest) ++bits;
+        h->P.idx_bits = bits;
+    }
     h->smem = (int)mt_smem_bytes(N);
     DcaMtState probe;
     const size_t bytes = mt_carve_state(&probe, nullptr, n_env, N);
@@ -505,6 +518,11 @@ static int mt_state_io(DcaMtHandle *h, const DcaMtState *u, bool import, dca_str
                                         cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
         if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_mt state io: ") + cudaGetErrorString(e));
     }
+    return DCA_OK;
+}
+int dca_mt_debug_phase_clocks(DcaMtHandle *h, uint64_t *clocks) {
+    if (!h) return DCA_E_INVALID;
+    h->P.prof = (unsigned long long *)clocks;
     return DCA_OK;
 }
 int dca_mt_export_state(DcaMtHandle *h, const DcaMtState *dst, dca_stream_t stream) { return mt_state_io(h, dst, false, stream); }

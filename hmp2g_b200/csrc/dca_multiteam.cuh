@@ -15,7 +15,12 @@ namespace dca {
 constexpr int kMtRow = DCA_MT_OBS_ROW;          // 17 floats per entity record
 constexpr int kMtLen = kObsRows * kMtRow;       // 204 floats per agent
 constexpr int kMtThreads = 128;
+constexpr int kMtPairCap = 512;                 // queued in-range laser pairs per env (overflow is tested in place)
 enum : uint32_t { SITE_MT_LASER = 4 };
+#define MT_PROF(P, e, k)                                                                      \
+    do {                                                                                      \
+        if ((P).prof != nullptr && threadIdx.x == 0) (P).prof[(size_t)(e) * 16 + (k)] = clock64(); \
+    } while (0)
 enum : uint8_t { MT_ALIVE = 1, MT_JUST_DIED = 2, MT_HIT = 4, MT_WAS_HIT = 8, MT_BSA = 16 };
 
 struct MtParams {
@@ -24,21 +29,25 @@ struct MtParams {
     DcaMtState st;     // library-owned SoA state
     DcaMtBuffers out;  // caller-owned outputs
     unsigned long long jam_thresh;
+    float smax[2];  // largest float32 s with sqrt_rn(s) <= 2.0 / 3.0: "s <= smax" is the reference's "d <= range"
+    int idx_bits;   // key bits that hold the list position
+    unsigned long long *prof;  // diagnostics: [E,16] clock64() of thread 0 at phase boundaries (NULL = off)
 };
 
 struct MtSmem {
     double *px, *py, *vx, *vy, *atk, *ter;
     float *xs, *ys, *table;  // table: [(N+1)][17], record N = zeros
     int *hitf;               // per agent: bit 0 = hit someone, bit 1 = was hit (this step)
+    int *pairq;              // [kMtPairCap] shooter * N + target
     int16_t *sid;            // [N,12]
     uint8_t *flags, *team, *tid;
-    int *misc;               // [0..7] alive count per team, 8 done, 9.. ranking
+    int *misc;               // [0..7] alive count per team, [16] queued laser pairs, [20..28] first uid of each team
 };
 
 __host__ __device__ inline size_t mt_smem_bytes(int N) {
     size_t b = 6 * sizeof(double) * N;
     b += 2 * sizeof(float) * N + sizeof(float) * (size_t)(N + 1) * kMtRow;
-    b += sizeof(int) * N + sizeof(int16_t) * (size_t)N * kObsRows + 3 * (size_t)N + sizeof(int) * 32;
+    b += sizeof(int) * N + sizeof(int) * kMtPairCap + sizeof(int16_t) * (size_t)N * kObsRows + 3 * (size_t)N + sizeof(int) * 32;
     return (b + 63) & ~(size_t)15;
 }
 
@@ -55,6 +64,7 @@ __device__ __forceinline__ MtSmem mt_carve(unsigned char *p, int N) {
     s.table = (float *)p; p += sizeof(float) * (size_t)(N + 1) * kMtRow;
     s.hitf = (int *)p; p += sizeof(int) * N;
     s.misc = (int *)p; p += sizeof(int) * 32;
+    s.pairq = (int *)p; p += sizeof(int) * kMtPairCap;
     s.sid = (int16_t *)p; p += sizeof(int16_t) * (size_t)N * kObsRows;
     s.flags = p; p += N;
     s.team = p; p += N;
@@ -80,9 +90,62 @@ __device__ __forceinline__ void mt_build_row(const MtSmem &s, int i) {
     s.ys[i] = alive ? y : CUDART_INF_F;
 }
 
+// exact laser test of the ordered pair p = shooter * N + target (already inside the shooter's radius):
+// laser_hit_improve3 (dca_multiteam/cython_func.pyx:22-53), then the success draw core.py:178-190
+// (plain pointers / scalars only: a struct passed by reference to an out-of-line function would live in local memory)
+__device__ __noinline__ void mt_laser_pair(const double *px, const double *py, const double *atk, const double *ter,
+                                           int *hitf, int N, uint32_t gid, uint32_t counter, uint32_t k0, uint32_t k1,
+                                           int p) {
+    const int i = p / N, j = p - i * N;
+    const double win = kPi / 4;
+    const double dx = px[j] - px[i], dy = py[j] - py[i];
+    const double dir = atk[i];
+    const double tt = atan2(dy, dx);
+    const double d1 = fabs(reg_angle((dir + win / 2) - tt)), d2 = fabs(reg_angle((dir - win / 2) - tt));
+    if (!(d1 <= win && d2 <= win)) return;
+    const double adv = fmax(fmin(ter[i] - ter[j], 0.1), -0.1);
+    const double prob = 0.8 + adv;
+    const uint4 w = philox4x32_10(gid, counter, (uint32_t)p, SITE_MT_LASER, k0, k1);
+    if (((double)w.x * 0x1p-32) < prob) { atomicOr(&hitf[i], 1); atomicOr(&hitf[j], 2); }
+}
+
+// Exact (rare) path of one observation task: the 6 nearest in-range candidates by (sqrt_rn distance, list position),
+// taken when two keys of the fast path are too close to call.
+__device__ __noinline__ unsigned long long mt_top6_exact(const float *xs, const float *ys, int g, int lst, int own0,
+                                                          int own1, int N, float lim, int *n_out) {
+    float bd[kVisN];
+    int bi[kVisN];
+#pragma unroll
+    for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
+    const float gx = xs[g], gy = ys[g];
+    const int j0 = lst == 1 ? own0 : 0, j1 = lst == 1 ? own1 : N;
+    for (int j = j0; j < j1; ++j) {
+        if (lst == 0 && j >= own0 && j < own1) { j = own1 - 1; continue; }
+        const float d = f32_dist(gx, gy, xs[j], ys[j]);  // dead = +inf
+        if (d <= lim) {
+            bool p[kVisN];
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k) p[k] = d < bd[k];
+#pragma unroll
+            for (int k = kVisN - 1; k >= 1; --k) {
+                bd[k] = p[k] ? (p[k - 1] ? bd[k - 1] : d) : bd[k];
+                bi[k] = p[k] ? (p[k - 1] ? bi[k - 1] : j) : bi[k];
+            }
+            bd[0] = p[0] ? d : bd[0];
+            bi[0] = p[0] ? j : bi[0];
+        }
+    }
+    unsigned long long vis = 0;
+    int n = 0;
+#pragma unroll
+    for (int k = 0; k < kVisN; ++k)
+        if (bi[k] >= 0) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
+    *n_out = n;
+    return vis;
+}
+
 // observation of every agent (envs/collective_assault_env.py:131-226) + coalesced gather into dest [N,12,17]
-__device__ __forceinline__ void mt_obs_pass(const MtSmem &s, const MtParams &P, int e, float *dest, uint32_t counter,
-                                            const int *first) {
+__device__ __forceinline__ void mt_obs_pass(const MtSmem &s, const MtParams &P, int e, float *dest, uint32_t counter) {
     const int tid = threadIdx.x, N = P.N;
     const uint32_t k0 = (uint32_t)P.cfg.seed, k1 = (uint32_t)(P.cfg.seed >> 32);
     const uint32_t gid = (uint32_t)(P.cfg.env_gid0 + e);
@@ -94,75 +157,96 @@ __device__ __forceinline__ void mt_obs_pass(const MtSmem &s, const MtParams &P, 
             for (int k = 0; k < kVisN; ++k) sid[k] = -1;
             if (!(s.flags[g] & MT_ALIVE)) continue;  // :176-179 zeros, no draws
             const int tm = s.team[g];
-            const int own0 = first[tm], own1 = first[tm + 1];
-            const float lim = lst == 0 ? 2.0f : 3.0f;  // obs_range, obs_range * 1.5
+            const int own0 = s.misc[20 + tm], own1 = s.misc[21 + tm];
+            const float lim = lst == 0 ? 2.0f : 3.0f;  // obs_range, obs_range * 1.5 (P.smax = the same limits, squared)
             const float gx = s.xs[g], gy = s.ys[g];
-            float bd[kVisN];
-            int bi[kVisN];
-#pragma unroll
-            for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
             // candidates in uid order (ally list = own team, foe list = the other teams in team order, :162-170);
-            // argsort()[:6] + range mask == the 6 nearest in range, ties by list position
+            // argsort()[:6] + range mask == the 6 nearest in range, ties by list position.
+            // Fast path (as DCA's knn_task): 7-slot min/max network on 32-bit keys = float32 squared-distance bits with
+            // the low idx_bits replaced by the list position; sqrt_rn is monotone, so key order == (distance, position)
+            // order unless two of the kept keys are within one key step -- then the exact serial path decides.
             const int j0 = lst == 1 ? own0 : 0, j1 = lst == 1 ? own1 : N;
+            const int nown = own1 - own0;
+            const float q0 = P.smax[lst];
+            const uint32_t im = (1u << P.idx_bits) - 1u;
+            uint32_t b[kVisN + 1];
+#pragma unroll
+            for (int k = 0; k <= kVisN; ++k) b[k] = 0x80000000u + ((uint32_t)k << 8);  // empty: distinct, ascending
             for (int j = j0; j < j1; ++j) {
                 if (lst == 0 && j >= own0 && j < own1) { j = own1 - 1; continue; }
-                const float d = f32_dist(gx, gy, s.xs[j], s.ys[j]);  // dead = +inf
-                if (d <= lim) {
-                    bool p[kVisN];
+                const float sq = f32_sqdist(gx, gy, s.xs[j], s.ys[j]);  // dead = +inf
+                const uint32_t pos = (uint32_t)(lst == 1 ? j - own0 : (j < own0 ? j : j - nown));
+                uint32_t key = sq <= q0 ? ((__float_as_uint(sq) & ~im) | pos) : 0xFFFFFFFFu;
 #pragma unroll
-                    for (int k = 0; k < kVisN; ++k) p[k] = d < bd[k];
-#pragma unroll
-                    for (int k = kVisN - 1; k >= 1; --k) {
-                        bd[k] = p[k] ? (p[k - 1] ? bd[k - 1] : d) : bd[k];
-                        bi[k] = p[k] ? (p[k - 1] ? bi[k - 1] : j) : bi[k];
-                    }
-                    bd[0] = p[0] ? d : bd[0];
-                    bi[0] = p[0] ? j : bi[0];
+                for (int k = 0; k <= kVisN; ++k) {
+                    const uint32_t lo = min(b[k], key);
+                    key = max(b[k], key);
+                    b[k] = lo;
                 }
             }
+            bool close_call = false;
+#pragma unroll
+            for (int k = 0; k < kVisN; ++k)
+                close_call |= ((int32_t)b[k + 1] >= 0) && ((b[k + 1] >> P.idx_bits) - (b[k] >> P.idx_bits) <= 1u);
+            // visible uids packed one byte each, nearest first
+            unsigned long long vis = 0;
             int n = 0;
+            if (close_call) {
+                vis = mt_top6_exact(s.xs, s.ys, g, lst, own0, own1, N, lim, &n);
+            } else {
 #pragma unroll
-            for (int k = 0; k < kVisN; ++k) n += bi[k] >= 0;
-            int row = 0, firstv = 0;
-            if (lst == 1) { sid[row++] = (int16_t)bi[0]; firstv = 1; }  // self = first visible friend (:207-208)
-            const int m = n - firstv;
-            int keep = m;
-            if (m > 0) {
-                uint32_t w[DCA_RNG_WORDS];
-#pragma unroll
-                for (int b = 0; b < 3; ++b) {
-                    const uint4 q = philox4x32_10(gid, counter, (uint32_t)(g * 2 + lst), SITE_OBS | (b << 8), k0, k1);
-                    w[4 * b] = q.x; w[4 * b + 1] = q.y; w[4 * b + 2] = q.z; w[4 * b + 3] = q.w;
+                for (int k = 0; k < kVisN; ++k) {
+                    if ((int32_t)b[k] >= 0) {
+                        const int pos = (int)(b[k] & im);
+                        const int uid = lst == 1 ? own0 + pos : (pos < own0 ? pos : pos + nown);
+                        vis |= (unsigned long long)uid << (8 * n);
+                        ++n;
+                    }
                 }
-                // item_random_mv :103-113 on positions firstv .. firstv+m-1
+            }
+            int row = 0;
+            if (lst == 1) {  // self = first visible friend (:207-208), excluded from shuffle / jamming
+                sid[row++] = (int16_t)(vis & 0xff);
+                vis >>= 8; --n;
+            }
+            if (n > 0) {  // item_random_mv :103-113 with the keyed words (shuffle i = n-1..1, then jam draws)
+                uint32_t w[DCA_RNG_WORDS];
+                const int nblk = n <= 2 ? 1 : (n <= 4 ? 2 : 3);
+#pragma unroll
+                for (int bb = 0; bb < 3; ++bb) {
+                    if (bb < nblk) {
+                        const uint4 q = philox4x32_10(gid, counter, (uint32_t)(g * 2 + lst), SITE_OBS | (bb << 8), k0, k1);
+                        w[4 * bb] = q.x; w[4 * bb + 1] = q.y; w[4 * bb + 2] = q.z; w[4 * bb + 3] = q.w;
+                    } else {
+                        w[4 * bb] = w[4 * bb + 1] = w[4 * bb + 2] = w[4 * bb + 3] = 0;
+                    }
+                }
 #pragma unroll
                 for (int i = kVisN - 1; i >= 1; --i) {
-                    if (i < m) {
-                        const int j = (int)__umulhi(w[2 * i], (uint32_t)(i + 1));
-                        // swap entries firstv+i and firstv+j (register array: resolved by unrolled selects)
-                        int vi = 0, vj = 0;
-#pragma unroll
-                        for (int k = 0; k < kVisN; ++k) { vi = (k == firstv + i) ? bi[k] : vi; vj = (k == firstv + j) ? bi[k] : vj; }
-#pragma unroll
-                        for (int k = 0; k < kVisN; ++k) bi[k] = (k == firstv + i) ? vj : ((k == firstv + j) ? vi : bi[k]);
+                    if (i < n) {
+                        const int j = (int)__umulhi(w[2 * i], (uint32_t)(i + 1));  // SHUF_W[i] = 2i
+                        const unsigned long long x = ((vis >> (8 * i)) ^ (vis >> (8 * j))) & 0xffull;
+                        vis ^= (x << (8 * i)) | (x << (8 * j));
                     }
                 }
                 int n_mv = 0;
 #pragma unroll
                 for (int k = 0; k < kVisN; ++k) {
-                    const int wi = k == 0 ? 0 : 2 * k - 1;
-                    if (k < m) n_mv += ((unsigned long long)w[wi] < P.jam_thresh) ? 1 : 0;
+                    const int wi = k == 0 ? 0 : 2 * k - 1;  // JAM_W = {0,1,3,5,7,9}
+                    if (k < n) n_mv += ((unsigned long long)w[wi] < P.jam_thresh) ? 1 : 0;
                 }
-                keep = m - n_mv;
+                n -= n_mv;
             }
 #pragma unroll
             for (int k = 0; k < kVisN; ++k)
-                if (k >= firstv && k < firstv + keep) sid[row++] = (int16_t)bi[k];
+                if (k < n && row < kVisN) sid[row++] = (int16_t)((vis >> (8 * k)) & 0xff);
         }
     }
     __syncthreads();
+    MT_PROF(P, e, 6);
     if (dest != nullptr) {
         // gather: float4 stores over the env's contiguous [N*204] floats; a float4 may straddle two records
+        // (staging whole 68-byte records in shared memory first was slower: the extra 26 KB cost two resident CTAs)
         float4 *o4 = (float4 *)(dest + (size_t)e * N * kMtLen);
         const int total4 = N * kMtLen / 4;  // 204 = 4 * 51
         for (int q = tid; q < total4; q += kMtThreads) {
@@ -211,11 +295,17 @@ __device__ __forceinline__ void mt_reset_world(const MtSmem &s, const MtParams &
     }
 }
 
-__device__ __forceinline__ void mt_load(const MtSmem &s, const MtParams &P, int e, int *first) {
+__device__ __forceinline__ void mt_load(const MtSmem &s, const MtParams &P, int e) {
     const int N = P.N;
-    int k = 0;
-    for (int t = 0; t < P.cfg.n_team; ++t) { first[t] = k; k += P.cfg.team_size[t]; }
-    for (int t = P.cfg.n_team; t <= DCA_MT_MAX_TEAMS; ++t) first[t] = k;
+    if (threadIdx.x < 20) s.misc[threadIdx.x] = 0;
+    if (threadIdx.x <= DCA_MT_MAX_TEAMS) {  // team uid ranges (arrange_id): misc[20 + t] = first uid of team t
+        int k = 0;
+#pragma unroll
+        for (int t = 0; t < DCA_MT_MAX_TEAMS; ++t) k += (t < (int)threadIdx.x && t < P.cfg.n_team) ? P.cfg.team_size[t] : 0;
+        s.misc[20 + threadIdx.x] = k;
+    }
+    for (int c = threadIdx.x; c < kMtRow; c += kMtThreads) s.table[(size_t)N * kMtRow + c] = 0.f;
+    __syncthreads();
     for (int i = threadIdx.x; i < N; i += kMtThreads) {
         const size_t g = (size_t)e * N + i;
         const double2 p = ((const double2 *)P.st.pos)[g], v = ((const double2 *)P.st.vel)[g];
@@ -224,11 +314,9 @@ __device__ __forceinline__ void mt_load(const MtSmem &s, const MtParams &P, int 
         s.flags[i] = (uint8_t)((P.st.alive[g] ? MT_ALIVE : 0) | (P.st.just_died[g] ? MT_JUST_DIED : 0) |
                                (P.st.hit[g] ? MT_HIT : 0) | (P.st.was_hit[g] ? MT_WAS_HIT : 0) | (P.st.bsa[g] ? MT_BSA : 0));
         int tm = 0;
-        while (i >= first[tm + 1]) ++tm;
-        s.team[i] = (uint8_t)tm; s.tid[i] = (uint8_t)(i - first[tm]);
+        while (i >= s.misc[21 + tm]) ++tm;
+        s.team[i] = (uint8_t)tm; s.tid[i] = (uint8_t)(i - s.misc[20 + tm]);
     }
-    for (int c = threadIdx.x; c < kMtRow; c += kMtThreads) s.table[(size_t)N * kMtRow + c] = 0.f;
-    if (threadIdx.x < 32) s.misc[threadIdx.x] = 0;
 }
 
 __device__ __forceinline__ void mt_store(const MtSmem &s, const MtParams &P, int e) {
@@ -252,14 +340,15 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
     if (skip != nullptr && skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay
     const MtSmem s = mt_carve(mt_raw, N);
     const DcaMtConfig &c = P.cfg;
-    int first[DCA_MT_MAX_TEAMS + 1];
-    mt_load(s, P, e, first);
+    MT_PROF(P, e, 0);
+    mt_load(s, P, e);
     double theta = P.st.init_theta[e];
     const int time_step = P.st.time_step[e];
     uint32_t counter = P.st.obs_counter[e], episode = P.st.episode[e];
     const uint32_t k0 = (uint32_t)c.seed, k1 = (uint32_t)(c.seed >> 32);
     const uint32_t gid = (uint32_t)(c.env_gid0 + e);
     __syncthreads();
+    MT_PROF(P, e, 1);
     // ---- set_terrain_adv (parallel_run.py:164) for the agents of the previous step's list; then World.step's new list,
     // hit flags cleared for its members (core.py:101, :161-165)
     {
@@ -274,26 +363,33 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
         }
     }
     __syncthreads();
-    // ---- laser core.py:167-190: every alive shooter against every alive agent of another team
-    for (int i = tid; i < N; i += kMtThreads) {
-        if (!(s.flags[i] & MT_BSA)) continue;
-        const double radius = 0.4 * s.ter[i], r2 = radius * radius, win = kPi / 4;
-        const double xi = s.px[i], yi = s.py[i], dir = s.atk[i];
-        const int tm = s.team[i];
-        for (int j = 0; j < N; ++j) {
-            if (!(s.flags[j] & MT_BSA) || s.team[j] == tm) continue;
-            const double dx = s.px[j] - xi, dy = s.py[j] - yi;
-            if (dx * dx + dy * dy > r2) continue;
-            const double tt = atan2(dy, dx);
-            const double d1 = fabs(reg_angle((dir + win / 2) - tt)), d2 = fabs(reg_angle((dir - win / 2) - tt));
-            if (!(d1 <= win && d2 <= win)) continue;
-            const double adv = fmax(fmin(s.ter[i] - s.ter[j], 0.1), -0.1);
-            const double prob = 0.8 + adv;
-            const uint4 w = philox4x32_10(gid, counter, (uint32_t)(i * N + j), SITE_MT_LASER, k0, k1);
-            if (((double)w.x * 0x1p-32) < prob) { atomicOr(&s.hitf[i], 1); atomicOr(&s.hitf[j], 2); }
+    MT_PROF(P, e, 2);
+    // ---- laser core.py:167-190: every alive shooter against every alive agent of another team.  A warp takes a
+    // shooter, its lanes the targets; pairs inside the shooter's radius are queued and the exact angle test + keyed
+    // success draw then run one queued pair per thread (the keyed draw makes the outcome order-independent).
+    {
+        const int lane = tid & 31, warp = tid >> 5;
+        for (int i = warp; i < N; i += kMtThreads / 32) {
+            if (!(s.flags[i] & MT_BSA)) continue;  // warp-uniform
+            const double radius = 0.4 * s.ter[i], r2 = radius * radius;
+            const double xi = s.px[i], yi = s.py[i];
+            const int tm = s.team[i];
+            for (int j = lane; j < N; j += 32) {
+                if (!(s.flags[j] & MT_BSA) || s.team[j] == tm) continue;
+                const double dx = s.px[j] - xi, dy = s.py[j] - yi;
+                if (dx * dx + dy * dy > r2) continue;
+                const int q = atomicAdd(&s.misc[16], 1);
+                if (q < kMtPairCap) s.pairq[q] = i * N + j;
+                else mt_laser_pair(s.px, s.py, s.atk, s.ter, s.hitf, N, gid, counter, k0, k1, i * N + j);  // queue full
+            }
         }
+        __syncthreads();
+        const int nq = min(s.misc[16], kMtPairCap);
+        for (int q = tid; q < nq; q += kMtThreads)
+            mt_laser_pair(s.px, s.py, s.atk, s.ter, s.hitf, N, gid, counter, k0, k1, s.pairq[q]);
     }
     __syncthreads();
+    MT_PROF(P, e, 3);
     // ---- deaths (:193-201), integrate (:204-222, just-killed agents still move), kill circle (:115-132), records
     {
         const double frac = fmin((double)time_step / (double)c.steps_to_narrow, 1.0);
@@ -336,6 +432,7 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
         }
     }
     __syncthreads();
+    MT_PROF(P, e, 4);
     // ---- done / ranking parallel_run.py:219-245 (every thread computes the same flags)
     int teams_alive = 0;
     for (int t = 0; t < c.n_team; ++t) teams_alive += s.misc[t] > 0;
@@ -357,7 +454,7 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
     int new_time = time_step + 1;
     counter += 1;
     if (done && autoreset) {
-        mt_obs_pass(s, P, e, P.out.tobs, counter, first);  // terminal obs = info['obs-echo'] (tobs may be NULL)
+        mt_obs_pass(s, P, e, P.out.tobs, counter);  // terminal obs = info['obs-echo'] (tobs may be NULL)
         __syncthreads();
         episode += 1;
         mt_reset_world(s, P, e, episode, &theta);
@@ -365,8 +462,11 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
         counter += 1;
         __syncthreads();
     }
-    mt_obs_pass(s, P, e, P.out.obs, counter, first);
+    MT_PROF(P, e, 5);
+    mt_obs_pass(s, P, e, P.out.obs, counter);
+    MT_PROF(P, e, 7);
     mt_store(s, P, e);
+    MT_PROF(P, e, 8);
     if (tid == 0) {
         P.st.init_theta[e] = theta; P.st.time_step[e] = new_time;
         P.st.obs_counter[e] = counter; P.st.episode[e] = episode;
@@ -379,14 +479,13 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_reset(const MtParams P, const
     const int e = blockIdx.x;
     if (mask != nullptr && !mask[e]) return;
     const MtSmem s = mt_carve(mt_raw, P.N);
-    int first[DCA_MT_MAX_TEAMS + 1];
-    mt_load(s, P, e, first);
+    mt_load(s, P, e);
     const uint32_t episode = P.st.episode[e] + 1, counter = P.st.obs_counter[e] + 1;
     double theta;
     __syncthreads();
     mt_reset_world(s, P, e, episode, &theta);
     __syncthreads();
-    mt_obs_pass(s, P, e, P.out.obs, counter, first);
+    mt_obs_pass(s, P, e, P.out.obs, counter);
     mt_store(s, P, e);
     if (threadIdx.x == 0) {
         P.st.init_theta[e] = theta; P.st.time_step[e] = 0;

@@ -230,6 +230,9 @@ int dca_mt_reset(DcaMtHandle *h, const uint8_t *env_mask, dca_stream_t stream);
 int dca_mt_step(DcaMtHandle *h, const int32_t *actions, const uint8_t *skip, int autoreset, dca_stream_t stream);
 int dca_mt_export_state(DcaMtHandle *h, const DcaMtState *dst, dca_stream_t stream);
 int dca_mt_import_state(DcaMtHandle *h, const DcaMtState *src, dca_stream_t stream);
+/* Diagnostics, as dca_debug_phase_clocks: slots 0 start, 1 loaded, 2 terrain, 3 laser, 4 deaths+integrate, 5 done/ranking
+ * (+ terminal obs and reset on done), 6 observation tasks, 7 gather, 8 state stored. */
+int dca_mt_debug_phase_clocks(DcaMtHandle *h, uint64_t *clocks);
 
 /* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a
  * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
