@@ -388,7 +388,9 @@ def run_ours(args):
         'multiteam_kernel': {'bound': 'hbm', 'kernel': 'k_mt_step', 'workload': 'dca_multiteam 25v25, terrain on, jam 0.05, %d envs' % E,
                              'kernel_ms': ms_mt, 'agent_steps_per_sec': E * mt_N / (ms_mt * 1e-3), 'unit': 'GB/s',
                              'achieved': mt_bytes / (ms_mt * 1e-3) / 1e9, 'peak': peak,
-                             'frac': mt_bytes / (ms_mt * 1e-3) / 1e9 / peak, 'alive_fraction_at_end': mt_alive},
+                             'frac': mt_bytes / (ms_mt * 1e-3) / 1e9 / peak, 'alive_fraction_at_end': mt_alive,
+                             'algorithmic_bytes_per_launch': mt_bytes,
+                             'traffic': ncu.get('k_mt_step_dram_bytes_per_launch') if E == ncu.get('envs_per_gpu') else None},
         'gae_kernel': {'bound': 'hbm', 'kernel': 'k_gae', 'unit': 'GB/s',
                        'shape_TEG': [T, E, G], 'kernel_ms': ms_gae, 'achieved': gae_bytes / (ms_gae * 1e-3) / 1e9,
                        'peak': peak, 'frac': gae_bytes / (ms_gae * 1e-3) / 1e9 / peak},
