@@ -17,6 +17,7 @@ constexpr int kMtLen = kObsRows * kMtRow;       // 204 floats per agent
 constexpr int kMtThreads = 128;
 constexpr int kMtPairCap = 512;                 // queued in-range laser pairs per env (overflow is tested in place)
 enum : uint32_t { SITE_MT_LASER = 4 };
+constexpr double kCosHalfWin2 = 0.85355339059327376220;  // cos^2(pi/8) = (2 + sqrt 2) / 4: half of shootWin = pi/4
 #define MT_PROF(P, e, k)                                                                      \
     do {                                                                                      \
         if ((P).prof != nullptr && threadIdx.x == 0) (P).prof[(size_t)(e) * 16 + (k)] = clock64(); \
@@ -36,18 +37,20 @@ struct MtParams {
 
 struct MtSmem {
     double *px, *py, *vx, *vy, *atk, *ter;
+    double *ux, *uy;         // unit heading (cos, sin of atk_rad) of the agents that can shoot this step
     float *xs, *ys, *table;  // table: [(N+1)][17], record N = zeros
     int *hitf;               // per agent: bit 0 = hit someone, bit 1 = was hit (this step)
     int *pairq;              // [kMtPairCap] shooter * N + target
+    float *bbox;             // [8][4] x0 x1 y0 y1 of each team's alive agents
     int16_t *sid;            // [N,12]
     uint8_t *flags, *team, *tid;
     int *misc;               // [0..7] alive count per team, [16] queued laser pairs, [20..28] first uid of each team
 };
 
 __host__ __device__ inline size_t mt_smem_bytes(int N) {
-    size_t b = 6 * sizeof(double) * N;
+    size_t b = 8 * sizeof(double) * N;
     b += 2 * sizeof(float) * N + sizeof(float) * (size_t)(N + 1) * kMtRow;
-    b += sizeof(int) * N + sizeof(int) * kMtPairCap + sizeof(int16_t) * (size_t)N * kObsRows + 3 * (size_t)N + sizeof(int) * 32;
+    b += sizeof(int) * N + sizeof(int) * kMtPairCap + sizeof(int16_t) * (size_t)N * kObsRows + 3 * (size_t)N + sizeof(int) * 32 + sizeof(float) * 4 * DCA_MT_MAX_TEAMS;
     return (b + 63) & ~(size_t)15;
 }
 
@@ -59,12 +62,15 @@ __device__ __forceinline__ MtSmem mt_carve(unsigned char *p, int N) {
     s.vy = (double *)p; p += sizeof(double) * N;
     s.atk = (double *)p; p += sizeof(double) * N;
     s.ter = (double *)p; p += sizeof(double) * N;
+    s.ux = (double *)p; p += sizeof(double) * N;
+    s.uy = (double *)p; p += sizeof(double) * N;
     s.xs = (float *)p; p += sizeof(float) * N;
     s.ys = (float *)p; p += sizeof(float) * N;
     s.table = (float *)p; p += sizeof(float) * (size_t)(N + 1) * kMtRow;
     s.hitf = (int *)p; p += sizeof(int) * N;
     s.misc = (int *)p; p += sizeof(int) * 32;
     s.pairq = (int *)p; p += sizeof(int) * kMtPairCap;
+    s.bbox = (float *)p; p += sizeof(float) * 4 * DCA_MT_MAX_TEAMS;
     s.sid = (int16_t *)p; p += sizeof(int16_t) * (size_t)N * kObsRows;
     s.flags = p; p += N;
     s.team = p; p += N;
@@ -90,19 +96,30 @@ __device__ __forceinline__ void mt_build_row(const MtSmem &s, int i) {
     s.ys[i] = alive ? y : CUDART_INF_F;
 }
 
+// float32 bound of a shooter's squared laser reach: |coord| <= 64 and r < 1 keep the float32 squared distance within
+// 1e-4 of the exact one, so a pair beyond r^2 * 1.01 + 1e-3 cannot pass the fp64 test (+inf = no bound)
+__device__ __forceinline__ float mt_reach2f(double x, double y, double terrain) {
+    const double radius = 0.4 * terrain, r2 = radius * radius;
+    const bool ok = fabs(x) <= 64.0 && fabs(y) <= 64.0 && r2 < 1.0;
+    return ok ? __fadd_ru(__fmul_ru((float)r2, 1.01f), 1.0e-3f) : CUDART_INF_F;
+}
+
 // exact laser test of the ordered pair p = shooter * N + target (already inside the shooter's radius):
 // laser_hit_improve3 (dca_multiteam/cython_func.pyx:22-53), then the success draw core.py:178-190
 // (plain pointers / scalars only: a struct passed by reference to an out-of-line function would live in local memory)
 __device__ __noinline__ void mt_laser_pair(const double *px, const double *py, const double *atk, const double *ter,
                                            int *hitf, int N, uint32_t gid, uint32_t counter, uint32_t k0, uint32_t k1,
-                                           int p) {
+                                           int entry) {
+    const int p = entry & 0x3fffffff;
     const int i = p / N, j = p - i * N;
-    const double win = kPi / 4;
-    const double dx = px[j] - px[i], dy = py[j] - py[i];
-    const double dir = atk[i];
-    const double tt = atan2(dy, dx);
-    const double d1 = fabs(reg_angle((dir + win / 2) - tt)), d2 = fabs(reg_angle((dir - win / 2) - tt));
-    if (!(d1 <= win && d2 <= win)) return;
+    if (entry >> 30) {  // the cone test was too close to call: the reference's own arithmetic decides
+        const double win = kPi / 4;
+        const double dx = px[j] - px[i], dy = py[j] - py[i];
+        const double dir = atk[i];
+        const double tt = atan2(dy, dx);
+        const double d1 = fabs(reg_angle((dir + win / 2) - tt)), d2 = fabs(reg_angle((dir - win / 2) - tt));
+        if (!(d1 <= win && d2 <= win)) return;
+    }
     const double adv = fmax(fmin(ter[i] - ter[j], 0.1), -0.1);
     const double prob = 0.8 + adv;
     const uint4 w = philox4x32_10(gid, counter, (uint32_t)p, SITE_MT_LASER, k0, k1);
@@ -172,7 +189,7 @@ __device__ __forceinline__ void mt_obs_pass(const MtSmem &s, const MtParams &P, 
             uint32_t b[kVisN + 1];
 #pragma unroll
             for (int k = 0; k <= kVisN; ++k) b[k] = 0x80000000u + ((uint32_t)k << 8);  // empty: distinct, ascending
-            for (int j = j0; j < j1; ++j) {
+            for (int j = j0; j < j1; ++j) {  // (unrolling this loop costs registers -> resident CTAs: slower)
                 if (lst == 0 && j >= own0 && j < own1) { j = own1 - 1; continue; }
                 const float sq = f32_sqdist(gx, gy, s.xs[j], s.ys[j]);  // dead = +inf
                 const uint32_t pos = (uint32_t)(lst == 1 ? j - own0 : (j < own0 ? j : j - nown));
@@ -333,7 +350,7 @@ __device__ __forceinline__ void mt_store(const MtSmem &s, const MtParams &P, int
     }
 }
 
-__global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const int32_t *__restrict__ actions,
+__global__ void __launch_bounds__(kMtThreads, 8) k_mt_step(const MtParams P, const int32_t *__restrict__ actions,
                                                          const uint8_t *__restrict__ skip, int autoreset) {
     extern __shared__ __align__(16) unsigned char mt_raw[];
     const int e = blockIdx.x, tid = threadIdx.x, N = P.N;
@@ -357,9 +374,17 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
             uint8_t f = s.flags[i];
             if (f & MT_BSA) s.ter[i] = c.introduce_terrain ? terrain_fn(c.terrain_A, c.terrain_B, s.px[i], s.py[i], ct, st) : 1.0;
             f = (uint8_t)(f & ~MT_BSA);
-            if (f & MT_ALIVE) f = (uint8_t)((f | MT_BSA) & ~(MT_HIT | MT_WAS_HIT));
+            if (f & MT_ALIVE) {
+                f = (uint8_t)((f | MT_BSA) & ~(MT_HIT | MT_WAS_HIT));
+                double sn, cs;
+                sincos(s.atk[i], &sn, &cs);
+                s.ux[i] = cs; s.uy[i] = sn;
+            }
             s.flags[i] = f;
             s.hitf[i] = 0;
+            // float32 positions of the possible shooters / targets for the laser pre-filter (others = +inf)
+            s.xs[i] = (f & MT_BSA) ? (float)s.px[i] : CUDART_INF_F;
+            s.ys[i] = (f & MT_BSA) ? (float)s.py[i] : CUDART_INF_F;
         }
     }
     __syncthreads();
@@ -369,21 +394,73 @@ __global__ void __launch_bounds__(kMtThreads) k_mt_step(const MtParams P, const 
     // success draw then run one queued pair per thread (the keyed draw makes the outcome order-independent).
     {
         const int lane = tid & 31, warp = tid >> 5;
-        for (int i = warp; i < N; i += kMtThreads / 32) {
-            if (!(s.flags[i] & MT_BSA)) continue;  // warp-uniform
-            const double radius = 0.4 * s.ter[i], r2 = radius * radius;
-            const double xi = s.px[i], yi = s.py[i];
+        // bounding box of each team's possible targets (float32 positions; dead = +inf are left out): a shooter only
+        // scans the teams whose box is within its reach -- none at all while the teams are still apart
+        for (int t = warp; t < c.n_team; t += kMtThreads / 32) {
+            float x0 = CUDART_INF_F, x1 = -CUDART_INF_F, y0 = CUDART_INF_F, y1 = -CUDART_INF_F;
+            for (int j = s.misc[20 + t] + lane; j < s.misc[21 + t]; j += 32) {
+                const float x = s.xs[j], y = s.ys[j];
+                if (x < CUDART_INF_F) { x0 = fminf(x0, x); x1 = fmaxf(x1, x); y0 = fminf(y0, y); y1 = fmaxf(y1, y); }
+            }
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                x0 = fminf(x0, __shfl_xor_sync(0xffffffffu, x0, o)); x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+                y0 = fminf(y0, __shfl_xor_sync(0xffffffffu, y0, o)); y1 = fmaxf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+            }
+            if (lane == 0) { s.bbox[4 * t] = x0; s.bbox[4 * t + 1] = x1; s.bbox[4 * t + 2] = y0; s.bbox[4 * t + 3] = y1; }
+        }
+        __syncthreads();
+        MT_PROF(P, e, 9);
+        // (1) one thread per shooter: which other teams' boxes are within its reach?  -> work list of (shooter, team)
+        // (lives in the sid rows, which are not written before the observation pass)
+        int16_t *work = s.sid;
+        for (int i = tid; i < N; i += kMtThreads) {
+            if (!(s.flags[i] & MT_BSA)) continue;
+            const float xif = s.xs[i], yif = s.ys[i];
+            const float r2f = mt_reach2f(s.px[i], s.py[i], s.ter[i]);
             const int tm = s.team[i];
-            for (int j = lane; j < N; j += 32) {
-                if (!(s.flags[j] & MT_BSA) || s.team[j] == tm) continue;
-                const double dx = s.px[j] - xi, dy = s.py[j] - yi;
-                if (dx * dx + dy * dy > r2) continue;
-                const int q = atomicAdd(&s.misc[16], 1);
-                if (q < kMtPairCap) s.pairq[q] = i * N + j;
-                else mt_laser_pair(s.px, s.py, s.atk, s.ter, s.hitf, N, gid, counter, k0, k1, i * N + j);  // queue full
+            for (int t = 0; t < c.n_team; ++t) {
+                if (t == tm) continue;
+                const float bx = fmaxf(fmaxf(s.bbox[4 * t] - xif, xif - s.bbox[4 * t + 1]), 0.f);
+                const float by = fmaxf(fmaxf(s.bbox[4 * t + 2] - yif, yif - s.bbox[4 * t + 3]), 0.f);
+                if (bx * bx + by * by <= r2f) work[atomicAdd(&s.misc[17], 1)] = (int16_t)(i | (t << 8));  // empty box: inf
             }
         }
         __syncthreads();
+        // (2) one warp per work item, lanes over the members of that team
+        const int n_work = s.misc[17];
+        for (int k = warp; k < n_work; k += kMtThreads / 32) {
+            const int i = work[k] & 0xff, t = work[k] >> 8;
+            const double radius = 0.4 * s.ter[i], r2 = radius * radius;
+            const double xi = s.px[i], yi = s.py[i], uxi = s.ux[i], uyi = s.uy[i];
+            const float r2f = mt_reach2f(xi, yi, s.ter[i]);
+            const float xif = s.xs[i], yif = s.ys[i];
+            {
+                for (int j = s.misc[20 + t] + lane; j < s.misc[21 + t]; j += 32) {
+                const float dxf = s.xs[j] - xif, dyf = s.ys[j] - yif;
+                if (!(dxf * dxf + dyf * dyf <= r2f)) continue;
+                if (!(s.flags[j] & MT_BSA)) continue;
+                const double dx = s.px[j] - xi, dy = s.py[j] - yi;
+                const double len2 = dx * dx + dy * dy;
+                if (len2 > r2) continue;
+                // cone test of laser_hit_improve3: both |reg(dir +- w/2 - theta)| <= w  <=>  the target direction is
+                // within w/2 of the heading  <=>  dot >= cos(w/2) |d|.  Decided here without atan2 unless it is within
+                // 1e-9 (relative) of the boundary -- ~1e6 times the rounding error of either formulation.
+                const double dot = dx * uxi + dy * uyi;
+                const double margin = dot * dot - kCosHalfWin2 * len2;
+                int amb = 0;
+                if (!(len2 > 1e-100) || fabs(margin) <= 1e-9 * len2) amb = 1;
+                else if (dot <= 0.0 || margin < 0.0) continue;  // outside the cone
+                const int q = atomicAdd(&s.misc[16], 1);
+                const int entry = (i * N + j) | (amb << 30);
+                if (q < kMtPairCap) s.pairq[q] = entry;
+                else mt_laser_pair(s.px, s.py, s.atk, s.ter, s.hitf, N, gid, counter, k0, k1, entry);  // queue full
+                }
+            }
+        }
+        MT_PROF(P, e, 10);
+        __syncthreads();
+        MT_PROF(P, e, 11);
         const int nq = min(s.misc[16], kMtPairCap);
         for (int q = tid; q < nq; q += kMtThreads)
             mt_laser_pair(s.px, s.py, s.atk, s.ter, s.hitf, N, gid, counter, k0, k1, s.pairq[q]);

@@ -231,7 +231,8 @@ int dca_mt_step(DcaMtHandle *h, const int32_t *actions, const uint8_t *skip, int
 int dca_mt_export_state(DcaMtHandle *h, const DcaMtState *dst, dca_stream_t stream);
 int dca_mt_import_state(DcaMtHandle *h, const DcaMtState *src, dca_stream_t stream);
 /* Diagnostics, as dca_debug_phase_clocks: slots 0 start, 1 loaded, 2 terrain, 3 laser, 4 deaths+integrate, 5 done/ranking
- * (+ terminal obs and reset on done), 6 observation tasks, 7 gather, 8 state stored. */
+ * (+ terminal obs and reset on done), 6 observation tasks, 7 gather, 8 state stored; inside the laser phase: 9 team
+ * boxes, 10 scan done, 11 barrier passed. */
 int dca_mt_debug_phase_clocks(DcaMtHandle *h, uint64_t *clocks);
 
 /* Options.  DCA_OPT_EMPTY_ROWS_NAN: write invisible / jammed / empty observation rows (and the whole observation of a

@@ -22,6 +22,7 @@ def main(steps=80, E=4096):
     prof = torch.zeros((E, 16), dtype=torch.int64, device=env.device)
     acc = np.zeros(8)
     life = 0.0
+    sub = None
     for t in range(steps):
         act = torch.randint(0, 7, (E, env.N), generator=g, device=env.device, dtype=torch.int32)
         on = t >= steps - 20
@@ -31,8 +32,12 @@ def main(steps=80, E=4096):
             c = prof.cpu().numpy().astype(np.float64)
             acc += np.diff(c[:, :9], axis=1).mean(0)
             life += (c[:, 8] - c[:, 0]).mean()
+            x = np.stack([c[:, 9] - c[:, 2], c[:, 10] - c[:, 9], c[:, 11] - c[:, 10], c[:, 3] - c[:, 11]], 1).mean(0)
+            sub = x if sub is None else sub + x
     acc /= 20
     life /= 20
+    if sub is not None:
+        print('laser sub-phases: bbox %.0f  scan %.0f  barrier %.0f  queue %.0f' % tuple(sub / 20))
     for n, v in zip(NAMES, acc):
         print('%-18s %9.0f cycles  %5.1f%%' % (n, v, 100 * v / life))
     print('CTA lifetime       %9.0f cycles' % life)
