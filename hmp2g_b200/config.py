@@ -112,6 +112,11 @@ _SCENARIO_GROUPS = (
     'MISSION.dca.collective_assault_parallel_run->ScenarioConfig',
     'hmp2g_b200.config.py->ScenarioConfig',
 )
+_MT_SCENARIO_GROUPS = (
+    'MISSION.dca_multiteam.collective_assault_parallel_run.py->ScenarioConfig',
+    'MISSION.dca_multiteam.collective_assault_parallel_run->ScenarioConfig',
+    'hmp2g_b200.multiteam.py->MtScenarioConfig',
+)
 _GLOBAL_GROUPS = ('config.py->GlobalConfig', 'hmp2g_b200.config.py->GlobalConfig')
 _STALE_KEYS = {'num_steps': 'MaxEpisodeStep'}
 _STALE_ENV_NAMES = {'collective_assault': 'dca'}
@@ -228,6 +233,10 @@ def inject(json_data, scenario_cls=ScenarioConfig, global_cls=GlobalConfig):
                     body[new] = body.pop(old)
                     rep.renamed.append((old, new))
             rep.altered_chained += override_config(scenario_cls, body)
+            rep.applied.append(group)
+        elif group in _MT_SCENARIO_GROUPS:  # the sibling env MISSION/dca_multiteam
+            from .multiteam import MtScenarioConfig
+            rep.altered_chained += override_config(MtScenarioConfig, dict(body))
             rep.applied.append(group)
         elif group in _GLOBAL_GROUPS:
             known = {k: v for k, v in body.items() if hasattr(global_cls, k)}

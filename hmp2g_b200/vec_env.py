@@ -328,9 +328,12 @@ class DcaSuperpoolEnv(object):
 
 
 def make_parallel_envs(process_pool=None, marker=''):
-    """MISSION.env_router.make_parallel_envs (env_router.py:68-117) for env_name 'dca'."""
-    assert GlobalConfig.env_name in ('dca', 'collective_assault'), GlobalConfig.env_name
+    """MISSION.env_router.make_parallel_envs (env_router.py:68-117) for env_name 'dca' and 'dca_multiteam'."""
+    assert GlobalConfig.env_name in ('dca', 'collective_assault', 'dca_multiteam'), GlobalConfig.env_name
     env_args_dict_list = [({'env_name': GlobalConfig.env_name,
                             'proc_index': i if 'test' not in marker else -(i + 1),
                             'marker': marker},) for i in range(GlobalConfig.num_threads)]
+    if GlobalConfig.env_name == 'dca_multiteam':
+        from .multiteam import DcaMultiTeamSuperpoolEnv, MtScenarioConfig
+        return DcaMultiTeamSuperpoolEnv(process_pool, env_args_dict_list, scfg=MtScenarioConfig, seed=GlobalConfig.seed)
     return DcaSuperpoolEnv(process_pool, env_args_dict_list)

@@ -178,3 +178,30 @@ def test_two_rank_gloo_stats_and_advantage_moments(tmp_path):
                          env=env, capture_output=True, text=True, timeout=280)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count('ok') == 2, out.stdout
+
+
+def test_multiteam_jsonc_injection_and_chainvars():
+    """The dca_multiteam ScenarioConfig group (MISSION/dca_multiteam/collective_assault_parallel_run.py:27-77) is
+    injected with the reference's rules: coercion to the default's type, chained AGENT_ID_EACH_TEAM recomputed."""
+    from hmp2g_b200 import config
+    from hmp2g_b200.multiteam import MtScenarioConfig, pod_mt_config
+    snap = config.reset_defaults(MtScenarioConfig)
+    try:
+        rep = config.inject({
+            'MISSION.dca_multiteam.collective_assault_parallel_run.py->ScenarioConfig': {
+                'N_AGENT_EACH_TEAM': [7, 9, 8], 'random_jam_prob': 0.2, 'introduce_terrain': True,
+                'terrain_parameters': [0.05, 0.2], 'MaxEpisodeStep': 45, 'StepsToNarrowCircle': 15, 'size': 3},
+            'ALGORITHM.conc_4hist.foundation.py->AlgorithmConfig': {'train_traj_needed': 64},
+        })
+        assert rep.applied and rep.ignored_groups == ['ALGORITHM.conc_4hist.foundation.py->AlgorithmConfig']
+        assert MtScenarioConfig.N_AGENT_EACH_TEAM == [7, 9, 8]
+        assert [list(r) for r in MtScenarioConfig.AGENT_ID_EACH_TEAM] == [list(range(0, 7)), list(range(7, 16)),
+                                                                         list(range(16, 24))]
+        assert isinstance(MtScenarioConfig.size, float) and MtScenarioConfig.size == 3.0
+        pod = pod_mt_config(MtScenarioConfig, seed=5, env_gid0=11)
+        assert (pod.n_team, list(pod.team_size)[:3], pod.max_episode_step, pod.steps_to_narrow) == (3, [7, 9, 8], 45, 15)
+        assert (pod.terrain_A, pod.terrain_B, pod.seed, pod.env_gid0) == (0.05, 0.2, 5, 11)
+        with pytest.raises(Exception):
+            config.inject({'hmp2g_b200.multiteam.py->MtScenarioConfig': {'no_such_key': 1}})
+    finally:
+        config.reset_defaults(MtScenarioConfig, snap)
