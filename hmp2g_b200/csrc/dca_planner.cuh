@@ -15,8 +15,8 @@
 namespace dca {
 
 enum : uint32_t { SITE_PLAN = 3 };
-constexpr int kPlanThreads = 64;
-constexpr int kSerialTeam = 8;  // member <-> slot assignments up to this size run on a single thread
+constexpr int kPlanThreads = 32;  // one warp per env: no cross-warp waiting; 32 envs in flight per SM
+constexpr int kPlanTeamPre = 8;  // teams up to this size get their cost matrix precomputed (independent sqrt chains)
 
 // persistent team state of one env (World.start_flag / teams_result_step1 / team_centroid_step1 survive resets)
 struct PlanState {
@@ -44,6 +44,7 @@ struct PlanSmem {
     int16_t *toff;                  // [K+1] member list offsets
     int16_t *mem, *tof;             // [A] members grouped by team / team of that list position
     double *c1;                     // [K*K] team-centroid <-> target distances
+    double *cw;                     // [warps][kPlanTeamPre^2] member <-> slot distances of the team a warp is working on
     double *hu, *hv, *hminv;        // [A+K+2] assignment workspaces (team t owns [toff[t]+t, +n_t+1))
     int16_t *hp, *hway;             // [A+K+2]
     uint8_t *hused;                 // [A+K+2]
@@ -68,6 +69,7 @@ __host__ __device__ inline int plan_smem_bytes(int G, int A) {
     o += align_up(K * AW * 4, 16);       // lmask
     o += align_up(K * 2, 16) + align_up((K + 1) * 2, 16) + 2 * align_up(A * 2, 16);  // team_target toff mem tof
     o += align_up(K * K * 8, 16);        // c1
+    o += (kPlanThreads / 32) * kPlanTeamPre * kPlanTeamPre * 8;  // cw: one member x slot cost matrix per warp
     o += 3 * align_up(H * 8, 16) + 2 * align_up(H * 2, 16) + align_up(H, 16);  // hu hv hminv hp hway hused
     o += align_up(A * 2, 16);            // hcol
     o += 2 * align_up(A * 8, 16);        // sx sy
@@ -97,6 +99,7 @@ __device__ __forceinline__ PlanSmem plan_carve(unsigned char *p, int G, int A) {
     s.toff = (int16_t *)p; p += align_up((K + 1) * 2, 16);
     s.mem = (int16_t *)p; p += a2; s.tof = (int16_t *)p; p += a2;
     s.c1 = (double *)p; p += align_up(K * K * 8, 16);
+    s.cw = (double *)p; p += (kPlanThreads / 32) * kPlanTeamPre * kPlanTeamPre * 8;
     const int h8 = align_up(H * 8, 16), h2 = align_up(H * 2, 16);
     s.hu = (double *)p; p += h8; s.hv = (double *)p; p += h8; s.hminv = (double *)p; p += h8;
     s.hp = (int16_t *)p; p += h2; s.hway = (int16_t *)p; p += h2;
@@ -168,6 +171,91 @@ __device__ __forceinline__ void assign_warp(CostFn cost, int n, int m, double *u
     __syncwarp();
 }
 
+// order-preserving map double -> u64 (and back); -0.0 is folded into +0.0 first so that equal doubles get equal keys
+__device__ __forceinline__ u64 plan_dkey(double x) {
+    const long long b = __double_as_longlong(x + 0.0);
+    return (u64)(b ^ ((b >> 63) | (long long)0x8000000000000000ull));
+}
+__device__ __forceinline__ double plan_dkey_inv(u64 k) {
+    const long long b = (long long)k;
+    return __longlong_as_double(b < 0 ? (long long)(k ^ 0x8000000000000000ull) : ~b);
+}
+
+// The same assignment with the whole state in registers (m <= 32 columns): lane j-1 owns column j -- v[j], minv[j],
+// way[j], used[j], the row p[j] matched to it and that row's potential u[p[j]] (it travels with the row when the
+// augmenting path is flipped); the row being inserted sits in the virtual column 0, held uniformly.  Same arithmetic in
+// the same order as the serial routine (identical potentials, identical ties: lowest column), no shared-memory traffic.
+// cost_col(i0) = cost(row i0, this lane's column).
+template <typename CostFn>
+__device__ __forceinline__ void assign_warp_reg(CostFn cost_col, int n, int m, int16_t *col_of_row) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const bool col = lane < m;
+    int width = 1;
+    while (width < m) width <<= 1;  // lanes taking part in the reductions
+    double v = 0.0, uc = 0.0;
+    int p = 0;
+    for (int i = 1; i <= n; ++i) {
+        double u0 = 0.0, minv = CUDART_INF;
+        int way = 0, j0 = 0;
+        bool used = !col;  // lanes without a column never compete
+        for (;;) {
+            if (lane == j0 - 1) used = true;
+            const int src = j0 > 0 ? j0 - 1 : 0;
+            const int pj = __shfl_sync(full, p, src);
+            const double uj = __shfl_sync(full, uc, src);
+            const int i0 = j0 == 0 ? i : pj;
+            const double ui0 = j0 == 0 ? u0 : uj;
+            u64 key = ~0ull;  // order-preserving integer image of minv[j]; used / missing columns never win
+            if (!used) {
+                const double cur = (cost_col(i0 - 1) - ui0) - v;
+                if (cur < minv) { minv = cur; way = j0; }
+                key = plan_dkey(minv);
+            }
+            // arg-min over the columns, ties -> lowest column: min of the keys over the first `width` lanes, then the
+            // lowest lane holding it
+            u64 kmin = key;
+            for (int o = width >> 1; o > 0; o >>= 1) {
+                const u64 other = __shfl_xor_sync(full, kmin, o);
+                kmin = other < kmin ? other : kmin;
+            }
+            kmin = __shfl_sync(full, kmin, 0);
+            const unsigned holders = __ballot_sync(full, key == kmin && !used);
+            const int bj = holders ? __ffs(holders) : 0x7fffffff;
+            const double delta = plan_dkey_inv(kmin);
+            if (col) {
+                if (used) { uc += delta; v -= delta; }
+                else minv -= delta;
+            }
+            u0 += delta;  // column 0 is used from the first round on: u[p[0]] = u[i]
+            j0 = bj == 0x7fffffff ? 0 : bj;
+            if (__shfl_sync(full, p, j0 > 0 ? j0 - 1 : 0) == 0 || j0 == 0) break;
+        }
+        while (j0) {  // flip the augmenting path: p[j0] = p[way[j0]], the row's potential moves with it
+            const int j1 = __shfl_sync(full, way, j0 - 1);
+            const int s1 = j1 > 0 ? j1 - 1 : 0;
+            const int pj1 = __shfl_sync(full, p, s1);
+            const double uj1 = __shfl_sync(full, uc, s1);
+            if (lane == j0 - 1) { p = j1 == 0 ? i : pj1; uc = j1 == 0 ? u0 : uj1; }
+            j0 = j1;
+        }
+    }
+    if (col && p) col_of_row[p - 1] = (int16_t)lane;
+    __syncwarp();
+}
+
+// assign_warp_reg with the n x m costs evaluated up front into `scratch` (row-major): the square roots then run as
+// independent chains instead of sitting inside the augmenting loop's dependency chain.
+template <typename CostFn>
+__device__ __forceinline__ void assign_warp_reg_pre(CostFn cost_col, int n, int m, double *scratch, int16_t *col_of_row) {
+    const int lane = threadIdx.x & 31;
+    if (lane < m)
+        for (int r = 0; r < n; ++r) scratch[r * m + lane] = cost_col(r);
+    __syncwarp();
+    auto pre = [=](int r) { return scratch[r * m + lane]; };
+    assign_warp_reg(pre, n, m, col_of_row);
+}
+
 __device__ __forceinline__ double plan_sq2(double ax, double ay, double bx, double by) {
     const double dx = ax - bx, dy = ay - by;
     double d = 0;
@@ -181,45 +269,6 @@ __device__ __forceinline__ uint32_t plan_word(const DcaConfig &c, uint32_t gid, 
                                   (uint32_t)(c.seed >> 32));
     const int k = d & 3;
     return k == 0 ? q.x : (k == 1 ? q.y : (k == 2 ? q.z : q.w));
-}
-
-// The same assignment by ONE thread (small problems: a team's members <-> its ring slots); workspaces hold m+1 entries.
-template <typename CostFn>
-__device__ __forceinline__ void assign_serial(CostFn cost, int n, int m, double *u, double *v, double *minv, int16_t *p,
-                                              int16_t *way, uint8_t *used, int16_t *col_of_row) {
-    for (int j = 0; j <= m; ++j) { v[j] = 0; p[j] = 0; }
-    for (int i = 0; i <= n; ++i) u[i] = 0;
-    for (int i = 1; i <= n; ++i) {
-        p[0] = (int16_t)i;
-        int j0 = 0;
-        for (int j = 0; j <= m; ++j) { minv[j] = CUDART_INF; used[j] = 0; }
-        do {
-            used[j0] = 1;
-            const int i0 = p[j0];
-            const double ui0 = u[i0];
-            double delta = CUDART_INF;
-            int j1 = 0;
-            for (int j = 1; j <= m; ++j) {
-                if (used[j]) continue;
-                const double cur = (cost(i0 - 1, j - 1) - ui0) - v[j];
-                double mv = minv[j];
-                if (cur < mv) { mv = cur; minv[j] = cur; way[j] = (int16_t)j0; }
-                if (mv < delta) { delta = mv; j1 = j; }
-            }
-            for (int j = 0; j <= m; ++j) {
-                if (used[j]) { u[p[j]] += delta; v[j] -= delta; }
-                else minv[j] -= delta;
-            }
-            j0 = j1;
-        } while (p[j0] != 0);
-        do {
-            const int j1 = way[j0];
-            p[j0] = p[j1];
-            j0 = j1;
-        } while (j0);
-    }
-    for (int j = 1; j <= m; ++j)
-        if (p[j]) col_of_row[p[j] - 1] = (int16_t)(j - 1);
 }
 
 // Bit rows of the team labels: lmask[k][w] bit b <=> attacker 32 w + b is in team k (warp ballots).  CTA-wide, no sync.
@@ -318,7 +367,7 @@ __device__ __forceinline__ void plan_kmeans(const PlanSmem &s, const DcaConfig &
 // ------------------------------------------------------------------ planner kernel
 // inj_label (i32[E,A]) / inj_cent (f64[E,K,2]) != nullptr: use these teams (the parity harness injects the
 // reference's own k-means result) and leave the persistent state alone.
-__global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const PlanState ps,
+__global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const PlanState ps,
                                                           double *__restrict__ att_force,
                                                           const int32_t *__restrict__ inj_label,
                                                           const double *__restrict__ inj_cent) {
@@ -332,6 +381,7 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
     const double *bpx = (const double *)(blob + L.px), *bpy = (const double *)(blob + L.py);
     const uint8_t *bfl = blob + L.flags;
     double2 *out = (double2 *)att_force + (size_t)e * A;
+    DCA_PROF(P, e, 0);
     for (int i = tid; i < L.N; i += nt) {
         const bool alive = bfl[i] & F_ALIVE;
         if (i < G) { s.gx[i] = bpx[i]; s.gy[i] = bpy[i]; s.galive[i] = alive; }
@@ -339,6 +389,7 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
     }
     __syncthreads();
 
+    DCA_PROF(P, e, 1);
     // ---- teams (cheat_script_ai.py:103-117)
     if (inj_label != nullptr) {
         for (int a = tid; a < A; a += nt) s.lab[a] = (int16_t)inj_label[(size_t)e * A + a];
@@ -372,6 +423,7 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         if (tid == 0) { ps.counter[e] = counter; ps.flags[2 * e] = 1; ps.flags[2 * e + 1] = small ? 1 : 0; }
     }
 
+    DCA_PROF(P, e, 2);
     // ---- targets: DBSCAN(eps .5, min_samples 2) of the alive guards (cheat_script_ai.py:49-101)
     if (tid == 0) {
         int n = 0;
@@ -396,6 +448,7 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         s.csize[a] = 0;
     }
     __syncthreads();
+    DCA_PROF(P, e, 3);
     // connected components by min-label propagation with pointer jumping: comp[a] -> lowest member of a's component
     for (;;) {
         if (tid == 0) s.misc[4] = 0;
@@ -418,6 +471,7 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         __syncthreads();
         if (!changed) break;
     }
+    DCA_PROF(P, e, 4);
     for (int a = tid; a < n; a += nt) atomicAdd(&s.csize[s.comp[a]], 1);
     __syncthreads();
     if (tid == 0) {
@@ -454,11 +508,14 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         s.cnt[t] = cntk;
     }
     __syncthreads();
+    DCA_PROF(P, e, 5);
     // ---- team -> target (:153-157): distances centroid <-> target, then the assignment by warp 0
-    for (int q = tid; q < K * K; q += nt) {
-        const int r = q / K, cc = q - r * K;
-        const double dx = s.tx[cc] - s.cx[r], dy = s.ty[cc] - s.cy[r];
-        s.c1[q] = sqrt(dx * dx + dy * dy);
+    if (K > 32) {  // cost matrix for the shared-memory routine (more than 32 targets)
+        for (int q = tid; q < K * K; q += nt) {
+            const int r = q / K, cc = q - r * K;
+            const double dx = s.tx[cc] - s.cx[r], dy = s.ty[cc] - s.cy[r];
+            s.c1[q] = sqrt(dx * dx + dy * dy);
+        }
     }
     if (tid == 0) {
         int o = 0;
@@ -466,25 +523,36 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         s.toff[K] = (int16_t)o;
     }
     __syncthreads();
-    if ((tid >> 5) == 0) {
-        const double *c1 = s.c1;
-        auto cost1 = [c1, K](int r, int cc) { return c1[r * K + cc]; };
-        assign_warp(cost1, K, K, s.hu, s.hv, s.hminv, s.hp, s.hway, s.hused, s.team_target);
-    } else {
-        // meanwhile the other warps lay out the member lists (attacker index order inside a team)
-        for (int k = tid - 32; k < K; k += nt - 32) {
-            int o = s.toff[k];
-            for (int w = 0; w < AW; ++w) {
-                uint32_t m = s.lmask[k * AW + w];
-                while (m) {
-                    const int a = w * 32 + __ffs(m) - 1;
-                    m &= m - 1;
-                    s.mem[o] = (int16_t)a; s.tof[o] = (int16_t)k; ++o;
-                }
+    // member lists (attacker index order inside a team), one team per thread
+    for (int k = tid; k < K; k += nt) {
+        int o = s.toff[k];
+        for (int w = 0; w < AW; ++w) {
+            uint32_t m = s.lmask[k * AW + w];
+            while (m) {
+                const int a = w * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                s.mem[o] = (int16_t)a; s.tof[o] = (int16_t)k; ++o;
             }
         }
     }
+    if ((tid >> 5) == 0) {
+        if (K <= 32) {
+            const int lane = tid & 31;
+            const double txj = lane < K ? s.tx[lane] : 0.0, tyj = lane < K ? s.ty[lane] : 0.0;
+            const double *cx = s.cx, *cy = s.cy;
+            auto cost1 = [=](int r) {
+                const double dx = txj - cx[r], dy = tyj - cy[r];
+                return sqrt(dx * dx + dy * dy);
+            };
+            assign_warp_reg_pre(cost1, K, K, s.c1, s.team_target);
+        } else {
+            const double *c1 = s.c1;
+            auto cost1 = [c1, K](int r, int cc) { return c1[r * K + cc]; };
+            assign_warp(cost1, K, K, s.hu, s.hv, s.hminv, s.hp, s.hway, s.hused, s.team_target);
+        }
+    }
     __syncthreads();
+    DCA_PROF(P, e, 6);
     // ---- ring slots (:160-170), by list position
     for (int i = tid; i < A; i += nt) {
         const int k = s.tof[i], nm = s.cnt[k], j = i - s.toff[k];
@@ -494,37 +562,37 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         s.sy[i] = s.ty[tg] + 0.8 * sin(delta * j);
     }
     __syncthreads();
-    // ---- member -> slot (:171-173): teams of up to kSerialTeam members get one thread each (spread over the warps),
-    // larger ones a whole warp
+    DCA_PROF(P, e, 7);
+    // ---- member -> slot (:171-173): one warp per team; up to 32 members entirely in registers
     {
-        const int nw = nt >> 5, k = (tid & 31) * nw + (tid >> 5);
+        const int nw = nt >> 5, lane = tid & 31;
         const double *ax = s.ax, *ay = s.ay;
-        if ((tid & 31) * nw < K && k < K && s.cnt[k] > 0 && s.cnt[k] <= kSerialTeam) {
-            const int off = s.toff[k], nm = s.cnt[k], ho = off + k;
-            const double *sx = s.sx + off, *sy = s.sy + off;
-            const int16_t *mem = s.mem + off;
-            auto cost2 = [=](int i, int j) {
-                const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];
-                return sqrt(dx * dx + dy * dy);
-            };
-            assign_serial(cost2, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
-                          s.hcol + off);
-        }
-        __syncwarp();
         for (int kk = tid >> 5; kk < K; kk += nw) {  // warp-uniform
-            if (s.cnt[kk] <= kSerialTeam) continue;
-            const int off = s.toff[kk], nm = s.cnt[kk], ho = off + kk;
+            const int nm = s.cnt[kk];
+            if (nm == 0) continue;
+            const int off = s.toff[kk], ho = off + kk;
             const double *sx = s.sx + off, *sy = s.sy + off;
             const int16_t *mem = s.mem + off;
-            auto cost2 = [=](int i, int j) {
-                const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];
-                return sqrt(dx * dx + dy * dy);
-            };
-            assign_warp(cost2, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
-                        s.hcol + off);
+            if (nm <= 32) {
+                const double sxj = lane < nm ? sx[lane] : 0.0, syj = lane < nm ? sy[lane] : 0.0;
+                auto cost2 = [=](int i) {
+                    const double dx = ax[mem[i]] - sxj, dy = ay[mem[i]] - syj;
+                    return sqrt(dx * dx + dy * dy);
+                };
+                if (nm <= kPlanTeamPre) assign_warp_reg_pre(cost2, nm, nm, s.cw + (tid >> 5) * kPlanTeamPre * kPlanTeamPre, s.hcol + off);
+                else assign_warp_reg(cost2, nm, nm, s.hcol + off);
+            } else {
+                auto cost2 = [=](int i, int j) {
+                    const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];
+                    return sqrt(dx * dx + dy * dy);
+                };
+                assign_warp(cost2, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
+                            s.hcol + off);
+            }
         }
     }
     __syncthreads();
+    DCA_PROF(P, e, 8);
     // ---- forces (:175-188)
     for (int i = tid; i < A; i += nt) {
         const int a = s.mem[i];
@@ -534,6 +602,7 @@ __global__ void __launch_bounds__(kPlanThreads, 16) k_plan(const Params P, const
         if (c.disable_red_function) { fx = -fx; fy = -fy; }
         out[a] = make_double2(fx, fy);
     }
+    DCA_PROF(P, e, 9);
 }
 
 }  // namespace dca

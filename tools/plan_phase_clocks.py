@@ -1,0 +1,49 @@
+"""Diagnostics: per-phase clock breakdown of k_plan (thread-0 clock64 at phase boundaries, averaged over CTAs)."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from hmp2g_b200.config import ScenarioConfig  # noqa: E402
+from hmp2g_b200.vec_env import DcaVecEnv  # noqa: E402
+
+NAMES = ['load', 'teams (labels / k-means)', 'guard list + adjacency', 'components', 'targets + means', 'team->target',
+         'ring slots', 'member->slot', 'forces']
+
+
+def main(last=100, window=20, E=4096):
+    scfg = type('S', (ScenarioConfig,), dict(bench.WORKLOAD))
+    env = DcaVecEnv(E, scfg=scfg, seed=1)
+    env.reset()
+    g = torch.Generator(device=env.device)
+    g.manual_seed(0)
+    prof = torch.zeros((E, 16), dtype=torch.int64, device=env.device)
+    acc = np.zeros(9)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ms = 0.0
+    for t in range(last):
+        act = torch.randint(0, 7, (E, env.G), generator=g, device=env.device, dtype=torch.int32)
+        on = t >= last - window
+        env.lib.dca_debug_phase_clocks(env.handle, C.c_void_p(prof.data_ptr()) if on else None)
+        ev[0].record()
+        f = env.plan()
+        ev[1].record()
+        env.lib.dca_debug_phase_clocks(env.handle, None)
+        env.step(act, f)
+        if on:
+            torch.cuda.synchronize()
+            ms += ev[0].elapsed_time(ev[1])
+            c = prof.cpu().numpy().astype(np.float64)
+            acc += np.diff(c[:, :10], axis=1).mean(0)
+    acc /= window
+    for n, v in zip(NAMES, acc):
+        print('%-26s %9.0f cycles  %5.1f%%' % (n, v, 100 * v / acc.sum()))
+    print('CTA lifetime %.0f cycles, k_plan %.3f ms per launch' % (acc.sum(), ms / window))
+
+
+if __name__ == '__main__':
+    main(*(int(a) for a in sys.argv[1:3]))
