@@ -44,7 +44,7 @@ struct PlanSmem {
     int16_t *toff;                  // [K+1] member list offsets
     int16_t *mem, *tof;             // [A] members grouped by team / team of that list position
     double *c1;                     // [K*K] team-centroid <-> target distances
-    double *cw;                     // [warps][kPlanTeamPre^2] member <-> slot distances of the team a warp is working on
+    double *cw;                     // [warps][4][kPlanTeamPre^2] member <-> slot distances of the four teams a warp works on
     double *hu, *hv, *hminv;        // [A+K+2] assignment workspaces (team t owns [toff[t]+t, +n_t+1))
     int16_t *hp, *hway;             // [A+K+2]
     uint8_t *hused;                 // [A+K+2]
@@ -69,7 +69,7 @@ __host__ __device__ inline int plan_smem_bytes(int G, int A) {
     o += align_up(K * AW * 4, 16);       // lmask
     o += align_up(K * 2, 16) + align_up((K + 1) * 2, 16) + 2 * align_up(A * 2, 16);  // team_target toff mem tof
     o += align_up(K * K * 8, 16);        // c1
-    o += (kPlanThreads / 32) * kPlanTeamPre * kPlanTeamPre * 8;  // cw: one member x slot cost matrix per warp
+    o += (kPlanThreads / 32) * 4 * kPlanTeamPre * kPlanTeamPre * 8;  // cw: four member x slot cost matrices per warp
     o += 3 * align_up(H * 8, 16) + 2 * align_up(H * 2, 16) + align_up(H, 16);  // hu hv hminv hp hway hused
     o += align_up(A * 2, 16);            // hcol
     o += 2 * align_up(A * 8, 16);        // sx sy
@@ -99,7 +99,7 @@ __device__ __forceinline__ PlanSmem plan_carve(unsigned char *p, int G, int A) {
     s.toff = (int16_t *)p; p += align_up((K + 1) * 2, 16);
     s.mem = (int16_t *)p; p += a2; s.tof = (int16_t *)p; p += a2;
     s.c1 = (double *)p; p += align_up(K * K * 8, 16);
-    s.cw = (double *)p; p += (kPlanThreads / 32) * kPlanTeamPre * kPlanTeamPre * 8;
+    s.cw = (double *)p; p += (kPlanThreads / 32) * 4 * kPlanTeamPre * kPlanTeamPre * 8;
     const int h8 = align_up(H * 8, 16), h2 = align_up(H * 2, 16);
     s.hu = (double *)p; p += h8; s.hv = (double *)p; p += h8; s.hminv = (double *)p; p += h8;
     s.hp = (int16_t *)p; p += h2; s.hway = (int16_t *)p; p += h2;
@@ -254,6 +254,72 @@ __device__ __forceinline__ void assign_warp_reg_pre(CostFn cost_col, int n, int 
     __syncwarp();
     auto pre = [=](int r) { return scratch[r * m + lane]; };
     assign_warp_reg(pre, n, m, col_of_row);
+}
+
+// Four independent square assignments (n <= 8 each) advanced in lock-step by ONE warp: lanes 8g .. 8g+7 own the columns
+// of problem g and run assign_warp_reg's state machine on it (same arithmetic, same order, same ties); a problem that
+// has finished its search / its flip idles until the slowest one of the four is through, so the step count is the
+// maximum over the four problems instead of their sum.  `cost` is this lane's problem, row-major with stride 8;
+// n = 0 marks an empty segment.
+__device__ __forceinline__ void assign_seg8(const double *cost, int n, int16_t *col_of_row) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, base = lane & 24, lc = lane & 7;
+    const bool col = lc < n;
+    int nmax = n;
+    nmax = max(nmax, __shfl_xor_sync(full, nmax, 8));
+    nmax = max(nmax, __shfl_xor_sync(full, nmax, 16));
+    double v = 0.0, uc = 0.0;
+    int p = 0;
+    for (int i = 1; i <= nmax; ++i) {
+        double u0 = 0.0, minv = CUDART_INF;
+        int way = 0, j0 = 0;
+        bool used = !col;
+        bool go = i <= n;  // uniform over a segment
+        while (__any_sync(full, go)) {
+            if (go && lc == j0 - 1) used = true;
+            const int src = base + (j0 > 0 ? j0 - 1 : 0);
+            const int pj = __shfl_sync(full, p, src);
+            const double uj = __shfl_sync(full, uc, src);
+            const int i0 = j0 == 0 ? i : pj;
+            const double ui0 = j0 == 0 ? u0 : uj;
+            u64 key = ~0ull;
+            if (go && !used) {
+                const double cur = (cost[(i0 - 1) * 8 + lc] - ui0) - v;
+                if (cur < minv) { minv = cur; way = j0; }
+                key = plan_dkey(minv);
+            }
+            u64 kmin = key;
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) {
+                const u64 other = __shfl_xor_sync(full, kmin, o);
+                kmin = other < kmin ? other : kmin;
+            }
+            const unsigned holders = (__ballot_sync(full, go && !used && key == kmin) >> base) & 0xffu;
+            const double delta = plan_dkey_inv(kmin);
+            if (go) {
+                if (col) {
+                    if (used) { uc += delta; v -= delta; }
+                    else minv -= delta;
+                }
+                u0 += delta;
+                j0 = holders ? __ffs(holders) : 0;
+            }
+            const int pn = __shfl_sync(full, p, base + (j0 > 0 ? j0 - 1 : 0));
+            if (pn == 0 || j0 == 0) go = false;
+        }
+        while (__any_sync(full, j0 != 0)) {  // flip the augmenting paths
+            const int j1 = __shfl_sync(full, way, base + (j0 > 0 ? j0 - 1 : 0));
+            const int s1 = base + (j1 > 0 ? j1 - 1 : 0);
+            const int pj1 = __shfl_sync(full, p, s1);
+            const double uj1 = __shfl_sync(full, uc, s1);
+            if (j0 != 0) {
+                if (lc == j0 - 1) { p = j1 == 0 ? i : pj1; uc = j1 == 0 ? u0 : uj1; }
+                j0 = j1;
+            }
+        }
+    }
+    if (col && p) col_of_row[p - 1] = (int16_t)lc;
+    __syncwarp();
 }
 
 __device__ __forceinline__ double plan_sq2(double ax, double ay, double bx, double by) {
@@ -563,13 +629,38 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
     }
     __syncthreads();
     DCA_PROF(P, e, 7);
-    // ---- member -> slot (:171-173): one warp per team; up to 32 members entirely in registers
+    // ---- member -> slot (:171-173): teams of up to 8 go four at a time through one warp (assign_seg8), larger ones
+    // one warp per team (up to 32 members entirely in registers)
     {
-        const int nw = nt >> 5, lane = tid & 31;
+        const int nw = nt >> 5, warp = tid >> 5, lane = tid & 31, sg = lane >> 3, lc = lane & 7;
         const double *ax = s.ax, *ay = s.ay;
-        for (int kk = tid >> 5; kk < K; kk += nw) {  // warp-uniform
+        for (int kk = 0, b = 0;;) {  // warp-uniform scan for the next four small teams
+            int myk = -1, c4 = 0;
+            for (; kk < K && c4 < 4; ++kk) {
+                const int nm = s.cnt[kk];
+                if (nm >= 1 && nm <= kPlanTeamPre) {
+                    if (c4 == sg) myk = kk;
+                    ++c4;
+                }
+            }
+            if (c4 == 0) break;
+            if ((b++ % nw) != warp) continue;
+            const int nm = myk >= 0 ? s.cnt[myk] : 0, off = myk >= 0 ? s.toff[myk] : 0;
+            double *cs = s.cw + (warp * 4 + sg) * kPlanTeamPre * kPlanTeamPre;
+            if (lc < nm) {
+                const double sxj = s.sx[off + lc], syj = s.sy[off + lc];
+                for (int r = 0; r < nm; ++r) {
+                    const int a = s.mem[off + r];
+                    const double dx = ax[a] - sxj, dy = ay[a] - syj;
+                    cs[r * 8 + lc] = sqrt(dx * dx + dy * dy);
+                }
+            }
+            __syncwarp();
+            assign_seg8(cs, nm, s.hcol + off);
+        }
+        for (int kk = warp; kk < K; kk += nw) {  // warp-uniform
             const int nm = s.cnt[kk];
-            if (nm == 0) continue;
+            if (nm <= kPlanTeamPre) continue;
             const int off = s.toff[kk], ho = off + kk;
             const double *sx = s.sx + off, *sy = s.sy + off;
             const int16_t *mem = s.mem + off;
@@ -579,8 +670,7 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
                     const double dx = ax[mem[i]] - sxj, dy = ay[mem[i]] - syj;
                     return sqrt(dx * dx + dy * dy);
                 };
-                if (nm <= kPlanTeamPre) assign_warp_reg_pre(cost2, nm, nm, s.cw + (tid >> 5) * kPlanTeamPre * kPlanTeamPre, s.hcol + off);
-                else assign_warp_reg(cost2, nm, nm, s.hcol + off);
+                assign_warp_reg(cost2, nm, nm, s.hcol + off);
             } else {
                 auto cost2 = [=](int i, int j) {
                     const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];

@@ -28,6 +28,10 @@ echo "ncu full k_observe rc=$?"
 timeout 300 $SHORT > $out/plain4.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_mt_step -s 60 -c 1 -o $out/prof_mt $SHORT > $out/ncu_full_mt.log 2>&1
 echo "ncu full k_mt_step rc=$?"
+timeout 300 $SHORT > $out/plain5.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_plan -s 3 -c 1 -o $out/prof_plan $SHORT > $out/ncu_full_plan.log 2>&1
+echo "ncu full k_plan rc=$?"
+timeout 300 python tools/plan_phase_clocks.py > $out/plan_phase.log 2>&1; cat $out/plan_phase.log
 timeout 300 python tools/step_profile.py > $out/step_profile.txt 2>&1
 timeout 300 python tools/mt_phase_clocks.py > $out/mt_phase.log 2>&1
 ls -la $out
