@@ -26,6 +26,9 @@ struct DcaHandle {
     int64_t launches;
     PlanState plan;
     int plan_smem;
+    bool overlap_planner;           // DCA_OPT_OVERLAP_PLANNER
+    const void *planned_force;      // att_force / stream of the planner launch, if that was the handle's last launch
+    cudaStream_t planned_stream;
     std::string err;
 };
 
@@ -74,19 +77,37 @@ static float sq_limit(float lim) {
     return s;
 }
 
+// One launch path for the per-env kernels.  pdl: programmatic dependent launch (sm_90+) -- the grid may become resident
+// while the preceding kernel of the stream is still running; the kernel orders itself behind that kernel's results
+// with griddepcontrol.wait (k_step: just before it reads actions / attacker forces).
+template <typename... KArgs, typename... Args>
+static void launch_env_kernel(void (*kernel)(KArgs...), int grid, int threads, int smem, cudaStream_t st, bool pdl,
+                              Args... args) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)grid);
+    lc.blockDim = dim3((unsigned)threads);
+    lc.dynamicSmemBytes = (size_t)smem;
+    lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at;
+    lc.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&lc, kernel, KArgs(args)...);  // errors surface through cudaGetLastError() at the call site
+}
+
 // Kernel instantiations: the BASELINE team sizes get compile-time layouts, everything else the generic build.
-#define DCA_DISPATCH(h, KERNEL, ...)                                                                        \
-    do {                                                                                                    \
-        const int G_ = (h)->P.L.G, A_ = (h)->P.L.A;                                                         \
-        const dim3 grid_((h)->P.E);                                                                         \
-        if ((h)->threads == 128) {                                                                          \
-            if (G_ == 50 && A_ == 50) KERNEL<128, 50, 50><<<grid_, 128, (h)->smem, st_>>>(__VA_ARGS__);      \
-            else if (G_ == 50 && A_ == 55) KERNEL<128, 50, 55><<<grid_, 128, (h)->smem, st_>>>(__VA_ARGS__); \
-            else KERNEL<128, 0, 0><<<grid_, 128, (h)->smem, st_>>>(__VA_ARGS__);                             \
-        } else {                                                                                            \
-            if (G_ == 100 && A_ == 100) KERNEL<256, 100, 100><<<grid_, 256, (h)->smem, st_>>>(__VA_ARGS__);  \
-            else KERNEL<256, 0, 0><<<grid_, 256, (h)->smem, st_>>>(__VA_ARGS__);                             \
-        }                                                                                                   \
+#define DCA_DISPATCH(h, PDL, KERNEL, ...)                                                                      \
+    do {                                                                                                       \
+        const int G_ = (h)->P.L.G, A_ = (h)->P.L.A, E_ = (h)->P.E, sm_ = (h)->smem;                            \
+        if ((h)->threads == 128) {                                                                             \
+            if (G_ == 50 && A_ == 50) launch_env_kernel(KERNEL<128, 50, 50>, E_, 128, sm_, st_, PDL, __VA_ARGS__);      \
+            else if (G_ == 50 && A_ == 55) launch_env_kernel(KERNEL<128, 50, 55>, E_, 128, sm_, st_, PDL, __VA_ARGS__); \
+            else launch_env_kernel(KERNEL<128, 0, 0>, E_, 128, sm_, st_, PDL, __VA_ARGS__);                    \
+        } else {                                                                                               \
+            if (G_ == 100 && A_ == 100) launch_env_kernel(KERNEL<256, 100, 100>, E_, 256, sm_, st_, PDL, __VA_ARGS__);  \
+            else launch_env_kernel(KERNEL<256, 0, 0>, E_, 256, sm_, st_, PDL, __VA_ARGS__);                    \
+        }                                                                                                      \
     } while (0)
 
 template <typename K>
@@ -127,6 +148,9 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     h->device = device;
     h->bound = false;
     h->launches = 0;
+    h->overlap_planner = false;
+    h->planned_force = nullptr;
+    h->planned_stream = nullptr;
     std::memset(&h->P, 0, sizeof(Params));
     h->P.cfg = *cfg;
     h->P.L = make_layout(G, A);
@@ -213,8 +237,9 @@ int dca_reset(DcaHandle *h, const uint8_t *env_mask, dca_stream_t stream) {
     if (int rc = check_ready(h, "dca_reset")) return rc;
     DeviceGuard guard(h->device);
     cudaStream_t st_ = (cudaStream_t)stream;
-    DCA_DISPATCH(h, k_reset, h->P, env_mask);
+    DCA_DISPATCH(h, false, k_reset, h->P, env_mask);
     CUDA_TRY(h, cudaGetLastError());
+    h->planned_force = nullptr;
     h->launches += 1;
     return DCA_OK;
 }
@@ -227,8 +252,13 @@ int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, cons
         return fail(h, DCA_E_INVALID, "dca_step: att_force / rng_words must be 16-byte aligned");
     DeviceGuard guard(h->device);
     cudaStream_t st_ = (cudaStream_t)stream;
-    DCA_DISPATCH(h, k_step, h->P, actions, att_force, skip, rng_words, autoreset);
+    // Overlap with the planner (DCA_OPT_OVERLAP_PLANNER): only when this handle's previous launch was the planner that
+    // filled this att_force on this stream -- then everything k_step touches before its pdl_wait() (its own blobs,
+    // `skip`) is settled, and the forces are read after the wait.
+    const bool pdl = h->overlap_planner && h->planned_force == (const void *)att_force && h->planned_stream == st_;
+    DCA_DISPATCH(h, pdl, k_step, h->P, actions, att_force, skip, rng_words, autoreset);
     CUDA_TRY(h, cudaGetLastError());
+    h->planned_force = nullptr;
     h->launches += 1;
     return DCA_OK;
 }
@@ -237,8 +267,9 @@ int dca_observe(DcaHandle *h, const uint32_t *rng_words, dca_stream_t stream) {
     if (int rc = check_ready(h, "dca_observe")) return rc;
     DeviceGuard guard(h->device);
     cudaStream_t st_ = (cudaStream_t)stream;
-    DCA_DISPATCH(h, k_observe, h->P, rng_words);
+    DCA_DISPATCH(h, false, k_observe, h->P, rng_words);
     CUDA_TRY(h, cudaGetLastError());
+    h->planned_force = nullptr;
     h->launches += 1;
     return DCA_OK;
 }
@@ -249,6 +280,8 @@ int dca_plan_centroid(DcaHandle *h, double *att_force, dca_stream_t stream) {
     const int threads = 128, warps_per_block = threads / 32;
     k_plan_centroid<<<(h->P.E + warps_per_block - 1) / warps_per_block, threads, 0, (cudaStream_t)stream>>>(h->P, att_force);
     CUDA_TRY(h, cudaGetLastError());
+    h->planned_force = att_force;
+    h->planned_stream = (cudaStream_t)stream;
     h->launches += 1;
     return DCA_OK;
 }
@@ -262,6 +295,8 @@ int dca_plan(DcaHandle *h, double *att_force, const int32_t *team_label, const d
     DeviceGuard guard(h->device);
     k_plan<<<h->P.E, kPlanThreads, h->plan_smem, (cudaStream_t)stream>>>(h->P, h->plan, att_force, team_label, team_centroid);
     CUDA_TRY(h, cudaGetLastError());
+    h->planned_force = att_force;
+    h->planned_stream = (cudaStream_t)stream;
     h->launches += 1;
     return DCA_OK;
 }
@@ -278,6 +313,7 @@ static int state_io(DcaHandle *h, const DcaState *st, int import, dca_stream_t s
     const int blocks = (int)((total + 255) / 256);
     k_state_io<<<blocks, 256, 0, (cudaStream_t)stream>>>(h->P, *st, import);
     CUDA_TRY(h, cudaGetLastError());
+    h->planned_force = nullptr;
     h->launches += 1;
     return DCA_OK;
 }
@@ -531,6 +567,7 @@ int dca_mt_import_state(DcaMtHandle *h, const DcaMtState *src, dca_stream_t stre
 int dca_set_option(DcaHandle *h, int option, int value) {
     if (!h) return DCA_E_INVALID;
     if (option == DCA_OPT_EMPTY_ROWS_NAN) { h->P.empty_nan = value != 0; return DCA_OK; }
+    if (option == DCA_OPT_OVERLAP_PLANNER) { h->overlap_planner = value != 0; return DCA_OK; }
     return fail(h, DCA_E_INVALID, "dca_set_option: unknown option");
 }
 

@@ -172,12 +172,32 @@ __device__ __forceinline__ float f32_sqdist(float xi, float yi, float xj, float 
     return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
 }
 
-// 256-bit global store (sm_100: STG.E.ENL2.256); p must be 32-byte aligned
+// L2 residency hints: the observation tile is written once per step and never read back by these kernels, while the
+// env blobs (28 MB at 4096 x 50v50) are re-read by the next launch -- so obs stores carry L2::evict_first and the blob
+// bulk copies an evict_last policy, and the blobs stay in the 126 MB L2 under the 157 MB/step obs stream.
+#ifndef DCA_L2_HINTS
+#define DCA_L2_HINTS 1
+#endif
+
+// 256-bit global store (sm_100: STG.E.{ENL2,EFL2}.256); p must be 32-byte aligned
 __device__ __forceinline__ void st_global_256(float *p, float4 a, float4 b) {
+#if DCA_L2_HINTS
+    asm volatile("st.global.L2::evict_first.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z),
+                 "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
+                 : "memory");
+#else
     asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w),
                  "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
                  : "memory");
+#endif
 }
+
+// ------------------------------------------------------------------ programmatic dependent launch (PDL)
+// pdl_trigger: the next kernel of the stream, if launched with the programmatic-serialization attribute, may become
+// resident from here on.  pdl_wait: returns once the preceding kernel has completed and its writes are visible
+// (no-op for a normal launch).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // ------------------------------------------------------------------ TMA bulk copy (1-D) + mbarrier
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -205,18 +225,37 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase) {
             : "memory");
     } while (!ok);
 }
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
 // global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+#if DCA_L2_HINTS
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(l2_policy_evict_last())
+        : "memory");
+#else
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(smem_dst)),
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+#endif
 }
 // shared -> global bulk store
 __device__ __forceinline__ void tma_store_1d(void *gdst, const void *smem_src, uint32_t bytes) {
+#if DCA_L2_HINTS
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst),
+                 "r"(smem_u32(smem_src)), "r"(bytes), "l"(l2_policy_evict_last())
+                 : "memory");
+#else
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
                  "r"(bytes)
                  : "memory");
+#endif
 }
 __device__ __forceinline__ void tma_store_commit_wait() {
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");

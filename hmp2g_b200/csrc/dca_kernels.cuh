@@ -87,15 +87,13 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
 
 // Fetch the env blob with one TMA bulk copy; returns after the data has landed for every thread.
 __device__ __forceinline__ void load_blob(const Smem &s, const Params &P, const BlobLayout &L, int e) {
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0) {  // the copy is in flight before anybody else reaches the barrier below
         mbar_init(s.bar, 1);
         fence_barrier_init();
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
         mbar_expect_tx(s.bar, (uint32_t)L.bytes);
         tma_load_1d(s.blob, P.blobs + (size_t)e * L.bytes, (uint32_t)L.bytes, s.bar);
     }
+    __syncthreads();  // the mbarrier is initialised for every waiter
     mbar_wait(s.bar, 0);
 }
 
@@ -612,7 +610,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     const uint8_t *__restrict__ skip, const uint32_t *__restrict__ rng_words, int autoreset) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
-    if (skip != nullptr && skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay in place
+    if (skip != nullptr) {
+        pdl_wait();  // the pause mask may come from the kernel right before this one: no overlap when it is given
+        if (skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay in place
+    }
     const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
     const DcaConfig &c = P.cfg;
     const Smem s = carve(smem_raw, L);
@@ -758,6 +759,9 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     // phase D: deaths core.py:266-279, _set_action parallel_run.py:326-374 / planner force cheat_script_ai.py:183-184,
     // wall force core.py:210-222,339-353, integrate_state :282-302 (survivors only); then the agent's float32 entity
     // record and list position for the observation pass.
+    // Everything above read only the env's own blob (and `skip`); actions and attacker forces may come from the kernel
+    // right before this one in the stream (DCA_OPT_OVERLAP_PLANNER), so order behind it here.
+    pdl_wait();
     for (int q = tid; q < n_alive; q += nt) {
         const int i = s.alist[q];
         {
@@ -957,6 +961,7 @@ __global__ void k_init_blobs(const Params P) {
 // ------------------------------------------------------------------ benchmark planner stand-in (one warp per env)
 // force = centroid(alive guards) - pos for alive attackers.  NOT the reference planner (cheat_script_ai.py:28-194).
 __global__ void k_plan_centroid(const Params P, double *__restrict__ att_force) {
+    pdl_trigger();  // a dca_step launched behind this kernel may start its force-independent phases now
     const BlobLayout &L = P.L;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= P.E) return;

@@ -438,6 +438,7 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
                                                           const int32_t *__restrict__ inj_label,
                                                           const double *__restrict__ inj_cent) {
     extern __shared__ __align__(16) unsigned char plan_raw[];
+    pdl_trigger();  // a dca_step launched behind this kernel may start its force-independent phases now
     const BlobLayout &L = P.L;
     const DcaConfig &c = P.cfg;
     const int G = L.G, A = L.A, K = A / 5 > 0 ? A / 5 : 1, W = (G + 63) / 64, AW = (A + 31) / 32;

@@ -43,7 +43,7 @@ class DcaVecEnv(object):
     """n_env DCA envs resident on one GPU.  All tensors returned are views of buffers written in place."""
 
     def __init__(self, n_env, scfg=ScenarioConfig, device=None, seed=0, env_gid0=0, debug_outputs=False,
-                 empty_rows_nan=False):
+                 empty_rows_nan=False, overlap_planner=True):
         if not torch.cuda.is_available():
             raise _lib.DcaError('hmp2g_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
         self.lib = _lib.load()
@@ -72,6 +72,8 @@ class DcaVecEnv(object):
         self._force = torch.zeros((E, A, 2), dtype=torch.float64, device=dev)
         if empty_rows_nan:  # hand observations over the way conc's ShellEnvWrapper makes them (shell_env.py:72-75)
             _lib.check(self.lib.dca_set_option(self.handle, 1, 1), self.handle)
+        # DCA_OPT_OVERLAP_PLANNER: a step issued right behind plan() / plan_centroid() starts under the planner kernel
+        _lib.check(self.lib.dca_set_option(self.handle, 2, int(bool(overlap_planner))), self.handle)
 
     # -- lifetime -----------------------------------------------------------------------
     def close(self):

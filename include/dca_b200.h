@@ -239,6 +239,12 @@ int dca_mt_debug_phase_clocks(DcaMtHandle *h, uint64_t *clocks);
  * dead guard) as NaN instead of 0 -- what ShellEnvWrapper does to every observation on the host before the policy sees
  * it (ALGORITHM/conc/shell_env.py:72-75); default 0 = the env's own zeros (collective_assault_env.py:313-316,340-343). */
 #define DCA_OPT_EMPTY_ROWS_NAN 1
+/* DCA_OPT_OVERLAP_PLANNER: a dca_step that directly follows dca_plan / dca_plan_centroid on the same stream (same
+ * att_force, nothing enqueued between them) is launched as a programmatic dependent of the planner kernel: blob load,
+ * terrain, aim and laser run while the planner is still computing the forces; the step orders itself behind the
+ * planner right before it reads them.  Results are identical; `nearest` may be overwritten while the planner runs.
+ * Default 0. */
+#define DCA_OPT_OVERLAP_PLANNER 2
 int dca_set_option(DcaHandle *h, int option, int value);
 
 const char *dca_last_error(const DcaHandle *h); /* host string; h may be NULL for create/gae errors */

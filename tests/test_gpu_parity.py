@@ -427,6 +427,35 @@ def test_cuda_superpool_plan_ahead_equals_plan_in_step():
     assert n_done >= E
 
 
+@pytest.mark.parametrize('planner', ['centroid', 'scripted'])
+def test_cuda_step_overlapping_its_planner_is_bit_identical(planner):
+    """DCA_OPT_OVERLAP_PLANNER (the step kernel launched as a programmatic dependent of the planner kernel, ordering
+    itself behind it only before it reads the forces) must not change a single bit: full-size 50v50 batch, both planner
+    kernels, outputs and exported state compared with a strictly serial run."""
+    torch = _torch()
+    from hmp2g_b200.vec_env import DcaVecEnv
+    cfg = dict(num_guards=50, num_attackers=50, MaxEpisodeStep=40, random_jam_prob=0.05, introduce_terrain=True)
+    E = 4096
+    envs = [DcaVecEnv(E, scfg=scenario_from_dict(cfg), seed=11, env_gid0=0, overlap_planner=o) for o in (True, False)]
+    for env in envs:
+        env.reset()
+    gen = torch.Generator(device=envs[0].device)
+    gen.manual_seed(3)
+    n_done = 0
+    for t in range(90 if planner == 'centroid' else 50):
+        a = torch.randint(0, 7, (E, 50), generator=gen, device=envs[0].device, dtype=torch.int32)
+        for env in envs:
+            force = env.plan_centroid() if planner == 'centroid' else env.plan()
+            env.step(a, force)
+        for name in ('obs', 'tobs', 'reward', 'done', 'win', 'alive'):
+            assert torch.equal(getattr(envs[0], name), getattr(envs[1], name)), (t, name)
+        n_done += int(envs[0].done.sum().item())
+    assert n_done >= E
+    s0, s1 = envs[0].export_state(), envs[1].export_state()
+    for k in s0:
+        assert np.array_equal(np.asarray(s0[k]).view(np.uint8), np.asarray(s1[k]).view(np.uint8)), k
+
+
 def test_cuda_advantage_normalisation_matches_numpy_formula():
     """adv = ret - value; (adv - adv.mean()) / (adv.std() + 1e-5) as ALGORITHM/conc/ppo.py:53-55 evaluates it on the
     pooled float32 numpy batch (population std); tolerance 1e-5 (the reference sums in float32, the kernel in fp64)."""
