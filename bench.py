@@ -197,8 +197,14 @@ def run_ours(args):
     fptr = C.c_void_p(force.data_ptr())
     aptrs = [C.c_void_p(a.data_ptr()) for a in act_pool]
 
+    if args.planner == 'scripted':  # the reference's formation planner on the GPU (k_plan) instead of the stand-in
+        def plan_call(h_, f_, s_):
+            return lib.dca_plan(h_, f_, None, None, s_)
+    else:
+        plan_call = lib.dca_plan_centroid
+
     def one_step(i):
-        rc = lib.dca_plan_centroid(h, fptr, sptr)
+        rc = plan_call(h, fptr, sptr)
         rc |= lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
         return rc
 
@@ -221,7 +227,7 @@ def run_ours(args):
     # the planner stand-in, DCA_OPT_OVERLAP_PLANNER: an event between the two launches would serialise them)
     t_begin.record(stream)
     for i in range(K):
-        lib.dca_plan_centroid(h, fptr, sptr)
+        plan_call(h, fptr, sptr)
         lib.dca_step(h, aptrs[(W + i) % n_pool], fptr, None, None, 1, sptr)
     t_end.record(stream)
     torch.cuda.synchronize()
@@ -237,7 +243,7 @@ def run_ours(args):
     ev_e = [torch.cuda.Event(enable_timing=True) for _ in range(Kk)]
     lib.dca_set_option(h, 2, 0)
     for i in range(Kk):
-        lib.dca_plan_centroid(h, fptr, sptr)
+        plan_call(h, fptr, sptr)
         ev_s[i].record(stream)
         lib.dca_step(h, aptrs[(W + K + i) % n_pool], fptr, None, None, 1, sptr)
         ev_e[i].record(stream)
@@ -378,8 +384,10 @@ def run_ours(args):
         'warmup': W, 'ms_per_step': ms_total / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'f64', 'data': 'synthetic',
         'config': {'workload': 'DCA %dv%d step+obs+autoreset, %d envs/GPU, injected random guard actions, '
-                               'centroid planner stand-in (BASELINE.json configs[1]%s)'
-                               % (G, A, E, '' if args.scenario == '50v50' else ' at another team size'),
+                               '%s (BASELINE.json configs[1]%s)'
+                               % (G, A, E, 'centroid planner stand-in' if args.planner == 'centroid' else
+                                  'scripted formation planner k_plan in the timed region',
+                                  '' if args.scenario == '50v50' else ' at another team size'),
                    'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD, 'overlap_planner': bool(overlap),
                    'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
                          '> 126 MB L2' % ((E * (G * 768 + 2 * 5760)) / 1e6, E * G * 768 / 1e6, 2 * E * 5760 / 1e6),
@@ -442,6 +450,8 @@ def main():
     ap.add_argument('--envs-per-gpu', type=int, default=ENVS_PER_GPU)
     ap.add_argument('--e2e-steps', type=int, default=40)
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--planner', default='centroid', choices=['centroid', 'scripted'],
+                    help='attacker forces: the centroid stand-in of configs[1] (default) or the scripted formation planner k_plan')
     ap.add_argument('--no-overlap', action='store_true',
                     help='launch the step kernel strictly after the planner stand-in (DCA_OPT_OVERLAP_PLANNER off)')
     ap.add_argument('--traffic', type=float, default=None,

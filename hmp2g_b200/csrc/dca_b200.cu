@@ -577,6 +577,15 @@ int dca_debug_phase_clocks(DcaHandle *h, uint64_t *clocks) {
     return DCA_OK;
 }
 
+#ifdef DCA_DIAG_COUNT
+int dca_debug_counters(unsigned long long *out8, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out8, dca::g_diag, sizeof(unsigned long long) * 8);
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(dca::g_diag, z, sizeof(z)); }
+    return 0;
+}
+#endif
+
 int dca_kernel_launches(const DcaHandle *h, int64_t *count) {
     if (!h || !count) return DCA_E_INVALID;
     *count = h->launches;

@@ -9,8 +9,17 @@
 
 namespace dca {
 
+#ifndef DCA_KNN_SORT8
+#define DCA_KNN_SORT8 1  // kNN candidates: eight at a time through a sorting network (1) or one by one (0)
+#endif
+#ifndef DCA_AIM_SPLIT
+#define DCA_AIM_SPLIT 0  // scripted aim: a lane pair per attacker (1) or one lane (0)
+#endif
 #ifndef DCA_CTAS_128
 #define DCA_CTAS_128 8  // resident CTAs per SM the 128-thread kernels are register-budgeted for
+#endif
+#ifdef DCA_DIAG_COUNT
+__device__ unsigned long long g_diag[8];  // diagnostics build only: kNN task / close-call counters
 #endif
 constexpr int kPairCap = 256;  // queued (shooter, target) laser candidates per env; overflow is tested in place
 constexpr int kHintN = kVisN + 1;  // neighbours remembered per (guard, list) for the next pass
@@ -155,26 +164,31 @@ __device__ __forceinline__ void put_xy(const Smem &s, const BlobLayout &L, int i
 // Index-ordered list of the alive agents in [lo, hi): list[0..n), returns n (to every thread).
 // Warps that hold no alive agent then issue nothing in the loops over the list -- dead agents cost no issue slots.
 // CTA-wide; ends with a barrier (the list is visible to everyone on return).
-__device__ __forceinline__ int compact_alive(const Smem &s, int lo, int hi, int16_t *list) {
+// *n_below (optional): how many of them have an index below `split` (the alive guards, for split = G).
+__device__ __forceinline__ int compact_alive(const Smem &s, int lo, int hi, int16_t *list, int split = 0,
+                                             int *n_below = nullptr) {
     const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
-    int base = 0;
+    int base = 0, below = 0;
     for (int r0 = lo; r0 < hi; r0 += nt) {  // uniform
         const int i = r0 + tid;
         const bool alive = i < hi && (s.flags[i] & F_ALIVE);
         const uint32_t b = __ballot_sync(0xffffffffu, alive);
+        const uint32_t bb = __ballot_sync(0xffffffffu, alive && i < split);
         if (r0 != lo) __syncthreads();  // the previous round's counts have been read
-        if (lane == 0) s.misc[8 + warp] = __popc(b);
+        if (lane == 0) s.misc[8 + warp] = __popc(b) | (__popc(bb) << 16);
         __syncthreads();
         int off = base, tot = 0;
         for (int w = 0; w < nw; ++w) {
             const int cw = s.misc[8 + w];
-            off += w < warp ? cw : 0;
+            off += w < warp ? (cw & 0xffff) : 0;
             tot += cw;
         }
         if (alive) list[off + __popc(b & ((1u << lane) - 1u))] = (int16_t)i;
-        base += tot;
+        base += tot & 0xffff;
+        below += tot >> 16;
     }
     __syncthreads();
+    if (n_below) *n_below = below;
     return base;
 }
 
@@ -249,6 +263,7 @@ __device__ __noinline__ unsigned long long knn_exact(const float *lx, const floa
     int bi[kVisN];
 #pragma unroll
     for (int k = 0; k < kVisN; ++k) { bd[k] = CUDART_INF_F; bi[k] = -1; }
+    float lim = CUDART_INF_F;  // upper bound of the squares that can still enter the list
     const u64 px2 = pack2(pgx, pgx), py2 = pack2(pgy, pgy);
     const int nquad = (cnt + 3) >> 2;
     for (int c0 = 0; c0 < cnt; c0 += 32) {
@@ -257,7 +272,16 @@ __device__ __noinline__ unsigned long long knn_exact(const float *lx, const floa
             const int j = c0 + __ffs(m) - 1;
             m &= m - 1;
             const float sq = f32_sqdist(pgx, pgy, lx[j], ly[j]);
-            if (sq <= q0) top6_insert(bd, bi, __fsqrt_rn(sq), j);
+            // a candidate enters only if it is strictly nearer than the current 6th (ties keep the earlier, lower
+            // index): cheap bound on the square first, then the exact distance -- a stack of equidistant
+            // candidates costs a compare each, not an insertion
+            if (sq <= q0 && sq <= lim) {
+                const float d = __fsqrt_rn(sq);
+                if (d < bd[kVisN - 1]) {
+                    top6_insert(bd, bi, d, j);
+                    lim = __fmul_ru(__fmul_ru(bd[kVisN - 1], bd[kVisN - 1]), 1.000001f);  // inf while fewer than 6
+                }
+            }
         }
     }
     unsigned long long vis = 0;
@@ -265,6 +289,38 @@ __device__ __noinline__ unsigned long long knn_exact(const float *lx, const floa
 #pragma unroll
     for (int k = 0; k < kVisN; ++k)
         if (bi[k] >= 0) { vis |= (unsigned long long)bi[k] << (8 * n); ++n; }
+    *n_out = n;
+    return vis;
+}
+
+// Close call among the 7 kept keys only (the usual one): their exact (sqrt_rn distance, index) order decides, no
+// other candidate can reach the first six.  b0..b6 = the kept keys (index in the low bits, top bit = empty slot).
+__device__ __noinline__ unsigned long long knn_local_exact(const float *lx, const float *ly, float pgx, float pgy,
+                                                            uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3,
+                                                            uint32_t b4, uint32_t b5, uint32_t b6, uint32_t im,
+                                                            int *n_out) {
+    const uint32_t b[kHintN] = {b0, b1, b2, b3, b4, b5, b6};
+    u64 k[kHintN];
+#pragma unroll
+    for (int t = 0; t < kHintN; ++t) {
+        const bool valid = (int32_t)b[t] >= 0;
+        const int j = valid ? (int)(b[t] & im) : 0;
+        const float d = __fsqrt_rn(f32_sqdist(pgx, pgy, lx[j], ly[j]));
+        k[t] = valid ? (((u64)__float_as_uint(d) << 32) | (u64)j) : ~0ull;
+    }
+#define DCA_CEX(i, j) { const u64 lo_ = k[i] < k[j] ? k[i] : k[j]; k[j] = k[i] < k[j] ? k[j] : k[i]; k[i] = lo_; }
+    DCA_CEX(0, 6) DCA_CEX(2, 3) DCA_CEX(4, 5)
+    DCA_CEX(0, 2) DCA_CEX(1, 4) DCA_CEX(3, 6)
+    DCA_CEX(0, 1) DCA_CEX(2, 5) DCA_CEX(3, 4)
+    DCA_CEX(1, 2) DCA_CEX(4, 6)
+    DCA_CEX(2, 3) DCA_CEX(4, 5)
+    DCA_CEX(1, 2) DCA_CEX(3, 4) DCA_CEX(5, 6)
+#undef DCA_CEX
+    unsigned long long vis = 0;
+    int n = 0;
+#pragma unroll
+    for (int t = 0; t < kVisN; ++t)
+        if (k[t] != ~0ull) { vis |= (k[t] & 0xffull) << (8 * n); ++n; }
     *n_out = n;
     return vis;
 }
@@ -295,9 +351,66 @@ __device__ __forceinline__ unsigned long long knn_task(const float *lx, const fl
     const float thr = fminf(__fmul_ru(tub, 1.000001f), q0c);
     const u64 px2 = pack2(pgx, pgx), py2 = pack2(pgy, pgy);
     uint32_t b[kHintN];
+    uint32_t drop = 0xFFFFFFFFu;  // smallest key that did not make it into b[] (the 8th smallest overall)
+    const int nquad = (cnt + 3) >> 2;
+#if DCA_KNN_SORT8
+    // Exact key of candidate j (list padding measures +inf -> "no key").
+    auto key_of = [&](int j) -> uint32_t {
+        const float sq = f32_sqdist(pgx, pgy, lx[j], ly[j]);
+        return sq <= q0 ? ((__float_as_uint(sq) & ~im) | (uint32_t)j) : 0xFFFFFFFFu;
+    };
+    // The first 64 candidates: both chunk masks in one word.  When some task of the warp has more than a handful of
+    // candidates (warp-uniform test: the callers keep all 32 lanes in the task loop), the first eight of each lane are
+    // evaluated side by side -- independent loads and arithmetic instead of a loop-carried chain -- and ordered by a
+    // 19-exchange sorting network; the 7 smallest seed the insertion slots.  Whatever is left (and any candidate
+    // beyond the first 64) goes through the insertion chain below.
+    u64 m = (u64)scan_chunk(lx, ly, 0, min(8, nquad), px2, py2, thr);
+    if (cnt > 32) m |= (u64)scan_chunk(lx, ly, 32, min(8, nquad - 8), px2, py2, thr) << 32;
+    if (__reduce_max_sync(0xffffffffu, (unsigned)__popcll(m)) > 3u) {
+        uint32_t k[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const int j = m ? __ffsll((long long)m) - 1 : cnt;
+            m &= m - 1;
+            k[t] = key_of(j);
+        }
+#define DCA_CEX(i, j) { const uint32_t lo_ = min(k[i], k[j]); k[j] = max(k[i], k[j]); k[i] = lo_; }
+        DCA_CEX(0, 2) DCA_CEX(1, 3) DCA_CEX(4, 6) DCA_CEX(5, 7)
+        DCA_CEX(0, 4) DCA_CEX(1, 5) DCA_CEX(2, 6) DCA_CEX(3, 7)
+        DCA_CEX(0, 1) DCA_CEX(2, 3) DCA_CEX(4, 5) DCA_CEX(6, 7)
+        DCA_CEX(2, 4) DCA_CEX(3, 5)
+        DCA_CEX(1, 4) DCA_CEX(3, 6)
+        DCA_CEX(1, 2) DCA_CEX(3, 4) DCA_CEX(5, 6)
+#undef DCA_CEX
+#pragma unroll
+        for (int t = 0; t < kHintN; ++t) b[t] = k[t];
+        drop = k[7];
+    } else {
+#pragma unroll
+        for (int t = 0; t < kHintN; ++t) b[t] = 0xFFFFFFFFu;
+    }
+    for (int c0 = 0; c0 < cnt; c0 += 64) {
+        if (c0 > 0) {
+            m = (u64)scan_chunk(lx, ly, c0, min(8, nquad - (c0 >> 2)), px2, py2, thr);
+            if (cnt > c0 + 32) m |= (u64)scan_chunk(lx, ly, c0 + 32, min(8, nquad - 8 - (c0 >> 2)), px2, py2, thr) << 32;
+        }
+        while (m) {
+            uint32_t key = key_of(c0 + __ffsll((long long)m) - 1);
+            m &= m - 1;
+            if (key < b[kHintN - 1]) {  // anything else would fall straight through the chain
+#pragma unroll
+                for (int t = 0; t < kHintN; ++t) {
+                    const uint32_t lo = min(b[t], key);
+                    key = max(b[t], key);
+                    b[t] = lo;
+                }
+            }
+            drop = min(drop, key);  // what fell off the end (or never entered)
+        }
+    }
+#else
 #pragma unroll
     for (int k = 0; k < kHintN; ++k) b[k] = 0x80000000u + ((uint32_t)k << 8);  // empty slots: distinct, ascending
-    const int nquad = (cnt + 3) >> 2;
     for (int c0 = 0; c0 < cnt; c0 += 32) {
         uint32_t m = scan_chunk(lx, ly, c0, min(8, nquad - (c0 >> 2)), px2, py2, thr);
         while (m) {
@@ -311,16 +424,44 @@ __device__ __forceinline__ unsigned long long knn_task(const float *lx, const fl
                 key = max(b[k], key);
                 b[k] = lo;
             }
+            drop = min(drop, key);
         }
     }
+#endif
     bool close_call = false;
 #pragma unroll
     for (int k = 0; k < kVisN; ++k)
         close_call |= ((int32_t)b[k + 1] >= 0) && ((b[k + 1] >> idx_bits) - (b[k] >> idx_bits) <= 1u);
     unsigned long long vis = 0;
     int n = 0;
+#ifdef DCA_DIAG_NOEXACT
+    close_call = false;
+#endif
+#ifdef DCA_DIAG_NEVEREXACT
+    close_call = close_call && q0 < 0.f;  // never true at run time, unknown at compile time
+#endif
+#ifdef DCA_DIAG_COUNT
+    atomicAdd(&g_diag[0], 1ull);
     if (close_call) {
-        vis = knn_exact(lx, ly, cnt, pgx, pgy, thr, q0, &n);
+        atomicAdd(&g_diag[1], 1ull);
+        int nc = 0;
+        for (int j = 0; j < cnt; ++j) nc += f32_sqdist(pgx, pgy, lx[j], ly[j]) <= thr ? 1 : 0;
+        atomicAdd(&g_diag[2], (unsigned long long)nc);
+        int same = 0;
+#pragma unroll
+        for (int k = 0; k < kVisN; ++k) same += ((int32_t)b[k + 1] >= 0 && (b[k + 1] >> idx_bits) == (b[k] >> idx_bits)) ? 1 : 0;
+        atomicAdd(&g_diag[3], same > 0 ? 1ull : 0ull);
+        atomicAdd(&g_diag[4], cnt == 50 && lx != nullptr ? 1ull : 0ull);
+    }
+#endif
+    if (close_call) {
+        // Candidates outside b[] matter only if the tie chain runs through the 6th/7th kept key into the best dropped
+        // one; otherwise every dropped candidate is strictly farther (>= one whole key step in the square) than the
+        // first six, and the exact order of the kept keys settles it.
+        const bool c56 = ((int32_t)b[6] >= 0) && ((b[6] >> idx_bits) - (b[5] >> idx_bits) <= 1u);
+        const bool c6d = ((int32_t)drop >= 0) && ((drop >> idx_bits) - (b[6] >> idx_bits) <= 1u);
+        if (c56 && c6d) vis = knn_exact(lx, ly, cnt, pgx, pgy, thr, q0, &n);
+        else vis = knn_local_exact(lx, ly, pgx, pgy, b[0], b[1], b[2], b[3], b[4], b[5], b[6], im, &n);
     } else {
 #pragma unroll
         for (int k = 0; k < kVisN; ++k)
@@ -364,8 +505,16 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
     const uint32_t gid = (uint32_t)(P.cfg.env_gid0 + e);
     // One task per (alive guard, list), packed densely over the threads: warps beyond the last task issue nothing.
     // (Dead guards' rows were preset to "empty"; their hints are not needed before the next reset rewrites them.)
-    for (int task = tid; task < 2 * n_obs_guards; task += nt) {
-        const int g = s.glist[task >> 1], lst = task & 1;  // 0 = hostile (:318-328), 1 = friend (:330-342)
+    // Hostile-list tasks first, friend-list tasks after them: a warp then holds tasks of one kind, and the hostile ones
+    // (often no candidate in range, no RNG draws) do not sit idle in the lanes next to a friend list's candidate loop.
+    // All 32 lanes of a warp stay in the loop (knn_task votes across the warp): lanes past the last task repeat it
+    // and write nothing.
+    const int n_tasks = 2 * n_obs_guards;
+    for (int task0 = tid & ~31; task0 < n_tasks; task0 += nt) {
+        const bool valid = task0 + (tid & 31) < n_tasks;
+        const int task = valid ? task0 + (tid & 31) : n_tasks - 1;
+        const int lst = task >= n_obs_guards ? 1 : 0;  // 0 = hostile (:318-328), 1 = friend (:330-342)
+        const int g = s.glist[task - (lst ? n_obs_guards : 0)];
         int16_t *sid = s.sid + g * kObsRows + (lst == 0 ? kVisN : 0);  // friend rows 0..5, hostile rows 6..11 (:344)
         const int cnt = lst == 0 ? L.A : L.G;
         const int hint_slot = 2 * g + lst;
@@ -375,6 +524,7 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
         float nearest;
         unsigned long long vis = knn_task(lst == 0 ? s.xa : s.xg, lst == 0 ? s.ya : s.yg, cnt, s.xg[g], s.yg[g],
                                           s.knn_ids[hint_slot], P.smax[lst], P.idx_bits, &n, &ids, &nearest);
+        if (!valid) continue;
         s.knn_ids[hint_slot] = ids;
         if (lst == 0) s.hmin[g] = nearest;
         int row = 0;
@@ -393,7 +543,11 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
                     w[4 * b] = q.x; w[4 * b + 1] = q.y; w[4 * b + 2] = q.z; w[4 * b + 3] = q.w;
                 }
             } else {
+#ifdef DCA_DIAG_NOPHILOX
+                const int nblk = 0;
+#else
                 const int nblk = n <= 2 ? 1 : (n <= 4 ? 2 : 3);
+#endif
 #pragma unroll
                 for (int b = 0; b < 3; ++b) {
                     if (b < nblk) {
@@ -640,16 +794,8 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
             if (i >= L.G && P.out.nearest) P.out.nearest[(size_t)e * L.A + (i - L.G)] = -1;
         }
     }
-    const int n_alive = compact_alive(s, 0, L.N, s.alist);
-    int n_alive_g = 0;  // alive guards = entries of alist below G (index order)
-    {
-        int lo = 0, hi = n_alive;
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            if (s.alist[mid] < L.G) lo = mid + 1; else hi = mid;
-        }
-        n_alive_g = lo;
-    }
+    int n_alive_g = 0;  // alive guards = the entries of alist below G (index order: they come first)
+    const int n_alive = compact_alive(s, 0, L.N, s.alist, L.G, &n_alive_g);
     // phase A: terrain (core.py:224-234), clear hit flags (core.py:239-242), float32 position lists of the pre-move
     // state.  (Action decode and the injected planner force are read where they are used, in phase D.)
     for (int q = tid; q < n_alive; q += nt) {
@@ -669,6 +815,60 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     {
         const uint32_t im = (1u << P.idx_bits) - 1u;
         const int Gq = (L.G + 3) >> 2;
+#if DCA_AIM_SPLIT
+        // A lane pair per alive attacker: each lane scans half of the guard quads, the two (smallest, runner-up) key
+        // pairs are merged with one shuffle each; then the even lane resolves the angle and the odd lane the shooter
+        // test.  All 32 lanes of a warp run the same number of rounds (the shuffles need them).
+        const int n_att = n_alive - n_alive_g, Gh = (Gq + 1) >> 1;
+        for (int p0 = (tid & ~31) >> 1; p0 < n_att; p0 += nt >> 1) {
+            const int p = p0 + ((tid & 31) >> 1), half = tid & 1;
+            const bool active = p < n_att;
+            const int i = active ? s.alist[n_alive_g + p] : L.G, t = i - L.G;
+            const float pox = s.xa[t], poy = s.ya[t];
+            const u64 px2 = pack2(pox, pox), py2 = pack2(poy, poy);
+            const ulonglong2 *x4 = (const ulonglong2 *)s.xg, *y4 = (const ulonglong2 *)s.yg;
+            uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
+            const int q_lo = half ? Gh : 0, q_hi = active ? (half ? Gq : Gh) : 0;
+#pragma unroll 4
+            for (int q = q_lo; q < q_hi; ++q) {
+                const ulonglong2 xs = x4[q], ys = y4[q];
+                const u64 s01 = sqdist2(xs.x, ys.x, px2, py2), s23 = sqdist2(xs.y, ys.y, px2, py2);
+                const uint32_t ka = (__float_as_uint(lo2(s01)) & ~im) | (uint32_t)(4 * q);
+                const uint32_t kb = (__float_as_uint(hi2(s01)) & ~im) | (uint32_t)(4 * q + 1);
+                const uint32_t kc = (__float_as_uint(lo2(s23)) & ~im) | (uint32_t)(4 * q + 2);
+                const uint32_t kd = (__float_as_uint(hi2(s23)) & ~im) | (uint32_t)(4 * q + 3);
+                const uint32_t lab = min(ka, kb), hab = max(ka, kb), lcd = min(kc, kd), hcd = max(kc, kd);
+                const uint32_t lo4 = min(lab, lcd), se4 = min(max(lab, lcd), min(hab, hcd));
+                m2 = min(min(m2, se4), max(m1, lo4));
+                m1 = min(m1, lo4);
+            }
+            {
+                const uint32_t o1 = __shfl_xor_sync(0xffffffffu, m1, 1), o2 = __shfl_xor_sync(0xffffffffu, m2, 1);
+                m2 = min(max(m1, o1), min(m2, o2));
+                m1 = min(m1, o1);
+            }
+            if (!active) continue;
+            if (half == 0) {
+                int best = (int)(m1 & im);
+                if ((m2 >> P.idx_bits) - (m1 >> P.idx_bits) <= 1u && m1 < 0x7F800000u) {
+                    float bd = CUDART_INF_F;
+                    best = 0;
+                    for (int g = 0; g < L.G; ++g) {
+                        const float d = f32_dist(pox, poy, s.xg[g], s.yg[g]);
+                        if (d < bd) { bd = d; best = g; }
+                    }
+                }
+                if (m1 >= 0x7F800000u) best = 0;  // no guard alive: argmin of an all-inf row is 0
+                double th = atan2(s.py[best] - s.py[i], s.px[best] - s.px[i]);
+                if (th < 0) th += 2 * kPi;
+                s.atk[i] = th;
+                if (P.out.nearest) P.out.nearest[(size_t)e * L.A + t] = best;
+            } else {
+                // can_fire (cheat_script_ai.py:214-217): candidate shooter if the nearest guard may be inside the radius
+                if (!c.disable_red_function && __uint_as_float(m1 & ~im) <= laser_r2f(s, c, i)) push_shooter(s, i);
+            }
+        }
+#else
         for (int q = n_alive_g + tid; q < n_alive; q += nt) {
             const int i = s.alist[q], t = i - L.G;
             int best = -1;
@@ -709,6 +909,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
             }
             if (P.out.nearest) P.out.nearest[(size_t)e * L.A + t] = best;
         }
+#endif
         // guards: hmin = lower bound of the squared distance to the nearest alive attacker, left by the last
         // observation pass (same positions, same alive set)
         for (int q = tid; q < n_alive_g; q += nt) {

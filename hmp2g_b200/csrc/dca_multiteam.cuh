@@ -275,7 +275,11 @@ __device__ __forceinline__ void mt_obs_pass(const MtSmem &s, const MtParams &P, 
                 const int id = s.sid[slot];
                 v[u] = s.table[(size_t)(id < 0 ? N : id) * kMtRow + c];
             }
+#if DCA_L2_HINTS
+            __stcs(&o4[q], make_float4(v[0], v[1], v[2], v[3]));  // written once, read by the policy: stream past L2
+#else
             o4[q] = make_float4(v[0], v[1], v[2], v[3]);
+#endif
         }
         if (P.out.slot_id) {
             int16_t *o = P.out.slot_id + (size_t)e * N * kObsRows;

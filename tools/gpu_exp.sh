@@ -3,8 +3,10 @@
 tag=${1:-exp}
 out=gpurun_out/$tag
 mkdir -p $out
+if [ -z "$SKIP_PYTEST" ]; then
 timeout 900 python -m pytest tests -m gpu -x -q > $out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
 tail -5 $out/pytest_gpu.log
+fi
 B="--no-cpu-baseline --steps 900 --warmup 100 --e2e-steps 3"
 show() { python - "$1" "$2" <<'PY'
 import json,sys
@@ -16,11 +18,12 @@ except Exception as e:
 PY
 }
 timeout 300 python bench.py $B > $out/bench_default.json 2> $out/bench_default.err; show default $out/bench_default.json
-timeout 300 python bench.py $B --no-overlap > $out/bench_nooverlap.json 2> $out/bench_nooverlap.err; show no-overlap $out/bench_nooverlap.json
 cp hmp2g_b200/libdca_b200.so /tmp/default.so
+shopt -s nullglob
 for v in tools/variants/*.so; do
   n=$(basename $v .so)
   cp $v hmp2g_b200/libdca_b200.so
+  [[ $n == diag* ]] || timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "matches_reference_golden or no_resync or full_size_4096 or 100v100 or ragged" > $out/pytest_$n.log 2>&1; echo "$n parity subset rc=$? $(tail -1 $out/pytest_$n.log)"
   timeout 300 python bench.py $B > $out/bench_$n.json 2> $out/bench_$n.err; show $n $out/bench_$n.json
 done
 cp /tmp/default.so hmp2g_b200/libdca_b200.so
