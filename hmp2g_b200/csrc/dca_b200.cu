@@ -168,6 +168,13 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
         const double t = std::ceil(cfg->random_jam_prob * 4294967296.0);
         h->P.jam_thresh = t <= 0 ? 0ull : (t >= 4294967296.0 ? 4294967296ull : (unsigned long long)t);
     }
+    {
+        // laser_hit_improve3 (cython_func.pyx:22-46) accepts a target iff |reg(dir + w/2 - theta)| <= w and
+        // |reg(dir - w/2 - theta)| <= w; for w < 2 pi / 3 the wrapped branches can never pass, and the test is "the
+        // target direction lies within w/2 of the heading": dot(heading, d) >= cos(w/2) |d|
+        const double w = cfg->agent_shoot_win;
+        h->P.cone_cos2 = (w > 0.0 && w <= 2.0) ? std::cos(w / 2) * std::cos(w / 2) : 0.0;
+    }
     h->threads = (G + A) <= 128 ? 128 : 256;
     h->smem = smem_bytes(h->P.L);
     const size_t bytes = (size_t)n_env * h->P.L.bytes;

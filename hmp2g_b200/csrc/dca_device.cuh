@@ -82,6 +82,7 @@ struct Params {
     float smax[2];     // [hostile, friend]: largest f32 s with sqrt_rn(s) <= obs range (2.0 / 3.0)
     int idx_bits;      // low bits of a kNN / aim key that hold the candidate index
     unsigned long long jam_thresh;  // a jam draw w (u32) removes an item iff w < jam_thresh  (== w * 2^-32 < random_jam_prob)
+    double cone_cos2;  // cos^2(agent_shoot_win / 2) when the laser window test can be done as a cone test, else 0
     int empty_nan;     // DCA_OPT_EMPTY_ROWS_NAN: invisible / jammed / empty obs rows (and dead guards' obs) are NaN, not 0
 };
 

@@ -140,12 +140,13 @@ __device__ __forceinline__ double terrain_at(const DcaConfig &c, double X, doubl
 }
 
 // Padding slots of the float32 position lists (+inf) and the all-zero table row; once per kernel.
-__device__ __forceinline__ void init_pads(const Smem &s, const BlobLayout &L, const Params &P) {
+__device__ __forceinline__ void init_pads(const Smem &s, const BlobLayout &L, const Params &P, bool lists = true,
+                                          bool zero_row = true) {
     const int t = threadIdx.x;
     const int ng = list_pad(L.G) - L.G, na = list_pad(L.A) - L.A;  // 1..4 each
-    if (t < ng) { s.xg[L.G + t] = CUDART_INF_F; s.yg[L.G + t] = CUDART_INF_F; }
-    else if (t < ng + na) { s.xa[L.A + t - ng] = CUDART_INF_F; s.ya[L.A + t - ng] = CUDART_INF_F; }
-    else if (t < ng + na + 4) {
+    if (t < ng) { if (lists) { s.xg[L.G + t] = CUDART_INF_F; s.yg[L.G + t] = CUDART_INF_F; } }
+    else if (t < ng + na) { if (lists) { s.xa[L.A + t - ng] = CUDART_INF_F; s.ya[L.A + t - ng] = CUDART_INF_F; } }
+    else if (t < ng + na + 4 && zero_row) {
         // the conc / conc_4hist policies turn all-zero rows into NaN first thing (ALGORITHM/conc/shell_env.py:72-75):
         // with DCA_OPT_EMPTY_ROWS_NAN the kernel hands them over that way
         const float z = P.empty_nan ? __int_as_float(0x7fc00000) : 0.f;
@@ -645,8 +646,20 @@ __device__ __forceinline__ void reset_world(const Smem &s, const Params &P, cons
         s.sc->cos_theta = ct;
         s.sc->sin_theta = sn;
     }
-    // positions jump: no kNN hints (every remembered neighbour = the marker slot, which measures +inf)
-    for (int k = tid; k < 2 * L.G; k += nt) s.knn_ids[k] = 0x0101010101010101ull * (u64)((k & 1) ? L.G : L.A);
+    // positions jump: the remembered neighbours are void.  Hostile lists: no hint (every entry = the marker slot, which
+    // measures +inf).  Friend lists: the formation puts guards in index order along a line (:115-119), so the 7 index
+    // neighbours of a guard are a good hint -- any 7 distinct live candidates bound the search radius, and all guards
+    // are alive after a reset.
+    for (int k = tid; k < 2 * L.G; k += nt) {
+        u64 ids = 0x0101010101010101ull * (u64)((k & 1) ? L.G : L.A);
+        if ((k & 1) && L.G >= kHintN) {
+            const int g = k >> 1, lo = min(max(g - kHintN / 2, 0), L.G - kHintN);
+            ids = 0;
+#pragma unroll
+            for (int t = 0; t < kHintN; ++t) ids |= (u64)(lo + t) << (8 * t);
+        }
+        s.knn_ids[k] = ids;
+    }
     for (int i = tid; i < L.N; i += nt) {
         const uint4 a = philox4x32_10(gid, ep, (uint32_t)(1 + i), SITE_RESET, k0, k1);
         const bool attacker = i >= L.G;
@@ -919,10 +932,21 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     }
     __syncthreads();
     DCA_PROF(P, e, 3);
-    // phase C: apply_laser_effect core.py:244-263.  C1: every listed shooter scans the opposing team with the packed
-    // float32 pre-filter and queues the few (shooter, target) candidates; C2: one exact fp64 test per queued pair.
+    // phase C: apply_laser_effect core.py:244-263.  C1: every listed shooter resolves its unit heading and scans the
+    // opposing team with the packed float32 pre-filter, queueing (shooter, target) candidates; C2: the whole CTA works
+    // through the queue, one pair per thread: the reference's range test (d2 > r2 -> miss, same arithmetic), then its
+    // window test in cone form -- |reg(dir +- w/2 - theta)| <= w  <=>  dot(heading, d) >= cos(w/2) |d| -- unless that
+    // is within 1e-9 (relative) of the boundary, ~1e6 times the rounding error of either formulation; those pairs
+    // (and every pair when the window is too wide for the cone form) get the atan2 test.  A serial loop per shooter
+    // (fp64 chains, divergent outcomes) was the longest thing in the kernel for envs where the teams are on top of each
+    // other: 30 k cycles against a CTA lifetime of 29 k.  Headings and queue live in the entity-table region, which is
+    // not written before phase D.
     const int nsh = s.misc[2];
     if (nsh > 0) {  // uniform over the CTA
+        double *hx = (double *)s.table, *hy = hx + L.N;
+        uint32_t *pairq = (uint32_t *)(hy + L.N);
+        const int pair_cap = 12 * L.N;  // table region = (N + 1) * 64 B = 16 N (headings) + 48 N + 64
+        const double cc2 = P.cone_cos2;
         for (int q = tid; q < nsh; q += nt) {
             const int i = s.shooters[q];
             const bool att = i >= L.G;
@@ -932,6 +956,11 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
             const u64 px2 = pack2(pox, pox), py2 = pack2(poy, poy);
             const float r2f = laser_r2f(s, c, i);
             const int nquad = (opp_cnt + 3) >> 2;
+            if (cc2 > 0) {
+                double sn_, cs_;
+                sincos(s.atk[i], &sn_, &cs_);
+                hx[i] = cs_; hy[i] = sn_;
+            }
             for (int c0 = 0; c0 < opp_cnt; c0 += 32) {
                 uint32_t m = scan_chunk(ox, oy, c0, min(8, nquad - (c0 >> 2)), px2, py2, r2f);
                 if (r2f == CUDART_INF_F) {  // no bound: every alive opponent is a candidate (inf <= inf passes above)
@@ -939,24 +968,60 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
                     for (int j = 0; j < 32 && c0 + j < opp_cnt; ++j)
                         if (s.flags[opp_base + c0 + j] & F_ALIVE) m |= 1u << j;
                 }
+                // Queue slots for the whole warp with ONE atomic (the lanes in this loop are a prefix of the warp):
+                // one atomic per candidate on the single counter word serialised the CTA -- 500 pairs took 27 k cycles.
+                const unsigned act = __activemask();
+                const int lane = tid & 31, cntm = __popc(m);
+                int incl = cntm;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(act, incl, o);
+                    if (lane >= o) incl += v;
+                }
+                const int last = 31 - __clz(act);
+                int slot = 0;
+                if (lane == last && incl > 0) slot = atomicAdd(&s.misc[3], incl);
+                slot = __shfl_sync(act, slot, last) + incl - cntm;
                 while (m) {
                     const int j = opp_base + c0 + __ffs(m) - 1;
                     m &= m - 1;
-                    const int slot = atomicAdd(&s.misc[3], 1);
-                    if (slot < kPairCap) s.pairs[slot] = ((uint32_t)i << 16) | (uint32_t)j;
-                    else laser_pair(s, c, i, j);
+                    if (slot < pair_cap) pairq[slot] = ((uint32_t)i << 16) | (uint32_t)j;
+                    else laser_pair(s, c, i, j);  // queue full: the reference's arithmetic, in place
+                    ++slot;
                 }
             }
         }
         __syncthreads();
-        const int np = min(s.misc[3], kPairCap);
+        const int np = min(s.misc[3], pair_cap);
         for (int q = tid; q < np; q += nt) {
-            const uint32_t pr = s.pairs[q];
-            laser_pair(s, c, (int)(pr >> 16), (int)(pr & 0xffffu));
+            const uint32_t pr = pairq[q];
+            const int i = (int)(pr >> 16), j = (int)(pr & 0xffffu);
+            if (cc2 > 0) {
+                const double radius = c.agent_shoot_base_radius * s.ter[i], r2 = radius * radius;
+                const double dx = s.px[j] - s.px[i], dy = s.py[j] - s.py[i];
+                const double len2 = dx * dx + dy * dy;
+                if (len2 > r2) continue;  // out of range (cython_func.pyx:30-31)
+                const double dot = dx * hx[i] + dy * hy[i];
+                const double margin = dot * dot - cc2 * len2;
+                if (len2 > 1e-100 && fabs(margin) > 1e-9 * len2) {
+                    if (dot > 0.0 && margin > 0.0) {
+                        // piled-up agents hit the same target from neighbouring queue slots: lanes with the same
+                        // target add once instead of fighting over one shared-memory word
+                        atomicAdd(&s.shots[i], 1);
+                        const unsigned same = __match_any_sync(__activemask(), j);
+                        if ((int)(__ffs(same) - 1) == (tid & 31)) atomicAdd(&s.hitcnt[j], __popc(same));
+                    }
+                    continue;
+                }
+            }
+            laser_pair(s, c, i, j);
         }
         __syncthreads();
+        // the table region is the observation pass's again: restore its all-zero record
+        init_pads(s, L, P, false, true);
     }
     DCA_PROF(P, e, 4);
+
     // phase D: deaths core.py:266-279, _set_action parallel_run.py:326-374 / planner force cheat_script_ai.py:183-184,
     // wall force core.py:210-222,339-353, integrate_state :282-302 (survivors only); then the agent's float32 entity
     // record and list position for the observation pass.
@@ -1060,6 +1125,13 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     DCA_PROF(P, e, 10);
     store_blob(s, P, L, e);
     DCA_PROF(P, e, 11);
+    if (P.prof != nullptr && threadIdx.x == 0) {  // diagnostics: wall-clock end of the CTA (ns) and the SM it ran on
+        unsigned long long gt;
+        unsigned sm;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        P.prof[(size_t)e * 16 + 15] = (gt << 8) | (unsigned long long)(sm & 0xffu);
+    }
 }
 
 // reset kernel: SuperpoolEnv.reset -> collective_assaultGlobalEnv.reset parallel_run.py:248-270
