@@ -1007,9 +1007,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
                     if (dot > 0.0 && margin > 0.0) {
                         // piled-up agents hit the same target from neighbouring queue slots: lanes with the same
                         // target add once instead of fighting over one shared-memory word
-                        atomicAdd(&s.shots[i], 1);
-                        const unsigned same = __match_any_sync(__activemask(), j);
-                        if ((int)(__ffs(same) - 1) == (tid & 31)) atomicAdd(&s.hitcnt[j], __popc(same));
+                        const unsigned hit = __activemask();
+                        const unsigned same_j = __match_any_sync(hit, j), same_i = __match_any_sync(hit, i);
+                        if ((int)(__ffs(same_j) - 1) == (tid & 31)) atomicAdd(&s.hitcnt[j], __popc(same_j));
+                        if ((int)(__ffs(same_i) - 1) == (tid & 31)) atomicAdd(&s.shots[i], __popc(same_i));
                     }
                     continue;
                 }
