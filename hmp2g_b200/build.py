@@ -6,7 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB_PATH = os.path.join(HERE, 'libdca_b200.so')
 SOURCES = ['dca_b200.cu']
-HEADERS = ['dca_device.cuh', 'dca_kernels.cuh', os.path.join('..', '..', 'include', 'dca_b200.h')]
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith('.cuh')) + [os.path.join('..', '..', 'include', 'dca_b200.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               # numpy evaluates every product and sum with its own rounding: never contract into FMA
               '-fmad=false', '-shared', '-Xcompiler', '-fPIC']

@@ -67,6 +67,24 @@ struct DeviceGuard {
         if (prev >= 0) cudaSetDevice(prev);
     }
 };
+// The handle-less entry points (dca_gae, dca_runner_*, dca_histpool_roll, dca_adv_*) launch on the device that owns
+// their buffers, whatever device is current in the calling thread.
+struct PtrDeviceGuard {
+    int prev = -1;
+    explicit PtrDeviceGuard(const void *p) {
+        cudaPointerAttributes a;
+        if (p && cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeDevice) {
+            cudaGetDevice(&prev);
+            if (prev != a.device) cudaSetDevice(a.device);
+            else prev = -1;
+        } else {
+            cudaGetLastError();  // not a device pointer known to the runtime: leave the current device alone
+        }
+    }
+    ~PtrDeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
 }  // namespace
 
 // largest float s with sqrtf(s) <= lim (sqrtf is correctly rounded, like __fsqrt_rn and numpy's float32 sqrt)
@@ -192,11 +210,18 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
         if (e == cudaSuccess) e = cudaMemset(h->plan.label, 0, (size_t)n_env * A);
         if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.cent, (size_t)n_env * K * 16);
         if (e == cudaSuccess) e = cudaMemset(h->plan.cent, 0, (size_t)n_env * K * 16);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, h->plan_smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     std::max(plan_smem_bytes(250, 250), plan_smem_bytes(kMaxN - 6, 6)));
     }
-    DCA_ALLOW_SMEM(k_step, h->smem);
-    DCA_ALLOW_SMEM(k_reset, h->smem);
-    DCA_ALLOW_SMEM(k_observe, h->smem);
+    // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-function (per-device) setting shared by every handle: raise
+    // it once to what the largest admissible layout needs instead of each handle overwriting it with its own size
+    {
+        const int max_smem = smem_bytes(make_layout(kMaxN / 2, kMaxN - kMaxN / 2));
+        DCA_ALLOW_SMEM(k_step, max_smem);
+        DCA_ALLOW_SMEM(k_reset, max_smem);
+        DCA_ALLOW_SMEM(k_observe, max_smem);
+    }
     if (e == cudaSuccess) {
         k_init_blobs<<<(n_env + 255) / 256, 256>>>(h->P);
         e = cudaGetLastError();
@@ -333,6 +358,7 @@ int dca_gae(const float *reward, const float *value, const uint8_t *dead, const 
             dca_stream_t stream) {
     if (!reward || !value || !dead || !ret || T <= 0 || E <= 0 || G <= 0)
         return fail(nullptr, DCA_E_INVALID, "dca_gae: null argument or empty shape");
+    PtrDeviceGuard guard(reward);
     const size_t S = (size_t)E * G;
     const int threads = 128;
     k_gae<<<(unsigned)((S + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
@@ -346,16 +372,18 @@ int dca_runner_init(const DcaRunnerState *s, int n_env, int n_agent, dca_stream_
     if (!s || !s->pause || !s->suffered || !s->cur_step || !s->ep_cnt || !s->reward_sum || !s->counters || !s->fin_slot ||
         !s->log_meta || !s->log_reward || n_env <= 0 || n_agent <= 0 || s->log_capacity < n_env)
         return fail(nullptr, DCA_E_INVALID, "dca_runner_init: null buffer, empty shape or log_capacity < n_env");
+    PtrDeviceGuard guard(s->pause);
     cudaStream_t st = (cudaStream_t)stream;
-    cudaMemsetAsync(s->pause, 0, n_env, st);
-    cudaMemsetAsync(s->suffered, 1, n_env, st);
-    cudaMemsetAsync(s->cur_step, 0, sizeof(int32_t) * n_env, st);
-    cudaMemsetAsync(s->ep_cnt, 0, sizeof(int32_t) * n_env, st);
-    cudaMemsetAsync(s->reward_sum, 0, sizeof(double) * n_env * n_agent, st);
-    cudaMemsetAsync(s->counters, 0, sizeof(int64_t) * 8, st);
-    cudaMemsetAsync(s->fin_slot, 0, sizeof(int32_t) * n_env, st);
-    cudaMemsetAsync(s->log_meta, 0, sizeof(int64_t) * 4 * s->log_capacity, st);
-    cudaError_t e = cudaMemsetAsync(s->log_reward, 0, sizeof(double) * (size_t)s->log_capacity * n_agent, st);
+    cudaError_t e = cudaMemsetAsync(s->pause, 0, n_env, st);
+    auto also = [&e](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    also(cudaMemsetAsync(s->suffered, 1, n_env, st));
+    also(cudaMemsetAsync(s->cur_step, 0, sizeof(int32_t) * n_env, st));
+    also(cudaMemsetAsync(s->ep_cnt, 0, sizeof(int32_t) * n_env, st));
+    also(cudaMemsetAsync(s->reward_sum, 0, sizeof(double) * n_env * n_agent, st));
+    also(cudaMemsetAsync(s->counters, 0, sizeof(int64_t) * 8, st));
+    also(cudaMemsetAsync(s->fin_slot, 0, sizeof(int32_t) * n_env, st));
+    also(cudaMemsetAsync(s->log_meta, 0, sizeof(int64_t) * 4 * s->log_capacity, st));
+    also(cudaMemsetAsync(s->log_reward, 0, sizeof(double) * (size_t)s->log_capacity * n_agent, st));
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_runner_init: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
@@ -364,6 +392,7 @@ int dca_runner_update(const DcaRunnerState *s, int n_env, int n_agent, int align
                       const uint8_t *win, const float *reward, dca_stream_t stream) {
     if (!s || !done || !win || !reward || n_env <= 0 || n_agent <= 0 || s->log_capacity < n_env)
         return fail(nullptr, DCA_E_INVALID, "dca_runner_update: null argument, empty shape or log_capacity < n_env");
+    PtrDeviceGuard guard(s->pause);
     cudaStream_t st = (cudaStream_t)stream;
     k_runner_scan<<<1, kRunnerThreads, 0, st>>>(*s, n_env, align_episode != 0, done, win);
     const size_t n = (size_t)n_env * n_agent;
@@ -378,6 +407,7 @@ int dca_runner_report(const DcaRunnerState *s, int n_agent, int64_t first_episod
     if (!s || !team_of_agent || !out || n_agent <= 0 || n_team <= 0 || first_episode < 1 || n_episodes <= 0 ||
         n_episodes > s->log_capacity)
         return fail(nullptr, DCA_E_INVALID, "dca_runner_report: bad window (1-based first episode, at most log_capacity)");
+    PtrDeviceGuard guard(out);
     k_runner_report<<<1, 256, 0, (cudaStream_t)stream>>>(*s, n_agent, (long long)first_episode, n_episodes,
                                                          team_of_agent, n_team, out);
     cudaError_t e = cudaGetLastError();
@@ -391,6 +421,7 @@ int dca_histpool_roll(const float *obs, float *his_pool, const uint8_t *pause, c
         return fail(nullptr, DCA_E_INVALID, "dca_histpool_roll: null buffer or empty shape");
     if (((uintptr_t)obs | (uintptr_t)his_pool | (uintptr_t)obs_feed) & 15)
         return fail(nullptr, DCA_E_INVALID, "dca_histpool_roll: buffers must be 16-byte aligned");
+    PtrDeviceGuard guard(obs);
     const size_t n = (size_t)n_env * n_agent;  // one warp each
     k_histpool<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
         (const float4 *)obs, (float4 *)his_pool, pause, suffered_reset, (float4 *)obs_feed, n_env, n_agent);
@@ -403,6 +434,7 @@ int dca_adv_moments(const float *ret, const float *value, const uint8_t *valid, 
                     double *scratch, double *stats, dca_stream_t stream) {
     if (!ret || !value || !scratch || !stats || n == 0 || (valid && valid_group <= 0))
         return fail(nullptr, DCA_E_INVALID, "dca_adv_moments: null buffer, empty batch or bad valid_group");
+    PtrDeviceGuard guard(ret);
     cudaStream_t st = (cudaStream_t)stream;
     k_adv_partial<<<kAdvBlocks, kAdvThreads, 0, st>>>(ret, value, valid, valid ? valid_group : 1, (size_t)n, scratch);
     k_adv_final<<<1, kAdvThreads, 0, st>>>(scratch, stats);
@@ -415,6 +447,7 @@ int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid
                       const double *stats, float *adv, dca_stream_t stream) {
     if (!ret || !value || !stats || !adv || n == 0 || (valid && valid_group <= 0))
         return fail(nullptr, DCA_E_INVALID, "dca_adv_normalize: null buffer, empty batch or bad valid_group");
+    PtrDeviceGuard guard(ret);
     const size_t blocks = std::min<size_t>((n + kAdvThreads - 1) / kAdvThreads, 148 * 16);
     k_adv_normalize<<<(unsigned)blocks, kAdvThreads, 0, (cudaStream_t)stream>>>(ret, value, valid, valid ? valid_group : 1,
                                                                              (size_t)n, stats, adv);
@@ -490,14 +523,18 @@ int dca_mt_create(const DcaMtConfig *cfg, int n_env, int device, DcaMtHandle **o
     const size_t bytes = mt_carve_state(&probe, nullptr, n_env, N);
     cudaError_t e = cudaMalloc(&h->slab, bytes);
     if (e != cudaSuccess) { delete h; return fail(nullptr, DCA_E_CUDA, std::string("dca_mt_create: cudaMalloc: ") + cudaGetErrorString(e)); }
-    cudaMemset(h->slab, 0, bytes);
+    e = cudaMemset(h->slab, 0, bytes);
     mt_carve_state(&h->P.st, (char *)h->slab, n_env, N);
-    if (h->smem > 48 * 1024) {
-        cudaFuncSetAttribute(k_mt_step, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
-        cudaFuncSetAttribute(k_mt_reset, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem);
+    {   // per-function setting shared by every handle: always the largest admissible env (252 agents)
+        const int max_smem = (int)mt_smem_bytes(252);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_mt_step, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_mt_reset, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     }
-    k_mt_init<<<(n_env + 127) / 128, 128>>>(h->P);
-    e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) {
+        k_mt_init<<<(n_env + 127) / 128, 128>>>(h->P);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { cudaFree(h->slab); delete h; return fail(nullptr, DCA_E_CUDA, std::string("dca_mt_create: ") + cudaGetErrorString(e)); }
     *out = h;
     return DCA_OK;

@@ -947,38 +947,47 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
         uint32_t *pairq = (uint32_t *)(hy + L.N);
         const int pair_cap = 12 * L.N;  // table region = (N + 1) * 64 B = 16 N (headings) + 48 N + 64
         const double cc2 = P.cone_cos2;
-        for (int q = tid; q < nsh; q += nt) {
-            const int i = s.shooters[q];
+        // Every lane of a warp runs the same number of rounds (a guard shooter scans L.A opponents, an attacker L.G:
+        // with ceil(G/32) != ceil(A/32) their chunk counts differ), lanes without a shooter or past their own list
+        // contribute an empty mask: the warp-wide slot allocation below needs all 32 lanes.
+        const int cmax = L.G > L.A ? L.G : L.A;
+        for (int q0 = tid & ~31; q0 < nsh; q0 += nt) {
+            const int lane = tid & 31, q = q0 + lane;
+            const bool has = q < nsh;
+            const int i = has ? (int)s.shooters[q] : 0;
             const bool att = i >= L.G;
             const float *ox = att ? s.xg : s.xa, *oy = att ? s.yg : s.ya;
-            const int opp_cnt = att ? L.G : L.A, opp_base = att ? 0 : L.G;
+            const int opp_cnt = has ? (att ? L.G : L.A) : 0, opp_base = att ? 0 : L.G;
             const float pox = att ? s.xa[i - L.G] : s.xg[i], poy = att ? s.ya[i - L.G] : s.yg[i];
             const u64 px2 = pack2(pox, pox), py2 = pack2(poy, poy);
             const float r2f = laser_r2f(s, c, i);
             const int nquad = (opp_cnt + 3) >> 2;
-            if (cc2 > 0) {
+            if (has && cc2 > 0) {
                 double sn_, cs_;
                 sincos(s.atk[i], &sn_, &cs_);
                 hx[i] = cs_; hy[i] = sn_;
             }
-            for (int c0 = 0; c0 < opp_cnt; c0 += 32) {
-                uint32_t m = scan_chunk(ox, oy, c0, min(8, nquad - (c0 >> 2)), px2, py2, r2f);
-                if (r2f == CUDART_INF_F) {  // no bound: every alive opponent is a candidate (inf <= inf passes above)
-                    m = 0;
-                    for (int j = 0; j < 32 && c0 + j < opp_cnt; ++j)
-                        if (s.flags[opp_base + c0 + j] & F_ALIVE) m |= 1u << j;
+            for (int c0 = 0; c0 < cmax; c0 += 32) {  // warp-uniform
+                uint32_t m = 0;
+                if (c0 < opp_cnt) {
+                    m = scan_chunk(ox, oy, c0, min(8, nquad - (c0 >> 2)), px2, py2, r2f);
+                    if (r2f == CUDART_INF_F) {  // no bound: every alive opponent is a candidate (inf <= inf passes above)
+                        m = 0;
+                        for (int j = 0; j < 32 && c0 + j < opp_cnt; ++j)
+                            if (s.flags[opp_base + c0 + j] & F_ALIVE) m |= 1u << j;
+                    }
                 }
-                // Queue slots for the whole warp with ONE atomic (the lanes in this loop are a prefix of the warp):
-                // one atomic per candidate on the single counter word serialised the CTA -- 500 pairs took 27 k cycles.
-                const unsigned act = __activemask();
-                const int lane = tid & 31, cntm = __popc(m);
+                // Queue slots for the whole warp with ONE atomic: one atomic per candidate on the single counter word
+                // serialised the CTA -- 500 pairs took 27 k cycles.
+                const unsigned act = 0xffffffffu;
+                const int cntm = __popc(m);
                 int incl = cntm;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const int v = __shfl_up_sync(act, incl, o);
                     if (lane >= o) incl += v;
                 }
-                const int last = 31 - __clz(act);
+                const int last = 31;
                 int slot = 0;
                 if (lane == last && incl > 0) slot = atomicAdd(&s.misc[3], incl);
                 slot = __shfl_sync(act, slot, last) + incl - cntm;

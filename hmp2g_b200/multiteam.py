@@ -87,7 +87,10 @@ class DcaMultiTeamVecEnv(object):
         self.lib = _lib.load()
         if not torch.cuda.is_available():
             raise _lib.DcaError('hmp2g_b200 needs a CUDA device; there is no CPU fallback')
-        self.device = torch.device(device if device is not None else 'cuda:%d' % torch.cuda.current_device())
+        self.device = torch.device(device if device is not None else 'cuda')
+        assert self.device.type == 'cuda'
+        if self.device.index is None:  # 'cuda' means the current device, exactly as DcaVecEnv resolves it
+            self.device = torch.device('cuda', torch.cuda.current_device())
         scfg = scfg or MtScenarioConfig
         self.cfg = pod_mt_config(scfg, seed, env_gid0)
         self.E, self.n_team = int(n_env), self.cfg.n_team
@@ -95,7 +98,7 @@ class DcaMultiTeamVecEnv(object):
         self.N = sum(self.team_size)
         self.agent_id_each_team = arrange_id(self.team_size)
         self.handle = C.c_void_p()
-        _lib.check(self.lib.dca_mt_create(C.byref(self.cfg), self.E, self.device.index or 0, C.byref(self.handle)))
+        _lib.check(self.lib.dca_mt_create(C.byref(self.cfg), self.E, self.device.index, C.byref(self.handle)))
         E, N, dev = self.E, self.N, self.device
         z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)
         self.obs = z((E, N, 12, 17), torch.float32)

@@ -25,7 +25,10 @@ class HistoryPool(object):
         self.lib = _lib.load()
         if not torch.cuda.is_available():
             raise _lib.DcaError('hmp2g_b200 needs a CUDA device; there is no CPU fallback')
-        self.device = torch.device(device if device is not None else 'cuda:%d' % torch.cuda.current_device())
+        self.device = torch.device(device if device is not None else 'cuda')
+        assert self.device.type == 'cuda'
+        if self.device.index is None:  # 'cuda' means the current device, exactly as DcaVecEnv resolves it
+            self.device = torch.device('cuda', torch.cuda.current_device())
         self.E, self.G = int(n_env), int(n_agent)
         self.his_pool = torch.zeros((self.E, self.G, 12, 16), dtype=torch.float32, device=self.device)
         self.obs_feed = torch.zeros((self.E, self.G, 24, 16), dtype=torch.float32, device=self.device)

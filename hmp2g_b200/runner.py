@@ -23,7 +23,10 @@ class DeviceRunner(object):
         self.lib = _lib.load()
         if not torch.cuda.is_available():
             raise _lib.DcaError('hmp2g_b200 needs a CUDA device; there is no CPU fallback')
-        self.device = torch.device(device if device is not None else 'cuda:%d' % torch.cuda.current_device())
+        self.device = torch.device(device if device is not None else 'cuda')
+        assert self.device.type == 'cuda'
+        if self.device.index is None:  # 'cuda' means the current device, exactly as DcaVecEnv resolves it
+            self.device = torch.device('cuda', torch.cuda.current_device())
         self.E, self.G = int(n_env), int(n_agent)
         self.align_episode = bool(align_episode)
         self.report_interval = int(report_interval)
