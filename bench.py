@@ -52,6 +52,16 @@ def ncu_traffic():
         return {}
 
 
+def dram_frac(ncu, kernel, kernel_ms, peak, E, scenario):
+    """DRAM-counter roofline fraction: dram__bytes (read + write) per launch, captured by ncu over a RANGE of
+    back-to-back launches (tools/dram_range.py -> profiles/latest_ncu.json, so write-backs deferred past a kernel's end
+    are charged), divided by the live CUDA-event duration and the measured peak.  None without a matching capture."""
+    b = ncu.get(kernel + '_dram_bytes_range_per_launch')
+    if not b or E != ncu.get('envs_per_gpu') or scenario != '50v50':
+        return None
+    return b / (kernel_ms * 1e-3) / 1e9 / peak
+
+
 def measured_peak():
     p = os.path.join(REPO, 'MEASURED_PEAKS.json')
     if os.path.exists(p):
@@ -140,28 +150,70 @@ def cpu_port_run(n_env, steps, warmup, threads, seed=SEED, full_planner=True):
     return n_env * env.N * steps / dt, dt
 
 
+def reference_pool_run(scenario, steps, warmup, procs=None, fold=2, timeout=600):
+    """The UNMODIFIED reference path (SmartPool + SuperpoolEnv + EnvAutoReset + MISSION/dca, staged into oracle/_ref by
+    __graft_entry__.build()) timed in its own process by oracle/ref_pool_bench.py.  None if it is not staged or fails."""
+    import subprocess
+    sys.path.insert(0, os.path.join(REPO, 'oracle'))
+    import stage_ref
+    if not stage_ref.staged():
+        return None
+    procs = procs or (os.cpu_count() or 1)
+    cmd = [sys.executable, os.path.join(REPO, 'oracle', 'ref_pool_bench.py'), '--scenario', scenario, '--procs', str(procs),
+           '--fold', str(fold), '--steps', str(steps), '--warmup', str(warmup), '--seed', str(SEED)]
+    try:
+        out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=timeout, text=True).stdout
+    except Exception as e:  # pragma: no cover
+        sys.stderr.write('reference pool run failed: %r\n' % (e,))
+        return None
+    for ln in out.splitlines():
+        if ln.startswith('REF_POOL_JSON '):
+            return json.loads(ln[len('REF_POOL_JSON '):])
+    sys.stderr.write('reference pool run printed no result:\n' + out[-2000:] + '\n')
+    return None
+
+
 def run_reference_arm(args):
-    """--impl reference: the reference's CPU implementation of the path on this box's host cores.  The reference
-    is Python (cannot travel to the GPU box; no oracle/_ref), so this is the oracle port with every host thread.
-    Each step is a bounded sample: 1024 envs instead of 4096 per GPU (throughput per env-step is size independent
-    on the CPU)."""
+    """--impl reference: the reference's own CPU implementation of the path on this box's host cores -- SmartPool with
+    one worker process per host core, fold 2 (E_cpu = 2 x cores), SuperpoolEnv.step with random guard
+    actions; the scripted attacker planner runs inside World.step as it always does in the reference.  Each step is a
+    bounded sample (2 x cores envs instead of 4096 per GPU: env-steps/s of the process pool does not depend on how many
+    envs queue behind each worker).  If oracle/_ref is not staged the arm falls back to the C/OpenMP port of the same
+    work and says so (kind: "port")."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_env = 1024
     steps = max(1, min(args.steps, 200))
     warm = max(3, min(args.warmup, 20))
-    value, dt = cpu_port_run(n_env, steps, warm, cores)
+    ref = reference_pool_run(args.scenario, steps, warm, procs=cores, fold=2)
+    # the C/OpenMP port of the same work on the same cores: the port / reference calibration on ONE machine
+    port_v, port_dt = cpu_port_run(1024, min(steps, 60), 5, cores)
+    port_v0, _ = cpu_port_run(1024, min(steps, 60), 5, cores, full_planner=False)
+    if ref is not None:
+        value, ms, kind = ref['agent_steps_per_sec'], ref['ms_per_step'], 'reference'
+        sample = ('%d envs (SmartPool: %d worker processes x fold %d) x %d steps of the %s workload through '
+                  'SuperpoolEnv.step, unmodified reference staged in oracle/_ref (%.1f s)'
+                  % (ref['envs'], ref['procs'], ref['fold'], steps, args.scenario, ref['seconds']))
+        n_env = ref['envs']
+    else:
+        value, ms, kind = port_v, port_dt / min(steps, 60) * 1e3, 'port'
+        sample = '1024 envs x %d steps incl. the scripted attacker planner, C port, OpenMP over envs' % min(steps, 60)
+        n_env = 1024
     line = {
         'impl': 'reference', 'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s',
-        'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': dt / steps * 1e3,
+        'n_gpus': args.gpus, 'steps': steps, 'warmup': warm, 'ms_per_step': ms,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': 'DCA 50v50 scripted-attacker planner + step + obs + autoreset, injected random guard actions',
+        'config': {'workload': 'DCA %s scripted-attacker planner + step + obs + autoreset, injected random guard actions'
+                               % args.scenario,
                    'envs_per_step_sample': n_env, 'scenario': WORKLOAD},
-        'cpu_baseline': {'value': value, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
-                         'sample': '%d envs x %d steps of the 50v50 workload incl. the scripted attacker planner, C port, '
-                                   'OpenMP over envs' % (n_env, steps)},
+        'cpu_baseline': {'value': value, 'unit': 'agent-steps/s', 'cores': cores, 'kind': kind, 'sample': sample,
+                         'port_value': port_v, 'port_value_without_planner': port_v0,
+                         'port_over_reference': (port_v / value) if kind == 'reference' else None,
+                         'note': 'port_* = oracle/dca_oracle.c + dca_planner.c (OpenMP, same cores, same workload); the '
+                                 'reference cannot run without its planner (core.py:189-196), so value_without_planner '
+                                 'exists for the port only'},
+        'value_without_planner': port_v0 if kind == 'port' else None,
         'e2e': {'value': value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
@@ -169,6 +221,109 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
+def quick_config_run(name, E, dev, rank, steps=360, warm=40):
+    """BASELINE.json configs[2] / [3] (100v100, 50v55) at the same env count: step+obs+autoreset with the centroid
+    stand-in (value) and k_step alone per launch over two episodes (kernel_ms, roofline fraction), plus k_plan."""
+    import ctypes as C
+    import torch
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.vec_env import DcaVecEnv
+    wl = dict(WORKLOAD, **SCENARIOS[name])
+    scfg = type('BenchScenarioConfig_' + name, (ScenarioConfig,), wl)
+    env = DcaVecEnv(E, scfg=scfg, device=dev, seed=SEED, env_gid0=rank * E)
+    G, A, N = env.G, env.A, env.N
+    lib, h = env.lib, env.handle
+    stream = torch.cuda.current_stream(dev)
+    sptr = C.c_void_p(stream.cuda_stream)
+    force = torch.zeros((E, A, 2), dtype=torch.float64, device=dev)
+    fptr = C.c_void_p(force.data_ptr())
+    pool = [torch.randint(0, 7, (E, G), device=dev, dtype=torch.int32) for _ in range(8)]
+    aptrs = [C.c_void_p(a.data_ptr()) for a in pool]
+    env.reset()
+    for i in range(warm):
+        lib.dca_plan_centroid(h, fptr, sptr)
+        lib.dca_step(h, aptrs[i % 8], fptr, None, None, 1, sptr)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0.record(stream)
+    for i in range(steps):
+        lib.dca_plan_centroid(h, fptr, sptr)
+        lib.dca_step(h, aptrs[i % 8], fptr, None, None, 1, sptr)
+    t1.record(stream)
+    torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / steps
+    es = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ee = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    lib.dca_set_option(h, 2, 0)
+    for i in range(steps):
+        lib.dca_plan_centroid(h, fptr, sptr)
+        es[i].record(stream)
+        lib.dca_step(h, aptrs[i % 8], fptr, None, None, 1, sptr)
+        ee[i].record(stream)
+    torch.cuda.synchronize()
+    k_ms = sum(es[i].elapsed_time(ee[i]) for i in range(steps)) / steps
+    ps = [torch.cuda.Event(enable_timing=True) for _ in range(180)]
+    pe = [torch.cuda.Event(enable_timing=True) for _ in range(180)]
+    for i in range(180):
+        ps[i].record(stream)
+        lib.dca_plan(h, fptr, None, None, sptr)
+        pe[i].record(stream)
+        lib.dca_step(h, aptrs[i % 8], fptr, None, None, 1, sptr)
+    torch.cuda.synchronize()
+    plan_ms = sum(ps[i].elapsed_time(pe[i]) for i in range(180)) / 180
+    peak, _ = measured_peak()
+    algo = bytes_per_env_step(G, A) * E
+    out = {'workload': 'DCA %dv%d step+obs+autoreset, %d envs, centroid stand-in' % (G, A, E), 'value': E * N / (ms * 1e-3),
+           'unit': 'agent-steps/s', 'ms_per_step': ms, 'k_step_ms': k_ms, 'k_plan_ms': plan_ms,
+           'algorithmic_bytes_per_launch': algo, 'achieved_gbs': algo / (k_ms * 1e-3) / 1e9,
+           'frac': algo / (k_ms * 1e-3) / 1e9 / peak, 'steps': steps, 'threads_per_cta': 128 if N <= 128 else 256}
+    env.close()
+    del env, force, pool
+    torch.cuda.empty_cache()
+    return out
+
+
+def collective_timings(E, G, dev, world):
+    """the three collectives of a sharded rollout, on NCCL: (i) flat fp32 gradient all-reduce of the conc
+    policy (63 370 parameters), (ii) advantage moments inside normalized_advantage over a [180,E,G] buffer, (iii) rollout
+    statistics.  CUDA events, max over ranks, microseconds per call."""
+    import torch
+    import torch.distributed as dist
+    from hmp2g_b200.gae import allreduce_moments, normalized_advantage
+    from hmp2g_b200.sharding import RolloutStats
+    stream = torch.cuda.current_stream(dev)
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        a.record(stream)
+        for _ in range(n):
+            fn()
+        b.record(stream)
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / n * 1e3], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    grad = torch.randn(63370, device=dev)
+    T = 180 if E * G * 180 * 12 < 4e9 else 45
+    ret = torch.randn((T, E, G), device=dev)
+    val = torch.randn((T, E, G), device=dev)
+    stats3 = torch.ones(3, dtype=torch.float64, device=dev)
+    rs = RolloutStats(dev)
+    out = {'world': world, 'backend': dist.get_backend(),
+           'grad_allreduce_us': timed(lambda: dist.all_reduce(grad), 50), 'grad_params': 63370,
+           'moments_allreduce_us': timed(lambda: allreduce_moments(stats3), 50),
+           'normalized_advantage_us': timed(lambda: normalized_advantage(ret, val), 10), 'advantage_shape': [T, E, G],
+           'rollout_stats_reduce_us': timed(lambda: rs.reduce(), 20)}
+    del ret, val
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -215,7 +370,7 @@ def run_ours(args):
     for i in range(W):
         assert one_step(i) == 0
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(physical_gpu_index(local_rank)) if rank == 0 else None
+    sampler = ClockSampler(physical_gpu_index(local_rank), period=0.002) if rank == 0 else None
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -238,7 +393,8 @@ def run_ours(args):
     ms_total = t_begin.elapsed_time(t_end)
     # k_step's own launch duration (the roofline figure): the next Kk steps of the same episodes, the kernel launched
     # stand-alone (no overlap with the planner stand-in) between two events each
-    Kk = min(K, 720)
+    Kk = min(max(K, 360), 720)  # at least two whole episodes, so a short driver run also reports the episode average
+    Kfirst = min(K, Kk)
     ev_s = [torch.cuda.Event(enable_timing=True) for _ in range(Kk)]
     ev_e = [torch.cuda.Event(enable_timing=True) for _ in range(Kk)]
     lib.dca_set_option(h, 2, 0)
@@ -249,8 +405,44 @@ def run_ours(args):
         ev_e[i].record(stream)
     torch.cuda.synchronize()
     lib.dca_set_option(h, 2, overlap)
+    per_launch = [ev_s[i].elapsed_time(ev_e[i]) for i in range(Kk)]
+    ms_step_kernel = sum(per_launch[:Kfirst]) / Kfirst  # the K steps that follow the timed region
+    ms_step_kernel_episode = sum(per_launch) / Kk       # >= two whole episodes
+    # ---- like-for-like with the reference arm: the scripted formation planner (k_plan, what World.step runs in the
+    # reference, core.py:189-196) + step, over whole episodes, the step launched under its planner as in the timed region
+    Ks = 360
+    for i in range(20):
+        lib.dca_plan(h, fptr, None, None, sptr)
+        lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    s0.record(stream)
+    for i in range(Ks):
+        lib.dca_plan(h, fptr, None, None, sptr)
+        lib.dca_step(h, aptrs[(20 + i) % n_pool], fptr, None, None, 1, sptr)
+    s1.record(stream)
+    torch.cuda.synchronize()
+    ms_scripted = s0.elapsed_time(s1) / Ks
+    pe_s = [torch.cuda.Event(enable_timing=True) for _ in range(180)]
+    pe_e = [torch.cuda.Event(enable_timing=True) for _ in range(180)]
+    lib.dca_set_option(h, 2, 0)
+    for i in range(180):  # k_plan alone, on the states of one more episode
+        pe_s[i].record(stream)
+        lib.dca_plan(h, fptr, None, None, sptr)
+        pe_e[i].record(stream)
+        lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
+    torch.cuda.synchronize()
+    lib.dca_set_option(h, 2, overlap)
+    ms_plan_episode = sum(pe_s[i].elapsed_time(pe_e[i]) for i in range(180)) / 180
+    ts_ = torch.tensor([ms_scripted], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ts_, op=dist.ReduceOp.MAX)
+    scripted = {'value': world * E * N / (float(ts_.item()) * 1e-3), 'unit': 'agent-steps/s',
+                'ms_per_step': float(ts_.item()), 'k_plan_ms': ms_plan_episode, 'steps': Ks,
+                'what': 'dca_plan (scripted formation planner, cheat_script_ai.py:28-194) + dca_step per step over two '
+                        'episodes: the work of one World.step + observation in the reference (--impl reference times '
+                        'exactly this on the host)'}
     clocks = sampler.stop() if sampler else None
-    ms_step_kernel = sum(ev_s[i].elapsed_time(ev_e[i]) for i in range(Kk)) / Kk
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -330,6 +522,12 @@ def run_ours(args):
     mt_alive = float(mt.alive.float().mean().item())
     mt_N = mt.N
     del mt, mt_pool
+    # ---- BASELINE.json configs[2] / [3] at the same env count (extra report lines; not the headline)
+    other = {}
+    if args.scenario == '50v50' and not args.no_other_configs:
+        for name in ('100v100', '50v55'):
+            other[name] = quick_config_run(name, E, dev, rank)
+    coll = collective_timings(E, G, dev, world) if world > 1 else None
 
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
@@ -398,13 +596,18 @@ def run_ours(args):
                      'algorithmic_bytes_per_launch': algo_bytes, 'kernel_ms': ms_step_kernel,
                      'kernel_ms_source': 'CUDA events around each k_step launch over the %d steps that follow the '
                                          'timed region (same episodes; launched stand-alone: in the timed region the '
-                                         'kernel starts under the planner stand-in, DCA_OPT_OVERLAP_PLANNER)' % Kk,
+                                         'kernel starts under the planner stand-in, DCA_OPT_OVERLAP_PLANNER)' % Kfirst,
+                     'kernel_ms_episode_avg': ms_step_kernel_episode, 'episode_avg_steps': Kk,
+                     'frac_episode_avg': algo_bytes / (ms_step_kernel_episode * 1e-3) / 1e9 / peak,
+                     'dram_frac': dram_frac(ncu, 'k_step', ms_step_kernel_episode, peak, E, args.scenario),
                      'traffic_source': ncu.get('source')},
         'roofline_gather_kernel': {'bound': 'hbm', 'kernel': 'k_observe', 'unit': 'GB/s', 'peak': peak,
                                    'achieved': gather_bytes / (ms_gather * 1e-3) / 1e9,
                                    'frac': gather_bytes / (ms_gather * 1e-3) / 1e9 / peak,
                                    'algorithmic_bytes_per_launch': gather_bytes, 'kernel_ms': ms_gather,
-                                   'traffic': ncu.get('k_observe_dram_bytes_per_launch')},
+                                   'traffic': ncu.get('k_observe_dram_bytes_per_launch'),
+                                   'dram_frac': dram_frac(ncu, 'k_observe', ms_gather, peak, E, args.scenario),
+                                   'dram_frac_source': ncu.get('range_source')},
         'histpool_kernel': {'bound': 'hbm', 'kernel': 'k_histpool', 'unit': 'GB/s', 'kernel_ms': ms_hist,
                             'achieved': hist_bytes / (ms_hist * 1e-3) / 1e9, 'peak': peak,
                             'frac': hist_bytes / (ms_hist * 1e-3) / 1e9 / peak},
@@ -421,6 +624,9 @@ def run_ours(args):
         'e2e': {'value': e2e_value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy actions in; planner + step on device; numpy '
                                     'obs/reward/done/info out)'},
+        'with_scripted_planner': scripted,
+        'other_configs': other,
+        'collectives': coll,
         'gpu_launches': gpu_launches,
         'clocks': clocks,
     }
@@ -430,10 +636,21 @@ def run_ours(args):
         v, dt = cpu_port_run(n_cpu_env, cpu_steps, 5, cores)
         v0, _ = cpu_port_run(n_cpu_env, cpu_steps, 5, cores, full_planner=False)
         v1, dt1 = cpu_port_run(128, 40, 3, 1)
-        line['cpu_baseline'] = {'value': v, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
-                                'sample': '%d envs x %d steps of the same 50v50 workload incl. the scripted attacker '
-                                          'planner (%.1f s)' % (n_cpu_env, cpu_steps, dt),
-                                'single_core_value': v1, 'value_without_planner': v0}
+        ref = reference_pool_run(args.scenario, 40, 5, procs=cores, fold=2)
+        if ref is not None:  # the reference's own path (SmartPool + SuperpoolEnv + MISSION/dca), staged in oracle/_ref
+            line['cpu_baseline'] = {
+                'value': ref['agent_steps_per_sec'], 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'reference',
+                'sample': '%d envs (%d worker processes x fold %d) x 40 steps of the same %s workload through the '
+                          'unmodified SuperpoolEnv.step, scripted attacker planner inside World.step (%.1f s)'
+                          % (ref['envs'], ref['procs'], ref['fold'], args.scenario, ref['seconds']),
+                'port_value': v, 'port_value_without_planner': v0, 'port_single_core_value': v1,
+                'port_over_reference': v / ref['agent_steps_per_sec']}
+        else:
+            line['cpu_baseline'] = {'value': v, 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'port',
+                                    'sample': '%d envs x %d steps of the same workload incl. the scripted attacker '
+                                              'planner, C/OpenMP port (oracle/_ref not staged) (%.1f s)'
+                                              % (n_cpu_env, cpu_steps, dt),
+                                    'single_core_value': v1, 'value_without_planner': v0}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -450,6 +667,7 @@ def main():
     ap.add_argument('--envs-per-gpu', type=int, default=ENVS_PER_GPU)
     ap.add_argument('--e2e-steps', type=int, default=40)
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-other-configs', action='store_true', help='skip the 100v100 / 50v55 report lines')
     ap.add_argument('--planner', default='centroid', choices=['centroid', 'scripted'],
                     help='attacker forces: the centroid stand-in of configs[1] (default) or the scripted formation planner k_plan')
     ap.add_argument('--no-overlap', action='store_true',
