@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -453,6 +454,62 @@ int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid
                                                                              (size_t)n, stats, adv);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_normalize: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+// ---- dca_adv_moments_static: the same two kernels with the per-CTA partials in a library-owned array ---------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (graph capture, serving loops).  The array lives in every GPU context that loads the library until exit.
+static __device__ __align__(256) double g_adv_static_scratch[dca::kAdvBlocks * 3];  // 592 x 3 doubles = 14 208 B
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+double *g_adv_static_ptr[kStaticMaxDevices];  // device address of g_adv_static_scratch on each device, resolved once
+bool g_adv_static_ready[kStaticMaxDevices];
+std::mutex g_adv_static_mu;
+
+// In host code `g_adv_static_scratch` is only a stand-in for the symbol, never a device address: resolve the address once per
+// device, with that device current, and hand the kernels the resolved pointer.
+cudaError_t adv_static_scratch(int device, double **out) {
+    std::lock_guard<std::mutex> lock(g_adv_static_mu);
+    if (!g_adv_static_ready[device]) {
+        double *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_adv_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_adv_static_ptr[device] = p;
+        g_adv_static_ready[device] = true;
+    }
+    *out = g_adv_static_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+int dca_adv_moments_static(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
+                           double *stats, dca_stream_t stream) {
+    if (!ret || !value || !stats || n == 0 || (valid && valid_group <= 0))
+        return fail(nullptr, DCA_E_INVALID, "dca_adv_moments_static: null buffer, empty batch or bad valid_group");
+    if (n > DCA_ADV_STATIC_MAX_N)
+        return fail(nullptr, DCA_E_INVALID, "dca_adv_moments_static: n = " + std::to_string(n) + " exceeds DCA_ADV_STATIC_MAX_N = " +
+                                                std::to_string((uint64_t)DCA_ADV_STATIC_MAX_N) +
+                                                " elements; use dca_adv_moments with a caller-owned scratch buffer");
+    PtrDeviceGuard guard(ret);
+    int device = -1;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_moments_static: cudaGetDevice: ") + cudaGetErrorString(e));
+    if (device < 0 || device >= kStaticMaxDevices)
+        return fail(nullptr, DCA_E_INVALID, "dca_adv_moments_static: device index beyond the per-device address table");
+    double *scratch = nullptr;
+    e = adv_static_scratch(device, &scratch);
+    if (e != cudaSuccess || !scratch)
+        return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_moments_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps the previous call's partials; every slot is rewritten by k_adv_partial, cleared first all the same
+    e = cudaMemsetAsync(scratch, 0, sizeof(double) * kAdvBlocks * 3, st);
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_moments_static: memset: ") + cudaGetErrorString(e));
+    k_adv_partial<<<kAdvBlocks, kAdvThreads, 0, st>>>(ret, value, valid, valid ? valid_group : 1, (size_t)n, scratch);
+    k_adv_final<<<1, kAdvThreads, 0, st>>>(scratch, stats);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_moments_static: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
 

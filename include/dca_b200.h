@@ -180,6 +180,17 @@ int dca_adv_moments(const float *ret, const float *value, const uint8_t *valid, 
                     double *scratch, double *stats, dca_stream_t stream);
 int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
                       const double *stats, float *adv, dca_stream_t stream);
+/* dca_adv_moments_static: NO counterpart in the reference -- added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Same
+ * kernels, arguments and result as dca_adv_moments, minus `scratch`: the per-CTA partials live in a library-owned
+ * `static __device__` array (592 x 3 doubles = 14 208 B, held by every GPU that loads the library until exit; its
+ * device address is resolved with cudaGetSymbolAddress once per device).  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine).  n > DCA_ADV_STATIC_MAX_N is refused with DCA_E_INVALID.  Every call on a
+ * device shares the one array (cleared at the start of each call): calls that overlap on the GPU -- two streams, or
+ * two host threads -- race; serialise them on one stream or use dca_adv_moments with separate scratch buffers. */
+#define DCA_ADV_STATIC_MAX_N (1ull << 28) /* 268 435 456 elements = 7 x a [180,4096,50] rollout buffer */
+int dca_adv_moments_static(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
+                           double *stats, dca_stream_t stream);
 
 /* ---- dca_multiteam -------------------------------------------------------------------------------------------------
  * The sibling env MISSION/dca_multiteam (N teams, every agent policy-controlled, per-hit success draw, shrinking kill
