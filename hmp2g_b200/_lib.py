@@ -96,7 +96,8 @@ def load(build_if_missing=False):
     lib.dca_set_option.argtypes = [_P, C.c_int, C.c_int]
     lib.dca_export_state.argtypes = [_P, C.POINTER(DcaState), _P]
     lib.dca_import_state.argtypes = [_P, C.POINTER(DcaState), _P]
-    lib.dca_gae.argtypes = [_P, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, _P]
+    lib.dca_gae.argtypes = [_P, _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                            C.c_int, _P]
     lib.dca_runner_init.argtypes = [C.POINTER(DcaRunnerState), C.c_int, C.c_int, _P]
     lib.dca_runner_update.argtypes = [C.POINTER(DcaRunnerState), C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]
     lib.dca_runner_report.argtypes = [C.POINTER(DcaRunnerState), C.c_int, C.c_int64, C.c_int, _P, C.c_int, _P, _P]

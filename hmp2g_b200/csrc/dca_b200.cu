@@ -144,7 +144,7 @@ static cudaError_t allow_smem(K kernel, int bytes) {
 
 extern "C" {
 
-int dca_abi_version(void) { return 1; }
+int dca_abi_version(void) { return 2; }
 
 const char *dca_last_error(const DcaHandle *h) { return h ? h->err.c_str() : g_err.c_str(); }
 
@@ -212,7 +212,7 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
         if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.cent, (size_t)n_env * K * 16);
         if (e == cudaSuccess) e = cudaMemset(h->plan.cent, 0, (size_t)n_env * K * 16);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            e = cudaFuncSetAttribute(k_plan<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      std::max(plan_smem_bytes(250, 250), plan_smem_bytes(kMaxN - 6, 6)));
     }
     // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-function (per-device) setting shared by every handle: raise
@@ -326,7 +326,14 @@ int dca_plan(DcaHandle *h, double *att_force, const int32_t *team_label, const d
         return fail(h, DCA_E_INVALID, "dca_plan: team_label and team_centroid are injected together or not at all");
     if ((uintptr_t)att_force & 15) return fail(h, DCA_E_INVALID, "dca_plan: att_force must be 16-byte aligned");
     DeviceGuard guard(h->device);
-    k_plan<<<h->P.E, kPlanThreads, h->plan_smem, (cudaStream_t)stream>>>(h->P, h->plan, att_force, team_label, team_centroid);
+    {   // compile-time team sizes for the BASELINE configurations, the generic build for everything else
+        const int G = h->P.L.G, A = h->P.L.A;
+        auto kernel = k_plan<0, 0>;
+        if (G == 50 && A == 50) kernel = k_plan<50, 50>;
+        else if (G == 50 && A == 55) kernel = k_plan<50, 55>;
+        else if (G == 100 && A == 100) kernel = k_plan<100, 100>;
+        kernel<<<h->P.E, kPlanThreads, h->plan_smem, (cudaStream_t)stream>>>(h->P, h->plan, att_force, team_label, team_centroid);
+    }
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = att_force;
     h->planned_stream = (cudaStream_t)stream;
@@ -355,15 +362,17 @@ int dca_export_state(DcaHandle *h, const DcaState *dst, dca_stream_t stream) { r
 int dca_import_state(DcaHandle *h, const DcaState *src, dca_stream_t stream) { return state_io(h, src, 1, stream); }
 
 int dca_gae(const float *reward, const float *value, const uint8_t *dead, const int32_t *traj_len, float *ret,
-            float *threat, float *reward_pushed, int T, int E, int G, double gamma, double tau, int threat_limit,
-            dca_stream_t stream) {
+            float *threat, float *reward_pushed, int T, int E, int G, double gamma, double tau, double gamma_fwd,
+            int threat_limit, dca_stream_t stream) {
     if (!reward || !value || !dead || !ret || T <= 0 || E <= 0 || G <= 0)
         return fail(nullptr, DCA_E_INVALID, "dca_gae: null argument or empty shape");
+    if (!(gamma_fwd == gamma_fwd))
+        return fail(nullptr, DCA_E_INVALID, "dca_gae: gamma_fwd is NaN (pass 1.0 when gamma_in_reward_forwarding is off)");
     PtrDeviceGuard guard(reward);
     const size_t S = (size_t)E * G;
     const int threads = 128;
     k_gae<<<(unsigned)((S + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
-        reward, value, dead, traj_len, ret, threat, reward_pushed, T, E, G, gamma, tau, threat_limit);
+        reward, value, dead, traj_len, ret, threat, reward_pushed, T, E, G, gamma, tau, gamma_fwd, threat_limit);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_gae: ") + cudaGetErrorString(e));
     return DCA_OK;

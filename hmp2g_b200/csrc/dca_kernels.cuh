@@ -1271,13 +1271,14 @@ __global__ void k_plan_centroid(const Params P, double *__restrict__ att_force) 
 
 // ------------------------------------------------------------------ GAE / return
 // trajectory.finalize ALGORITHM/conc/trajectory.py:67-117: reward_push_forward :60-64, threat :75-86,
-// gae_finalize_return :92-117.  Rollout buffers are [T,E,G]; one thread owns one (env, guard) column and scans
+// gae_finalize_return :92-117.  gamma_fwd = gamma_in_reward_forwarding_value when gamma_in_reward_forwarding is set
+// (ALGORITHM/common/traj_gae.py:54-60, conc_4hist/trajectory.py:57-63), else 1.  Rollout buffers are [T,E,G]; one thread owns one (env, guard) column and scans
 // time backwards (loads coalesced across the E*G columns).  dtype walk as numpy: gamma*V[t+1] in f32,
 // delta / gae in f64, return stored f32.
 __global__ void k_gae(const float *__restrict__ reward, const float *__restrict__ value,
                       const uint8_t *__restrict__ dead, const int32_t *__restrict__ traj_len, float *__restrict__ ret,
                       float *__restrict__ threat, float *__restrict__ reward_pushed, int T, int E, int G, double gamma,
-                      double tau, int threat_limit) {
+                      double tau, double gamma_fwd, int threat_limit) {
     const size_t S = (size_t)E * G;
     const size_t c = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (c >= S) return;
@@ -1293,7 +1294,7 @@ __global__ void k_gae(const float *__restrict__ reward, const float *__restrict_
         const size_t k = (size_t)i * S + c;
         double r = (double)rw + carry;
         if (i > 0) {
-            carry = r * (double)d;
+            carry = (r * gamma_fwd) * (double)d;  // np.where(dead_mask[i], reward[i] * gamma_fwd, 0); 1.0 = plain push
             r = r * (double)(!d);
         }
         if (reward_pushed) reward_pushed[k] = (float)r;

@@ -1,4 +1,4 @@
-// dca_planner.cuh -- the scripted attacker formation planner on the GPU, one CTA per env.
+// dca_planner.cuh -- the scripted attacker formation planner on the GPU, one warp (= one CTA) per env.
 // CheatScriptAI.attackers_policy_1 MISSION/dca/cheat_script_ai.py:19-194 and get_groups :259-297 (paths relative to
 // /root/reference): DBSCAN clusters of the alive guards -> targets; k-means teams of the attackers; team -> target and
 // member -> ring-slot assignments; force = slot - position.  The reference calls sklearn / scipy for the three
@@ -15,8 +15,9 @@
 namespace dca {
 
 enum : uint32_t { SITE_PLAN = 3 };
-constexpr int kPlanThreads = 32;  // one warp per env: no cross-warp waiting; 32 envs in flight per SM
-constexpr int kPlanTeamPre = 8;  // teams up to this size get their cost matrix precomputed (independent sqrt chains)
+constexpr int kPlanThreads = 32;  // one warp per env: no cross-warp waiting, every phase is warp-synchronous
+constexpr int kPlanTeamPre = 8;   // teams up to this size go four at a time through assign_seg8
+constexpr int kPlanTeamPre2 = 16; // teams up to this size get their cost matrix precomputed (independent sqrt chains)
 
 // persistent team state of one env (World.start_flag / teams_result_step1 / team_centroid_step1 survive resets)
 struct PlanState {
@@ -26,6 +27,11 @@ struct PlanState {
     double *cent;       // [E,K,2]
 };
 
+// Shared-memory plan of one env.  The env is worked on by ONE warp phase after phase, so workspaces of different
+// phases share one region (`un`): k-means {d2, pre}, DBSCAN {gidx, adj, comp, csize, tsrc}, team->target {c1 (+ the
+// h* workspaces when there are more than 32 targets)}, member->slot {cw | h*: small teams first, then the large ones}.
+// Guard positions (dead once the targets exist) share their space with the ring slots.  50v50: 4.8 KB per env, so all
+// 4096 envs of the benchmark are resident at once (28 per SM; 9.8 KB gave 21 per SM = 1.3 waves).
 struct PlanSmem {
     double *gx, *gy, *ax, *ay;      // positions
     uint8_t *galive, *aalive;
@@ -37,15 +43,15 @@ struct PlanSmem {
     double *tx, *ty;                // [K] targets
     double *cx, *cy;                // [K] centroids (code book)
     int32_t *cnt;                   // [K]
-    double *d2, *prob;              // [A]
+    double *d2, *pre;               // [A] squared distance to the nearest centre so far / lane-local running sums
     int16_t *lab;                   // [A] team label in use
     uint32_t *lmask;                // [K][AW] members of team k as bit rows over the attackers
     int16_t *team_target;           // [K]
     int16_t *toff;                  // [K+1] member list offsets
     int16_t *mem, *tof;             // [A] members grouped by team / team of that list position
     double *c1;                     // [K*K] team-centroid <-> target distances
-    double *cw;                     // [warps][4][kPlanTeamPre^2] member <-> slot distances of the four teams a warp works on
-    double *hu, *hv, *hminv;        // [A+K+2] assignment workspaces (team t owns [toff[t]+t, +n_t+1))
+    double *cw;                     // [kPlanTeamPre2^2] member <-> slot distances: four 8x8 problems or one up to 16x16
+    double *hu, *hv, *hminv;        // [A+K+2] assignment workspaces of the shared-memory routine (> 32 columns)
     int16_t *hp, *hway;             // [A+K+2]
     uint8_t *hused;                 // [A+K+2]
     int16_t *hcol;                  // [A] slot of list position i
@@ -53,60 +59,76 @@ struct PlanSmem {
     int32_t *misc;                  // [0] n alive guards, [2] n targets, [3] raised flag, [4] changed flag
 };
 
-__host__ __device__ inline int plan_smem_bytes(int G, int A) {
-    const int K = A / 5 > 0 ? A / 5 : 1, H = A + K + 2, W = (G + 63) / 64, AW = (A + 31) / 32;
+__host__ __device__ constexpr int plan_max(int a, int b) { return a > b ? a : b; }
+__host__ __device__ constexpr int plan_h_bytes(int H) {
+    return 3 * align_up(H * 8, 16) + 2 * align_up(H * 2, 16) + align_up(H, 16);  // hu hv hminv hp hway hused
+}
+__host__ __device__ constexpr int plan_union_bytes(int G, int A) {
+    const int K = A / 5 > 0 ? A / 5 : 1, H = A + K + 2, W = (G + 63) / 64;
+    const int km = 2 * align_up(A * 8, 16);
+    const int db = align_up(G * 2, 16) + G * W * 8 + align_up(G * 2, 16) + align_up(G * 4, 16) + align_up(K * 2, 16);
+    const int tt = align_up(K * K * 8, 16) + (K > 32 ? plan_h_bytes(H) : 0);
+    const int ms = plan_max(kPlanTeamPre2 * kPlanTeamPre2 * 8, plan_h_bytes(H));
+    return plan_max(plan_max(km, db), plan_max(tt, ms));
+}
+__host__ __device__ constexpr int plan_smem_bytes(int G, int A) {
+    const int K = A / 5 > 0 ? A / 5 : 1, AW = (A + 31) / 32;
     int o = 0;
-    o += 2 * G * 8 + 2 * A * 8;          // positions
-    o += align_up(G + A, 16);            // alive
-    o += align_up(G * 2, 16);            // gidx
-    o += G * W * 8;                      // adj
-    o += align_up(G * 2, 16) + align_up(G * 4, 16);  // comp csize
-    o += align_up(K * 2, 16);            // tsrc
-    o += 4 * align_up(K * 8, 16);        // tx ty cx cy
-    o += align_up(K * 4, 16);            // cnt
-    o += 2 * align_up(A * 8, 16);        // d2 prob
-    o += align_up(A * 2, 16);            // lab
-    o += align_up(K * AW * 4, 16);       // lmask
+    o += 2 * plan_max(G, A) * 8 + 2 * A * 8;  // gx gy (later sx sy), ax ay
+    o += align_up(G + A, 16);                 // alive
+    o += 4 * align_up(K * 8, 16);             // tx ty cx cy
+    o += align_up(K * 4, 16);                 // cnt
+    o += align_up(A * 2, 16);                 // lab
+    o += align_up(K * AW * 4, 16);            // lmask
     o += align_up(K * 2, 16) + align_up((K + 1) * 2, 16) + 2 * align_up(A * 2, 16);  // team_target toff mem tof
-    o += align_up(K * K * 8, 16);        // c1
-    o += (kPlanThreads / 32) * 4 * kPlanTeamPre * kPlanTeamPre * 8;  // cw: four member x slot cost matrices per warp
-    o += 3 * align_up(H * 8, 16) + 2 * align_up(H * 2, 16) + align_up(H, 16);  // hu hv hminv hp hway hused
-    o += align_up(A * 2, 16);            // hcol
-    o += 2 * align_up(A * 8, 16);        // sx sy
-    o += 32;
+    o += align_up(A * 2, 16);                 // hcol
+    o += 32;                                  // misc
+    o += plan_union_bytes(G, A);
     return o;
 }
 
 __device__ __forceinline__ PlanSmem plan_carve(unsigned char *p, int G, int A) {
     const int K = A / 5 > 0 ? A / 5 : 1, H = A + K + 2, W = (G + 63) / 64, AW = (A + 31) / 32;
+    const int GA = plan_max(G, A);
     PlanSmem s;
-    s.gx = (double *)p; p += G * 8; s.gy = (double *)p; p += G * 8;
+    s.gx = (double *)p; s.sx = s.gx; p += GA * 8; s.gy = (double *)p; s.sy = s.gy; p += GA * 8;
     s.ax = (double *)p; p += A * 8; s.ay = (double *)p; p += A * 8;
     s.galive = p; s.aalive = p + G; p += align_up(G + A, 16);
-    s.gidx = (int16_t *)p; p += align_up(G * 2, 16);
-    s.adj = (unsigned long long *)p; p += G * W * 8;
-    s.comp = (int16_t *)p; p += align_up(G * 2, 16);
-    s.csize = (int32_t *)p; p += align_up(G * 4, 16);
-    s.tsrc = (int16_t *)p; p += align_up(K * 2, 16);
     const int k8 = align_up(K * 8, 16), a8 = align_up(A * 8, 16), a2 = align_up(A * 2, 16);
     s.tx = (double *)p; p += k8; s.ty = (double *)p; p += k8;
     s.cx = (double *)p; p += k8; s.cy = (double *)p; p += k8;
     s.cnt = (int32_t *)p; p += align_up(K * 4, 16);
-    s.d2 = (double *)p; p += a8; s.prob = (double *)p; p += a8;
     s.lab = (int16_t *)p; p += a2;
     s.lmask = (uint32_t *)p; p += align_up(K * AW * 4, 16);
     s.team_target = (int16_t *)p; p += align_up(K * 2, 16);
     s.toff = (int16_t *)p; p += align_up((K + 1) * 2, 16);
     s.mem = (int16_t *)p; p += a2; s.tof = (int16_t *)p; p += a2;
-    s.c1 = (double *)p; p += align_up(K * K * 8, 16);
-    s.cw = (double *)p; p += (kPlanThreads / 32) * 4 * kPlanTeamPre * kPlanTeamPre * 8;
-    const int h8 = align_up(H * 8, 16), h2 = align_up(H * 2, 16);
-    s.hu = (double *)p; p += h8; s.hv = (double *)p; p += h8; s.hminv = (double *)p; p += h8;
-    s.hp = (int16_t *)p; p += h2; s.hway = (int16_t *)p; p += h2;
-    s.hused = p; p += align_up(H, 16);
     s.hcol = (int16_t *)p; p += a2;
-    s.sx = (double *)p; p += a8; s.sy = (double *)p; p += a8;
-    s.misc = (int32_t *)p;
+    s.misc = (int32_t *)p; p += 32;
+    unsigned char *un = p;  // ---- the phase union
+    {   // k-means
+        unsigned char *q = un;
+        s.d2 = (double *)q; q += a8; s.pre = (double *)q;
+    }
+    {   // DBSCAN / targets
+        unsigned char *q = un;
+        s.gidx = (int16_t *)q; q += align_up(G * 2, 16);
+        s.adj = (unsigned long long *)q; q += G * W * 8;
+        s.comp = (int16_t *)q; q += align_up(G * 2, 16);
+        s.csize = (int32_t *)q; q += align_up(G * 4, 16);
+        s.tsrc = (int16_t *)q;
+    }
+    unsigned char *hb = un;
+    s.c1 = (double *)un;                      // team -> target
+    if (K > 32) hb = un + align_up(K * K * 8, 16);
+    s.cw = (double *)un;                      // member -> slot, small teams (before the large ones)
+    {
+        unsigned char *q = hb;
+        const int h8 = align_up(H * 8, 16), h2 = align_up(H * 2, 16);
+        s.hu = (double *)q; q += h8; s.hv = (double *)q; q += h8; s.hminv = (double *)q; q += h8;
+        s.hp = (int16_t *)q; q += h2; s.hway = (int16_t *)q; q += h2;
+        s.hused = q;
+    }
     return s;
 }
 
@@ -181,56 +203,58 @@ __device__ __forceinline__ double plan_dkey_inv(u64 k) {
     return __longlong_as_double(b < 0 ? (long long)(k ^ 0x8000000000000000ull) : ~b);
 }
 
+// arg-min of 64-bit keys over the warp with two 32-bit REDUX steps (high words, then the low words of the lanes that
+// hold the smallest high word); returns the key, `holders` = lanes holding it
+__device__ __forceinline__ u64 plan_warp_min_key(u64 key, unsigned *holders) {
+    const unsigned full = 0xffffffffu;
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned hmin = __reduce_min_sync(full, hi);
+    const unsigned lmin = __reduce_min_sync(full, hi == hmin ? lo : 0xffffffffu);
+    *holders = __ballot_sync(full, hi == hmin && lo == lmin);
+    return ((u64)hmin << 32) | lmin;
+}
+
 // The same assignment with the whole state in registers (m <= 32 columns): lane j-1 owns column j -- v[j], minv[j],
 // way[j], used[j], the row p[j] matched to it and that row's potential u[p[j]] (it travels with the row when the
 // augmenting path is flipped); the row being inserted sits in the virtual column 0, held uniformly.  Same arithmetic in
 // the same order as the serial routine (identical potentials, identical ties: lowest column), no shared-memory traffic.
-// cost_col(i0) = cost(row i0, this lane's column).
+// cost_col(i0) = cost(row i0, this lane's column).  The set of unmatched columns is a ballot kept per row.
 template <typename CostFn>
 __device__ __forceinline__ void assign_warp_reg(CostFn cost_col, int n, int m, int16_t *col_of_row) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const bool col = lane < m;
-    int width = 1;
-    while (width < m) width <<= 1;  // lanes taking part in the reductions
     double v = 0.0, uc = 0.0;
     int p = 0;
+    unsigned freem = m >= 32 ? full : ((1u << m) - 1u);  // columns no row is matched to yet
     for (int i = 1; i <= n; ++i) {
         double u0 = 0.0, minv = CUDART_INF;
         int way = 0, j0 = 0;
         bool used = !col;  // lanes without a column never compete
+        int i0 = i;        // row matched to column j0 (the inserted row sits in the virtual column 0) ...
+        double ui0 = 0.0;  // ... and its potential
         for (;;) {
-            if (lane == j0 - 1) used = true;
-            const int src = j0 > 0 ? j0 - 1 : 0;
-            const int pj = __shfl_sync(full, p, src);
-            const double uj = __shfl_sync(full, uc, src);
-            const int i0 = j0 == 0 ? i : pj;
-            const double ui0 = j0 == 0 ? u0 : uj;
             u64 key = ~0ull;  // order-preserving integer image of minv[j]; used / missing columns never win
             if (!used) {
                 const double cur = (cost_col(i0 - 1) - ui0) - v;
                 if (cur < minv) { minv = cur; way = j0; }
                 key = plan_dkey(minv);
             }
-            // arg-min over the columns, ties -> lowest column: min of the keys over the first `width` lanes, then the
-            // lowest lane holding it
-            u64 kmin = key;
-            for (int o = width >> 1; o > 0; o >>= 1) {
-                const u64 other = __shfl_xor_sync(full, kmin, o);
-                kmin = other < kmin ? other : kmin;
-            }
-            kmin = __shfl_sync(full, kmin, 0);
-            const unsigned holders = __ballot_sync(full, key == kmin && !used);
-            const int bj = holders ? __ffs(holders) : 0x7fffffff;
+            unsigned holders;
+            const u64 kmin = plan_warp_min_key(key, &holders);  // ties -> lowest column
             const double delta = plan_dkey_inv(kmin);
             if (col) {
                 if (used) { uc += delta; v -= delta; }
                 else minv -= delta;
             }
             u0 += delta;  // column 0 is used from the first round on: u[p[0]] = u[i]
-            j0 = bj == 0x7fffffff ? 0 : bj;
-            if (__shfl_sync(full, p, j0 > 0 ? j0 - 1 : 0) == 0 || j0 == 0) break;
+            j0 = __ffs(holders);
+            if ((freem >> (j0 - 1)) & 1u) break;
+            if (lane == j0 - 1) used = true;
+            i0 = __shfl_sync(full, p, j0 - 1);
+            ui0 = __shfl_sync(full, uc, j0 - 1);
         }
+        freem &= ~(1u << (j0 - 1));
         while (j0) {  // flip the augmenting path: p[j0] = p[way[j0]], the row's potential moves with it
             const int j1 = __shfl_sync(full, way, j0 - 1);
             const int s1 = j1 > 0 ? j1 - 1 : 0;
@@ -270,18 +294,13 @@ __device__ __forceinline__ void assign_seg8(const double *cost, int n, int16_t *
     nmax = max(nmax, __shfl_xor_sync(full, nmax, 16));
     double v = 0.0, uc = 0.0;
     int p = 0;
+    unsigned freem = (1u << n) - 1u;  // this segment's unmatched columns
     for (int i = 1; i <= nmax; ++i) {
-        double u0 = 0.0, minv = CUDART_INF;
-        int way = 0, j0 = 0;
+        double u0 = 0.0, minv = CUDART_INF, ui0 = 0.0;
+        int way = 0, j0 = 0, i0 = i;
         bool used = !col;
         bool go = i <= n;  // uniform over a segment
         while (__any_sync(full, go)) {
-            if (go && lc == j0 - 1) used = true;
-            const int src = base + (j0 > 0 ? j0 - 1 : 0);
-            const int pj = __shfl_sync(full, p, src);
-            const double uj = __shfl_sync(full, uc, src);
-            const int i0 = j0 == 0 ? i : pj;
-            const double ui0 = j0 == 0 ? u0 : uj;
             u64 key = ~0ull;
             if (go && !used) {
                 const double cur = (cost[(i0 - 1) * 8 + lc] - ui0) - v;
@@ -295,18 +314,29 @@ __device__ __forceinline__ void assign_seg8(const double *cost, int n, int16_t *
                 kmin = other < kmin ? other : kmin;
             }
             const unsigned holders = (__ballot_sync(full, go && !used && key == kmin) >> base) & 0xffu;
-            const double delta = plan_dkey_inv(kmin);
+            int jn = 0;
             if (go) {
+                const double delta = plan_dkey_inv(kmin);
                 if (col) {
                     if (used) { uc += delta; v -= delta; }
                     else minv -= delta;
                 }
                 u0 += delta;
-                j0 = holders ? __ffs(holders) : 0;
+                jn = __ffs(holders);  // never 0 while the segment is searching: an unused column always exists
             }
-            const int pn = __shfl_sync(full, p, base + (j0 > 0 ? j0 - 1 : 0));
-            if (pn == 0 || j0 == 0) go = false;
+            const int src = base + (jn > 0 ? jn - 1 : 0);
+            const int pn = __shfl_sync(full, p, src);
+            const double un = __shfl_sync(full, uc, src);
+            if (go) {
+                j0 = jn;
+                if ((freem >> (jn - 1)) & 1u) go = false;
+                else {
+                    if (lc == jn - 1) used = true;
+                    i0 = pn; ui0 = un;
+                }
+            }
         }
+        if (i <= n) freem &= ~(1u << (j0 - 1));
         while (__any_sync(full, j0 != 0)) {  // flip the augmenting paths
             const int j1 = __shfl_sync(full, way, base + (j0 > 0 ? j0 - 1 : 0));
             const int s1 = base + (j1 > 0 ? j1 - 1 : 0);
@@ -330,17 +360,27 @@ __device__ __forceinline__ double plan_sq2(double ax, double ay, double bx, doub
     return d;
 }
 
-__device__ __forceinline__ uint32_t plan_word(const DcaConfig &c, uint32_t gid, uint32_t counter, int attempt, int d) {
-    const uint4 q = philox4x32_10(gid, counter, (uint32_t)(attempt * 64 + d / 4), SITE_PLAN, (uint32_t)c.seed,
-                                  (uint32_t)(c.seed >> 32));
+// Keyed draws of one k-means call: word d of (env, call counter, attempt); a Philox block holds four of them and is
+// kept until the next block is needed.
+struct PlanDraws {
+    uint4 q;
+    int block;
+};
+__device__ __forceinline__ uint32_t plan_word(PlanDraws &dr, const DcaConfig &c, uint32_t gid, uint32_t counter, int attempt,
+                                              int d) {
+    const int blk = attempt * 64 + d / 4;
+    if (dr.block != blk) {
+        dr.block = blk;
+        dr.q = philox4x32_10(gid, counter, (uint32_t)blk, SITE_PLAN, (uint32_t)c.seed, (uint32_t)(c.seed >> 32));
+    }
     const int k = d & 3;
-    return k == 0 ? q.x : (k == 1 ? q.y : (k == 2 ? q.z : q.w));
+    return k == 0 ? dr.q.x : (k == 1 ? dr.q.y : (k == 2 ? dr.q.z : dr.q.w));
 }
 
-// Bit rows of the team labels: lmask[k][w] bit b <=> attacker 32 w + b is in team k (warp ballots).  CTA-wide, no sync.
+// Bit rows of the team labels: lmask[k][w] bit b <=> attacker 32 w + b is in team k (warp ballots).  No sync inside.
 __device__ __forceinline__ void plan_label_masks(const PlanSmem &s, int A, int K) {
-    const int AW = (A + 31) / 32, tid = threadIdx.x, lane = tid & 31;
-    for (int j0 = (tid >> 5) * 32; j0 < A; j0 += blockDim.x) {  // warp-uniform
+    const int AW = (A + 31) / 32, lane = threadIdx.x & 31;
+    for (int j0 = 0; j0 < A; j0 += 32) {  // warp-uniform
         const int j = j0 + lane;
         const int l = j < A ? (int)s.lab[j] : -1;
         for (int k = 0; k < K; ++k) {
@@ -351,63 +391,73 @@ __device__ __forceinline__ void plan_label_masks(const PlanSmem &s, int A, int K
 }
 
 // get_groups' kmeans2(attacker positions, K, iter=20, minit='++', missing='raise') with up to 5 redraws, then
-// missing='warn' (cheat_script_ai.py:276-288), CTA-wide.  Result: s.lab[A], s.lmask, s.cx/s.cy[K].
-// The means are sequential sums in index order (update_cluster_means); a Lloyd round that changes no label is a
+// missing='warn' (cheat_script_ai.py:276-288), by one warp.  Result: s.lab[A], s.lmask, s.cx/s.cy[K].
+// Seeding (_kpp): centre i is the first attacker whose running sum of squared distances to the nearest centre so far
+// reaches r * total.  The running sums have a fixed, warp-shaped order (the draws are keyed, not the reference's MT19937
+// stream, so the order is ours to choose; the CPU checker uses the same one): lane l owns ceil(A/32) consecutive
+// attackers and sums them in index order, the lane totals go through a Kogge-Stone inclusive scan.
+// Lloyd: the means are sequential sums in index order (update_cluster_means); a round that changes no label is a
 // fixed point, so the remaining rounds of the 20 are skipped without changing the result.
 __device__ __forceinline__ void plan_kmeans(const PlanSmem &s, const DcaConfig &c, int A, int K, uint32_t gid,
                                             uint32_t counter) {
-    const int tid = threadIdx.x, nt = blockDim.x, AW = (A + 31) / 32;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, AW = (A + 31) / 32;
+    const int ch = (A + 31) / 32, jb = min(A, lane * ch), je = min(A, jb + ch);
     for (int attempt = 0;; ++attempt) {
-        // _kpp seeding
-        if (tid == 0) {
-            const int pick = (int)__umulhi(plan_word(c, gid, counter, attempt, 0), (uint32_t)A);
-            s.cx[0] = s.ax[pick]; s.cy[0] = s.ay[pick];
-            s.misc[3] = 0; s.misc[4] = 0;  // raised / changed flags
-        }
-        for (int j = tid; j < A; j += nt) { s.d2[j] = CUDART_INF; s.lab[j] = -1; }
-        __syncthreads();
+        PlanDraws dr;
+        dr.block = -1;
+        int pick = (int)__umulhi(plan_word(dr, c, gid, counter, attempt, 0), (uint32_t)A);
+        double ccx = s.ax[pick], ccy = s.ay[pick];  // the centre drawn last
+        if (lane == 0) { s.cx[0] = ccx; s.cy[0] = ccy; }
+        for (int j = lane; j < A; j += 32) { s.d2[j] = CUDART_INF; s.lab[j] = -1; }
+        __syncwarp();
         for (int i = 1; i < K; ++i) {
-            for (int j = tid; j < A; j += nt) {
-                const double d = plan_sq2(s.cx[i - 1], s.cy[i - 1], s.ax[j], s.ay[j]);
-                if (d < s.d2[j]) s.d2[j] = d;
+            double run = 0.0;
+            for (int j = jb; j < je; ++j) {
+                const double d = plan_sq2(ccx, ccy, s.ax[j], s.ay[j]);
+                double m = s.d2[j];
+                if (d < m) { m = d; s.d2[j] = d; }
+                run += m;
+                s.pre[j] = run;
             }
-            __syncthreads();
-            {   // every thread forms the same sequential total, then its own probabilities
-                double tot = 0;
-                for (int j = 0; j < A; ++j) tot += s.d2[j];
-                for (int j = tid; j < A; j += nt) s.prob[j] = s.d2[j] / tot;
+            double sc = run;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const double t = __shfl_up_sync(full, sc, o);
+                if (lane >= o) sc += t;
             }
-            __syncthreads();
-            if (tid == 0) {
-                const double r = (double)plan_word(c, gid, counter, attempt, i) * 0x1p-32;
-                double cum = 0;
-                int pick = A - 1;
-                for (int j = 0; j < A; ++j) {
-                    cum += s.prob[j];
-                    if (cum >= r) { pick = j; break; }
-                }
-                s.cx[i] = s.ax[pick]; s.cy[i] = s.ay[pick];
-            }
-            __syncthreads();
+            const double tot = __shfl_sync(full, sc, 31);
+            double excl = __shfl_up_sync(full, sc, 1);
+            if (lane == 0) excl = 0.0;
+            const double thr = ((double)plan_word(dr, c, gid, counter, attempt, i) * 0x1p-32) * tot;
+            int first = 0x7fffffff;
+            for (int j = je - 1; j >= jb; --j)
+                if (excl + s.pre[j] >= thr) first = j;
+            first = __reduce_min_sync(full, first);
+            pick = first == 0x7fffffff ? A - 1 : first;
+            ccx = s.ax[pick]; ccy = s.ay[pick];
+            if (lane == 0) { s.cx[i] = ccx; s.cy[i] = ccy; }
         }
+        __syncwarp();
         // Lloyd rounds
         bool raised = false;
         for (int it = 0; it < 20; ++it) {
-            for (int j = tid; j < A; j += nt) {  // vq: nearest code, first minimum
-                double best = plan_sq2(s.ax[j], s.ay[j], s.cx[0], s.cy[0]);
+            bool changed = false;
+            for (int j = lane; j < A; j += 32) {  // vq: nearest code, first minimum
+                const double xj = s.ax[j], yj = s.ay[j];
+                double best = plan_sq2(xj, yj, s.cx[0], s.cy[0]);
                 int bl = 0;
                 for (int k = 1; k < K; ++k) {
-                    const double d = plan_sq2(s.ax[j], s.ay[j], s.cx[k], s.cy[k]);
+                    const double d = plan_sq2(xj, yj, s.cx[k], s.cy[k]);
                     if (d < best) { best = d; bl = k; }
                 }
-                if (bl != s.lab[j]) { s.lab[j] = (int16_t)bl; s.misc[4] = 1; }
+                if (bl != s.lab[j]) { s.lab[j] = (int16_t)bl; changed = true; }
             }
-            __syncthreads();
-            if (s.misc[4] == 0) break;  // same labels as last round: the code book already holds their means
+            if (!__any_sync(full, changed)) break;  // same labels as last round: the code book already holds their means
             plan_label_masks(s, A, K);
-            __syncthreads();
-            if (tid == 0) s.misc[4] = 0;  // everyone has read it; the next labelling pass may set it again
-            for (int k = tid; k < K; k += nt) {  // update_cluster_means: sequential sums in index order
+            __syncwarp();
+            bool miss = false;
+            for (int k = lane; k < K; k += 32) {  // update_cluster_means: sequential sums in index order
                 double sx = 0, sy = 0;
                 int n = 0;
                 for (int w = 0; w < AW; ++w) {
@@ -419,13 +469,12 @@ __device__ __forceinline__ void plan_kmeans(const PlanSmem &s, const DcaConfig &
                     }
                 }
                 if (n) { s.cx[k] = sx / n; s.cy[k] = sy / n; }
-                else if (attempt < 5) s.misc[3] = 1;  // missing='raise'; ('warn': the old centre stays)
+                else if (attempt < 5) miss = true;  // missing='raise'; ('warn': the old centre stays)
             }
-            __syncthreads();
-            raised = s.misc[3] != 0;
+            raised = __any_sync(full, miss);
             if (raised) break;
         }
-        __syncthreads();
+        __syncwarp();
         if (!raised) return;
     }
 }
@@ -433,35 +482,36 @@ __device__ __forceinline__ void plan_kmeans(const PlanSmem &s, const DcaConfig &
 // ------------------------------------------------------------------ planner kernel
 // inj_label (i32[E,A]) / inj_cent (f64[E,K,2]) != nullptr: use these teams (the parity harness injects the
 // reference's own k-means result) and leave the persistent state alone.
+// GC / AC: compile-time team sizes (0 = take them from the layout at run time).
+template <int GC, int AC>
 __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const PlanState ps,
                                                           double *__restrict__ att_force,
                                                           const int32_t *__restrict__ inj_label,
                                                           const double *__restrict__ inj_cent) {
+    static_assert(kPlanThreads == 32, "the shared-memory plan assumes one warp per env");
     extern __shared__ __align__(16) unsigned char plan_raw[];
     pdl_trigger();  // a dca_step launched behind this kernel may start its force-independent phases now
+    const unsigned full = 0xffffffffu;
     const BlobLayout &L = P.L;
     const DcaConfig &c = P.cfg;
-    const int G = L.G, A = L.A, K = A / 5 > 0 ? A / 5 : 1, W = (G + 63) / 64, AW = (A + 31) / 32;
-    const int e = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const int G = GC ? GC : L.G, A = AC ? AC : L.A, K = A / 5 > 0 ? A / 5 : 1, W = (G + 63) / 64, AW = (A + 31) / 32;
+    const int e = blockIdx.x, lane = threadIdx.x;
     const PlanSmem s = plan_carve(plan_raw, G, A);
     const unsigned char *blob = P.blobs + (size_t)e * L.bytes;
     const double *bpx = (const double *)(blob + L.px), *bpy = (const double *)(blob + L.py);
     const uint8_t *bfl = blob + L.flags;
     double2 *out = (double2 *)att_force + (size_t)e * A;
     DCA_PROF(P, e, 0);
-    for (int i = tid; i < L.N; i += nt) {
-        const bool alive = bfl[i] & F_ALIVE;
-        if (i < G) { s.gx[i] = bpx[i]; s.gy[i] = bpy[i]; s.galive[i] = alive; }
-        else { s.ax[i - G] = bpx[i]; s.ay[i - G] = bpy[i]; s.aalive[i - G] = alive; out[i - G] = make_double2(0.0, 0.0); }
-    }
-    __syncthreads();
+    for (int g = lane; g < G; g += 32) { s.gx[g] = bpx[g]; s.gy[g] = bpy[g]; s.galive[g] = bfl[g] & F_ALIVE; }
+    for (int a = lane; a < A; a += 32) { s.ax[a] = bpx[G + a]; s.ay[a] = bpy[G + a]; s.aalive[a] = bfl[G + a] & F_ALIVE; }
+    __syncwarp();
 
     DCA_PROF(P, e, 1);
     // ---- teams (cheat_script_ai.py:103-117)
     if (inj_label != nullptr) {
-        for (int a = tid; a < A; a += nt) s.lab[a] = (int16_t)inj_label[(size_t)e * A + a];
-        for (int k = tid; k < K; k += nt) { s.cx[k] = inj_cent[((size_t)e * K + k) * 2]; s.cy[k] = inj_cent[((size_t)e * K + k) * 2 + 1]; }
-        __syncthreads();
+        for (int a = lane; a < A; a += 32) s.lab[a] = (int16_t)inj_label[(size_t)e * A + a];
+        for (int k = lane; k < K; k += 32) { s.cx[k] = inj_cent[((size_t)e * K + k) * 2]; s.cy[k] = inj_cent[((size_t)e * K + k) * 2 + 1]; }
+        __syncwarp();
         plan_label_masks(s, A, K);
     } else {
         const uint32_t gid = (uint32_t)(c.env_gid0 + e);
@@ -470,38 +520,44 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
         bool small = ps.flags[2 * e + 1] != 0;
         if (start) {
             plan_kmeans(s, c, A, K, gid, counter++);
-            for (int a = tid; a < A; a += nt) ps.label[(size_t)e * A + a] = (uint8_t)s.lab[a];
-            for (int k = tid; k < K; k += nt) {
+            for (int a = lane; a < A; a += 32) ps.label[(size_t)e * A + a] = (uint8_t)s.lab[a];
+            bool tiny = false;
+            for (int k = lane; k < K; k += 32) {
                 ps.cent[((size_t)e * K + k) * 2] = s.cx[k]; ps.cent[((size_t)e * K + k) * 2 + 1] = s.cy[k];
-                int n = 0;
-                for (int w = 0; w < AW; ++w) n += __popc(s.lmask[k * AW + w]);
-                if (n > 0 && n <= 3) s.misc[3] = 1;  // a team of <= 3: regroup on every call from now on (:112-117)
+                int m = 0;
+                for (int w = 0; w < AW; ++w) m += __popc(s.lmask[k * AW + w]);
+                if (m > 0 && m <= 3) tiny = true;  // a team of <= 3: regroup on every call from now on (:112-117)
             }
-            __syncthreads();
-            small = s.misc[3] != 0;
-            __syncthreads();
+            small = __any_sync(full, tiny);
         } else if (!small) {
-            for (int a = tid; a < A; a += nt) s.lab[a] = ps.label[(size_t)e * A + a];
-            for (int k = tid; k < K; k += nt) { s.cx[k] = ps.cent[((size_t)e * K + k) * 2]; s.cy[k] = ps.cent[((size_t)e * K + k) * 2 + 1]; }
-            __syncthreads();
+            for (int a = lane; a < A; a += 32) s.lab[a] = ps.label[(size_t)e * A + a];
+            for (int k = lane; k < K; k += 32) { s.cx[k] = ps.cent[((size_t)e * K + k) * 2]; s.cy[k] = ps.cent[((size_t)e * K + k) * 2 + 1]; }
+            __syncwarp();
             plan_label_masks(s, A, K);
         }
         if (small) plan_kmeans(s, c, A, K, gid, counter++);
-        if (tid == 0) { ps.counter[e] = counter; ps.flags[2 * e] = 1; ps.flags[2 * e + 1] = small ? 1 : 0; }
+        if (lane == 0) { ps.counter[e] = counter; ps.flags[2 * e] = 1; ps.flags[2 * e + 1] = small ? 1 : 0; }
     }
+    __syncwarp();
 
     DCA_PROF(P, e, 2);
     // ---- targets: DBSCAN(eps .5, min_samples 2) of the alive guards (cheat_script_ai.py:49-101)
-    if (tid == 0) {
-        int n = 0;
-        for (int g = 0; g < G; ++g)
-            if (s.galive[g]) s.gidx[n++] = (int16_t)g;
-        s.misc[0] = n;
+    // (the k-means workspaces are dead: the shared region now holds the guard list and the graph).  Alive guards are
+    // compacted into index order with ballots.
+    int n = 0;
+    for (int g0 = 0; g0 < G; g0 += 32) {  // warp-uniform
+        const int g = g0 + lane;
+        const bool alive = g < G && s.galive[g];
+        const unsigned b = __ballot_sync(full, alive);
+        if (alive) s.gidx[n + __popc(b & ((1u << lane) - 1u))] = (int16_t)g;
+        n += __popc(b);
     }
-    __syncthreads();
-    const int n = s.misc[0];
-    if (n == 0) return;  // no guard alive: nothing to aim at (the reference would raise); forces stay zero
-    for (int a = tid; a < n; a += nt) {
+    __syncwarp();
+    if (n == 0) {  // no guard alive: nothing to aim at (the reference would raise); forces are zero
+        for (int a = lane; a < A; a += 32) out[a] = make_double2(0.0, 0.0);
+        return;
+    }
+    for (int a = lane; a < n; a += 32) {
         const double xa = s.gx[s.gidx[a]], ya = s.gy[s.gidx[a]];
         for (int w = 0; w < W; ++w) {
             unsigned long long m = 0;
@@ -514,13 +570,12 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
         s.comp[a] = (int16_t)a;
         s.csize[a] = 0;
     }
-    __syncthreads();
+    __syncwarp();
     DCA_PROF(P, e, 3);
     // connected components by min-label propagation with pointer jumping: comp[a] -> lowest member of a's component
     for (;;) {
-        if (tid == 0) s.misc[4] = 0;
-        __syncthreads();
-        for (int a = tid; a < n; a += nt) {
+        bool changed = false;
+        for (int a = lane; a < n; a += 32) {
             int best = s.comp[a];
             for (int w = 0; w < W; ++w) {
                 unsigned long long m = s.adj[a * W + w];
@@ -531,17 +586,16 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
                 }
             }
             best = min(best, (int)s.comp[best]);
-            if (best < s.comp[a]) { s.comp[a] = (int16_t)best; s.misc[4] = 1; }
+            if (best < s.comp[a]) { s.comp[a] = (int16_t)best; changed = true; }
         }
-        __syncthreads();
-        const bool changed = s.misc[4] != 0;
-        __syncthreads();
-        if (!changed) break;
+        if (!__any_sync(full, changed)) break;
+        __syncwarp();
     }
+    __syncwarp();
     DCA_PROF(P, e, 4);
-    for (int a = tid; a < n; a += nt) atomicAdd(&s.csize[s.comp[a]], 1);
-    __syncthreads();
-    if (tid == 0) {
+    for (int a = lane; a < n; a += 32) atomicAdd(&s.csize[s.comp[a]], 1);
+    __syncwarp();
+    if (lane == 0) {
         // target list in the reference's order: labels by first appearance (a cluster first appears at its lowest
         // member); the noise label expands to all its points where it first appears
         int ntg = 0;
@@ -558,9 +612,9 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
         }
         s.misc[2] = ntg;
     }
-    __syncthreads();
+    __syncwarp();
     const int ntg = s.misc[2];
-    for (int t = tid; t < K; t += nt) {  // :129-141 first len(teams) targets, or the last one repeated
+    for (int t = lane; t < K; t += 32) {  // :129-141 first len(teams) targets, or the last one repeated
         const int src = s.tsrc[t < ntg ? t : ntg - 1];
         if (src >= 0) {  // cluster mean = kmeans2(k=1): sequential sum in index order / count
             double sx = 0, sy = 0;
@@ -574,24 +628,17 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
         for (int w = 0; w < AW; ++w) cntk += __popc(s.lmask[t * AW + w]);
         s.cnt[t] = cntk;
     }
-    __syncthreads();
+    __syncwarp();  // from here on the guard positions and the DBSCAN workspaces are dead (ring slots / c1 take their place)
     DCA_PROF(P, e, 5);
-    // ---- team -> target (:153-157): distances centroid <-> target, then the assignment by warp 0
-    if (K > 32) {  // cost matrix for the shared-memory routine (more than 32 targets)
-        for (int q = tid; q < K * K; q += nt) {
-            const int r = q / K, cc = q - r * K;
-            const double dx = s.tx[cc] - s.cx[r], dy = s.ty[cc] - s.cy[r];
-            s.c1[q] = sqrt(dx * dx + dy * dy);
-        }
-    }
-    if (tid == 0) {
+    // ---- team -> target (:153-157): distances centroid <-> target, then the assignment
+    if (lane == 0) {
         int o = 0;
         for (int k = 0; k < K; ++k) { s.toff[k] = (int16_t)o; o += s.cnt[k]; }
         s.toff[K] = (int16_t)o;
     }
-    __syncthreads();
+    __syncwarp();
     // member lists (attacker index order inside a team), one team per thread
-    for (int k = tid; k < K; k += nt) {
+    for (int k = lane; k < K; k += 32) {
         int o = s.toff[k];
         for (int w = 0; w < AW; ++w) {
             uint32_t m = s.lmask[k * AW + w];
@@ -602,40 +649,43 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
             }
         }
     }
-    if ((tid >> 5) == 0) {
-        if (K <= 32) {
-            const int lane = tid & 31;
-            const double txj = lane < K ? s.tx[lane] : 0.0, tyj = lane < K ? s.ty[lane] : 0.0;
-            const double *cx = s.cx, *cy = s.cy;
-            auto cost1 = [=](int r) {
-                const double dx = txj - cx[r], dy = tyj - cy[r];
-                return sqrt(dx * dx + dy * dy);
-            };
-            assign_warp_reg_pre(cost1, K, K, s.c1, s.team_target);
-        } else {
-            const double *c1 = s.c1;
-            auto cost1 = [c1, K](int r, int cc) { return c1[r * K + cc]; };
-            assign_warp(cost1, K, K, s.hu, s.hv, s.hminv, s.hp, s.hway, s.hused, s.team_target);
+    if (K <= 32) {
+        const double txj = lane < K ? s.tx[lane] : 0.0, tyj = lane < K ? s.ty[lane] : 0.0;
+        const double *cx = s.cx, *cy = s.cy;
+        auto cost1 = [=](int r) {
+            const double dx = txj - cx[r], dy = tyj - cy[r];
+            return sqrt(dx * dx + dy * dy);
+        };
+        assign_warp_reg_pre(cost1, K, K, s.c1, s.team_target);
+    } else {  // cost matrix for the shared-memory routine (more than 32 targets)
+        for (int q = lane; q < K * K; q += 32) {
+            const int r = q / K, cc = q - r * K;
+            const double dx = s.tx[cc] - s.cx[r], dy = s.ty[cc] - s.cy[r];
+            s.c1[q] = sqrt(dx * dx + dy * dy);
         }
+        __syncwarp();
+        const double *c1 = s.c1;
+        auto cost1 = [c1, K](int r, int cc) { return c1[r * K + cc]; };
+        assign_warp(cost1, K, K, s.hu, s.hv, s.hminv, s.hp, s.hway, s.hused, s.team_target);
     }
-    __syncthreads();
+    __syncwarp();
     DCA_PROF(P, e, 6);
     // ---- ring slots (:160-170), by list position
-    for (int i = tid; i < A; i += nt) {
+    for (int i = lane; i < A; i += 32) {
         const int k = s.tof[i], nm = s.cnt[k], j = i - s.toff[k];
         const double delta = kPi / nm - 1;  // (float)(np.pi / len(team_agents) - 1) :163
         const int tg = s.team_target[k];
         s.sx[i] = s.tx[tg] + 0.8 * cos(delta * j);
         s.sy[i] = s.ty[tg] + 0.8 * sin(delta * j);
     }
-    __syncthreads();
+    __syncwarp();
     DCA_PROF(P, e, 7);
-    // ---- member -> slot (:171-173): teams of up to 8 go four at a time through one warp (assign_seg8), larger ones
-    // one warp per team (up to 32 members entirely in registers)
+    // ---- member -> slot (:171-173): teams of up to 8 go four at a time through the warp (assign_seg8), larger ones
+    // one at a time (up to 32 members entirely in registers, cost matrix precomputed up to 16)
     {
-        const int nw = nt >> 5, warp = tid >> 5, lane = tid & 31, sg = lane >> 3, lc = lane & 7;
+        const int sg = lane >> 3, lc = lane & 7;
         const double *ax = s.ax, *ay = s.ay;
-        for (int kk = 0, b = 0;;) {  // warp-uniform scan for the next four small teams
+        for (int kk = 0;;) {  // warp-uniform scan for the next four small teams
             int myk = -1, c4 = 0;
             for (; kk < K && c4 < 4; ++kk) {
                 const int nm = s.cnt[kk];
@@ -645,9 +695,8 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
                 }
             }
             if (c4 == 0) break;
-            if ((b++ % nw) != warp) continue;
             const int nm = myk >= 0 ? s.cnt[myk] : 0, off = myk >= 0 ? s.toff[myk] : 0;
-            double *cs = s.cw + (warp * 4 + sg) * kPlanTeamPre * kPlanTeamPre;
+            double *cs = s.cw + sg * kPlanTeamPre * kPlanTeamPre;
             if (lc < nm) {
                 const double sxj = s.sx[off + lc], syj = s.sy[off + lc];
                 for (int r = 0; r < nm; ++r) {
@@ -659,7 +708,7 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
             __syncwarp();
             assign_seg8(cs, nm, s.hcol + off);
         }
-        for (int kk = warp; kk < K; kk += nw) {  // warp-uniform
+        for (int kk = 0; kk < K; ++kk) {  // warp-uniform
             const int nm = s.cnt[kk];
             if (nm <= kPlanTeamPre) continue;
             const int off = s.toff[kk], ho = off + kk;
@@ -671,7 +720,8 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
                     const double dx = ax[mem[i]] - sxj, dy = ay[mem[i]] - syj;
                     return sqrt(dx * dx + dy * dy);
                 };
-                assign_warp_reg(cost2, nm, nm, s.hcol + off);
+                if (nm <= kPlanTeamPre2) assign_warp_reg_pre(cost2, nm, nm, s.cw, s.hcol + off);
+                else assign_warp_reg(cost2, nm, nm, s.hcol + off);
             } else {
                 auto cost2 = [=](int i, int j) {
                     const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];
@@ -682,15 +732,17 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
             }
         }
     }
-    __syncthreads();
+    __syncwarp();
     DCA_PROF(P, e, 8);
-    // ---- forces (:175-188)
-    for (int i = tid; i < A; i += nt) {
+    // ---- forces (:175-188); dead attackers get zero
+    for (int i = lane; i < A; i += 32) {
         const int a = s.mem[i];
-        if (!s.aalive[a]) continue;
-        const int slot = s.toff[s.tof[i]] + s.hcol[i];
-        double fx = -s.ax[a] + s.sx[slot], fy = -s.ay[a] + s.sy[slot];
-        if (c.disable_red_function) { fx = -fx; fy = -fy; }
+        double fx = 0.0, fy = 0.0;
+        if (s.aalive[a]) {
+            const int slot = s.toff[s.tof[i]] + s.hcol[i];
+            fx = -s.ax[a] + s.sx[slot]; fy = -s.ay[a] + s.sy[slot];
+            if (c.disable_red_function) { fx = -fx; fy = -fy; }
+        }
         out[a] = make_double2(fx, fy);
     }
     DCA_PROF(P, e, 9);

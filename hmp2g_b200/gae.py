@@ -12,9 +12,12 @@ def _ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
-def gae_return(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=11, want_pushed=False):
+def gae_return(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=11, want_pushed=False,
+               gamma_fwd=None):
     """reward f32 [T,E,G], value f32 [T,E,G], dead uint8/bool [T,E,G] (obs all-NaN, trajectory.py:72),
-    traj_len int32 [E] or None.  Returns (ret f32, threat f32[, reward_pushed f32]) -- rows >= traj_len untouched (0)."""
+    traj_len int32 [E] or None.  gamma_fwd: AlgorithmConfig.gamma_in_reward_forwarding_value when
+    gamma_in_reward_forwarding is on (traj_gae.py:55-60), None = off.
+    Returns (ret f32, threat f32[, reward_pushed f32]) -- rows >= traj_len untouched (0)."""
     lib = _lib.load()
     assert reward.is_cuda and reward.dtype == torch.float32 and reward.is_contiguous()
     T, E, G = reward.shape
@@ -31,7 +34,8 @@ def gae_return(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_
     stream = C.c_void_p(torch.cuda.current_stream(reward.device).cuda_stream)
     with torch.cuda.device(reward.device):
         _lib.check(lib.dca_gae(_ptr(reward), _ptr(value), _ptr(dead), _ptr(traj_len), _ptr(ret), _ptr(threat),
-                               _ptr(pushed), T, E, G, float(gamma), float(tau), int(threat_limit), stream))
+                               _ptr(pushed), T, E, G, float(gamma), float(tau),
+                               1.0 if gamma_fwd is None else float(gamma_fwd), int(threat_limit), stream))
     return (ret, threat, pushed) if want_pushed else (ret, threat)
 
 

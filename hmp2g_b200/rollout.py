@@ -48,7 +48,7 @@ class HistoryPool(object):
 
 
 class DeviceRollout(object):
-    def __init__(self, env, horizon=None, gamma=0.99, tau=0.95, threat_limit=11):
+    def __init__(self, env, horizon=None, gamma=0.99, tau=0.95, threat_limit=11, gamma_fwd=None):
         self.env = env
         E, G = env.E, env.G
         self.T = int(horizon or env.cfg.max_episode_step)
@@ -58,6 +58,7 @@ class DeviceRollout(object):
         self.dead = torch.zeros((self.T, E, G), dtype=torch.uint8, device=dev)
         self.length = torch.zeros((E,), dtype=torch.int32, device=dev)   # steps collected in the running episode
         self.gamma, self.tau, self.threat_limit = gamma, tau, threat_limit
+        self.gamma_fwd = gamma_fwd  # gamma_in_reward_forwarding_value, None = the flag is off (traj_gae.py:54-60)
         self._rows = torch.arange(E, device=dev)
 
     def alive_guards(self):
@@ -93,7 +94,7 @@ class DeviceRollout(object):
             finished = torch.ones((E,), dtype=torch.bool, device=self.reward.device)
         lens = torch.where(finished, self.length, torch.zeros_like(self.length)).clamp_max(self.T)
         ret, threat = gae_return(self.reward, self.value, self.dead, traj_len=lens, gamma=self.gamma, tau=self.tau,
-                                 threat_limit=self.threat_limit)
+                                 threat_limit=self.threat_limit, gamma_fwd=self.gamma_fwd)
         valid_te = torch.arange(self.T, device=lens.device)[:, None] < lens[None, :]
         adv = normalized_advantage(ret, self.value, valid=valid_te, group=group)
         valid = valid_te[:, :, None].expand_as(ret)

@@ -125,10 +125,13 @@ int dca_import_state(DcaHandle *h, const DcaState *src, dca_stream_t stream);
 /* replaces: trajectory.finalize / reward_push_forward / gae_finalize_return
  * ALGORITHM/conc/trajectory.py:60-117 (= ALGORITHM/common/traj_gae.py:54-133), batched over a
  * rollout buffer [T,E,G]; one trajectory per env column of length traj_len[e] (NULL = T).
- * reward f32 in; ret/threat f32 out; reward_pushed (f32, may be NULL) = reward after push-forward. */
+ * reward f32 in; ret/threat f32 out; reward_pushed (f32, may be NULL) = reward after push-forward.
+ * gamma_fwd: AlgorithmConfig.gamma_in_reward_forwarding_value when gamma_in_reward_forwarding is set -- a dead
+ * frame's reward moves to the previous frame scaled by it (traj_gae.py:55-60, conc_4hist/trajectory.py:57-63,
+ * ppo_ma/trajectory.py:59-60); 1.0 = the flag is off (plain push).  ABI version 2 added this argument. */
 int dca_gae(const float *reward, const float *value, const uint8_t *dead, const int32_t *traj_len,
             float *ret, float *threat, float *reward_pushed, int T, int E, int G,
-            double gamma, double tau, int threat_limit, dca_stream_t stream);
+            double gamma, double tau, double gamma_fwd, int threat_limit, dca_stream_t stream);
 
 /* ---- runner bookkeeping on the device -----------------------------------------------------------------------------
  * replaces: the per-env Python loop of task_runner.Runner.update_runner task_runner.py:95-138 (and its test-run twin

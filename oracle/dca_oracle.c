@@ -458,14 +458,16 @@ int orc_plan_centroid(const OrcConfig *cfg, const OrcState *st, int E, double *a
  * dtype walk (numpy): reward f64, value f32, gamma*value[t+1] evaluated in f32 (python scalar is
  * weak), delta/gae in f64, return stored f32. */
 int orc_gae(const double *reward, const float *value, const uint8_t *dead, const int32_t *traj_len, float *ret,
-            float *threat, double *reward_pushed, int T, int E, int G, double gamma, double tau, int threat_limit) {
+            float *threat, double *reward_pushed, int T, int E, int G, double gamma, double tau, double gamma_fwd,
+            int threat_limit) {
     const size_t S = (size_t)E * G;
     for (int e = 0; e < E; ++e) {
         const int L = traj_len ? traj_len[e] : T;
         if (L <= 0) continue;
         for (int g = 0; g < G; ++g) {
             const size_t c = (size_t)e * G + g;
-            /* reward push: r[i-1] += r[i]*dead[i]; r[i] *= !dead[i], i = L-1 .. 1 */
+            /* reward push: r[i-1] += r[i]*dead[i]; r[i] *= !dead[i], i = L-1 .. 1; with gamma_in_reward_forwarding
+             * (traj_gae.py:55-60, conc_4hist/trajectory.py:58-63) the pushed amount is r[i]*gamma_fwd (1.0 = off) */
             double carry_r = 0; /* r[i] after receiving pushes from i+1 */
             double gae = 0;
             double th = -1;
@@ -474,7 +476,7 @@ int orc_gae(const double *reward, const float *value, const uint8_t *dead, const
                 double r = reward[k] + carry_r;
                 const int d = dead[k] != 0;
                 if (i > 0) {
-                    carry_r = r * (double)d;      /* reward[i]*dead_mask[i].astype(int) */
+                    carry_r = (r * gamma_fwd) * (double)d; /* np.where(dead_mask[i], reward[i]*gamma, 0) */
                     r = r * (double)(!d);
                 }
                 if (reward_pushed) reward_pushed[k] = r;

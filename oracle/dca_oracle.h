@@ -77,7 +77,7 @@ int orc_plan_centroid(const OrcConfig *cfg, const OrcState *st, int E, double *a
  * Follows ALGORITHM/conc/trajectory.py:60-117 (reward_push_forward, threat, gae_finalize_return). */
 int orc_gae(const double *reward, const float *value, const uint8_t *dead, const int32_t *traj_len,
             float *ret, float *threat, double *reward_pushed, int T, int E, int G,
-            double gamma, double tau, int threat_limit);
+            double gamma, double tau, double gamma_fwd, int threat_limit);
 
 void orc_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]);
 

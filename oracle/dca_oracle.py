@@ -165,7 +165,7 @@ class OracleVecEnv(object):
             self.state[name][e] = np.asarray(d[name]).astype(dt)
 
 
-def gae(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=11):
+def gae(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=11, gamma_fwd=1.0):
     """reward f64 [T,E,G], value f32 [T,E,G], dead bool [T,E,G] -> (ret f32, threat f32, pushed reward f64)."""
     reward = np.ascontiguousarray(reward, np.float64)
     value = np.ascontiguousarray(value, np.float32)
@@ -176,7 +176,7 @@ def gae(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=1
     pushed = np.zeros((T, E, G), np.float64)
     tl = None if traj_len is None else np.ascontiguousarray(traj_len, np.int32)
     rc = lib().orc_gae(_ptr(reward), _ptr(value), _ptr(dead), _ptr(tl), _ptr(ret), _ptr(threat), _ptr(pushed),
-                       T, E, G, C.c_double(gamma), C.c_double(tau), int(threat_limit))
+                       T, E, G, C.c_double(gamma), C.c_double(tau), C.c_double(gamma_fwd), int(threat_limit))
     assert rc == 0
     return ret, threat, pushed
 

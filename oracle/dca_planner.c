@@ -191,16 +191,33 @@ int orc_kmeans(const double *pts, int n, int k, uint64_t seed, int64_t gid, uint
         int pick = (int)(((uint64_t)w * (uint64_t)n) >> 32);
         cb[0] = pts[2 * pick]; cb[1] = pts[2 * pick + 1];
         for (int i = 1; i < k; ++i) {
-            double tot = 0;
-            for (int j = 0; j < n; ++j) {
-                double m = INFINITY;
-                for (int c = 0; c < i; ++c) { const double d = sq2(cb + 2 * c, pts + 2 * j); if (d < m) m = d; }
-                d2[j] = m; tot += m;
+            /* running sums of d2 in a fixed, warp-shaped order (the draws are keyed, so the order is this
+             * restatement's to choose; the CUDA planner uses the same one): 32 "lanes" own ceil(n/32) consecutive
+             * points each and sum them in index order, the lane totals go through a Kogge-Stone inclusive scan;
+             * the pick is the first point whose running sum reaches r * total (= searchsorted(cumsum(p), r)) */
+            const int ch = (n + 31) / 32;
+            double pre[PL_MAX], sc[32], nx[32];
+            for (int l = 0; l < 32; ++l) {
+                double run = 0;
+                for (int j = l * ch; j < n && j < (l + 1) * ch; ++j) {
+                    double m = INFINITY;
+                    for (int c = 0; c < i; ++c) { const double d = sq2(cb + 2 * c, pts + 2 * j); if (d < m) m = d; }
+                    d2[j] = m; run += m; pre[j] = run;
+                }
+                sc[l] = run;
+            }
+            for (int o = 1; o < 32; o <<= 1) {
+                for (int l = 0; l < 32; ++l) nx[l] = l >= o ? sc[l] + sc[l - o] : sc[l];
+                memcpy(sc, nx, sizeof(sc));
             }
             const double r = plan_draw(seed, gid, counter, attempt, i, &w);
-            double cum = 0;
+            const double thr = r * sc[31];
             pick = n - 1;
-            for (int j = 0; j < n; ++j) { cum += d2[j] / tot; if (cum >= r) { pick = j; break; } }
+            for (int j = 0; j < n; ++j) {
+                const int l = j / ch;
+                const double excl = l > 0 ? sc[l - 1] : 0.0;
+                if (excl + pre[j] >= thr) { pick = j; break; }
+            }
             cb[2 * i] = pts[2 * pick]; cb[2 * i + 1] = pts[2 * pick + 1];
         }
         int raised = 0;

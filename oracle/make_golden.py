@@ -1,7 +1,7 @@
 """ORACLE / TEST INFRASTRUCTURE -- generates tests/golden/*.npz by EXECUTING THE REFERENCE.
 
 Run in the build container only (needs /root/reference):
-    python oracle/make_golden.py            # writes tests/golden/dca_<name>.npz + gae_conc.npz
+    python oracle/make_golden.py            # writes tests/golden/dca_<name>.npz + gae_conc.npz + gae_conc4hist_fwd.npz
 
 Each DCA file holds one env trajectory of the unmodified reference env
 (MISSION/dca via UTIL/shm_env.EnvAutoReset) under the keyed RNG stream: initial state after reset,
@@ -115,37 +115,41 @@ def run_case(name, spec):
           'alive end', int(rec['alive'][-1].sum()), '%.1f KB' % (os.path.getsize(path) / 1024))
 
 
-def run_gae():
-    """GAE fixtures from ALGORITHM/conc/trajectory.py (conc) run on synthetic trajectories."""
+def _load_trajectory_module(alg, **cfg):
+    """Import ALGORITHM/<alg>/trajectory.py alone: its `.foundation` (torch-heavy) is replaced by a stub module that
+    carries the AlgorithmConfig numbers trajectory.py reads (ALGORITHM/conc/foundation.py:9-10,
+    ALGORITHM/conc_4hist/foundation.py:15-16,45-46)."""
     from ref_env import setup_reference
     setup_reference()
+    import importlib
     import types
-    # conc.trajectory imports AlgorithmConfig from conc.foundation (torch-heavy); provide the two numbers it
-    # reads (ALGORITHM/conc/foundation.py:9-10) through a stub module so only trajectory.py itself executes.
-    stub = types.ModuleType('ALGORITHM.conc.foundation')
+    stub = types.ModuleType('ALGORITHM.%s.foundation' % alg)
 
     class AlgorithmConfig:
         gamma = 0.99
         tau = 0.95
+    for k, v in cfg.items():
+        setattr(AlgorithmConfig, k, v)
     stub.AlgorithmConfig = AlgorithmConfig
-    import importlib
-    pkg = types.ModuleType('ALGORITHM.conc')
-    pkg.__path__ = [os.path.join('/root/reference', 'ALGORITHM', 'conc')]
-    sys.modules['ALGORITHM.conc'] = pkg
-    sys.modules['ALGORITHM.conc.foundation'] = stub
-    if not hasattr(np, 'core'):
-        pass
-    traj_mod = importlib.import_module('ALGORITHM.conc.trajectory')
-    rng = np.random.RandomState(7)
+    pkg = types.ModuleType('ALGORITHM.%s' % alg)
+    pkg.__path__ = [os.path.join('/root/reference', 'ALGORITHM', alg)]
+    sys.modules['ALGORITHM.%s' % alg] = pkg
+    sys.modules['ALGORITHM.%s.foundation' % alg] = stub
+    sys.modules.pop('ALGORITHM.%s.trajectory' % alg, None)  # re-import under the new AlgorithmConfig
+    return importlib.import_module('ALGORITHM.%s.trajectory' % alg), AlgorithmConfig
+
+
+def _gae_cases(traj_mod, shapes, seed, rewards=(0.0, 1.0, -0.5, 0.5)):
+    rng = np.random.RandomState(seed)
     recs = {}
-    for idx, (T, G) in enumerate([(57, 50), (180, 50), (1, 6), (23, 100)]):
+    for idx, (T, G) in enumerate(shapes):
         tr = traj_mod.trajectory(traj_limit=T, env_id=0)
         # dead mask: agents die at random times and stay dead (obs rows all-NaN once dead)
         death = rng.randint(1, T + 30, size=G)
         obs = rng.randn(T, G, 12, 16).astype(np.float32)
         for g in range(G):
             obs[death[g]:, g] = np.nan
-        reward = rng.choice([0.0, 1.0, -0.5, 0.5], size=(T, G)).astype(np.float64)
+        reward = rng.choice(list(rewards), size=(T, G)).astype(np.float64)
         value = rng.randn(T, G, 1).astype(np.float32)
         tr.obs, tr.reward, tr.value = obs, reward.copy(), value
         tr.key_dict = ['obs', 'reward', 'value']
@@ -157,15 +161,42 @@ def run_gae():
         recs['c%d_return' % idx] = getattr(tr, 'return')[..., 0]
         recs['c%d_threat' % idx] = tr.threat[..., 0].astype(np.float32)
         recs['c%d_reward_pushed' % idx] = tr.reward
+    return recs
+
+
+def run_gae():
+    """GAE fixtures from ALGORITHM/conc/trajectory.py (conc) run on synthetic trajectories."""
+    traj_mod, _ = _load_trajectory_module('conc')
+    recs = _gae_cases(traj_mod, [(57, 50), (180, 50), (1, 6), (23, 100)], seed=7)
     path = os.path.join(OUT, 'gae_conc.npz')
     np.savez_compressed(path, **recs)
     print('gae_conc', '%.1f KB' % (os.path.getsize(path) / 1024))
 
 
+def run_gae_fwd():
+    """gamma_in_reward_forwarding fixtures from ALGORITHM/conc_4hist/trajectory.py:57-63 (SAFE_LIMIT 11): a dead
+    frame's reward moves to the previous frame scaled by gamma_in_reward_forwarding_value."""
+    recs = {}
+    for tag, gfv in (('a', 0.99), ('b', 0.9)):
+        traj_mod, cfg = _load_trajectory_module('conc_4hist', gamma_in_reward_forwarding=True,
+                                                gamma_in_reward_forwarding_value=gfv)
+        assert cfg.gamma_in_reward_forwarding and traj_mod.AlgorithmConfig is cfg
+        r = _gae_cases(traj_mod, [(57, 50), (180, 20), (2, 6)], seed=11 if tag == 'a' else 12,
+                       rewards=(0.0, 1.0, -0.5, 0.5, 0.3, -1.7))
+        for k, v in r.items():
+            recs[tag + '_' + k] = v
+        recs[tag + '_gamma_fwd'] = np.float64(gfv)
+    path = os.path.join(OUT, 'gae_conc4hist_fwd.npz')
+    np.savez_compressed(path, **recs)
+    print('gae_conc4hist_fwd', '%.1f KB' % (os.path.getsize(path) / 1024))
+
+
 if __name__ == '__main__':
-    which = sys.argv[1:] or (list(CASES) + ['gae'])
+    which = sys.argv[1:] or (list(CASES) + ['gae', 'gae_fwd'])
     for n in which:
         if n == 'gae':
             run_gae()
+        elif n == 'gae_fwd':
+            run_gae_fwd()
         else:
             run_case(n, CASES[n])

@@ -294,6 +294,27 @@ def test_cuda_gae_matches_reference_and_oracle():
     assert np.array_equal(ret.cpu().numpy().view(np.uint32), o_ret.view(np.uint32))
     assert np.array_equal(thr.cpu().numpy(), o_thr)
     assert np.array_equal(push.cpu().numpy().astype(np.float64), o_push)
+    # gamma_in_reward_forwarding (conc_4hist/trajectory.py:57-63): the reference's own fixtures, then ragged vs the oracle
+    z = np.load(gu.GOLDEN_DIR + '/gae_conc4hist_fwd.npz')
+    for tag in 'ab':
+        gf = float(z[tag + '_gamma_fwd'])
+        for i in range(3):
+            r_, v_, d_ = (z['%s_c%d_%s' % (tag, i, k)] for k in ('reward', 'value', 'dead'))
+            ret_, thr_, push_ = gae_return(torch.from_numpy(r_[:, None].astype(np.float32)).cuda().contiguous(),
+                                           torch.from_numpy(v_[:, None]).cuda().contiguous(),
+                                           torch.from_numpy(d_[:, None]).cuda(), want_pushed=True, gamma_fwd=gf)
+            want_push = z['%s_c%d_reward_pushed' % (tag, i)]
+            # rewards enter as float32 here (0.3 and -1.7 are not float32 numbers): compare at float32 resolution
+            np.testing.assert_allclose(push_[:, 0].cpu().numpy(), want_push, rtol=2e-7, atol=1e-7)
+            assert np.array_equal(thr_[:, 0].cpu().numpy(), z['%s_c%d_threat' % (tag, i)])
+            np.testing.assert_allclose(ret_[:, 0].cpu().numpy(), z['%s_c%d_return' % (tag, i)], rtol=1e-6, atol=1e-6)
+    r32 = r.astype(np.float32)
+    o_ret, o_thr, o_push = orc_gae(r32.astype(np.float64), v, d, traj_len=tl, threat_limit=11, gamma_fwd=0.97)
+    ret, thr, push = gae_return(torch.from_numpy(r32).cuda(), torch.from_numpy(v).cuda(), torch.from_numpy(d).cuda(),
+                                traj_len=torch.from_numpy(tl).cuda(), threat_limit=11, want_pushed=True, gamma_fwd=0.97)
+    assert np.array_equal(ret.cpu().numpy().view(np.uint32), o_ret.view(np.uint32))  # same f64 operations, one rounding
+    assert np.array_equal(thr.cpu().numpy(), o_thr)
+    assert np.array_equal(push.cpu().numpy(), o_push.astype(np.float32))
 
 
 def test_cuda_empty_rows_nan_option_and_device_rollout():

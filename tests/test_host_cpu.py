@@ -90,7 +90,7 @@ def test_c_abi_library_exports_every_declared_symbol():
     assert len(declared) >= 12 and declared == set(_lib.EXPORTS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert _lib.load().dca_abi_version() == 1
+    assert _lib.load().dca_abi_version() == 2
 
 
 def test_abi_struct_layout_matches_header():

@@ -98,3 +98,20 @@ def test_gae_matches_reference():
         assert np.array_equal(pushed[:, 0], z['c%d_reward_pushed' % i])
         assert np.array_equal(threat[:, 0], z['c%d_threat' % i])
         assert np.array_equal(ret[:, 0].view(np.uint32), z['c%d_return' % i].view(np.uint32)), i
+
+
+def test_gae_reward_forwarding_gamma_matches_reference():
+    """gamma_in_reward_forwarding (ALGORITHM/conc_4hist/trajectory.py:57-63 = ALGORITHM/common/traj_gae.py:54-60):
+    fixtures from the reference's conc_4hist trajectory class with the flag on, forwarding values 0.99 and 0.9."""
+    z = np.load(gu.GOLDEN_DIR + '/gae_conc4hist_fwd.npz')
+    for tag in 'ab':
+        gf = float(z[tag + '_gamma_fwd'])
+        n = len([k for k in z.files if k.startswith(tag + '_') and k.endswith('_reward')])
+        assert n >= 3
+        for i in range(n):
+            r, v, d = (z['%s_c%d_%s' % (tag, i, k)] for k in ('reward', 'value', 'dead'))
+            ret, threat, pushed = gae(r[:, None, :], v[:, None, :], d[:, None, :], gamma=0.99, tau=0.95, threat_limit=11,
+                                      gamma_fwd=gf)
+            assert np.array_equal(pushed[:, 0], z['%s_c%d_reward_pushed' % (tag, i)])
+            assert np.array_equal(threat[:, 0], z['%s_c%d_threat' % (tag, i)])
+            assert np.array_equal(ret[:, 0].view(np.uint32), z['%s_c%d_return' % (tag, i)].view(np.uint32)), (tag, i)
