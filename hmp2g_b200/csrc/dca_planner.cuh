@@ -16,7 +16,7 @@ namespace dca {
 
 enum : uint32_t { SITE_PLAN = 3 };
 constexpr int kPlanThreads = 32;  // one warp per env: no cross-warp waiting, every phase is warp-synchronous
-constexpr int kPlanTeamPre = 8;   // teams up to this size go four at a time through assign_seg8
+constexpr int kPlanTeamPre = 8;   // teams up to this size are matched by subset DP (assign_dp8)
 constexpr int kPlanTeamPre2 = 16; // teams up to this size get their cost matrix precomputed (independent sqrt chains)
 
 // persistent team state of one env (World.start_flag / teams_result_step1 / team_centroid_step1 survive resets)
@@ -29,8 +29,9 @@ struct PlanState {
 
 // Shared-memory plan of one env.  The env is worked on by ONE warp phase after phase, so workspaces of different
 // phases share one region (`un`): k-means {d2, pre}, DBSCAN {gidx, adj, comp, csize, tsrc}, team->target {c1 (+ the
-// h* workspaces when there are more than 32 targets)}, member->slot {cw | h*: small teams first, then the large ones}.
-// Guard positions (dead once the targets exist) share their space with the ring slots.  50v50: 4.8 KB per env, so all
+// h* workspaces when there are more than 32 targets)}, member->slot {cq, then cw | h*: small teams first, then the
+// large ones}.
+// Guard positions (dead once the targets exist) share their space with the ring slots.  50v50: 5.5 KB per env, so all
 // 4096 envs of the benchmark are resident at once (28 per SM; 9.8 KB gave 21 per SM = 1.3 waves).
 struct PlanSmem {
     double *gx, *gy, *ax, *ay;      // positions
@@ -50,7 +51,9 @@ struct PlanSmem {
     int16_t *toff;                  // [K+1] member list offsets
     int16_t *mem, *tof;             // [A] members grouped by team / team of that list position
     double *c1;                     // [K*K] team-centroid <-> target distances
-    double *cw;                     // [kPlanTeamPre2^2] member <-> slot distances: four 8x8 problems or one up to 16x16
+    double *cq, *dp;                // [64] member <-> slot distances of one team of up to 8 / [256] subset DP values
+    uint8_t *dpc;                   // [256] subset DP choices
+    double *cw;                     // [kPlanTeamPre2^2] member <-> slot distances of one team of 9..16
     double *hu, *hv, *hminv;        // [A+K+2] assignment workspaces of the shared-memory routine (> 32 columns)
     int16_t *hp, *hway;             // [A+K+2]
     uint8_t *hused;                 // [A+K+2]
@@ -68,7 +71,7 @@ __host__ __device__ constexpr int plan_union_bytes(int G, int A) {
     const int km = 2 * align_up(A * 8, 16);
     const int db = align_up(G * 2, 16) + G * W * 8 + align_up(G * 2, 16) + align_up(G * 4, 16) + align_up(K * 2, 16);
     const int tt = align_up(K * K * 8, 16) + (K > 32 ? plan_h_bytes(H) : 0);
-    const int ms = plan_max(kPlanTeamPre2 * kPlanTeamPre2 * 8, plan_h_bytes(H));
+    const int ms = plan_max(plan_max(64 * 8 + 256 * 8 + 256, kPlanTeamPre2 * kPlanTeamPre2 * 8), plan_h_bytes(H));
     return plan_max(plan_max(km, db), plan_max(tt, ms));
 }
 __host__ __device__ constexpr int plan_smem_bytes(int G, int A) {
@@ -121,7 +124,8 @@ __device__ __forceinline__ PlanSmem plan_carve(unsigned char *p, int G, int A) {
     unsigned char *hb = un;
     s.c1 = (double *)un;                      // team -> target
     if (K > 32) hb = un + align_up(K * K * 8, 16);
-    s.cw = (double *)un;                      // member -> slot, small teams (before the large ones)
+    s.cq = (double *)un; s.dp = s.cq + 64; s.dpc = (uint8_t *)(s.dp + 256);  // member -> slot: the small teams first ...
+    s.cw = (double *)un;                      // ... then the larger teams one by one
     {
         unsigned char *q = hb;
         const int h8 = align_up(H * 8, 16), h2 = align_up(H * 2, 16);
@@ -280,75 +284,71 @@ __device__ __forceinline__ void assign_warp_reg_pre(CostFn cost_col, int n, int 
     assign_warp_reg(pre, n, m, col_of_row);
 }
 
-// Four independent square assignments (n <= 8 each) advanced in lock-step by ONE warp: lanes 8g .. 8g+7 own the columns
-// of problem g and run assign_warp_reg's state machine on it (same arithmetic, same order, same ties); a problem that
-// has finished its search / its flip idles until the slowest one of the four is through, so the step count is the
-// maximum over the four problems instead of their sum.  `cost` is this lane's problem, row-major with stride 8;
-// n = 0 marks an empty segment.
-__device__ __forceinline__ void assign_seg8(const double *cost, int n, int16_t *col_of_row) {
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31, base = lane & 24, lc = lane & 7;
-    const bool col = lc < n;
-    int nmax = n;
-    nmax = max(nmax, __shfl_xor_sync(full, nmax, 8));
-    nmax = max(nmax, __shfl_xor_sync(full, nmax, 16));
-    double v = 0.0, uc = 0.0;
-    int p = 0;
-    unsigned freem = (1u << n) - 1u;  // this segment's unmatched columns
-    for (int i = 1; i <= nmax; ++i) {
-        double u0 = 0.0, minv = CUDART_INF, ui0 = 0.0;
-        int way = 0, j0 = 0, i0 = i;
-        bool used = !col;
-        bool go = i <= n;  // uniform over a segment
-        while (__any_sync(full, go)) {
-            u64 key = ~0ull;
-            if (go && !used) {
-                const double cur = (cost[(i0 - 1) * 8 + lc] - ui0) - v;
-                if (cur < minv) { minv = cur; way = j0; }
-                key = plan_dkey(minv);
+// ------------------------------------------------------------------ tiny assignments by subset DP (n <= 8)
+// linear_sum_assignment returns THE optimal matching; for up to 8 rows the warp finds it by dynamic programming over
+// column subsets instead of augmenting paths: dp[S] = min over j in S of dp[S - j] + cost(|S| - 1, j) -- row r = |S| - 1
+// takes column j -- layer by layer (|S| = 1 .. n, the C(n,|S|) subsets of a layer spread over the lanes), then the
+// matching is read back from the recorded choices.  n 2^(n-1) additions (80 for n = 5, 1024 for n = 8) against the
+// dozens of dependent search / flip rounds of the augmenting-path routine, whose rows all prefer the same ring slots.
+// The optimum is unique unless two matchings tie to the last bit of a double sum (ring slots and members are in general
+// position), so the result is the serial routine's; costs are added in row order.
+// kPlanPopMask: the subsets of {0..7} sorted by (size, value) -- the first C(n,k) entries of size class k are exactly
+// the subsets of {0..n-1}.
+__device__ const uint8_t kPlanPopMask[256] = {
+    0, 1, 2, 4, 8, 16, 32, 64, 128, 3, 5, 6, 9, 10, 12, 17, 18, 20, 24, 33, 34, 36, 40, 48, 65, 66, 68, 72, 80,
+    96, 129, 130, 132, 136, 144, 160, 192, 7, 11, 13, 14, 19, 21, 22, 25, 26, 28, 35, 37, 38, 41, 42, 44, 49, 50,
+    52, 56, 67, 69, 70, 73, 74, 76, 81, 82, 84, 88, 97, 98, 100, 104, 112, 131, 133, 134, 137, 138, 140, 145, 146,
+    148, 152, 161, 162, 164, 168, 176, 193, 194, 196, 200, 208, 224, 15, 23, 27, 29, 30, 39, 43, 45, 46, 51, 53,
+    54, 57, 58, 60, 71, 75, 77, 78, 83, 85, 86, 89, 90, 92, 99, 101, 102, 105, 106, 108, 113, 114, 116, 120, 135,
+    139, 141, 142, 147, 149, 150, 153, 154, 156, 163, 165, 166, 169, 170, 172, 177, 178, 180, 184, 195, 197, 198,
+    201, 202, 204, 209, 210, 212, 216, 225, 226, 228, 232, 240, 31, 47, 55, 59, 61, 62, 79, 87, 91, 93, 94, 103,
+    107, 109, 110, 115, 117, 118, 121, 122, 124, 143, 151, 155, 157, 158, 167, 171, 173, 174, 179, 181, 182, 185,
+    186, 188, 199, 203, 205, 206, 211, 213, 214, 217, 218, 220, 227, 229, 230, 233, 234, 236, 241, 242, 244, 248,
+    63, 95, 111, 119, 123, 125, 126, 159, 175, 183, 187, 189, 190, 207, 215, 219, 221, 222, 231, 235, 237, 238,
+    243, 245, 246, 249, 250, 252, 127, 191, 223, 239, 247, 251, 253, 254, 255};
+__constant__ uint8_t kPlanPopOff[9] = {0, 1, 9, 37, 93, 163, 219, 247, 255};
+__constant__ uint8_t kPlanBinom[9][9] = {
+    {1, 0, 0, 0, 0, 0, 0, 0, 0},
+    {1, 1, 0, 0, 0, 0, 0, 0, 0},
+    {1, 2, 1, 0, 0, 0, 0, 0, 0},
+    {1, 3, 3, 1, 0, 0, 0, 0, 0},
+    {1, 4, 6, 4, 1, 0, 0, 0, 0},
+    {1, 5, 10, 10, 5, 1, 0, 0, 0},
+    {1, 6, 15, 20, 15, 6, 1, 0, 0},
+    {1, 7, 21, 35, 35, 21, 7, 1, 0},
+    {1, 8, 28, 56, 70, 56, 28, 8, 1},
+};
+
+// cost: row-major with stride 8; dp[256], choice[256]: workspaces; col_of_row[n] receives the matching.
+__device__ __forceinline__ void assign_dp8(const double *cost, int n, double *dp, uint8_t *choice, int16_t *col_of_row) {
+    const int lane = threadIdx.x & 31;
+    if (lane == 0) dp[0] = 0.0;
+    __syncwarp();
+    for (int k = 1; k <= n; ++k) {
+        const int cnt = kPlanBinom[n][k], first = kPlanPopOff[k];
+        const double *crow = cost + (k - 1) * 8;
+        for (int idx = lane; idx < cnt; idx += 32) {
+            const unsigned mask = kPlanPopMask[first + idx];
+            double best = CUDART_INF;
+            int bj = 0;
+            for (unsigned m = mask; m; m &= m - 1) {  // k columns: the same trip count on every lane
+                const int j = __ffs(m) - 1;
+                const double val = dp[mask ^ (1u << j)] + crow[j];
+                if (val < best) { best = val; bj = j; }
             }
-            u64 kmin = key;
-#pragma unroll
-            for (int o = 4; o > 0; o >>= 1) {
-                const u64 other = __shfl_xor_sync(full, kmin, o);
-                kmin = other < kmin ? other : kmin;
-            }
-            const unsigned holders = (__ballot_sync(full, go && !used && key == kmin) >> base) & 0xffu;
-            int jn = 0;
-            if (go) {
-                const double delta = plan_dkey_inv(kmin);
-                if (col) {
-                    if (used) { uc += delta; v -= delta; }
-                    else minv -= delta;
-                }
-                u0 += delta;
-                jn = __ffs(holders);  // never 0 while the segment is searching: an unused column always exists
-            }
-            const int src = base + (jn > 0 ? jn - 1 : 0);
-            const int pn = __shfl_sync(full, p, src);
-            const double un = __shfl_sync(full, uc, src);
-            if (go) {
-                j0 = jn;
-                if ((freem >> (jn - 1)) & 1u) go = false;
-                else {
-                    if (lc == jn - 1) used = true;
-                    i0 = pn; ui0 = un;
-                }
-            }
+            dp[mask] = best;
+            choice[mask] = (uint8_t)bj;
         }
-        if (i <= n) freem &= ~(1u << (j0 - 1));
-        while (__any_sync(full, j0 != 0)) {  // flip the augmenting paths
-            const int j1 = __shfl_sync(full, way, base + (j0 > 0 ? j0 - 1 : 0));
-            const int s1 = base + (j1 > 0 ? j1 - 1 : 0);
-            const int pj1 = __shfl_sync(full, p, s1);
-            const double uj1 = __shfl_sync(full, uc, s1);
-            if (j0 != 0) {
-                if (lc == j0 - 1) { p = j1 == 0 ? i : pj1; uc = j1 == 0 ? u0 : uj1; }
-                j0 = j1;
-            }
+        __syncwarp();
+    }
+    if (lane == 0) {
+        unsigned mask = (1u << n) - 1u;
+        for (int r = n - 1; r >= 0; --r) {
+            const int j = choice[mask];
+            col_of_row[r] = (int16_t)j;
+            mask ^= 1u << j;
         }
     }
-    if (col && p) col_of_row[p - 1] = (int16_t)lc;
     __syncwarp();
 }
 
@@ -680,33 +680,26 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
     }
     __syncwarp();
     DCA_PROF(P, e, 7);
-    // ---- member -> slot (:171-173): teams of up to 8 go four at a time through the warp (assign_seg8), larger ones
-    // one at a time (up to 32 members entirely in registers, cost matrix precomputed up to 16)
+    // ---- member -> slot (:171-173): teams of up to 8 by subset DP (assign_dp8), larger ones by augmenting paths (up to 32
+    // members entirely in registers, cost matrix precomputed up to 16)
     {
-        const int sg = lane >> 3, lc = lane & 7;
         const double *ax = s.ax, *ay = s.ay;
-        for (int kk = 0;;) {  // warp-uniform scan for the next four small teams
-            int myk = -1, c4 = 0;
-            for (; kk < K && c4 < 4; ++kk) {
-                const int nm = s.cnt[kk];
-                if (nm >= 1 && nm <= kPlanTeamPre) {
-                    if (c4 == sg) myk = kk;
-                    ++c4;
-                }
-            }
-            if (c4 == 0) break;
-            const int nm = myk >= 0 ? s.cnt[myk] : 0, off = myk >= 0 ? s.toff[myk] : 0;
-            double *cs = s.cw + sg * kPlanTeamPre * kPlanTeamPre;
-            if (lc < nm) {
-                const double sxj = s.sx[off + lc], syj = s.sy[off + lc];
-                for (int r = 0; r < nm; ++r) {
+        // small teams, one after the other: the n x n distances (two entries per lane), then the subset DP
+        for (int kk = 0; kk < K; ++kk) {  // warp-uniform
+            const int nm = s.cnt[kk];
+            if (nm < 1 || nm > kPlanTeamPre) continue;
+            const int off = s.toff[kk];
+#pragma unroll
+            for (int q = lane; q < 64; q += 32) {
+                const int r = q >> 3, j = q & 7;
+                if (r < nm && j < nm) {
                     const int a = s.mem[off + r];
-                    const double dx = ax[a] - sxj, dy = ay[a] - syj;
-                    cs[r * 8 + lc] = sqrt(dx * dx + dy * dy);
+                    const double dx = ax[a] - s.sx[off + j], dy = ay[a] - s.sy[off + j];
+                    s.cq[q] = sqrt(dx * dx + dy * dy);
                 }
             }
             __syncwarp();
-            assign_seg8(cs, nm, s.hcol + off);
+            assign_dp8(s.cq, nm, s.dp, s.dpc, s.hcol + off);
         }
         for (int kk = 0; kk < K; ++kk) {  // warp-uniform
             const int nm = s.cnt[kk];

@@ -23,6 +23,7 @@ def main(last=100, window=20, E=4096):
     g.manual_seed(0)
     prof = torch.zeros((E, 16), dtype=torch.int64, device=env.device)
     acc = np.zeros(9)
+    life, span, tail = [], [], []
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     ms = 0.0
     for t in range(last):
@@ -39,10 +40,23 @@ def main(last=100, window=20, E=4096):
             ms += ev[0].elapsed_time(ev[1])
             c = prof.cpu().numpy().astype(np.float64)
             acc += np.diff(c[:, :10], axis=1).mean(0)
+            life.append(c[:, 9] - c[:, 0])
+            span.append(c[:, 9].max() - c[:, 0].min())
+            if t == last - 1:
+                d = np.diff(c[:, :10], axis=1)
+                worst = np.argsort(-life[-1])[:5]
+                for w in worst:
+                    tail.append('env %4d lifetime %7.0f: ' % (w, life[-1][w]) + ' '.join('%6.0f' % x for x in d[w]))
     acc /= window
     for n, v in zip(NAMES, acc):
         print('%-26s %9.0f cycles  %5.1f%%' % (n, v, 100 * v / acc.sum()))
     print('CTA lifetime %.0f cycles, k_plan %.3f ms per launch' % (acc.sum(), ms / window))
+    lf = np.concatenate(life)
+    print('lifetime percentiles (cycles): p50 %.0f  p90 %.0f  p99 %.0f  max %.0f; first start -> last end per launch %.0f'
+          % (np.percentile(lf, 50), np.percentile(lf, 90), np.percentile(lf, 99), lf.max(), np.mean(span)))
+    print('slowest envs of the last launch (phase cycles: ' + ', '.join(NAMES) + ')')
+    for l in tail:
+        print(l)
 
 
 if __name__ == '__main__':
