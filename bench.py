@@ -221,6 +221,66 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
+def policy_rollout_run(E, dev, rank, world, steps=60, warm=10):
+    """BASELINE.json configs[3] on the device end to end: RESULT/50RL-55opp -- 50 guards
+    driven by the shipped conc_4hist policy (sampled actions) against 55 scripted attackers: k_histpool -> DynamicNorm
+    kernels + torch Net -> k_plan + k_step -> rollout buffer, then k_gae + advantage normalisation over the buffer.
+    Nothing crosses PCIe inside the loop.  The checkpoint comes from tests/golden/policy_net_4hist.npz (the state dict
+    of RESULT/50RL-55opp/model.pt as arrays, written by oracle/make_golden_policy.py)."""
+    import torch
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.policy import ConcNet4Hist, PolicyRollout
+    from hmp2g_b200.vec_env import DcaVecEnv
+    path = os.path.join(REPO, 'tests', 'golden', 'policy_net_4hist.npz')
+    if not os.path.exists(path):
+        return None
+    z = np.load(path)
+    net = ConcNet4Hist(rawob_dim=16, n_action=7, n_focus_on=3)
+    net.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith('sd/')})
+    net = net.to(dev).train()
+    wl = dict(WORKLOAD, **SCENARIOS['50v55'])
+    scfg = type('BenchScenarioConfig_policy', (ScenarioConfig,), wl)
+    env = DcaVecEnv(E, scfg=scfg, device=dev, seed=SEED, env_gid0=rank * E, empty_rows_nan=True)
+    roll = PolicyRollout(env, net, gamma=0.99, tau=0.95, gamma_fwd=0.95, seed=SEED + rank)
+    stream = torch.cuda.current_stream(dev)
+    for _ in range(warm):
+        roll.step()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0.record(stream)
+    for _ in range(steps):
+        roll.step()
+    t1.record(stream)
+    torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / steps
+    # the policy forward alone (history roll + normalisation + Net.act) on the last observation
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record(stream)
+    for _ in range(5):
+        feed = roll.hist.roll(roll.obs, suffered_reset=roll.suffered)
+        net.act(feed, generator=roll.gen)
+    p1.record(stream)
+    torch.cuda.synchronize()
+    ms_policy = p0.elapsed_time(p1) / 5
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record(stream)
+    ret, threat, adv, valid = roll.buf.finalize(None)   # every env's (truncated) trajectory: GAE + normalised advantage
+    g1.record(stream)
+    torch.cuda.synchronize()
+    out = {'workload': 'RESULT/50RL-55opp: DCA 50 guards (conc_4hist policy, shipped model.pt, sampled actions) vs 55 '
+                       'scripted attackers (k_plan), %d envs/GPU, device-resident loop' % E,
+           'value': world * E * env.N / (ms * 1e-3), 'unit': 'agent-steps/s', 'ms_per_step': ms,
+           'policy_ms': ms_policy, 'env_ms': ms - ms_policy, 'steps': steps,
+           'gae_and_advantage_ms': g0.elapsed_time(g1), 'rollout_buffer_TEG': list(roll.buf.reward.shape),
+           'episodes_finished': int(roll.episodes.item()), 'wins': int(roll.wins.item()),
+           'policy': 'torch fp32 (cuBLAS) Net of hmp2g_b200/policy.py; normalisation moments / apply, history roll, '
+                     'planner, step, GAE: this library',
+           'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}
+    del roll, env, net
+    torch.cuda.empty_cache()
+    return out
+
+
 def quick_config_run(name, E, dev, rank, steps=360, warm=40):
     """BASELINE.json configs[2] / [3] (100v100, 50v55) at the same env count: step+obs+autoreset with the centroid
     stand-in (value) and k_step alone per launch over two episodes (kernel_ms, roofline fraction), plus k_plan."""
@@ -366,6 +426,19 @@ def run_ours(args):
     overlap = 0 if args.no_overlap else 1
     lib.dca_set_option(h, 2, overlap)
     env.reset()
+    # Pre-roll (set-up, untimed): env e is advanced by a random number of steps in [0, MaxEpisodeStep) -- it sits out
+    # (ENV-PAUSE mask) the first MaxEpisodeStep - offset[e] of MaxEpisodeStep steps -- so the timed steps sample the
+    # stationary mix of episode phases of a long-running job instead of steps W..W+K of 4096 synchronised first
+    # episodes (a driver run of 20 steps would otherwise sit entirely in the most expensive phase, where the teams
+    # meet).  --no-preroll times the synchronised start.
+    preroll = 0 if args.no_preroll else int(WORKLOAD.get('MaxEpisodeStep', 180))
+    if preroll:
+        offs = torch.randint(0, preroll, (E,), generator=gen, device=dev)
+        for s in range(preroll):
+            skip = (offs < (preroll - s)).to(torch.uint8)
+            plan_call(h, fptr, sptr)
+            assert lib.dca_step(h, aptrs[s % n_pool], fptr, C.c_void_p(skip.data_ptr()), None, 1, sptr) == 0
+        torch.cuda.synchronize()
     launches0 = env.kernel_launches()
     for i in range(W):
         assert one_step(i) == 0
@@ -528,6 +601,25 @@ def run_ours(args):
         for name in ('100v100', '50v55'):
             other[name] = quick_config_run(name, E, dev, rank)
     coll = collective_timings(E, G, dev, world) if world > 1 else None
+    policy_line = None
+    if args.scenario == '50v50' and not args.no_other_configs:
+        policy_line = policy_rollout_run(E, dev, rank, world)
+    # ---- k_step from a synchronised reset (what a 20-step run measured before the pre-roll existed): steps 5..25 of
+    # 4096 first episodes in lock-step, the most expensive phase (the teams meet)
+    env.reset()
+    lib.dca_set_option(h, 2, 0)
+    for i in range(5):
+        plan_call(h, fptr, sptr)
+        lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
+    ss = [torch.cuda.Event(enable_timing=True) for _ in range(20)]
+    se = [torch.cuda.Event(enable_timing=True) for _ in range(20)]
+    for i in range(20):
+        plan_call(h, fptr, sptr)
+        ss[i].record(stream)
+        lib.dca_step(h, aptrs[(5 + i) % n_pool], fptr, None, None, 1, sptr)
+        se[i].record(stream)
+    torch.cuda.synchronize()
+    ms_step_sync_start = sum(ss[i].elapsed_time(se[i]) for i in range(20)) / 20
 
     # ---- e2e: the reference-facing call (SuperpoolEnv.step surface) with HOST buffers, copies inside the timed region
     del env
@@ -587,6 +679,8 @@ def run_ours(args):
                                   'scripted formation planner k_plan in the timed region',
                                   '' if args.scenario == '50v50' else ' at another team size'),
                    'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD, 'overlap_planner': bool(overlap),
+                   'pre_roll': ('each env advanced by a random number of steps in [0, %d) before warm-up (untimed set-up): '
+                                'stationary mix of episode phases' % preroll) if preroll else 'none: synchronised reset',
                    'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
                          '> 126 MB L2' % ((E * (G * 768 + 2 * 5760)) / 1e6, E * G * 768 / 1e6, 2 * E * 5760 / 1e6),
                    'policy_agent_steps_per_sec': value * G / N, 'planner_kernel_ms': ms_plan,
@@ -598,6 +692,8 @@ def run_ours(args):
                                          'timed region (same episodes; launched stand-alone: in the timed region the '
                                          'kernel starts under the planner stand-in, DCA_OPT_OVERLAP_PLANNER)' % Kfirst,
                      'kernel_ms_episode_avg': ms_step_kernel_episode, 'episode_avg_steps': Kk,
+                     'kernel_ms_synchronised_start': ms_step_sync_start,
+                     'frac_synchronised_start': algo_bytes / (ms_step_sync_start * 1e-3) / 1e9 / peak,
                      'frac_episode_avg': algo_bytes / (ms_step_kernel_episode * 1e-3) / 1e9 / peak,
                      'dram_frac': dram_frac(ncu, 'k_step', ms_step_kernel_episode, peak, E, args.scenario),
                      'traffic_source': ncu.get('source')},
@@ -626,6 +722,7 @@ def run_ours(args):
                                     'obs/reward/done/info out)'},
         'with_scripted_planner': scripted,
         'other_configs': other,
+        'policy_rollout_50v55': policy_line,
         'collectives': coll,
         'gpu_launches': gpu_launches,
         'clocks': clocks,
@@ -670,6 +767,8 @@ def main():
     ap.add_argument('--no-other-configs', action='store_true', help='skip the 100v100 / 50v55 report lines')
     ap.add_argument('--planner', default='centroid', choices=['centroid', 'scripted'],
                     help='attacker forces: the centroid stand-in of configs[1] (default) or the scripted formation planner k_plan')
+    ap.add_argument('--no-preroll', action='store_true',
+                    help='time from a synchronised reset of all envs instead of the stationary episode-phase mix')
     ap.add_argument('--no-overlap', action='store_true',
                     help='launch the step kernel strictly after the planner stand-in (DCA_OPT_OVERLAP_PLANNER off)')
     ap.add_argument('--traffic', type=float, default=None,

@@ -15,6 +15,7 @@
 #include "dca_runner.cuh"
 #include "dca_histpool.cuh"
 #include "dca_multiteam.cuh"
+#include "dca_policy.cuh"
 
 using namespace dca;
 
@@ -463,6 +464,35 @@ int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid
                                                                              (size_t)n, stats, adv);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_adv_normalize: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_norm_moments(const float *x, uint64_t rows, int dim, double *scratch, double *stats, dca_stream_t stream) {
+    if (!x || !scratch || !stats || rows == 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_norm_moments: null buffer or empty batch");
+    if (dim != kNormDim || ((uintptr_t)x & 15))
+        return fail(nullptr, DCA_E_INVALID, "dca_norm_moments: rows must be 16 floats (obs_vec_length) and 16-byte aligned");
+    PtrDeviceGuard guard(x);
+    cudaStream_t st = (cudaStream_t)stream;
+    k_norm_partial<<<kNormBlocks, kNormThreads, 0, st>>>((const float4 *)x, (size_t)rows, scratch);
+    k_norm_final<<<1, 64, 0, st>>>(scratch, stats);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_norm_moments: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
+int dca_norm_apply(const float *x, const float *mean, const float *var, uint64_t rows, int dim, float *y,
+                   uint8_t *row_nan, dca_stream_t stream) {
+    if (!x || !mean || !var || !y || !row_nan || rows == 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_norm_apply: null buffer or empty batch");
+    if (dim != kNormDim || (((uintptr_t)x | (uintptr_t)y | (uintptr_t)mean | (uintptr_t)var) & 15))
+        return fail(nullptr, DCA_E_INVALID, "dca_norm_apply: rows must be 16 floats (obs_vec_length), buffers 16-byte aligned");
+    PtrDeviceGuard guard(x);
+    const size_t blocks = std::min<size_t>((rows * 4 + 255) / 256, 148 * 16);
+    k_norm_apply<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const float4 *)x, mean, var, (size_t)rows, (float4 *)y,
+                                                                    row_nan);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_norm_apply: ") + cudaGetErrorString(e));
     return DCA_OK;
 }
 

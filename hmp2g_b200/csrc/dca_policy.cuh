@@ -1,0 +1,117 @@
+// dca_policy.cuh -- observation normalisation for the conc / conc_4hist policy rollout on device tensors
+// (SURVEY.md section 8 row f2).  DynamicNorm ALGORITHM/common/norm.py:14-69 (paths relative to /root/reference):
+//   training: running mean / variance over the rows of the batch that hold no NaN (exclude_nan), merged with the stored
+//             moments by the parallel-variance formula; features that only ever took the values -1 / 0 / 1 keep their
+//             initial (0, 1) moments (exclude_one_hot);
+//   always:   x <- clip((x - mean) / sqrt(var + 1e-8), -10, 10); Net._act then takes mask = isnan(x).any(-1) and
+//             x <- nan_to_num(x, 0) (ALGORITHM/conc_4hist/net.py:196-198).
+// Here: one pass that reduces (sum x, sum x^2, #values outside {-1,0,1}) per feature and the row count in fp64 with a
+// fixed order (per-CTA partials, then one CTA) -- across GPUs the caller all-reduces those 49 doubles, which is the
+// "(sum x, sum x^2, n)" merge SURVEY.md section 8(e) names -- and one pass that applies the stored moments, writes the
+// row mask and zeroes the NaNs.  Rows are 16 floats (ScenarioConfig.obs_vec_length, parallel_run.py:70): a lane quad owns
+// a row, one float4 per lane, so a warp reads 512 contiguous bytes per step.
+#pragma once
+#include "dca_device.cuh"
+
+namespace dca {
+
+constexpr int kNormBlocks = 592, kNormThreads = 256, kNormDim = 16, kNormStats = 3 * kNormDim + 1;
+
+__device__ __forceinline__ bool norm_unit(float v) { return v == 0.f || v == 1.f || v == -1.f; }
+
+__global__ void __launch_bounds__(kNormThreads) k_norm_partial(const float4 *__restrict__ x, size_t rows,
+                                                               double *__restrict__ partial) {
+    __shared__ double sh[kNormThreads / 32][4][13];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, quad = lane & 3;
+    const unsigned full = 0xffffffffu;
+    double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0}, nu[4] = {0, 0, 0, 0}, cnt = 0;
+    const size_t rows_per_pass = (size_t)kNormBlocks * kNormThreads / 4;
+    const size_t first = ((size_t)blockIdx.x * kNormThreads + (tid & ~31)) / 4;  // first row of this warp
+    for (size_t base = first; base < rows; base += rows_per_pass) {               // warp-uniform
+        const size_t row = base + (lane >> 2);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        bool bad = true;
+        if (row < rows) {
+            v = x[row * 4 + quad];
+            bad = (v.x != v.x) || (v.y != v.y) || (v.z != v.z) || (v.w != v.w);
+        }
+        const unsigned b = __ballot_sync(full, bad);
+        if ((b >> (lane & ~3)) & 0xfu) continue;  // exclude_nan: a row with any NaN contributes nothing
+        const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const double d = (double)e[k];
+            s[k] += d; q[k] += d * d;
+            if (!norm_unit(e[k])) nu[k] += 1.0;
+        }
+        if (quad == 0) cnt += 1.0;
+    }
+    // lanes with the same quad hold the same four features: fold lane bits 2..4
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            s[k] += __shfl_xor_sync(full, s[k], o);
+            q[k] += __shfl_xor_sync(full, q[k], o);
+            nu[k] += __shfl_xor_sync(full, nu[k], o);
+        }
+        cnt += __shfl_xor_sync(full, cnt, o);
+    }
+    if (lane < 4) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { sh[warp][lane][k] = s[k]; sh[warp][lane][4 + k] = q[k]; sh[warp][lane][8 + k] = nu[k]; }
+        sh[warp][lane][12] = cnt;
+    }
+    __syncthreads();
+    if (tid < kNormStats) {  // stats layout: sum[16], sumsq[16], nonunit[16], count
+        const int grp = tid / kNormDim, f = tid % kNormDim;
+        double a = 0;
+        for (int w = 0; w < kNormThreads / 32; ++w)
+            a += tid == 3 * kNormDim ? sh[w][0][12] : sh[w][f >> 2][grp * 4 + (f & 3)];
+        partial[(size_t)blockIdx.x * kNormStats + tid] = a;
+    }
+}
+
+__global__ void __launch_bounds__(64) k_norm_final(const double *__restrict__ partial, double *__restrict__ stats) {
+    const int t = threadIdx.x;
+    if (t >= kNormStats) return;
+    double a = 0;
+    for (int b = 0; b < kNormBlocks; ++b) a += partial[(size_t)b * kNormStats + t];
+    stats[t] = a;
+}
+
+// y = nan_to_num(clip((x - mean) / sqrt(var + 1e-8), -10, 10), 0), row_nan[r] = any NaN in row r.  In place when y == x.
+__global__ void __launch_bounds__(256) k_norm_apply(const float4 *x, const float *__restrict__ mean,
+                                                    const float *__restrict__ var, size_t rows, float4 *y,
+                                                    uint8_t *__restrict__ row_nan) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, quad = lane & 3;
+    const float4 m = ((const float4 *)mean)[quad], vv = ((const float4 *)var)[quad];
+    const float sd[4] = {__fsqrt_rn(__fadd_rn(vv.x, 1e-8f)), __fsqrt_rn(__fadd_rn(vv.y, 1e-8f)),
+                         __fsqrt_rn(__fadd_rn(vv.z, 1e-8f)), __fsqrt_rn(__fadd_rn(vv.w, 1e-8f))};
+    const float mu[4] = {m.x, m.y, m.z, m.w};
+    const size_t rows_per_pass = (size_t)gridDim.x * blockDim.x / 4;
+    const size_t first = ((size_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) / 4;
+    for (size_t base = first; base < rows; base += rows_per_pass) {  // warp-uniform
+        const size_t row = base + (lane >> 2);
+        const bool in = row < rows;
+        float e[4] = {0.f, 0.f, 0.f, 0.f};
+        if (in) {
+            const float4 v = x[row * 4 + quad];
+            e[0] = v.x; e[1] = v.y; e[2] = v.z; e[3] = v.w;
+        }
+        bool bad = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (e[k] != e[k]) { bad = true; e[k] = 0.f; }
+            else e[k] = fminf(fmaxf(__fdiv_rn(__fsub_rn(e[k], mu[k]), sd[k]), -10.f), 10.f);
+        }
+        const unsigned b = __ballot_sync(full, bad);
+        if (in) {
+            y[row * 4 + quad] = make_float4(e[0], e[1], e[2], e[3]);
+            if (quad == 0) row_nan[row] = ((b >> lane) & 0xfu) != 0;
+        }
+    }
+}
+
+}  // namespace dca

@@ -58,9 +58,6 @@ class MtScenarioConfig(object):
 
 def pod_mt_config(scfg, seed=0, env_gid0=0):
     sizes = list(scfg.N_AGENT_EACH_TEAM)
-    if getattr(scfg, 'RewardAsUnity', False) or getattr(scfg, 'ObsAsUnity', False):
-        raise _lib.DcaError('dca_multiteam on the GPU implements the per-agent reward / observation mode '
-                            '(RewardAsUnity = ObsAsUnity = False, the defaults)')
     c = _lib.DcaMtConfig()
     c.n_team = len(sizes)
     if c.n_team > 8:
@@ -97,6 +94,12 @@ class DcaMultiTeamVecEnv(object):
         self.team_size = [self.cfg.team_size[i] for i in range(self.n_team)]
         self.N = sum(self.team_size)
         self.agent_id_each_team = arrange_id(self.team_size)
+        # team-level interface (collective_assault_parallel_run.py:166-186): RewardAsUnity -> one reward per team, 0
+        # (sparse_reward, envs/collective_assault_env.py:77-78) plus the ranking bonus on done (_get_done :245-266);
+        # ObsAsUnity -> only agent 0's observation is handed out.  The kernel computes the per-agent quantities either
+        # way (the keyed observation draws of agent 0 do not depend on the others being observed).
+        self.reward_as_unity = bool(getattr(scfg, 'RewardAsUnity', False))
+        self.obs_as_unity = bool(getattr(scfg, 'ObsAsUnity', False))
         self.handle = C.c_void_p()
         _lib.check(self.lib.dca_mt_create(C.byref(self.cfg), self.E, self.device.index, C.byref(self.handle)))
         E, N, dev = self.E, self.N, self.device
@@ -132,16 +135,33 @@ class DcaMultiTeamVecEnv(object):
         if env_mask is not None:
             self._check(env_mask, torch.uint8, (self.E,), 'env_mask')
         _lib.check(self.lib.dca_mt_reset(self.handle, _ptr(env_mask), self._stream()))
-        return self.obs
+        return self.obs_out()
+
+    def obs_out(self):
+        """What the env hands out as observation: every agent's, or agent 0's alone under ObsAsUnity."""
+        return self.obs[:, :1] if self.obs_as_unity else self.obs
+
+    def tobs_out(self):
+        return self.tobs[:, :1] if self.obs_as_unity else self.tobs
+
+    def reward_out(self):
+        """Per-agent reward f32 [E,N], or under RewardAsUnity f32 [E,n_team]: (n_team - 1 - rank) * 10 for a ranked team,
+        -10 when every team draws (rank -1), on the step that ends the episode; 0 otherwise."""
+        if not self.reward_as_unity:
+            return self.reward
+        rank = self.ranking.to(torch.float32)
+        bonus = torch.where(rank >= 0, (self.n_team - 1 - rank) * 10.0, torch.full_like(rank, -10.0))
+        return torch.where((self.done != 0)[:, None], bonus, torch.zeros_like(bonus))
 
     def step(self, actions, skip=None, autoreset=True):
         """actions int32 [E,N] (one of 0..6 per agent, all teams); skip uint8 [E].
-        Returns (obs f32 [E,N,12,17], reward f32 [E,N], done u8 [E], ranking i32 [E,n_team]) -- views, written in place."""
+        Returns (obs f32 [E,N,12,17], reward f32 [E,N], done u8 [E], ranking i32 [E,n_team]) -- views, written in place
+        (ObsAsUnity: obs [E,1,12,17]; RewardAsUnity: reward [E,n_team], a fresh tensor)."""
         self._check(actions, torch.int32, (self.E, self.N), 'actions')
         if skip is not None:
             self._check(skip, torch.uint8, (self.E,), 'skip')
         _lib.check(self.lib.dca_mt_step(self.handle, _ptr(actions), _ptr(skip), int(bool(autoreset)), self._stream()))
-        return self.obs, self.reward, self.done, self.ranking
+        return self.obs_out(), self.reward_out(), self.done, self.ranking
 
     _SPEC = (('pos', torch.float64, 2), ('vel', torch.float64, 2), ('atk_rad', torch.float64, 0),
              ('terrain', torch.float64, 0), ('alive', torch.uint8, 0), ('just_died', torch.uint8, 0),
@@ -191,9 +211,11 @@ class DcaMultiTeamSuperpoolEnv(object):
         self._h_skip = torch.zeros((E,), dtype=torch.uint8, **pin)
         self._d_act = torch.zeros((E, N), dtype=torch.int32, device=self.env.device)
         self._d_skip = torch.zeros((E,), dtype=torch.uint8, device=self.env.device)
-        self._h_obs_pair = [torch.zeros((E, N, 204), dtype=torch.float32, **pin) for _ in range(2)]
+        n_obs = 1 if self.env.obs_as_unity else N
+        n_rew = self.env.n_team if self.env.reward_as_unity else N
+        self._h_obs_pair = [torch.zeros((E, n_obs, 204), dtype=torch.float32, **pin) for _ in range(2)]
         self._flip = 0
-        self._h_rew = torch.zeros((E, N), dtype=torch.float32, **pin)
+        self._h_rew = torch.zeros((E, n_rew), dtype=torch.float32, **pin)
         self._h_done = torch.zeros((E,), dtype=torch.uint8, **pin)
         self._h_rank = torch.zeros((E, self.env.n_team), dtype=torch.int32, **pin)
         self._info = np.empty((E,), dtype=object)
@@ -210,8 +232,8 @@ class DcaMultiTeamSuperpoolEnv(object):
         env = self.env
         self._flip ^= 1
         self._h_obs = self._h_obs_pair[self._flip]
-        self._h_obs.copy_(env.obs.view(env.E, env.N, -1), non_blocking=True)
-        self._h_rew.copy_(env.reward, non_blocking=True)
+        self._h_obs.copy_(env.obs_out().reshape(env.E, -1, 204), non_blocking=True)
+        self._h_rew.copy_(env.reward_out(), non_blocking=True)
         self._h_done.copy_(env.done, non_blocking=True)
         self._h_rank.copy_(env.ranking, non_blocking=True)
         torch.cuda.current_stream(env.device).synchronize()
@@ -251,7 +273,7 @@ class DcaMultiTeamSuperpoolEnv(object):
         idx_done = np.nonzero(stepped & done)[0]
         if len(idx_done):
             sel = torch.from_numpy(idx_done).to(env.device)
-            tobs = env.tobs.view(env.E, env.N, -1)[sel].cpu().numpy()
+            tobs = env.tobs_out().reshape(env.E, -1, 204)[sel].cpu().numpy()
             rank = self._h_rank.numpy()
             for k, i in enumerate(idx_done):
                 info[i] = {'team_ranking': rank[i].astype(np.int64).copy(), 'end_reason': 'EndGame', 'obs-echo': tobs[k]}

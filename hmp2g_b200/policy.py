@@ -1,0 +1,250 @@
+"""The conc_4hist policy rollout on device tensors (BASELINE.json configs[3]).
+
+Host-side mirror of what the reference runs between two env steps when a conc_4hist team drives DCA
+(paths relative to /root/reference):
+
+  ShellEnvWrapper.interact_with_env   ALGORITHM/conc_4hist/shell_env.py:25-99   -> hmp2g_b200.rollout.HistoryPool (k_histpool)
+  Net._act / Net.act                  ALGORITHM/conc_4hist/net.py:163-233       -> ConcNet4Hist.act (below)
+  DynamicNorm.forward                 ALGORITHM/common/norm.py:31-69            -> DynamicNormDevice (dca_norm_moments /
+                                                                                    dca_norm_apply + the merge)
+  Concentration.forward               ALGORITHM/common/conc.py:28-63            -> ConcCore
+  Categorical(logits).sample()        ALGORITHM/conc_4hist/net.py:141-153       -> on the device, no numpy hop
+  trajectory / GAE                    ALGORITHM/conc_4hist/trajectory.py         -> hmp2g_b200.rollout.DeviceRollout (k_gae)
+
+The network is the reference's torch network: same parameter names, shapes and dtypes, so a shipped checkpoint
+(`RESULT/50RL-55opp/model.pt`, `torch.save(policy.state_dict())` foundation.py:171) loads with `load_state_dict`.  The
+module definitions are this repo's own: the attention scores and the attended value are formed without projecting every
+entity (q' = (vs Wq) Wk^T, compat = ve . q'; Va = (score ve) Wv -- the same numbers up to float32 rounding), which cuts
+two of the three [rows, 48] x [48, 48] products over the 24 entities of every agent.  PyTorch is the policy's home in the
+reference too (cuBLAS GEMMs); the env / history / normalisation / GAE kernels around it are this library's.
+"""
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class DynamicNormDevice(nn.Module):
+    """DynamicNorm(input_size, only_for_last_dim=True, exclude_one_hot=True, exclude_nan=True), norm.py:14-69.
+    Parameters as in the reference (mean, var float32 [D]; n_sample int64 [1]; one_hot_filter bool [D])."""
+
+    def __init__(self, input_size=16, group=None):
+        super().__init__()
+        self.input_size = input_size
+        self.mean = nn.Parameter(torch.zeros(input_size), requires_grad=False)
+        self.var = nn.Parameter(torch.ones(input_size), requires_grad=False)
+        self.n_sample = nn.Parameter(torch.zeros(1, dtype=torch.long), requires_grad=False)
+        self.one_hot_filter = nn.Parameter(torch.ones(input_size, dtype=torch.bool), requires_grad=False)
+        self.group = group  # torch.distributed group for the moments all-reduce (None = default group if initialised)
+        self._scratch = None
+
+    def batch_stats(self, x):
+        """(sum x[D], sum x^2[D], values outside {-1,0,1}[D], rows) over the rows of x without NaN: f64 [3D+1] on the device."""
+        lib = _lib.load()
+        x2 = x.reshape(-1, self.input_size)
+        assert x2.is_cuda and x2.dtype == torch.float32 and x2.is_contiguous()
+        if self._scratch is None or self._scratch.device != x2.device:
+            self._scratch = torch.empty(592 * 49, dtype=torch.float64, device=x2.device)
+        stats = torch.empty(49, dtype=torch.float64, device=x2.device)
+        stream = C.c_void_p(torch.cuda.current_stream(x2.device).cuda_stream)
+        _lib.check(lib.dca_norm_moments(_ptr(x2), x2.shape[0], self.input_size, _ptr(self._scratch), _ptr(stats), stream))
+        return stats
+
+    @torch.no_grad()
+    def update(self, x):
+        """The training-mode half of DynamicNorm.forward (norm.py:47-63) from the batch statistics; with
+        torch.distributed initialised the statistics of all ranks are summed first (one all-reduce of 49 doubles)."""
+        D = self.input_size
+        stats = self.batch_stats(x)
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            torch.distributed.all_reduce(stats, group=self.group)
+        return self.merge(stats)
+
+    @torch.no_grad()
+    def merge(self, stats):
+        D = self.input_size
+        s, q, nonunit, n = stats[:D], stats[D:2 * D], stats[2 * D:3 * D], stats[3 * D]
+        nb = torch.clamp(n, min=1.0)
+        b_mean = s / nb
+        b_var = torch.clamp(q / nb - b_mean * b_mean, min=0.0)     # torch.var(unbiased=False)
+        n0 = self.n_sample.to(torch.float64)
+        tot = n0 + n
+        mean0, var0 = self.mean.to(torch.float64), self.var.to(torch.float64)
+        delta = b_mean - mean0
+        new_mean = mean0 + delta * n / torch.clamp(tot, min=1.0)
+        m2 = var0 * n0 + b_var * n + delta * delta * n0 * n / torch.clamp(tot, min=1.0)
+        new_var = torch.clamp(m2 / torch.clamp(tot, min=1.0), min=0.01, max=1000.0)
+        some = n > 0                                                # an empty batch changes nothing (norm.py:41-44)
+        filt = self.one_hot_filter & ~((nonunit > 0) & some)
+        self.one_hot_filter.data = filt
+        keep = filt | ~some
+        self.mean.data = torch.where(keep, self.mean, new_mean.to(torch.float32))
+        self.var.data = torch.where(keep, self.var, new_var.to(torch.float32))
+        self.n_sample.data = (n0 + n).round().to(torch.long).reshape(1)
+        return self
+
+    def apply_norm(self, x, out=None):
+        """-> (normalised x with NaN -> 0, row mask uint8 = isnan(x).any(-1)); out may be x itself."""
+        lib = _lib.load()
+        shape = x.shape
+        x2 = x.reshape(-1, self.input_size)
+        assert x2.is_cuda and x2.dtype == torch.float32 and x2.is_contiguous()
+        y = torch.empty_like(x2) if out is None else out.reshape(-1, self.input_size)
+        mask = torch.empty((x2.shape[0],), dtype=torch.uint8, device=x2.device)
+        stream = C.c_void_p(torch.cuda.current_stream(x2.device).cuda_stream)
+        _lib.check(lib.dca_norm_apply(_ptr(x2), _ptr(self.mean.data), _ptr(self.var.data), x2.shape[0], self.input_size,
+                                      _ptr(y), _ptr(mask), stream))
+        return y.reshape(shape), mask.reshape(shape[:-1])
+
+    def forward(self, x):
+        if self.training:
+            self.update(x)
+        return self.apply_norm(x)
+
+
+class ConcCore(nn.Module):
+    """Concentration(n_focus_on, h_dim, skip_connect=True, skip_connect_dim), ALGORITHM/common/conc.py:7-63."""
+
+    def __init__(self, n_focus_on, h_dim, skip_connect_dim):
+        super().__init__()
+        self.n_focus_on = n_focus_on
+        self.h_dim = h_dim
+        self.CT_W_query = nn.Parameter(torch.empty(h_dim, h_dim))
+        self.CT_W_key = nn.Parameter(torch.empty(h_dim, h_dim))
+        self.CT_W_val = nn.Parameter(torch.empty(h_dim, h_dim))
+        self.CT_motivate_mlp = nn.Sequential(nn.Linear(h_dim * 2, h_dim), nn.ReLU(inplace=True))
+        self.AT_forward_mlp = nn.Sequential(nn.Linear((n_focus_on + 1) * (h_dim + skip_connect_dim), h_dim),
+                                            nn.ReLU(inplace=True))
+        for p in self.parameters():  # conc.py:23-26
+            stdv = 1. / math.sqrt(p.size(-1))
+            p.data.uniform_(-stdv, stdv)
+
+    def forward(self, vs, ve, ve_dead, ze, zs):
+        """vs [B,h], ve [B,n,h], ve_dead bool [B,n], ze [B,n,d], zs [B,d] -> (v_C [B,h], v_M [B,h])."""
+        qk = (vs @ self.CT_W_query) @ self.CT_W_key.t()                       # [B,h]
+        compat = torch.einsum('bnh,bh->bn', ve, qk) * (1.0 / math.sqrt(self.h_dim))
+        compat = compat.masked_fill(ve_dead, -math.inf)
+        score = torch.nan_to_num(torch.softmax(compat, dim=-1), 0.0)          # no live entity: all zero (conc.py:39-41)
+        va = torch.einsum('bn,bnh->bh', score, ve) @ self.CT_W_val
+        v_m = self.CT_motivate_mlp(torch.cat((vs, va), -1))
+        # The attention is often so peaked that float32 softmax gives several live entities a score of exactly 0, tied
+        # with the masked ones; torch.argsort's order among equal scores is unspecified (and differs between the CPU
+        # and the CUDA sort), so the reference's pick is implementation-defined there.  Stable order = lowest entity
+        # index first, which is what the reference computes on the CPU.
+        idx = torch.argsort(score, dim=-1, descending=True, stable=True)[..., :self.n_focus_on]
+        pv = torch.gather(ve, 1, idx.unsqueeze(-1).expand(-1, -1, ve.shape[-1]))   # gather first, concatenate the few
+        pz = torch.gather(ze, 1, idx.unsqueeze(-1).expand(-1, -1, ze.shape[-1]))
+        stack = torch.cat((torch.cat((vs, zs), -1).unsqueeze(1), torch.cat((pv, pz), -1)), 1)  # [B, n_focus_on + 1, h + d]
+        v_c = self.AT_forward_mlp(stack.reshape(stack.shape[0], -1))
+        return v_c, v_m
+
+
+class ConcNet4Hist(nn.Module):
+    """Net(rawob_dim=16, n_action=7, n_focus_on, dual_conc=True) of ALGORITHM/conc_4hist/net.py:87-233 for the rollout
+    (`act`): 24 entities per agent = self, 11 current, 12 from the history pool (div_entity :170-181)."""
+
+    H = 48
+
+    def __init__(self, rawob_dim=16, n_action=7, n_focus_on=3, group=None):
+        super().__init__()
+        h = self.H
+        self.rawob_dim, self.n_action, self.n_focus_on = rawob_dim, n_action, n_focus_on
+        self._batch_norm = DynamicNormDevice(rawob_dim, group=group)
+        self.AT_obs_encoder = nn.Sequential(nn.Linear(rawob_dim, h), nn.ReLU(inplace=True), nn.Linear(h, h))
+        self.MIX_conc_core_f = ConcCore(n_focus_on - 1, h, rawob_dim)
+        self.MIX_conc_core_h = ConcCore(n_focus_on, h, rawob_dim)
+        self.CT_get_value = nn.Sequential(nn.Linear(2 * h, h), nn.ReLU(inplace=True), nn.Linear(h, 1))
+        self.CT_get_threat = nn.Sequential(nn.Linear(2 * h, h), nn.ReLU(inplace=True), nn.Linear(h, 1))
+        self.AT_get_logit_db = nn.Sequential(nn.Linear(2 * h, h), nn.ReLU(inplace=True),
+                                             nn.Linear(h, h // 2), nn.ReLU(inplace=True), nn.Linear(h // 2, n_action))
+
+    @classmethod
+    def from_checkpoint(cls, path, device, n_focus_on=3, group=None):
+        sd = torch.load(path, map_location='cpu')
+        net = cls(rawob_dim=sd['AT_obs_encoder.0.weight'].shape[1], n_action=sd['AT_get_logit_db.4.weight'].shape[0],
+                  n_focus_on=n_focus_on, group=group)
+        net.load_state_dict(sd)
+        return net.to(device)
+
+    @torch.no_grad()
+    def heads(self, obs_feed, chunk=1 << 18):
+        """obs_feed f32 [..., 24, D] (empty rows NaN, a dead agent all NaN) -> (logits [..., n_action], value [...],
+        threat [...]).  Agents are processed `chunk` at a time (default: 4096 x 50 agents in one pass, about 2 GB of activations)."""
+        lead = obs_feed.shape[:-2]
+        x, dead = self._batch_norm(obs_feed)
+        x = x.reshape(-1, 24, self.rawob_dim)
+        dead = dead.reshape(-1, 24).bool()
+        B = x.shape[0]
+        logits = torch.empty((B, self.n_action), dtype=torch.float32, device=x.device)
+        value = torch.empty((B,), dtype=torch.float32, device=x.device)
+        threat = torch.empty((B,), dtype=torch.float32, device=x.device)
+        for b0 in range(0, B, chunk):
+            xs, ds = x[b0:b0 + chunk], dead[b0:b0 + chunk]
+            v = self.AT_obs_encoder(xs)
+            vf_c, vf_m = self.MIX_conc_core_f(v[:, 0], v[:, 1:12], ds[:, 1:12], xs[:, 1:12], xs[:, 0])
+            vh_c, vh_m = self.MIX_conc_core_h(v[:, 0], v[:, 12:24], ds[:, 12:24], xs[:, 12:24], xs[:, 0])
+            logits[b0:b0 + chunk] = self.AT_get_logit_db(torch.cat((vf_c, vh_c), -1))
+            vm = torch.cat((vf_m, vh_m), -1)
+            value[b0:b0 + chunk] = self.CT_get_value(vm)[:, 0]
+            t = self.CT_get_threat(vm)[:, 0]
+            r = 0.5 * 11
+            threat[b0:b0 + chunk] = (torch.tanh(t / r) + 1.0) * r              # re_scale, net.py:226-229
+        return logits.reshape(*lead, self.n_action), value.reshape(lead), threat.reshape(lead)
+
+    @torch.no_grad()
+    def act(self, obs_feed, test_mode=False, generator=None):
+        """Net.act: (action int32 [...], value f32 [...], log-prob f32 [...]).  test_mode: arg-max (net.py:147), else one
+        Categorical draw per agent (Gumbel arg-max of the logits, from `generator` on the device)."""
+        logits, value, _ = self.heads(obs_feed)
+        logp_all = torch.log_softmax(logits, -1)
+        if test_mode:
+            act = torch.argmax(logp_all, -1)
+        else:
+            u = torch.rand(logits.shape, dtype=torch.float32, device=logits.device, generator=generator)
+            act = torch.argmax(logp_all - torch.log(-torch.log(u.clamp_min(1e-20))), -1)
+        logp = torch.gather(logp_all, -1, act.unsqueeze(-1)).squeeze(-1)
+        return act.to(torch.int32), value, logp
+
+
+class PolicyRollout(object):
+    """The device-resident loop of INTEGRATION.md section 3 for BASELINE configs[3]: scripted attackers (k_plan) + env
+    step (k_step) + history pool (k_histpool) + conc_4hist policy + rollout buffer + GAE (k_gae), no host hop.
+    env: DcaVecEnv(empty_rows_nan=True) whose guards the policy drives."""
+
+    def __init__(self, env, net, gamma=0.99, tau=0.95, gamma_fwd=None, seed=0, test_mode=False):
+        from .rollout import DeviceRollout, HistoryPool
+        self.env, self.net, self.test_mode = env, net, test_mode
+        self.hist = HistoryPool(env.E, env.G, device=env.device)
+        self.buf = DeviceRollout(env, gamma=gamma, tau=tau, gamma_fwd=gamma_fwd)
+        self.gen = torch.Generator(device=env.device)
+        self.gen.manual_seed(seed)
+        self.suffered = torch.ones((env.E,), dtype=torch.uint8, device=env.device)  # Env-Suffered-Reset: all, at start
+        self.episodes = torch.zeros((), dtype=torch.int64, device=env.device)
+        self.wins = torch.zeros((), dtype=torch.int64, device=env.device)
+        self.steps_in_finished = torch.zeros((), dtype=torch.int64, device=env.device)
+        self.obs = env.reset()
+
+    def step(self, collect=True):
+        """One env step of every env: history roll -> policy -> plan -> step -> rollout buffer.  Returns the mask of
+        finished envs (device bool [E])."""
+        env = self.env
+        feed = self.hist.roll(self.obs, suffered_reset=self.suffered)
+        act, value, _ = self.net.act(feed, test_mode=self.test_mode, generator=self.gen)
+        alive_before = self.buf.alive_guards().clone() if collect else None
+        lens_before = self.buf.length.clone() if collect else None
+        self.obs, reward, done, win = env.step(act)   # plan() inside: the scripted attackers of World.step
+        fin = done != 0
+        if collect:
+            self.buf.add(alive_before, value, reward, done)
+            self.steps_in_finished += torch.where(fin, lens_before + 1, torch.zeros_like(lens_before)).sum()
+        self.suffered = done.clone()
+        self.episodes += fin.sum()
+        self.wins += (fin & (win != 0)).sum()
+        return fin

@@ -195,6 +195,20 @@ int dca_adv_normalize(const float *ret, const float *value, const uint8_t *valid
 int dca_adv_moments_static(const float *ret, const float *value, const uint8_t *valid, int valid_group, uint64_t n,
                            double *stats, dca_stream_t stream);
 
+/* ---- observation normalisation of the conc / conc_4hist policy -------------------------------------------------------
+ * replaces: DynamicNorm.forward ALGORITHM/common/norm.py:31-69 (exclude_nan, exclude_one_hot) as called from Net._act
+ * ALGORITHM/conc_4hist/net.py:194-198 (= ALGORITHM/conc/net.py:300-304), on the policy's input [rows, 16] float32.
+ * dca_norm_moments: stats f64[49] = sum x[16], sum x^2[16], number of values outside {-1,0,1}[16], row count, over the
+ *   rows that hold no NaN; scratch f64[592*49] (device).  The caller merges them into the running moments (and
+ *   all-reduces the 49 doubles across GPUs first: every rank then holds the same moments).
+ * dca_norm_apply: y = nan_to_num(clip((x - mean) / sqrt(var + 1e-8), -10, 10), 0) in float32 like torch; row_nan u8[rows] =
+ *   isnan(x).any(-1) (the policy's entity mask); y may alias x. */
+#define DCA_NORM_STATS 49
+#define DCA_NORM_SCRATCH (592 * 49)
+int dca_norm_moments(const float *x, uint64_t rows, int dim, double *scratch, double *stats, dca_stream_t stream);
+int dca_norm_apply(const float *x, const float *mean, const float *var, uint64_t rows, int dim, float *y,
+                   uint8_t *row_nan, dca_stream_t stream);
+
 /* ---- dca_multiteam -------------------------------------------------------------------------------------------------
  * The sibling env MISSION/dca_multiteam (N teams, every agent policy-controlled, per-hit success draw, shrinking kill
  * circle, team ranking).  Same conventions as the dca_* calls above. */

@@ -26,6 +26,11 @@ CASES = {
     '4x6': dict(cfg=dict(N_AGENT_EACH_TEAM=[6, 6, 6, 6], random_jam_prob=0.05, introduce_terrain=True,
                          terrain_parameters=[0.15, 0.2], MaxEpisodeStep=30, StepsToNarrowCircle=10, size=2.0,
                          init_distance=0.6), steps=100, seed=3, gid=9),
+    # the same four teams with the team-level interface: one reward per team (0, then the ranking bonus on done) and the
+    # observation of agent 0 only (collective_assault_parallel_run.py:166-186)
+    '4x6_unity': dict(cfg=dict(N_AGENT_EACH_TEAM=[6, 6, 6, 6], random_jam_prob=0.05, introduce_terrain=True,
+                               terrain_parameters=[0.15, 0.2], MaxEpisodeStep=30, StepsToNarrowCircle=10, size=2.0,
+                               init_distance=0.6, RewardAsUnity=True, ObsAsUnity=True), steps=100, seed=3, gid=9),
 }
 STATE_KEYS = ('pos', 'vel', 'atk_rad', 'terrain', 'alive', 'just_died', 'hit', 'was_hit', 'bsa', 'init_theta',
               'time_step', 'obs_counter', 'episode')
@@ -67,7 +72,7 @@ def run_case(name, spec):
         rec[k] = np.array(v)
     rec['done'] = rec['done'].astype(np.uint8)
     rec['tobs_steps'] = np.array(tobs_steps, np.int32)
-    rec['tobs'] = np.array(tobs, np.float32).reshape(len(tobs), N, 204)
+    rec['tobs'] = np.array(tobs, np.float32).reshape(len(tobs), -1, 204)
     path = os.path.join(OUT, 'mt_%s.npz' % name)
     np.savez_compressed(path, **rec)
     print(name, 'steps', spec['steps'], 'dones at', np.nonzero(rec['done'])[0].tolist(), 'rankings',

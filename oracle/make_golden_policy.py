@@ -140,6 +140,8 @@ def gen_net():
         rec['norm%d_filter' % i] = bn.one_hot_filter.numpy().copy()
         rec['norm%d_out' % i] = y.numpy()
     rec['norm_n0'] = sd0['_batch_norm.n_sample'].numpy().copy()
+    for k, v in sd0.items():   # the checkpoint itself, as arrays (the GPU box has no reference tree)
+        rec['sd/' + k] = v.numpy().copy()
     path = os.path.join(OUT, 'policy_net_4hist.npz')
     np.savez_compressed(path, **rec)
     print('policy_net_4hist %.1f KB; obs_feed %s, NaN rows %.1f%%' % (

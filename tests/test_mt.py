@@ -15,7 +15,8 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import golden_util as gu  # noqa: E402
 
 GOLDEN_DIR = os.path.join(REPO, 'tests', 'golden')
-CASES = sorted(os.path.basename(p)[3:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, 'mt_*.npz')))
+CASES = sorted(os.path.basename(p)[3:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, 'mt_*.npz'))
+               if not p.endswith('_unity.npz'))  # the team-level interface has its own test
 RTOL = 1e-5
 INT_KEYS = ('alive', 'just_died', 'hit', 'was_hit', 'bsa', 'time_step', 'obs_counter', 'episode')
 FLOAT_KEYS = ('pos', 'vel', 'atk_rad', 'terrain', 'init_theta')
@@ -269,3 +270,51 @@ def test_cuda_mt_superpool_facade_matches_reference_autoreset():
             assert info[0] == {}, tag
         last_info = info[0]
     assert n_done >= 2 and n_skip >= 2
+
+
+@pytest.mark.gpu
+def test_cuda_mt_unity_modes_match_reference():
+    """RewardAsUnity / ObsAsUnity (MISSION/dca_multiteam/collective_assault_parallel_run.py:166-186): one reward per
+    team (0, then the ranking bonus on done) and agent 0's observation alone, against a reference trajectory recorded
+    with both flags on (tests/golden/mt_4x6_unity.npz), through the device and the host surface."""
+    import torch
+    from hmp2g_b200.multiteam import DcaMultiTeamSuperpoolEnv, DcaMultiTeamVecEnv
+    case = load_case('4x6_unity')
+    plain = load_case('4x6')
+    assert case['cfg']['RewardAsUnity'] and case['cfg']['ObsAsUnity']
+    T = len(case['cfg']['N_AGENT_EACH_TEAM'])
+    env = DcaMultiTeamVecEnv(1, scfg=_mt_scfg(case['cfg']), seed=case['seed'], env_gid0=case['gid'])
+    host = DcaMultiTeamSuperpoolEnv(n_env=1, scfg=_mt_scfg(case['cfg']), seed=case['seed'], env_gid0=case['gid'])
+    obs0, _ = host.reset()
+    assert obs0.shape == (1, 1, 204)
+    for e in (env, host.env):
+        e.import_state({k: case['s0_' + k][None] for k in STATE_KEYS})
+    want_tobs = {int(t): case['tobs'][k] for k, t in enumerate(case['tobs_steps'])}
+    n_done = 0
+    for t in range(case['actions'].shape[0]):
+        a = case['actions'][t]
+        skip = bool(np.isnan(a).any())
+        act = torch.from_numpy(np.where(np.isnan(a), 0, a).astype(np.int32)[None]).to(env.device)
+        obs, rew, done, rank = env.step(act, skip=torch.full((1,), int(skip), dtype=torch.uint8, device=env.device))
+        tag = 'unity t=%d' % t
+        assert tuple(obs.shape) == (1, 1, 12, 17) and tuple(rew.shape) == (1, T)
+        assert int(done[0]) == int(case['done'][t]), tag
+        assert np.array_equal(rew[0].cpu().numpy().astype(np.float64), case['reward'][t]), tag
+        # agent 0's rows: the same comparison as the per-agent fixture, restricted to the first agent
+        o = obs[0].reshape(1, 204).cpu().numpy()
+        ida, idb = slot_ids(o), slot_ids(case['obs'][t])
+        assert np.array_equal(ida >= 0, idb >= 0), tag
+        same = (ida == idb)[..., None] & np.ones((1, 1, 17), bool)
+        gu.assert_close_rel(np.where(same, o.reshape(1, 12, 17), 0), np.where(same, case['obs'][t].reshape(1, 12, 17), 0),
+                            RTOL, tag + ' obs', atol=1e-12)
+        h_obs, h_rew, h_done, h_info = host.step(a[None])
+        assert h_obs.shape == (1, 1, 204) and h_rew.shape == (1, T) and h_rew.dtype == np.float64
+        assert np.array_equal(h_rew[0], case['reward'][t]) and bool(h_done[0]) == bool(case['done'][t]), tag
+        assert np.array_equal(h_obs[0], o), tag
+        if case['done'][t] and not skip:
+            n_done += 1
+            assert np.array_equal(rank[0].cpu().numpy(), case['ranking'][t]), tag
+            assert np.array_equal(h_info[0]['team_ranking'], case['ranking'][t]) and h_info[0]['obs-echo'].shape == (1, 204)
+            assert np.array_equal(slot_ids(h_info[0]['obs-echo']) >= 0, slot_ids(want_tobs[t]) >= 0), tag
+    assert n_done >= 5
+    assert np.array_equal(case['done'], plain['done'])  # the flags change what is handed out, not the simulation

@@ -1,0 +1,163 @@
+"""conc_4hist policy rollout on device tensors (BASELINE.json configs[3]): the normalisation
+kernels, the network and the rollout loop against fixtures produced by the unmodified reference
+(oracle/make_golden_policy.py: ALGORITHM/conc_4hist/net.py Net + ALGORITHM/common/norm.py DynamicNorm with the shipped
+RESULT/50RL-55opp/model.pt, on observations of the reference env)."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+
+
+def _fixture():
+    return np.load(os.path.join(gu.GOLDEN_DIR, 'policy_net_4hist.npz'))
+
+
+def _net(z, torch):
+    from hmp2g_b200.policy import ConcNet4Hist
+    net = ConcNet4Hist(rawob_dim=16, n_action=7, n_focus_on=3)
+    sd = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith('sd/')}
+    net.load_state_dict(sd)   # strict: same names, shapes and dtypes as the reference's state_dict
+    return net.cuda()
+
+
+def test_norm_moments_and_apply_match_numpy():
+    import torch
+    from hmp2g_b200.policy import DynamicNormDevice
+    z = _fixture()
+    x = z['obs_feed']
+    bn = DynamicNormDevice(16).cuda()
+    xt = torch.from_numpy(x).cuda()
+    stats = bn.batch_stats(xt).cpu().numpy()
+    rows = x.reshape(-1, 16)
+    ok = ~np.isnan(rows).any(-1)
+    r64 = rows[ok].astype(np.float64)
+    np.testing.assert_allclose(stats[:16], r64.sum(0), rtol=1e-12, atol=1e-9)
+    np.testing.assert_allclose(stats[16:32], (r64 * r64).sum(0), rtol=1e-12, atol=1e-9)
+    assert np.array_equal(stats[32:48], ((r64 != 0) & (r64 != 1) & (r64 != -1)).sum(0))
+    assert stats[48] == ok.sum()
+    again = bn.batch_stats(xt).cpu().numpy()
+    assert np.array_equal(stats.view(np.uint64), again.view(np.uint64))  # fixed summation order
+    # apply with the checkpoint's moments: float32 arithmetic like torch's
+    mean, var = z['eval_norm_mean'], z['eval_norm_var']
+    bn.mean.data.copy_(torch.from_numpy(mean)); bn.var.data.copy_(torch.from_numpy(var))
+    y, mask = bn.apply_norm(xt)
+    want = np.clip((rows - mean) / np.sqrt(var + np.float32(1e-8)), -10, 10)
+    want_mask = np.isnan(rows).any(-1)
+    assert np.array_equal(mask.cpu().numpy().reshape(-1).astype(bool), want_mask)
+    got = y.cpu().numpy().reshape(-1, 16)
+    assert np.array_equal(got[want_mask], np.zeros_like(got[want_mask]))
+    assert np.array_equal(got[~want_mask].view(np.uint32), want[~want_mask].astype(np.float32).view(np.uint32))
+
+
+def test_dynamic_norm_updates_match_reference():
+    """DynamicNorm in training mode from the checkpoint's moments over three batches (norm.py:47-63): running mean /
+    variance / sample count / one-hot filter after each batch, and the normalised batch."""
+    import torch
+    z = _fixture()
+    net = _net(z, torch)
+    bn = net._batch_norm
+    bn.train()
+    x = z['obs_feed']
+    assert int(bn.n_sample.item()) == int(z['norm_n0'][0])
+    for i in range(3):
+        xb = torch.from_numpy(x[i * 5:(i + 1) * 5].copy()).cuda()
+        y, mask = bn(xb)
+        np.testing.assert_allclose(bn.mean.cpu().numpy(), z['norm%d_mean' % i], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(bn.var.cpu().numpy(), z['norm%d_var' % i], rtol=1e-5, atol=1e-6)
+        assert int(bn.n_sample.item()) == int(z['norm%d_n' % i][0])
+        assert np.array_equal(bn.one_hot_filter.cpu().numpy(), z['norm%d_filter' % i])
+        want = z['norm%d_out' % i]
+        got = y.cpu().numpy()
+        nan = np.isnan(want)
+        assert np.array_equal(mask.cpu().numpy().astype(bool), nan.any(-1))
+        np.testing.assert_allclose(got[~nan], want[~nan], rtol=1e-5, atol=1e-5)
+        assert (got[nan] == 0).all()
+
+
+def test_net_matches_reference_net_on_reference_observations():
+    """ConcNet4Hist with the shipped checkpoint vs the reference Net (eval mode: frozen normalisation) on 1000 agents'
+    observations from a reference rollout: action probabilities to 1e-4, value / threat to 2e-3, arg-max actions equal wherever
+    the reference's top two probabilities are more than 1e-4 apart."""
+    import torch
+    z = _fixture()
+    net = _net(z, torch).eval()
+    x = torch.from_numpy(z['obs_feed']).cuda()
+    logits, value, threat = net.heads(x)
+    probs = torch.softmax(logits, -1).cpu().numpy()
+    # value / threat ride on the attention weights, a float32 softmax over logits in the hundreds (the checkpoint's
+    # attention is nearly one-hot): a 1e-3 absolute difference in a logit -- what the reference's own CPU and CUDA runs
+    # differ by -- moves a weight by 1e-3 relative.  The action head only depends on WHICH entities are picked.
+    np.testing.assert_allclose(value.cpu().numpy(), z['eval_value'], rtol=2e-3, atol=2e-3)
+    np.testing.assert_allclose(probs, z['eval_probs'], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(threat.cpu().numpy(), z['eval_threat'], rtol=2e-3, atol=2e-3)
+    act, v2, logp = net.act(x, test_mode=True)
+    top2 = np.sort(z['eval_probs'], -1)[..., -2:]
+    clear = (top2[..., 1] - top2[..., 0]) > 1e-4
+    assert clear.mean() > 0.9
+    assert np.array_equal(act.cpu().numpy()[clear], z['eval_act'][clear])
+    np.testing.assert_allclose(logp.cpu().numpy()[clear], z['eval_logp'][clear], rtol=1e-4, atol=1e-4)
+    # sampling: frequencies follow the probabilities (one agent's distribution, many draws through the batch axis)
+    one = x[:1, :1].expand(400, 50, 24, 16).contiguous()
+    g = torch.Generator(device='cuda'); g.manual_seed(5)
+    a, _, _ = net.act(one, test_mode=False, generator=g)
+    freq = np.bincount(a.cpu().numpy().reshape(-1), minlength=7) / a.numel()
+    assert np.abs(freq - probs[0, 0]).max() < 0.02
+
+
+def test_policy_rollout_50v55_statistics_match_reference_run():
+    """BASELINE configs[3] end to end on the device: the shipped conc_4hist policy (sampled actions) against the scripted
+    attackers, 256 envs x their first two episodes = 512 episodes, vs the same policy on the unmodified reference env
+    (tests/golden/policy_rollout_50v55.json, 512 episodes): win rate and mean episode length within sampling error.
+    The GAE pass runs on every finished trajectory with the configuration's gamma_in_reward_forwarding (0.95)."""
+    import torch
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.policy import PolicyRollout
+    from hmp2g_b200.vec_env import DcaVecEnv
+    ref = json.load(open(os.path.join(gu.GOLDEN_DIR, 'policy_rollout_50v55.json')))
+    z = _fixture()
+    net = _net(z, torch).train()   # the reference never calls .eval(): the normalisation keeps updating (norm.py:47)
+    scfg = type('S', (ScenarioConfig,), dict(num_guards=50, num_attackers=55, size=5.0, random_jam_prob=0.05,
+                                             introduce_terrain=True, terrain_parameters=[0.15, 0.2], MaxEpisodeStep=180,
+                                             half_death_reward=True, REWARD_DEBUG=True, REWARD_DEBUG_Value=3))
+    E, per_env = 256, 2
+    env = DcaVecEnv(E, scfg=scfg, seed=22333, empty_rows_nan=True)
+    roll = PolicyRollout(env, net, gamma=0.99, tau=0.95, gamma_fwd=0.95, seed=1)
+    ep = np.zeros(E, int); cur = np.zeros(E, int); cur_r = np.zeros(E)
+    lens, wins, rsum = [], [], []
+    n_fin_traj = 0
+    for t in range(per_env * 181 + 2):
+        fin = roll.step()
+        f = fin.cpu().numpy(); w = env.win.cpu().numpy()
+        cur += 1
+        cur_r += env.reward.mean(1).cpu().numpy()   # per-agent reward of the step, averaged over the guards
+        for e in np.nonzero(f)[0]:
+            if ep[e] < per_env:
+                lens.append(cur[e]); wins.append(bool(w[e])); rsum.append(cur_r[e])
+            ep[e] += 1; cur[e] = 0; cur_r[e] = 0
+        if f.any():
+            ret, threat, adv, valid = roll.buf.finalize(fin)
+            assert torch.isfinite(ret[valid]).all() and torch.isfinite(adv[valid]).all()
+            n_fin_traj += int(f.sum())
+        if (ep >= per_env).all():
+            break
+    assert len(lens) == E * per_env and n_fin_traj >= E * per_env
+    assert int(roll.episodes.item()) == n_fin_traj
+    win_rate, mean_len = float(np.mean(wins)), float(np.mean(lens))
+    print('policy rollout: %d episodes, win rate %.3f (reference %.3f), mean length %.1f +- %.1f (reference %.1f +- %.1f)'
+          % (len(lens), win_rate, ref['win_rate'], mean_len, np.std(lens), ref['mean_len'], ref['std_len']))
+    n_ref = ref['episodes']
+    p = 0.5 * (win_rate + ref['win_rate'])
+    se_p = np.sqrt(max(p * (1 - p), 1e-4) * (1.0 / len(lens) + 1.0 / n_ref))
+    assert abs(win_rate - ref['win_rate']) <= 4 * se_p + 0.01
+    se_len = np.sqrt(np.var(lens) / len(lens) + ref['std_len'] ** 2 / n_ref)
+    assert abs(mean_len - ref['mean_len']) <= 4 * se_len + 2.0
+    se_r = np.sqrt(np.var(rsum) / len(rsum) + ref['std_reward_sum'] ** 2 / n_ref)
+    print('mean reward sum %.3f +- %.3f (reference %.3f +- %.3f)' % (np.mean(rsum), np.std(rsum), ref['mean_reward_sum'],
+                                                                    ref['std_reward_sum']))
+    assert abs(np.mean(rsum) - ref['mean_reward_sum']) <= 4 * se_r + 0.05
