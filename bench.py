@@ -300,6 +300,7 @@ def quick_config_run(name, E, dev, rank, steps=360, warm=40):
     pool = [torch.randint(0, 7, (E, G), device=dev, dtype=torch.int32) for _ in range(8)]
     aptrs = [C.c_void_p(a.data_ptr()) for a in pool]
     env.reset()
+    lib.dca_set_option(h, 4, 1)  # value: launches pipelined as in the headline run; k_step_ms below: stand-alone
     for i in range(warm):
         lib.dca_plan_centroid(h, fptr, sptr)
         lib.dca_step(h, aptrs[i % 8], fptr, None, None, 1, sptr)
@@ -315,6 +316,7 @@ def quick_config_run(name, E, dev, rank, steps=360, warm=40):
     es = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     ee = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     lib.dca_set_option(h, 2, 0)
+    lib.dca_set_option(h, 4, 0)
     for i in range(steps):
         lib.dca_plan_centroid(h, fptr, sptr)
         es[i].record(stream)
@@ -424,7 +426,9 @@ def run_ours(args):
         return rc
 
     overlap = 0 if args.no_overlap else 1
+    piped = 0 if (args.no_pipeline or args.no_overlap) else 1
     lib.dca_set_option(h, 2, overlap)
+    lib.dca_set_option(h, 4, piped)  # DCA_OPT_PIPELINE_STEPS: plan / step / plan / step hand envs over one by one
     env.reset()
     # Pre-roll (set-up, untimed): env e is advanced by a random number of steps in [0, MaxEpisodeStep) -- it sits out
     # (ENV-PAUSE mask) the first MaxEpisodeStep - offset[e] of MaxEpisodeStep steps -- so the timed steps sample the
@@ -471,6 +475,7 @@ def run_ours(args):
     ev_s = [torch.cuda.Event(enable_timing=True) for _ in range(Kk)]
     ev_e = [torch.cuda.Event(enable_timing=True) for _ in range(Kk)]
     lib.dca_set_option(h, 2, 0)
+    lib.dca_set_option(h, 4, 0)
     for i in range(Kk):
         plan_call(h, fptr, sptr)
         ev_s[i].record(stream)
@@ -478,35 +483,49 @@ def run_ours(args):
         ev_e[i].record(stream)
     torch.cuda.synchronize()
     lib.dca_set_option(h, 2, overlap)
+    lib.dca_set_option(h, 4, piped)
     per_launch = [ev_s[i].elapsed_time(ev_e[i]) for i in range(Kk)]
     ms_step_kernel = sum(per_launch[:Kfirst]) / Kfirst  # the K steps that follow the timed region
     ms_step_kernel_episode = sum(per_launch) / Kk       # >= two whole episodes
     # ---- like-for-like with the reference arm: the scripted formation planner (k_plan, what World.step runs in the
-    # reference, core.py:189-196) + step, over whole episodes, the step launched under its planner as in the timed region
+    # reference, core.py:189-196) + step, over whole episodes, the step launched under its planner as in the timed
+    # region.  Its own env instance, driven by the scripted planner from the reset on (states produced by the centroid
+    # stand-in -- attackers collapsed onto one point -- are not states this planner ever sees), same pre-roll.
+    env2 = DcaVecEnv(E, scfg=scfg, device=dev, seed=SEED + 1, env_gid0=rank * E)
+    h2 = env2.handle
+    lib.dca_set_option(h2, 2, overlap)
+    lib.dca_set_option(h2, 4, piped)
+    env2.reset()
+    if preroll:
+        for s in range(preroll):
+            skip = (offs < (preroll - s)).to(torch.uint8)
+            lib.dca_plan(h2, fptr, None, None, sptr)
+            lib.dca_step(h2, aptrs[s % n_pool], fptr, C.c_void_p(skip.data_ptr()), None, 1, sptr)
     Ks = 360
     for i in range(20):
-        lib.dca_plan(h, fptr, None, None, sptr)
-        lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
+        lib.dca_plan(h2, fptr, None, None, sptr)
+        lib.dca_step(h2, aptrs[i % n_pool], fptr, None, None, 1, sptr)
     s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     s0.record(stream)
     for i in range(Ks):
-        lib.dca_plan(h, fptr, None, None, sptr)
-        lib.dca_step(h, aptrs[(20 + i) % n_pool], fptr, None, None, 1, sptr)
+        lib.dca_plan(h2, fptr, None, None, sptr)
+        lib.dca_step(h2, aptrs[(20 + i) % n_pool], fptr, None, None, 1, sptr)
     s1.record(stream)
     torch.cuda.synchronize()
     ms_scripted = s0.elapsed_time(s1) / Ks
     pe_s = [torch.cuda.Event(enable_timing=True) for _ in range(180)]
     pe_e = [torch.cuda.Event(enable_timing=True) for _ in range(180)]
-    lib.dca_set_option(h, 2, 0)
+    lib.dca_set_option(h2, 2, 0)
+    lib.dca_set_option(h2, 4, 0)
     for i in range(180):  # k_plan alone, on the states of one more episode
         pe_s[i].record(stream)
-        lib.dca_plan(h, fptr, None, None, sptr)
+        lib.dca_plan(h2, fptr, None, None, sptr)
         pe_e[i].record(stream)
-        lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
+        lib.dca_step(h2, aptrs[i % n_pool], fptr, None, None, 1, sptr)
     torch.cuda.synchronize()
-    lib.dca_set_option(h, 2, overlap)
     ms_plan_episode = sum(pe_s[i].elapsed_time(pe_e[i]) for i in range(180)) / 180
+    del env2
     ts_ = torch.tensor([ms_scripted], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ts_, op=dist.ReduceOp.MAX)
@@ -608,6 +627,7 @@ def run_ours(args):
     # 4096 first episodes in lock-step, the most expensive phase (the teams meet)
     env.reset()
     lib.dca_set_option(h, 2, 0)
+    lib.dca_set_option(h, 4, 0)
     for i in range(5):
         plan_call(h, fptr, sptr)
         lib.dca_step(h, aptrs[i % n_pool], fptr, None, None, 1, sptr)
@@ -678,7 +698,7 @@ def run_ours(args):
                                % (G, A, E, 'centroid planner stand-in' if args.planner == 'centroid' else
                                   'scripted formation planner k_plan in the timed region',
                                   '' if args.scenario == '50v50' else ' at another team size'),
-                   'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD, 'overlap_planner': bool(overlap),
+                   'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD, 'overlap_planner': bool(overlap), 'pipeline_steps': bool(piped),
                    'pre_roll': ('each env advanced by a random number of steps in [0, %d) before warm-up (untimed set-up): '
                                 'stationary mix of episode phases' % preroll) if preroll else 'none: synchronised reset',
                    'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
@@ -692,6 +712,12 @@ def run_ours(args):
                                          'timed region (same episodes; launched stand-alone: in the timed region the '
                                          'kernel starts under the planner stand-in, DCA_OPT_OVERLAP_PLANNER)' % Kfirst,
                      'kernel_ms_episode_avg': ms_step_kernel_episode, 'episode_avg_steps': Kk,
+                     'pipelined_ms_per_step': ms_total / K,
+                     'frac_pipelined': algo_bytes / (ms_total / K * 1e-3) / 1e9 / peak,
+                     'pipelined_note': 'in the timed region launch t+1 starts inside the last wave of launch t '
+                                       '(DCA_OPT_PIPELINE_STEPS), so a launch has no duration of its own there: this is '
+                                       'algorithmic bytes / (region time / K); kernel_ms is the same kernel launched '
+                                       'stand-alone',
                      'kernel_ms_synchronised_start': ms_step_sync_start,
                      'frac_synchronised_start': algo_bytes / (ms_step_sync_start * 1e-3) / 1e9 / peak,
                      'frac_episode_avg': algo_bytes / (ms_step_kernel_episode * 1e-3) / 1e9 / peak,
@@ -769,6 +795,8 @@ def main():
                     help='attacker forces: the centroid stand-in of configs[1] (default) or the scripted formation planner k_plan')
     ap.add_argument('--no-preroll', action='store_true',
                     help='time from a synchronised reset of all envs instead of the stationary episode-phase mix')
+    ap.add_argument('--no-pipeline', action='store_true',
+                    help='DCA_OPT_PIPELINE_STEPS off: every launch waits for the whole previous launch')
     ap.add_argument('--no-overlap', action='store_true',
                     help='launch the step kernel strictly after the planner stand-in (DCA_OPT_OVERLAP_PLANNER off)')
     ap.add_argument('--traffic', type=float, default=None,

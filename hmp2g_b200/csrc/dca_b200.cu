@@ -31,6 +31,11 @@ struct DcaHandle {
     bool overlap_planner;           // DCA_OPT_OVERLAP_PLANNER
     const void *planned_force;      // att_force / stream of the planner launch, if that was the handle's last launch
     cudaStream_t planned_stream;
+    bool pipeline_steps;            // DCA_OPT_PIPELINE_STEPS
+    uint32_t *epoch;                // [2E] per-env hand-over words: step epochs, planner epochs
+    uint32_t step_epoch, plan_epoch;  // launches published so far
+    bool last_was_step;             // the handle's last launch was a dca_step without a pause mask ...
+    cudaStream_t last_step_stream;  // ... on this stream
     std::string err;
 };
 
@@ -143,6 +148,18 @@ static cudaError_t allow_smem(K kernel, int bytes) {
         if (e == cudaSuccess) e = allow_smem(KERNEL<256, 0, 0>, bytes);                                 \
     } while (0)
 
+// Hand-over words for a planner launch: it waits per env for the step launched right before it on the same stream
+// (DCA_OPT_PIPELINE_STEPS) -- otherwise it is a normal launch behind everything earlier in the stream -- and always
+// publishes its own epoch.
+static Pipe planner_pipe(DcaHandle *h, cudaStream_t st) {
+    Pipe pipe;
+    pipe.epoch = h->pipeline_steps ? h->epoch : nullptr;
+    pipe.wait_step = (h->pipeline_steps && h->last_was_step && h->last_step_stream == st) ? h->step_epoch : 0u;
+    pipe.wait_plan = 0u;
+    pipe.publish = h->pipeline_steps ? ++h->plan_epoch : 0u;
+    return pipe;
+}
+
 extern "C" {
 
 int dca_abi_version(void) { return 2; }
@@ -171,6 +188,11 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     h->overlap_planner = false;
     h->planned_force = nullptr;
     h->planned_stream = nullptr;
+    h->pipeline_steps = false;
+    h->epoch = nullptr;
+    h->step_epoch = h->plan_epoch = 0;
+    h->last_was_step = false;
+    h->last_step_stream = nullptr;
     std::memset(&h->P, 0, sizeof(Params));
     h->P.cfg = *cfg;
     h->P.L = make_layout(G, A);
@@ -200,6 +222,8 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     const size_t bytes = (size_t)n_env * h->P.L.bytes;
     cudaError_t e = cudaMalloc((void **)&h->P.blobs, bytes);
     if (e == cudaSuccess) e = cudaMemset(h->P.blobs, 0, bytes);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&h->epoch, sizeof(uint32_t) * 2 * (size_t)n_env);
+    if (e == cudaSuccess) e = cudaMemset(h->epoch, 0, sizeof(uint32_t) * 2 * (size_t)n_env);
     {   // persistent team state of the scripted attacker planner (zero = teams not formed yet)
         const int K = A / 5 > 0 ? A / 5 : 1;
         std::memset(&h->plan, 0, sizeof(PlanState));
@@ -232,6 +256,7 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
     if (e != cudaSuccess) {
         const int rc = fail(nullptr, DCA_E_CUDA, std::string("dca_create: ") + cudaGetErrorString(e));
         if (h->P.blobs) cudaFree(h->P.blobs);
+        if (h->epoch) cudaFree(h->epoch);
         cudaFree(h->plan.flags); cudaFree(h->plan.counter); cudaFree(h->plan.label); cudaFree(h->plan.cent);
         delete h;
         return rc;
@@ -245,6 +270,7 @@ int dca_destroy(DcaHandle *h) {
     if (!h) return DCA_E_INVALID;
     DeviceGuard guard(h->device);
     cudaFree(h->P.blobs);
+    cudaFree(h->epoch);
     cudaFree(h->plan.flags); cudaFree(h->plan.counter); cudaFree(h->plan.label); cudaFree(h->plan.cent);
     delete h;
     return DCA_OK;
@@ -274,6 +300,7 @@ int dca_reset(DcaHandle *h, const uint8_t *env_mask, dca_stream_t stream) {
     DCA_DISPATCH(h, false, k_reset, h->P, env_mask);
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = nullptr;
+    h->last_was_step = false;
     h->launches += 1;
     return DCA_OK;
 }
@@ -289,10 +316,22 @@ int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, cons
     // Overlap with the planner (DCA_OPT_OVERLAP_PLANNER): only when this handle's previous launch was the planner that
     // filled this att_force on this stream -- then everything k_step touches before its pdl_wait() (its own blobs,
     // `skip`) is settled, and the forces are read after the wait.
-    const bool pdl = h->overlap_planner && h->planned_force == (const void *)att_force && h->planned_stream == st_;
-    DCA_DISPATCH(h, pdl, k_step, h->P, actions, att_force, skip, rng_words, autoreset);
+    const bool behind_planner = h->planned_force == (const void *)att_force && h->planned_stream == st_;
+    // DCA_OPT_PIPELINE_STEPS: the step takes its envs over one by one -- env e starts once the previous step launch has
+    // published e (its blob; trivially true when the planner was a normal launch behind that step) and reads e's forces
+    // once the planner warp of e has published them.  Every step / planner launch publishes, piped or not.
+    const bool piped = h->pipeline_steps && behind_planner && skip == nullptr;
+    const bool pdl = piped || (h->overlap_planner && behind_planner);
+    Pipe pipe;
+    pipe.epoch = h->pipeline_steps ? h->epoch : nullptr;  // epochs are published only while the option is on
+    pipe.wait_step = piped ? h->step_epoch : 0u;  // 0 on the very first step: nothing to wait for
+    pipe.wait_plan = piped ? h->plan_epoch : 0u;
+    pipe.publish = h->pipeline_steps ? ++h->step_epoch : 0u;
+    DCA_DISPATCH(h, pdl, k_step, h->P, actions, att_force, skip, rng_words, autoreset, pipe);
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = nullptr;
+    h->last_was_step = skip == nullptr;  // a pause mask orders the launch behind the whole previous kernel anyway
+    h->last_step_stream = st_;
     h->launches += 1;
     return DCA_OK;
 }
@@ -304,6 +343,7 @@ int dca_observe(DcaHandle *h, const uint32_t *rng_words, dca_stream_t stream) {
     DCA_DISPATCH(h, false, k_observe, h->P, rng_words);
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = nullptr;
+    h->last_was_step = false;
     h->launches += 1;
     return DCA_OK;
 }
@@ -312,10 +352,13 @@ int dca_plan_centroid(DcaHandle *h, double *att_force, dca_stream_t stream) {
     if (!h || !att_force) return fail(h, DCA_E_INVALID, "dca_plan_centroid: null argument");
     DeviceGuard guard(h->device);
     const int threads = 128, warps_per_block = threads / 32;
-    k_plan_centroid<<<(h->P.E + warps_per_block - 1) / warps_per_block, threads, 0, (cudaStream_t)stream>>>(h->P, att_force);
+    const Pipe pipe = planner_pipe(h, (cudaStream_t)stream);
+    launch_env_kernel(k_plan_centroid, (h->P.E + warps_per_block - 1) / warps_per_block, threads, 0, (cudaStream_t)stream,
+                      pipe.wait_step != 0, h->P, att_force, pipe);
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = att_force;
     h->planned_stream = (cudaStream_t)stream;
+    h->last_was_step = false;
     h->launches += 1;
     return DCA_OK;
 }
@@ -333,11 +376,14 @@ int dca_plan(DcaHandle *h, double *att_force, const int32_t *team_label, const d
         if (G == 50 && A == 50) kernel = k_plan<50, 50>;
         else if (G == 50 && A == 55) kernel = k_plan<50, 55>;
         else if (G == 100 && A == 100) kernel = k_plan<100, 100>;
-        kernel<<<h->P.E, kPlanThreads, h->plan_smem, (cudaStream_t)stream>>>(h->P, h->plan, att_force, team_label, team_centroid);
-    }
+        const Pipe pipe = planner_pipe(h, (cudaStream_t)stream);
+        launch_env_kernel(kernel, h->P.E, kPlanThreads, h->plan_smem, (cudaStream_t)stream, pipe.wait_step != 0, h->P,
+                          h->plan, att_force, team_label, team_centroid, pipe);
+        }
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = att_force;
     h->planned_stream = (cudaStream_t)stream;
+    h->last_was_step = false;
     h->launches += 1;
     return DCA_OK;
 }
@@ -355,6 +401,7 @@ static int state_io(DcaHandle *h, const DcaState *st, int import, dca_stream_t s
     k_state_io<<<blocks, 256, 0, (cudaStream_t)stream>>>(h->P, *st, import);
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = nullptr;
+    h->last_was_step = false;
     h->launches += 1;
     return DCA_OK;
 }
@@ -708,6 +755,18 @@ int dca_set_option(DcaHandle *h, int option, int value) {
     if (!h) return DCA_E_INVALID;
     if (option == DCA_OPT_EMPTY_ROWS_NAN) { h->P.empty_nan = value != 0; return DCA_OK; }
     if (option == DCA_OPT_OVERLAP_PLANNER) { h->overlap_planner = value != 0; return DCA_OK; }
+    if (option == DCA_OPT_PIPELINE_STEPS) {
+        if ((value != 0) != h->pipeline_steps) {  // (re)start the epochs from zero: nothing is published while it is off
+            DeviceGuard guard(h->device);
+            CUDA_TRY(h, cudaDeviceSynchronize());
+            CUDA_TRY(h, cudaMemset(h->epoch, 0, sizeof(uint32_t) * 2 * (size_t)h->P.E));
+            h->step_epoch = h->plan_epoch = 0;
+            h->last_was_step = false;
+            h->planned_force = nullptr;
+            h->pipeline_steps = value != 0;
+        }
+        return DCA_OK;
+    }
     return fail(h, DCA_E_INVALID, "dca_set_option: unknown option");
 }
 

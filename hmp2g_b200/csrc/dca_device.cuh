@@ -200,6 +200,36 @@ __device__ __forceinline__ void st_global_256(float *p, float4 a, float4 b) {
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// ------------------------------------------------------------------ per-env hand-over between launches
+// DCA_OPT_PIPELINE_STEPS: consecutive launches on one handle (step -> planner -> step ...) only depend on each other
+// env by env, so instead of the grid-wide griddepcontrol.wait the consumer CTA of env e waits for the epoch its
+// producer CTA published for env e: the next launch's first CTAs run in the slots the previous launch's last wave leaves
+// empty.  epoch words: [0,E) last dca_step launch that finished env e, [E,2E) last planner launch that filled e's forces.
+struct Pipe {
+    uint32_t *epoch;     // [2E] device words (nullptr: feature off)
+    uint32_t wait_step;  // consumer: wait until epoch[e] has reached this value (0 = do not wait)
+    uint32_t wait_plan;  // k_step only: wait until epoch[E + e] has reached this value before the forces are read
+    uint32_t publish;    // producer: value stored with release semantics when env e is done
+};
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// The producer is resident or finished whenever a consumer can run (the dependent grid is only scheduled once every
+// CTA of its predecessor has started), so the wait is short; a bounded spin turns a protocol bug into a trap, not a hang.
+__device__ __forceinline__ void pipe_wait(const uint32_t *p, uint32_t want) {
+    unsigned spins = 0;
+    while ((int32_t)(ld_acquire_u32(p) - want) < 0) {
+        __nanosleep(64);
+        if (++spins > (1u << 24)) __trap();
+    }
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 // ------------------------------------------------------------------ TMA bulk copy (1-D) + mbarrier
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -261,6 +291,14 @@ __device__ __forceinline__ void tma_store_1d(void *gdst, const void *smem_src, u
 __device__ __forceinline__ void tma_store_commit_wait() {
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_written() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// ... until the bulk store has been written (not just read out of shared memory): needed before the env is handed over
+__device__ __forceinline__ void tma_store_commit_wait_written() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 }  // namespace dca

@@ -95,8 +95,14 @@ __device__ __forceinline__ Smem carve(unsigned char *base, const BlobLayout &L) 
 }
 
 // Fetch the env blob with one TMA bulk copy; returns after the data has landed for every thread.
-__device__ __forceinline__ void load_blob(const Smem &s, const Params &P, const BlobLayout &L, int e) {
+// wait_on / want: DCA_OPT_PIPELINE_STEPS -- the blob is only fetched once the previous step launch has published env e.
+__device__ __forceinline__ void load_blob(const Smem &s, const Params &P, const BlobLayout &L, int e,
+                                          const uint32_t *wait_on = nullptr, uint32_t want = 0) {
     if (threadIdx.x == 0) {  // the copy is in flight before anybody else reaches the barrier below
+        if (wait_on != nullptr) {
+            pipe_wait(wait_on, want);
+            fence_proxy_async_all();  // the blob was written through the async proxy (bulk store) and is read through it
+        }
         mbar_init(s.bar, 1);
         fence_barrier_init();
         mbar_expect_tx(s.bar, (uint32_t)L.bytes);
@@ -107,12 +113,39 @@ __device__ __forceinline__ void load_blob(const Smem &s, const Params &P, const 
 }
 
 // Write the blob back with one TMA bulk store.  Generic-proxy writes are fenced into the async proxy first.
-__device__ __forceinline__ void store_blob(const Smem &s, const Params &P, const BlobLayout &L, int e) {
+// publish_to / value: the env's epoch word, stored with release semantics once the bulk store has completed (every
+// thread's output stores precede the barrier, so the release covers them too).
+__device__ __forceinline__ void store_blob(const Smem &s, const Params &P, const BlobLayout &L, int e,
+                                           uint32_t *publish_to = nullptr, uint32_t value = 0) {
     fence_proxy_async();
     __syncthreads();
     if (threadIdx.x == 0) {
         tma_store_1d(P.blobs + (size_t)e * L.bytes, s.blob, (uint32_t)L.bytes);
-        tma_store_commit_wait();
+        if (publish_to == nullptr) {
+            tma_store_commit_wait();
+        } else {
+            tma_store_commit_wait_written();
+            fence_proxy_async_all();
+            __threadfence();
+            st_release_u32(publish_to, value);
+        }
+    }
+}
+
+// End of a CTA whose blob store was issued early (obs_pass early_store): wait until shared memory has been read out --
+// or, when the env is handed to the next launch (publish_to), until the blob is written, every thread's output stores
+// are issued (barrier) and then release the env's epoch word.
+__device__ __forceinline__ void finish_blob(uint32_t *publish_to, uint32_t value) {
+    if (publish_to == nullptr) {
+        if (threadIdx.x == 0) tma_store_wait_read();
+        return;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        tma_store_wait_written();
+        fence_proxy_async_all();
+        __threadfence();
+        st_release_u32(publish_to, value);
     }
 }
 
@@ -485,11 +518,24 @@ __device__ __forceinline__ unsigned long long knn_task(const float *lx, const fl
 // prebuilt: the entity table and the position lists already describe the current state and the CTA has synchronised
 // since they were written (k_step builds them while integrating).  No barrier at the end: the caller synchronises
 // before shared memory is written again.
+// early_store: the caller promises not to touch the env's blob image again; it is written back (one bulk store, issued
+// by thread 0, not waited for) as soon as the observation tasks have left their hints in it, so the store runs under the
+// gather; the caller ends with finish_blob().
 __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const BlobLayout &L, int e, float *dest,
-                                         const uint32_t *rng_words, uint32_t counter, bool prebuilt, int prof_slot) {
+                                         const uint32_t *rng_words, uint32_t counter, bool prebuilt, int prof_slot,
+                                         bool early_store = false) {
     const int tid = threadIdx.x, nt = blockDim.x;
     if (dest == nullptr) {
         if (tid == 0) s.sc->obs_counter = counter;  // callers have synchronised since every thread read the old value
+        if (early_store) {
+            fence_proxy_async();
+            __syncthreads();
+            if (tid == 0) {
+                fence_proxy_async();
+                tma_store_1d(P.blobs + (size_t)e * L.bytes, s.blob, (uint32_t)L.bytes);
+                tma_store_commit();
+            }
+        }
         return;
     }
     int n_obs_guards = s.misc[6];  // prebuilt: the caller's list of guards alive now
@@ -584,9 +630,17 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
             }
         }
     }
+    if (early_store) fence_proxy_async();  // this thread's writes to the blob image -> visible to the bulk store
     __syncthreads();
     DCA_PROF(P, e, prof_slot + 1);
-    if (tid == 0) s.sc->obs_counter = counter;
+    if (tid == 0) {
+        s.sc->obs_counter = counter;
+        if (early_store) {
+            fence_proxy_async();
+            tma_store_1d(P.blobs + (size_t)e * L.bytes, s.blob, (uint32_t)L.bytes);
+            tma_store_commit();
+        }
+    }
     // gather: 12 records of 64 B per guard; a pair of threads copies one record, each thread its 32-byte half with
     // one 256-bit store (STG.256), so a warp instruction writes 1 KB of contiguous obs.  Empty slots read the zero
     // record.  Half-record index of the k-th round = tid + k * nt.
@@ -774,12 +828,19 @@ __device__ __forceinline__ void push_shooter(const Smem &s, int i) {
 template <int NT, int TG, int TA>
 __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     const Params P, const int32_t *__restrict__ actions, const double *__restrict__ att_force,
-    const uint8_t *__restrict__ skip, const uint32_t *__restrict__ rng_words, int autoreset) {
+    const uint8_t *__restrict__ skip, const uint32_t *__restrict__ rng_words, int autoreset, const Pipe pipe) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
+#ifndef DCA_NO_STEP_TRIGGER
+    pdl_trigger();  // DCA_OPT_PIPELINE_STEPS: the planner launched behind this step may become resident in its last wave
+#endif
+    uint32_t *const my_epoch = pipe.epoch != nullptr ? pipe.epoch + e : nullptr;
     if (skip != nullptr) {
         pdl_wait();  // the pause mask may come from the kernel right before this one: no overlap when it is given
-        if (skip[e]) return;  // ENV-PAUSE shm_env.py:37-41: cached outputs stay in place
+        if (skip[e]) {  // ENV-PAUSE shm_env.py:37-41: cached outputs stay in place
+            if (my_epoch != nullptr && threadIdx.x == 0) st_release_u32(my_epoch, pipe.publish);
+            return;
+        }
     }
     const BlobLayout L = TG > 0 ? make_layout(TG, TA) : P.L;
     const DcaConfig &c = P.cfg;
@@ -787,7 +848,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     const int tid = threadIdx.x, nt = NT;
     DCA_PROF(P, e, 0);
     if (tid < 16) s.misc[tid] = 0;  // ordered before any use by the barrier inside load_blob
-    load_blob(s, P, L, e);
+    load_blob(s, P, L, e, pipe.wait_step ? my_epoch : nullptr, pipe.wait_step);
     DCA_PROF(P, e, 1);
 
     // env scalars into registers: nobody reads them from shared memory again, so thread 0 may update them freely
@@ -1036,8 +1097,10 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     // wall force core.py:210-222,339-353, integrate_state :282-302 (survivors only); then the agent's float32 entity
     // record and list position for the observation pass.
     // Everything above read only the env's own blob (and `skip`); actions and attacker forces may come from the kernel
-    // right before this one in the stream (DCA_OPT_OVERLAP_PLANNER), so order behind it here.
-    pdl_wait();
+    // right before this one in the stream (DCA_OPT_OVERLAP_PLANNER), so order behind it here -- behind the whole
+    // planner grid, or (DCA_OPT_PIPELINE_STEPS) behind the planner warp that filled this env's forces.
+    if (pipe.wait_plan) pipe_wait(pipe.epoch + P.E + e, pipe.wait_plan);
+    else pdl_wait();
     for (int q = tid; q < n_alive; q += nt) {
         const int i = s.alist[q];
         {
@@ -1125,15 +1188,25 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
     float *dest = do_reset ? P.out.tobs : P.out.obs;
     const uint32_t *words = rng_words;
     for (int pass = 0;; ++pass) {
-        obs_pass(s, P, L, e, dest, words, obs_counter + 1 + pass, pass == 0, pass == 0 ? 7 : 12);
-        if (pass == 1 || !do_reset) break;
+        const bool last = pass == 1 || !do_reset;  // the blob image is final once this pass's tasks are through
+#ifndef DCA_NO_EARLY_STORE
+        const bool early = last;
+#else
+        const bool early = false;  // diagnostics build: blob stored at the very end, as before
+#endif
+        obs_pass(s, P, L, e, dest, words, obs_counter + 1 + pass, pass == 0, pass == 0 ? 7 : 12, early);
+        if (last) break;
         reset_world(s, P, L, e);
         dest = P.out.obs;
         words = nullptr;
     }
     write_alive(s, P, L, e);
     DCA_PROF(P, e, 10);
-    store_blob(s, P, L, e);
+#ifndef DCA_NO_EARLY_STORE
+    finish_blob(my_epoch, pipe.publish);  // the bulk store has been in flight since the observation tasks ended
+#else
+    store_blob(s, P, L, e, my_epoch, pipe.publish);
+#endif
     DCA_PROF(P, e, 11);
     if (P.prof != nullptr && threadIdx.x == 0) {  // diagnostics: wall-clock end of the CTA (ns) and the SM it ran on
         unsigned long long gt;
@@ -1243,11 +1316,13 @@ __global__ void k_init_blobs(const Params P) {
 
 // ------------------------------------------------------------------ benchmark planner stand-in (one warp per env)
 // force = centroid(alive guards) - pos for alive attackers.  NOT the reference planner (cheat_script_ai.py:28-194).
-__global__ void k_plan_centroid(const Params P, double *__restrict__ att_force) {
+__global__ void k_plan_centroid(const Params P, double *__restrict__ att_force, const Pipe pipe) {
     pdl_trigger();  // a dca_step launched behind this kernel may start its force-independent phases now
     const BlobLayout &L = P.L;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= P.E) return;
+    if (pipe.wait_step) pipe_wait(pipe.epoch + warp, pipe.wait_step);  // this env's blob is final (every lane acquires)
+    else pdl_wait();  // launched as a programmatic dependent without the per-env hand-over: behind the whole grid
     const unsigned char *b = P.blobs + (size_t)warp * L.bytes;
     const double *px = (const double *)(b + L.px), *py = (const double *)(b + L.py);
     const uint8_t *fl = b + L.flags;
@@ -1266,6 +1341,10 @@ __global__ void k_plan_centroid(const Params P, double *__restrict__ att_force) 
     for (int a = lane; a < L.A; a += 32) {
         const bool alive = fl[L.G + a] & F_ALIVE;
         out[a] = alive ? make_double2(cx - px[L.G + a], cy - py[L.G + a]) : make_double2(0.0, 0.0);
+    }
+    if (pipe.epoch != nullptr) {
+        __syncwarp();
+        if (lane == 0) { __threadfence(); st_release_u32(pipe.epoch + P.E + warp, pipe.publish); }
     }
 }
 

@@ -487,7 +487,7 @@ template <int GC, int AC>
 __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const PlanState ps,
                                                           double *__restrict__ att_force,
                                                           const int32_t *__restrict__ inj_label,
-                                                          const double *__restrict__ inj_cent) {
+                                                          const double *__restrict__ inj_cent, const Pipe pipe) {
     static_assert(kPlanThreads == 32, "the shared-memory plan assumes one warp per env");
     extern __shared__ __align__(16) unsigned char plan_raw[];
     pdl_trigger();  // a dca_step launched behind this kernel may start its force-independent phases now
@@ -502,6 +502,8 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
     const uint8_t *bfl = blob + L.flags;
     double2 *out = (double2 *)att_force + (size_t)e * A;
     DCA_PROF(P, e, 0);
+    if (pipe.wait_step) pipe_wait(pipe.epoch + e, pipe.wait_step);  // DCA_OPT_PIPELINE_STEPS: this env's blob is final
+    else pdl_wait();
     for (int g = lane; g < G; g += 32) { s.gx[g] = bpx[g]; s.gy[g] = bpy[g]; s.galive[g] = bfl[g] & F_ALIVE; }
     for (int a = lane; a < A; a += 32) { s.ax[a] = bpx[G + a]; s.ay[a] = bpy[G + a]; s.aalive[a] = bfl[G + a] & F_ALIVE; }
     __syncwarp();
@@ -555,6 +557,10 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
     __syncwarp();
     if (n == 0) {  // no guard alive: nothing to aim at (the reference would raise); forces are zero
         for (int a = lane; a < A; a += 32) out[a] = make_double2(0.0, 0.0);
+        if (pipe.epoch != nullptr) {
+            __syncwarp();
+            if (lane == 0) { __threadfence(); st_release_u32(pipe.epoch + P.E + e, pipe.publish); }
+        }
         return;
     }
     for (int a = lane; a < n; a += 32) {
@@ -737,6 +743,10 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
             if (c.disable_red_function) { fx = -fx; fy = -fy; }
         }
         out[a] = make_double2(fx, fy);
+    }
+    if (pipe.epoch != nullptr) {
+        __syncwarp();
+        if (lane == 0) { __threadfence(); st_release_u32(pipe.epoch + P.E + e, pipe.publish); }
     }
     DCA_PROF(P, e, 9);
 }

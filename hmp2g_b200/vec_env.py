@@ -43,7 +43,7 @@ class DcaVecEnv(object):
     """n_env DCA envs resident on one GPU.  All tensors returned are views of buffers written in place."""
 
     def __init__(self, n_env, scfg=ScenarioConfig, device=None, seed=0, env_gid0=0, debug_outputs=False,
-                 empty_rows_nan=False, overlap_planner=True):
+                 empty_rows_nan=False, overlap_planner=True, pipeline_steps=False):
         if not torch.cuda.is_available():
             raise _lib.DcaError('hmp2g_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
         self.lib = _lib.load()
@@ -74,6 +74,8 @@ class DcaVecEnv(object):
             _lib.check(self.lib.dca_set_option(self.handle, 1, 1), self.handle)
         # DCA_OPT_OVERLAP_PLANNER: a step issued right behind plan() / plan_centroid() starts under the planner kernel
         _lib.check(self.lib.dca_set_option(self.handle, 2, int(bool(overlap_planner))), self.handle)
+        # DCA_OPT_PIPELINE_STEPS: plan / step / plan / step ... issued back to back hand envs over one by one
+        _lib.check(self.lib.dca_set_option(self.handle, 4, int(bool(pipeline_steps))), self.handle)
 
     # -- lifetime -----------------------------------------------------------------------
     def close(self):

@@ -273,6 +273,15 @@ int dca_mt_debug_phase_clocks(DcaMtHandle *h, uint64_t *clocks);
  * planner right before it reads them.  Results are identical; `nearest` may be overwritten while the planner runs.
  * Default 0. */
 #define DCA_OPT_OVERLAP_PLANNER 2
+/* DCA_OPT_PIPELINE_STEPS: a loop that issues plan / step / plan / step ... back to back on one stream (nothing between
+ * a dca_step and the next dca_plan* call, the same att_force) hands every env over individually instead of launch by
+ * launch: the planner warp of env e waits only for the step CTA of env e (which publishes a per-env epoch word once its
+ * blob is stored), the next step's CTA of env e only for that planner warp and for its own blob.  The kernels are
+ * launched as programmatic dependents of each other, so the first CTAs of launch t+1 run in the SM slots the last,
+ * partly filled wave of launch t leaves empty (a quarter of a 4096-env launch on 148 SMs).  Results are identical.
+ * Anything else on the stream (a policy reading obs, dca_reset, a pause mask) is ordered behind the whole previous
+ * launch as usual and restarts the pipeline.  Default 0. */
+#define DCA_OPT_PIPELINE_STEPS 4
 int dca_set_option(DcaHandle *h, int option, int value);
 
 const char *dca_last_error(const DcaHandle *h); /* host string; h may be NULL for create/gae errors */

@@ -477,6 +477,40 @@ def test_cuda_step_overlapping_its_planner_is_bit_identical(planner):
         assert np.array_equal(np.asarray(s0[k]).view(np.uint8), np.asarray(s1[k]).view(np.uint8)), k
 
 
+@pytest.mark.parametrize('planner', ['centroid', 'scripted'])
+def test_cuda_pipelined_steps_are_bit_identical(planner):
+    """DCA_OPT_PIPELINE_STEPS (plan / step / plan / step issued back to back: every env is handed from launch to launch
+    through its own epoch word, the launches overlap at their edges) must not change a single bit: 4096 envs (3.5 waves
+    of step CTAs, so launch t+1 really starts inside launch t), bursts of 1..40 launches without anything between
+    them, time-limit resets inside, compared with a strictly serial run after every burst."""
+    torch = _torch()
+    from hmp2g_b200.vec_env import DcaVecEnv
+    cfg = dict(num_guards=50, num_attackers=50, MaxEpisodeStep=40, random_jam_prob=0.05, introduce_terrain=True)
+    E = 4096
+    piped = DcaVecEnv(E, scfg=scenario_from_dict(cfg), seed=11, env_gid0=0, overlap_planner=True, pipeline_steps=True)
+    serial = DcaVecEnv(E, scfg=scenario_from_dict(cfg), seed=11, env_gid0=0, overlap_planner=False, pipeline_steps=False)
+    for env in (piped, serial):
+        env.reset()
+    gen = torch.Generator(device=piped.device)
+    gen.manual_seed(3)
+    pool = [torch.randint(0, 7, (E, 50), generator=gen, device=piped.device, dtype=torch.int32) for _ in range(16)]
+    t = 0
+    n_done = 0
+    for burst in ([1, 2, 3, 7, 27, 5, 40] if planner == 'centroid' else [1, 2, 7, 30, 12]):  # t = 40: every env is done
+        for env in (piped, serial):
+            for k in range(burst):   # nothing but plan + step on the stream inside a burst
+                force = env.plan_centroid() if planner == 'centroid' else env.plan()
+                env.step(pool[(t + k) % 16], force)
+        t += burst
+        for name in ('obs', 'tobs', 'reward', 'done', 'win', 'alive'):
+            assert torch.equal(getattr(piped, name), getattr(serial, name)), (t, name)
+        s0, s1 = piped.export_state(), serial.export_state()
+        for k in s0:
+            assert np.array_equal(np.asarray(s0[k]).view(np.uint8), np.asarray(s1[k]).view(np.uint8)), (t, k)
+        n_done += int(serial.done.sum().item())
+    assert t >= 47 and n_done >= E
+
+
 def test_cuda_advantage_normalisation_matches_numpy_formula():
     """adv = ret - value; (adv - adv.mean()) / (adv.std() + 1e-5) as ALGORITHM/conc/ppo.py:53-55 evaluates it on the
     pooled float32 numpy batch (population std); tolerance 1e-5 (the reference sums in float32, the kernel in fp64)."""
