@@ -47,7 +47,7 @@ st.update(reward[sl].to(dev), done[sl].to(dev), win[sl].to(dev))
 tot = st.reduce()
 ref = RolloutStats('cpu'); ref.update(reward, done, win)
 for k, v in zip(ref.FIELDS, ref.buf.tolist()):
-    assert abs(v - tot[k]) < 1e-6, (k, v, tot[k])
+    assert abs(v - tot[k]) <= 1e-4 * max(1.0, abs(v)), (k, v, tot[k])  # reward sums are float32 reductions on the device
 # env sharding: this rank's slice of a 2-rank run == the same global env ids in a run that holds all of them
 scfg = type('S', (ScenarioConfig,), dict(num_guards=50, num_attackers=50, MaxEpisodeStep=30))
 mine = DcaVecEnv(n, scfg=scfg, device=dev, seed=9, env_gid0=gid0)
