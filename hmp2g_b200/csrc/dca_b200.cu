@@ -543,6 +543,23 @@ int dca_norm_apply(const float *x, const float *mean, const float *var, uint64_t
     return DCA_OK;
 }
 
+int dca_conc_attend(const float *v, const float *x, const uint8_t *dead, const float *qk, int first, int n, int n_focus,
+                    uint64_t n_agent, float *va, float *stack, dca_stream_t stream) {
+    if (!v || !x || !dead || !qk || !va || !stack || n_agent == 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_conc_attend: null buffer or empty batch");
+    if (first < 1 || n < 1 || n > 32 || first + n > kPolEnt || n_focus < 1 || n_focus > n)
+        return fail(nullptr, DCA_E_INVALID, "dca_conc_attend: entity range must lie in [1, 24) and 1 <= n_focus <= n <= 32");
+    if (((uintptr_t)v | (uintptr_t)qk) & 15)
+        return fail(nullptr, DCA_E_INVALID, "dca_conc_attend: v and qk must be 16-byte aligned");
+    PtrDeviceGuard guard(v);
+    const size_t blocks = (n_agent * 32 + 255) / 256;
+    k_conc_attend<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(v, x, dead, qk, first, n, n_focus, (size_t)n_agent, va,
+                                                                       stack);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_conc_attend: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
 // ---- dca_adv_moments_static: the same two kernels with the per-CTA partials in a library-owned array ---------------
 // No counterpart in the reference; added for callers that cannot call cudaMalloc
 // (graph capture, serving loops).  The array lives in every GPU context that loads the library until exit.

@@ -114,4 +114,84 @@ __global__ void __launch_bounds__(256) k_norm_apply(const float4 *x, const float
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Concentration.forward ALGORITHM/common/conc.py:28-63 between its matrix products, for one list of entities of every
+// agent (conc_4hist: entities 1..11 = "current", 12..23 = "history", ALGORITHM/conc_4hist/net.py:170-181): attention
+// scores of the agent's own encoding against its entities, masked softmax (no live entity: all zero), the attended
+// encoding sum_j score_j ve_j (the caller multiplies by W_val), and the forward branch's input -- the agent's own
+// [encoding | observation] followed by those of the n_focus entities with the highest scores.  Ties (float32 softmax
+// gives several live entities exactly 0 when the attention is peaked) go to the lowest entity index: torch.argsort's
+// order among equal scores is unspecified and differs between its CPU and CUDA sorts; the stable order is what the
+// reference computes on the CPU.
+// One warp per agent.  v [B,24,48] encodings, x [B,24,16] normalised observations (NaN -> 0), dead u8 [B,24],
+// qk [B,48] = (vs Wq) Wk^T; out: va [B,48], stack [B,(n_focus+1)*64].
+constexpr int kPolH = 48, kPolD = 16, kPolEnt = 24;
+
+__global__ void __launch_bounds__(256) k_conc_attend(const float *__restrict__ v, const float *__restrict__ x,
+                                                      const uint8_t *__restrict__ dead, const float *__restrict__ qk,
+                                                      int first, int n, int n_focus, size_t B, float *__restrict__ va,
+                                                      float *__restrict__ stack) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const size_t b = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= B) return;  // warp-uniform
+    const float *vb = v + b * kPolEnt * kPolH;
+    const float *xb = x + b * kPolEnt * kPolD;
+    // scores: lane j < n owns entity first + j
+    float compat = -CUDART_INF_F;
+    if (lane < n && !dead[b * kPolEnt + first + lane]) {
+        const float4 *row = (const float4 *)(vb + (first + lane) * kPolH);
+        const float4 *q4 = (const float4 *)(qk + b * kPolH);
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < kPolH / 4; ++k) {
+            const float4 a = row[k], q = q4[k];
+            acc = fmaf(a.x, q.x, acc); acc = fmaf(a.y, q.y, acc); acc = fmaf(a.z, q.z, acc); acc = fmaf(a.w, q.w, acc);
+        }
+        compat = acc * 0.14433756729740643f;  // 1 / sqrt(48)
+    }
+    float mx = compat;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(full, mx, o));
+    float ex = (lane < n && compat > -CUDART_INF_F) ? expf(compat - mx) : 0.f;
+    float sum = ex;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(full, sum, o);
+    const float score = sum > 0.f ? __fdiv_rn(ex, sum) : 0.f;  // nan_to_num(softmax(all -inf)) = 0
+    // attended encoding: lanes own dims lane and lane + 32 (< 48)
+    {
+        float a0 = 0.f, a1 = 0.f;
+        for (int j = 0; j < n; ++j) {
+            const float sj = __shfl_sync(full, score, j);
+            const float *row = vb + (first + j) * kPolH;
+            a0 = fmaf(sj, row[lane], a0);
+            if (lane < kPolH - 32) a1 = fmaf(sj, row[32 + lane], a1);
+        }
+        va[b * kPolH + lane] = a0;
+        if (lane < kPolH - 32) va[b * kPolH + 32 + lane] = a1;
+    }
+    // forward branch input: [vs | zs], then the n_focus best entities in stable descending score order
+    const int row_len = kPolH + kPolD;  // 64
+    float *sb = stack + b * (size_t)(n_focus + 1) * row_len;
+    {
+        sb[lane] = vb[lane];
+        if (lane < kPolH - 32) sb[32 + lane] = vb[32 + lane];
+        else sb[32 + lane] = xb[lane - (kPolH - 32)];  // lanes 16..31 -> x[0..15]
+    }
+    unsigned taken = 0;
+    for (int r = 1; r <= n_focus; ++r) {
+        // the highest remaining score; scores are >= 0, so their bit patterns order like the values
+        const unsigned key = (lane < n && !((taken >> lane) & 1u)) ? __float_as_uint(score) + 1u : 0u;
+        const unsigned best = __reduce_max_sync(full, key);
+        const int j = __ffs(__ballot_sync(full, key == best && key != 0u)) - 1;  // lowest index among equals
+        taken |= 1u << j;
+        const float *vr = vb + (first + j) * kPolH;
+        const float *xr = xb + (first + j) * kPolD;
+        float *o = sb + r * row_len;
+        o[lane] = vr[lane];
+        if (lane < kPolH - 32) o[32 + lane] = vr[32 + lane];
+        else o[32 + lane] = xr[lane - (kPolH - 32)];
+    }
+}
+
 }  // namespace dca

@@ -145,6 +145,23 @@ class ConcCore(nn.Module):
         v_c = self.AT_forward_mlp(stack.reshape(stack.shape[0], -1))
         return v_c, v_m
 
+    def forward_fused(self, v, x, dead_u8, first, n):
+        """The same on the whole [B,24,*] tensors with the part between the matrix products in one kernel
+        (dca_conc_attend: scores, masked softmax, attended encoding, stable top-n_focus gather): v f32 [B,24,h] entity
+        encodings, x f32 [B,24,d] normalised observations, dead_u8 [B,24]; the list is entities first .. first+n-1."""
+        lib = _lib.load()
+        B = v.shape[0]
+        vs = v[:, 0]
+        qk = ((vs @ self.CT_W_query) @ self.CT_W_key.t()).contiguous()
+        va = torch.empty((B, self.h_dim), dtype=torch.float32, device=v.device)
+        stack = torch.empty((B, (self.n_focus_on + 1) * (self.h_dim + x.shape[-1])), dtype=torch.float32, device=v.device)
+        stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
+        _lib.check(lib.dca_conc_attend(_ptr(v), _ptr(x), _ptr(dead_u8), _ptr(qk), first, n, self.n_focus_on, B, _ptr(va),
+                                       _ptr(stack), stream))
+        v_m = self.CT_motivate_mlp(torch.cat((vs, va @ self.CT_W_val), -1))
+        v_c = self.AT_forward_mlp(stack)
+        return v_c, v_m
+
 
 class ConcNet4Hist(nn.Module):
     """Net(rawob_dim=16, n_action=7, n_focus_on, dual_conc=True) of ALGORITHM/conc_4hist/net.py:87-233 for the rollout
@@ -173,6 +190,8 @@ class ConcNet4Hist(nn.Module):
         net.load_state_dict(sd)
         return net.to(device)
 
+    fused = True  # dca_conc_attend instead of torch bmm / softmax / sort / gather / cat between the matrix products
+
     @torch.no_grad()
     def heads(self, obs_feed, chunk=1 << 18):
         """obs_feed f32 [..., 24, D] (empty rows NaN, a dead agent all NaN) -> (logits [..., n_action], value [...],
@@ -180,7 +199,8 @@ class ConcNet4Hist(nn.Module):
         lead = obs_feed.shape[:-2]
         x, dead = self._batch_norm(obs_feed)
         x = x.reshape(-1, 24, self.rawob_dim)
-        dead = dead.reshape(-1, 24).bool()
+        dead_u8 = dead.reshape(-1, 24)
+        dead = dead_u8.bool()
         B = x.shape[0]
         logits = torch.empty((B, self.n_action), dtype=torch.float32, device=x.device)
         value = torch.empty((B,), dtype=torch.float32, device=x.device)
@@ -188,8 +208,13 @@ class ConcNet4Hist(nn.Module):
         for b0 in range(0, B, chunk):
             xs, ds = x[b0:b0 + chunk], dead[b0:b0 + chunk]
             v = self.AT_obs_encoder(xs)
-            vf_c, vf_m = self.MIX_conc_core_f(v[:, 0], v[:, 1:12], ds[:, 1:12], xs[:, 1:12], xs[:, 0])
-            vh_c, vh_m = self.MIX_conc_core_h(v[:, 0], v[:, 12:24], ds[:, 12:24], xs[:, 12:24], xs[:, 0])
+            if self.fused and v.is_cuda and self.H == 48 and self.rawob_dim == 16:
+                du = dead_u8[b0:b0 + chunk]
+                vf_c, vf_m = self.MIX_conc_core_f.forward_fused(v, xs, du, 1, 11)
+                vh_c, vh_m = self.MIX_conc_core_h.forward_fused(v, xs, du, 12, 12)
+            else:
+                vf_c, vf_m = self.MIX_conc_core_f(v[:, 0], v[:, 1:12], ds[:, 1:12], xs[:, 1:12], xs[:, 0])
+                vh_c, vh_m = self.MIX_conc_core_h(v[:, 0], v[:, 12:24], ds[:, 12:24], xs[:, 12:24], xs[:, 0])
             logits[b0:b0 + chunk] = self.AT_get_logit_db(torch.cat((vf_c, vh_c), -1))
             vm = torch.cat((vf_m, vh_m), -1)
             value[b0:b0 + chunk] = self.CT_get_value(vm)[:, 0]

@@ -209,6 +209,16 @@ int dca_norm_moments(const float *x, uint64_t rows, int dim, double *scratch, do
 int dca_norm_apply(const float *x, const float *mean, const float *var, uint64_t rows, int dim, float *y,
                    uint8_t *row_nan, dca_stream_t stream);
 
+/* replaces: the part of Concentration.forward between its matrix products, ALGORITHM/common/conc.py:30-58 (masked
+ * softmax attention of the agent's own encoding over one entity list, attended encoding, top-n_focus gather with the
+ * skip connection), for the conc / conc_4hist policy (ALGORITHM/conc_4hist/net.py:205-207).  One warp per agent.
+ *   v f32 [B,24,48] entity encodings, x f32 [B,24,16] normalised observations, dead u8 [B,24] (dca_norm_apply's row mask),
+ *   qk f32 [B,48] = (vs W_query) W_key^T; the list is entities first .. first+n-1 of the 24.
+ *   va f32 [B,48] = sum_j score_j ve_j (multiply by W_val); stack f32 [B,(n_focus+1)*64] = [vs|zs] ++ the n_focus
+ *   entities with the highest scores, [ve|ze] each, ties to the lowest entity index. */
+int dca_conc_attend(const float *v, const float *x, const uint8_t *dead, const float *qk, int first, int n, int n_focus,
+                    uint64_t n_agent, float *va, float *stack, dca_stream_t stream);
+
 /* ---- dca_multiteam -------------------------------------------------------------------------------------------------
  * The sibling env MISSION/dca_multiteam (N teams, every agent policy-controlled, per-hit success draw, shrinking kill
  * circle, team ranking).  Same conventions as the dca_* calls above. */

@@ -138,3 +138,57 @@ def test_cuda_planner_native_matches_oracle_in_a_rollout(cfg, E, steps):
         env.import_state(o.state)
     assert n_done > 0
     assert np.abs(want).max() > 0.1
+
+
+@pytest.mark.gpu
+def test_keyed_planner_episode_statistics_match_reference():
+    """The one statistical sub-step: the k-means++ team draws come from the keyed stream, not from
+    numpy's MT19937, so team composition is the reference's in distribution only.  640 episodes of the unmodified
+    reference env with its own sklearn / scipy planner under uniform random guard actions
+    (tests/golden/planner_stats_50v50.json, oracle/make_golden_planner_stats.py) against 640 episodes of the GPU env with
+    k_plan (320 envs x their first two episodes): episode length, guard win rate, share of time-limit endings and
+    guards alive at the end within sampling error."""
+    import json
+    import torch
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.vec_env import DcaVecEnv
+    ref = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'planner_stats_50v50.json')))
+    assert ref['episodes'] >= 500
+    scfg = type('S', (ScenarioConfig,), dict(num_guards=50, num_attackers=50, size=5.0, random_jam_prob=0.05,
+                                             introduce_terrain=True, terrain_parameters=[0.05, 0.2], MaxEpisodeStep=180,
+                                             half_death_reward=True, init_distance=4))
+    E, per_env = 320, 2
+    env = DcaVecEnv(E, scfg=scfg, seed=31337)
+    env.reset()
+    g = torch.Generator(device=env.device)
+    g.manual_seed(5)
+    ep = np.zeros(E, int); cur = np.zeros(E, int)
+    lens, wins, alive_end = [], [], []
+    for t in range(per_env * 181 + 2):
+        act = torch.randint(0, 7, (E, 50), generator=g, device=env.device, dtype=torch.int32)
+        env.step(act)   # plan() inside: the scripted attackers
+        done = env.done.cpu().numpy().astype(bool)
+        cur += 1
+        if done.any():
+            win = env.win.cpu().numpy()
+            tob = env.tobs.cpu().numpy()
+            for e in np.nonzero(done)[0]:
+                if ep[e] < per_env:
+                    lens.append(cur[e]); wins.append(bool(win[e])); alive_end.append(int((tob[e, :, 0, 0] > 0).sum()))
+                ep[e] += 1; cur[e] = 0
+        if (ep >= per_env).all():
+            break
+    n, n_ref = len(lens), ref['episodes']
+    assert n == E * per_env
+    mean_len, tl = float(np.mean(lens)), float(np.mean(np.array(lens) >= 180))
+    print('keyed planner: %d episodes, length %.1f +- %.1f (reference %.1f +- %.1f), time-limit endings %.3f (%.3f), guard '
+          'wins %.3f (%.3f), guards alive at the end %.3f (%.3f)' % (
+              n, mean_len, np.std(lens), ref['mean_len'], ref['std_len'], tl, ref['frac_time_limit'], np.mean(wins),
+              ref['guard_win_rate'], np.mean(alive_end), ref['mean_guards_alive_at_end']))
+    se_len = np.sqrt(np.var(lens) / n + ref['std_len'] ** 2 / n_ref)
+    assert abs(mean_len - ref['mean_len']) <= 4 * se_len + 1.0
+    p = 0.5 * (tl + ref['frac_time_limit'])
+    assert abs(tl - ref['frac_time_limit']) <= 4 * np.sqrt(max(p * (1 - p), 1e-4) * (1.0 / n + 1.0 / n_ref)) + 0.01
+    assert abs(np.mean(wins) - ref['guard_win_rate']) <= 0.02
+    se_a = np.sqrt(np.var(alive_end) / n + ref['std_guards_alive_at_end'] ** 2 / n_ref)
+    assert abs(np.mean(alive_end) - ref['mean_guards_alive_at_end']) <= 4 * se_a + 0.05
