@@ -252,6 +252,16 @@ def policy_rollout_run(E, dev, rank, world, steps=60, warm=10):
         roll.step()
     t1.record(stream)
     torch.cuda.synchronize()
+    ms_eager = t0.elapsed_time(t1) / steps
+    replay = roll.capture(warm=2)   # the same step as one CUDA graph launch
+    for _ in range(3):
+        replay()
+    torch.cuda.synchronize()
+    t0.record(stream)
+    for _ in range(steps):
+        replay()
+    t1.record(stream)
+    torch.cuda.synchronize()
     ms = t0.elapsed_time(t1) / steps
     # the policy forward alone (history roll + normalisation + Net.act) on the last observation
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -270,11 +280,13 @@ def policy_rollout_run(E, dev, rank, world, steps=60, warm=10):
     out = {'workload': 'RESULT/50RL-55opp: DCA 50 guards (conc_4hist policy, shipped model.pt, sampled actions) vs 55 '
                        'scripted attackers (k_plan), %d envs/GPU, device-resident loop' % E,
            'value': world * E * env.N / (ms * 1e-3), 'unit': 'agent-steps/s', 'ms_per_step': ms,
-           'policy_ms': ms_policy, 'env_ms': ms - ms_policy, 'steps': steps,
+           'ms_per_step_eager': ms_eager, 'launch': 'one CUDA graph per env step (PolicyRollout.capture)',
+           'policy_forward_ms_eager': ms_policy, 'steps': steps,
            'gae_and_advantage_ms': g0.elapsed_time(g1), 'rollout_buffer_TEG': list(roll.buf.reward.shape),
            'episodes_finished': int(roll.episodes.item()), 'wins': int(roll.wins.item()),
-           'policy': 'torch fp32 (cuBLAS) Net of hmp2g_b200/policy.py; normalisation moments / apply, history roll, '
-                     'planner, step, GAE: this library',
+           'policy': 'ConcNet4Hist (hmp2g_b200/policy.py): encoder + normalisation (k_policy_encode), attention / top-k '
+                     '(k_conc_attend), moments, history roll, planner, step, GAE: this library; the remaining [agents, '
+                     '48..256] x [.., 48] products: torch fp32 (cuBLAS)',
            'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}
     del roll, env, net
     torch.cuda.empty_cache()

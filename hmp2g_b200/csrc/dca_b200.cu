@@ -560,6 +560,31 @@ int dca_conc_attend(const float *v, const float *x, const uint8_t *dead, const f
     return DCA_OK;
 }
 
+int dca_policy_encode(const float *x, const float *mean, const float *var, const float *w1, const float *b1,
+                      const float *w2, const float *b2, uint64_t rows, float *x_norm, uint8_t *row_nan, float *v,
+                      dca_stream_t stream) {
+    if (!x || !mean || !var || !w1 || !b1 || !w2 || !b2 || !x_norm || !row_nan || !v || rows == 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_policy_encode: null buffer or empty batch");
+    if (((uintptr_t)x | (uintptr_t)x_norm | (uintptr_t)mean | (uintptr_t)var | (uintptr_t)v) & 15)
+        return fail(nullptr, DCA_E_INVALID, "dca_policy_encode: buffers must be 16-byte aligned");
+    PtrDeviceGuard guard(x);
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t ea = cudaFuncSetAttribute(k_policy_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+        if (ea != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_encode: ") + cudaGetErrorString(ea));
+        attr_set[dev] = true;
+    }
+    const size_t tiles = (rows + kEncTile - 1) / kEncTile;
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, 148 * 4);
+    k_policy_encode<<<grid, kEncThreads, sizeof(EncSmem), (cudaStream_t)stream>>>(
+        (const float4 *)x, mean, var, w1, b1, w2, b2, (size_t)rows, (float4 *)x_norm, row_nan, v);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_encode: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
 // ---- dca_adv_moments_static: the same two kernels with the per-CTA partials in a library-owned array ---------------
 // No counterpart in the reference; added for callers that cannot call cudaMalloc
 // (graph capture, serving loops).  The array lives in every GPU context that loads the library until exit.

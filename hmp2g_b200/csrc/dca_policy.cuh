@@ -194,4 +194,130 @@ __global__ void __launch_bounds__(256) k_conc_attend(const float *__restrict__ v
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// The observation encoder of the conc / conc_4hist policy on every entity row (Net._act ALGORITHM/conc_4hist/net.py:
+// 194-199): DynamicNorm apply + mask + nan_to_num (as k_norm_apply) + AT_obs_encoder = Linear(16,48), ReLU,
+// Linear(48,48), in one pass.  This is 60 % of the policy's arithmetic (24 entity rows per agent, 3 072 multiply-adds
+// each) and in torch four passes over a [rows, 48] activation plus two bias-epilogue kernels.  float32 FFMA (the policy's
+// attention logits reach the hundreds: tf32 inputs would move its picks), register-blocked like an SGEMM: a CTA owns a
+// tile of 128 rows, the normalised rows and the hidden activations sit in shared memory k-major, a thread accumulates
+// 8 rows x 6 columns (5 shared loads per 48 FFMA), the grid is persistent so the 12 KB of weights are staged once.
+// nn.Linear layout: w1 [48,16], w2 [48,48] (out, in).
+constexpr int kEncTile = 128, kEncThreads = 128;
+struct EncSmem {
+    float xs[kPolD][kEncTile];   // normalised observation rows, k-major
+    float hs[kPolH][kEncTile];   // hidden activations after the ReLU, k-major
+    float w1[kPolD][kPolH];      // w1^T
+    float w2[kPolH][kPolH];      // w2^T
+    float b1[kPolH], b2[kPolH];
+};
+
+__global__ void __launch_bounds__(kEncThreads) k_policy_encode(const float4 *__restrict__ x, const float *__restrict__ mean,
+                                                               const float *__restrict__ var,
+                                                               const float *__restrict__ w1, const float *__restrict__ b1,
+                                                               const float *__restrict__ w2, const float *__restrict__ b2,
+                                                               size_t rows, float4 *__restrict__ x_norm,
+                                                               uint8_t *__restrict__ row_nan, float *__restrict__ v) {
+    extern __shared__ __align__(16) unsigned char enc_raw[];
+    EncSmem &s = *reinterpret_cast<EncSmem *>(enc_raw);
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x, lane = tid & 31, quad = tid & 3;
+    for (int i = tid; i < kPolD * kPolH; i += kEncThreads) s.w1[i % kPolD][i / kPolD] = w1[i];  // w1[j][k] -> w1s[k][j]
+    for (int i = tid; i < kPolH * kPolH; i += kEncThreads) s.w2[i % kPolH][i / kPolH] = w2[i];
+    if (tid < kPolH) { s.b1[tid] = b1[tid]; s.b2[tid] = b2[tid]; }
+    const float4 m = ((const float4 *)mean)[quad], vv = ((const float4 *)var)[quad];
+    const float sd[4] = {__fsqrt_rn(__fadd_rn(vv.x, 1e-8f)), __fsqrt_rn(__fadd_rn(vv.y, 1e-8f)),
+                         __fsqrt_rn(__fadd_rn(vv.z, 1e-8f)), __fsqrt_rn(__fadd_rn(vv.w, 1e-8f))};
+    const float mu[4] = {m.x, m.y, m.z, m.w};
+    const int rg = tid >> 3, cg = tid & 7;  // this thread's 8 rows (rg*8 ..) and 6 columns (cg*6 ..)
+    const size_t tiles = (rows + kEncTile - 1) / kEncTile;
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const size_t r0 = tile * kEncTile;
+        __syncthreads();  // the previous tile's shared activations have been consumed; weights are in place
+        // ---- load + normalise 128 rows (4 float4 per thread; a lane quad holds one row)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int i = tid + q * kEncThreads, lr = i >> 2;  // local row, quad = i & 3 = tid & 3
+            const size_t row = r0 + lr;
+            float e[4] = {0.f, 0.f, 0.f, 0.f};
+            const bool in = row < rows;
+            if (in) {
+                const float4 t = x[row * 4 + quad];
+                e[0] = t.x; e[1] = t.y; e[2] = t.z; e[3] = t.w;
+            }
+            bool bad = false;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (e[k] != e[k]) { bad = true; e[k] = 0.f; }
+                else e[k] = fminf(fmaxf(__fdiv_rn(__fsub_rn(e[k], mu[k]), sd[k]), -10.f), 10.f);
+            }
+            const unsigned bb = __ballot_sync(full, bad);
+            if (in) {
+                x_norm[row * 4 + quad] = make_float4(e[0], e[1], e[2], e[3]);
+                if (quad == 0) row_nan[row] = ((bb >> lane) & 0xfu) != 0;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s.xs[quad * 4 + k][lr] = e[k];
+        }
+        __syncthreads();
+        // ---- layer 1: h = relu(x w1^T + b1)
+        float acc[8][6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            const float bias = s.b1[cg * 6 + c];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) acc[r][c] = bias;
+        }
+#pragma unroll 4
+        for (int k = 0; k < kPolD; ++k) {
+            const float4 a0 = *(const float4 *)&s.xs[k][rg * 8], a1 = *(const float4 *)&s.xs[k][rg * 8 + 4];
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float2 w01 = *(const float2 *)&s.w1[k][cg * 6], w23 = *(const float2 *)&s.w1[k][cg * 6 + 2],
+                         w45 = *(const float2 *)&s.w1[k][cg * 6 + 4];
+            const float w[6] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y};
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int c = 0; c < 6; ++c) acc[r][c] = fmaf(a[r], w[c], acc[r][c]);
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            *(float4 *)&s.hs[cg * 6 + c][rg * 8] = make_float4(fmaxf(acc[0][c], 0.f), fmaxf(acc[1][c], 0.f),
+                                                              fmaxf(acc[2][c], 0.f), fmaxf(acc[3][c], 0.f));
+            *(float4 *)&s.hs[cg * 6 + c][rg * 8 + 4] = make_float4(fmaxf(acc[4][c], 0.f), fmaxf(acc[5][c], 0.f),
+                                                                  fmaxf(acc[6][c], 0.f), fmaxf(acc[7][c], 0.f));
+        }
+        __syncthreads();
+        // ---- layer 2: v = h w2^T + b2
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            const float bias = s.b2[cg * 6 + c];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) acc[r][c] = bias;
+        }
+#pragma unroll 4
+        for (int k = 0; k < kPolH; ++k) {
+            const float4 a0 = *(const float4 *)&s.hs[k][rg * 8], a1 = *(const float4 *)&s.hs[k][rg * 8 + 4];
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float2 w01 = *(const float2 *)&s.w2[k][cg * 6], w23 = *(const float2 *)&s.w2[k][cg * 6 + 2],
+                         w45 = *(const float2 *)&s.w2[k][cg * 6 + 4];
+            const float w[6] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y};
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int c = 0; c < 6; ++c) acc[r][c] = fmaf(a[r], w[c], acc[r][c]);
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const size_t row = r0 + rg * 8 + r;
+            if (row < rows) {
+                float2 *o = (float2 *)(v + row * kPolH + cg * 6);
+                o[0] = make_float2(acc[r][0], acc[r][1]);
+                o[1] = make_float2(acc[r][2], acc[r][3]);
+                o[2] = make_float2(acc[r][4], acc[r][5]);
+            }
+        }
+    }
+}
+
 }  // namespace dca

@@ -83,11 +83,12 @@ class DynamicNormDevice(nn.Module):
         new_var = torch.clamp(m2 / torch.clamp(tot, min=1.0), min=0.01, max=1000.0)
         some = n > 0                                                # an empty batch changes nothing (norm.py:41-44)
         filt = self.one_hot_filter & ~((nonunit > 0) & some)
-        self.one_hot_filter.data = filt
         keep = filt | ~some
-        self.mean.data = torch.where(keep, self.mean, new_mean.to(torch.float32))
-        self.var.data = torch.where(keep, self.var, new_var.to(torch.float32))
-        self.n_sample.data = (n0 + n).round().to(torch.long).reshape(1)
+        # in place: the parameters keep their addresses (a captured CUDA graph replays these updates)
+        self.one_hot_filter.data.copy_(filt)
+        self.mean.data.copy_(torch.where(keep, self.mean, new_mean.to(torch.float32)))
+        self.var.data.copy_(torch.where(keep, self.var, new_var.to(torch.float32)))
+        self.n_sample.data.copy_((n0 + n).round().to(torch.long).reshape(1))
         return self
 
     def apply_norm(self, x, out=None):
@@ -190,17 +191,49 @@ class ConcNet4Hist(nn.Module):
         net.load_state_dict(sd)
         return net.to(device)
 
-    fused = True  # dca_conc_attend instead of torch bmm / softmax / sort / gather / cat between the matrix products
+    fused = True  # dca_policy_encode / dca_conc_attend instead of torch elementwise + GEMM + bmm / sort / gather passes
+
+    def encode_fused(self, obs_feed):
+        """DynamicNorm apply + mask + AT_obs_encoder in one kernel: -> (x f32 [B,24,D], dead u8 [B,24], v f32 [B,24,H])."""
+        lib = _lib.load()
+        x2 = obs_feed.reshape(-1, self.rawob_dim)
+        assert x2.is_cuda and x2.dtype == torch.float32 and x2.is_contiguous()
+        R = x2.shape[0]
+        xn = torch.empty_like(x2)
+        dead = torch.empty((R,), dtype=torch.uint8, device=x2.device)
+        v = torch.empty((R, self.H), dtype=torch.float32, device=x2.device)
+        bn, enc = self._batch_norm, self.AT_obs_encoder
+        stream = C.c_void_p(torch.cuda.current_stream(x2.device).cuda_stream)
+        _lib.check(lib.dca_policy_encode(_ptr(x2), _ptr(bn.mean.data), _ptr(bn.var.data), _ptr(enc[0].weight.data),
+                                         _ptr(enc[0].bias.data), _ptr(enc[2].weight.data), _ptr(enc[2].bias.data), R,
+                                         _ptr(xn), _ptr(dead), _ptr(v), stream))
+        return xn.reshape(-1, 24, self.rawob_dim), dead.reshape(-1, 24), v.reshape(-1, 24, self.H)
+
+    def _tail(self, vf_c, vf_m, vh_c, vh_m):
+        logits = self.AT_get_logit_db(torch.cat((vf_c, vh_c), -1))
+        vm = torch.cat((vf_m, vh_m), -1)
+        value = self.CT_get_value(vm)[:, 0]
+        t = self.CT_get_threat(vm)[:, 0]
+        r = 0.5 * 11
+        return logits, value, (torch.tanh(t / r) + 1.0) * r                   # re_scale, net.py:226-229
 
     @torch.no_grad()
     def heads(self, obs_feed, chunk=1 << 18):
         """obs_feed f32 [..., 24, D] (empty rows NaN, a dead agent all NaN) -> (logits [..., n_action], value [...],
-        threat [...]).  Agents are processed `chunk` at a time (default: 4096 x 50 agents in one pass, about 2 GB of activations)."""
+        threat [...]).  On the device with the fused kernels everything runs in one pass; the torch path processes
+        `chunk` agents at a time."""
         lead = obs_feed.shape[:-2]
+        if self.fused and obs_feed.is_cuda and self.H == 48 and self.rawob_dim == 16:
+            if self._batch_norm.training:
+                self._batch_norm.update(obs_feed)
+            x, dead_u8, v = self.encode_fused(obs_feed)
+            vf_c, vf_m = self.MIX_conc_core_f.forward_fused(v, x, dead_u8, 1, 11)
+            vh_c, vh_m = self.MIX_conc_core_h.forward_fused(v, x, dead_u8, 12, 12)
+            logits, value, threat = self._tail(vf_c, vf_m, vh_c, vh_m)
+            return logits.reshape(*lead, self.n_action), value.reshape(lead), threat.reshape(lead)
         x, dead = self._batch_norm(obs_feed)
         x = x.reshape(-1, 24, self.rawob_dim)
-        dead_u8 = dead.reshape(-1, 24)
-        dead = dead_u8.bool()
+        dead = dead.reshape(-1, 24).bool()
         B = x.shape[0]
         logits = torch.empty((B, self.n_action), dtype=torch.float32, device=x.device)
         value = torch.empty((B,), dtype=torch.float32, device=x.device)
@@ -208,19 +241,9 @@ class ConcNet4Hist(nn.Module):
         for b0 in range(0, B, chunk):
             xs, ds = x[b0:b0 + chunk], dead[b0:b0 + chunk]
             v = self.AT_obs_encoder(xs)
-            if self.fused and v.is_cuda and self.H == 48 and self.rawob_dim == 16:
-                du = dead_u8[b0:b0 + chunk]
-                vf_c, vf_m = self.MIX_conc_core_f.forward_fused(v, xs, du, 1, 11)
-                vh_c, vh_m = self.MIX_conc_core_h.forward_fused(v, xs, du, 12, 12)
-            else:
-                vf_c, vf_m = self.MIX_conc_core_f(v[:, 0], v[:, 1:12], ds[:, 1:12], xs[:, 1:12], xs[:, 0])
-                vh_c, vh_m = self.MIX_conc_core_h(v[:, 0], v[:, 12:24], ds[:, 12:24], xs[:, 12:24], xs[:, 0])
-            logits[b0:b0 + chunk] = self.AT_get_logit_db(torch.cat((vf_c, vh_c), -1))
-            vm = torch.cat((vf_m, vh_m), -1)
-            value[b0:b0 + chunk] = self.CT_get_value(vm)[:, 0]
-            t = self.CT_get_threat(vm)[:, 0]
-            r = 0.5 * 11
-            threat[b0:b0 + chunk] = (torch.tanh(t / r) + 1.0) * r              # re_scale, net.py:226-229
+            vf_c, vf_m = self.MIX_conc_core_f(v[:, 0], v[:, 1:12], ds[:, 1:12], xs[:, 1:12], xs[:, 0])
+            vh_c, vh_m = self.MIX_conc_core_h(v[:, 0], v[:, 12:24], ds[:, 12:24], xs[:, 12:24], xs[:, 0])
+            logits[b0:b0 + chunk], value[b0:b0 + chunk], threat[b0:b0 + chunk] = self._tail(vf_c, vf_m, vh_c, vh_m)
         return logits.reshape(*lead, self.n_action), value.reshape(lead), threat.reshape(lead)
 
     @torch.no_grad()
@@ -269,7 +292,28 @@ class PolicyRollout(object):
         if collect:
             self.buf.add(alive_before, value, reward, done)
             self.steps_in_finished += torch.where(fin, lens_before + 1, torch.zeros_like(lens_before)).sum()
-        self.suffered = done.clone()
+        self.suffered.copy_(done)   # in place: a captured graph reads the same buffer next step
         self.episodes += fin.sum()
         self.wins += (fin & (win != 0)).sum()
         return fin
+
+    def capture(self, warm=3, collect=True):
+        """Capture one step() as a CUDA graph (every op of the loop is an asynchronous launch on the current stream: the
+        library's kernels through the C-ABI, torch's GEMMs, the Categorical draw) and return a callable that replays it
+        -- one cudaGraphLaunch per env step instead of ~80 launches, which is what bounds a 4 ms step on the host.
+        The replayed step writes the same tensors every time (`finished` below, env.obs / reward / done, the rollout
+        buffer).  DCA_OPT_PIPELINE_STEPS keeps host-side epoch counters and must stay off on a captured env."""
+        for _ in range(warm):   # allocations, lazy module loads and per-function attributes happen outside the capture
+            self.step(collect)
+        torch.cuda.synchronize(self.env.device)
+        graph = torch.cuda.CUDAGraph()
+        if hasattr(graph, 'register_generator_state'):
+            graph.register_generator_state(self.gen)
+        with torch.cuda.graph(graph):
+            fin = self.step(collect)
+        self._graph, self.finished = graph, fin
+
+        def replay():
+            graph.replay()
+            return fin
+        return replay

@@ -98,5 +98,5 @@ class DeviceRollout(object):
         valid_te = torch.arange(self.T, device=lens.device)[:, None] < lens[None, :]
         adv = normalized_advantage(ret, self.value, valid=valid_te, group=group)
         valid = valid_te[:, :, None].expand_as(ret)
-        self.length = torch.where(finished, torch.zeros_like(self.length), self.length)
+        self.length.copy_(torch.where(finished, torch.zeros_like(self.length), self.length))  # in place (CUDA graphs)
         return ret, threat, adv, valid

@@ -209,6 +209,14 @@ int dca_norm_moments(const float *x, uint64_t rows, int dim, double *scratch, do
 int dca_norm_apply(const float *x, const float *mean, const float *var, uint64_t rows, int dim, float *y,
                    uint8_t *row_nan, dca_stream_t stream);
 
+/* replaces: DynamicNorm apply + mask + nan_to_num + AT_obs_encoder (Linear 16->48, ReLU, Linear 48->48) of Net._act
+ * ALGORITHM/conc_4hist/net.py:194-199 on every entity row, fused (float32 FFMA, nn.Linear layouts w1 [48,16], w2 [48,48]).
+ *   x f32 [rows,16] raw observation rows (NaN rows = empty / dead); x_norm f32 [rows,16], row_nan u8 [rows] as
+ *   dca_norm_apply; v f32 [rows,48] encodings. */
+int dca_policy_encode(const float *x, const float *mean, const float *var, const float *w1, const float *b1,
+                      const float *w2, const float *b2, uint64_t rows, float *x_norm, uint8_t *row_nan, float *v,
+                      dca_stream_t stream);
+
 /* replaces: the part of Concentration.forward between its matrix products, ALGORITHM/common/conc.py:30-58 (masked
  * softmax attention of the agent's own encoding over one entity list, attended encoding, top-n_focus gather with the
  * skip connection), for the conc / conc_4hist policy (ALGORITHM/conc_4hist/net.py:205-207).  One warp per agent.

@@ -197,3 +197,40 @@ def test_policy_rollout_50v55_statistics_match_reference_run():
     print('mean reward sum %.3f +- %.3f (reference %.3f +- %.3f)' % (np.mean(rsum), np.std(rsum), ref['mean_reward_sum'],
                                                                     ref['std_reward_sum']))
     assert abs(np.mean(rsum) - ref['mean_reward_sum']) <= 4 * se_r + 0.05
+
+
+def test_policy_rollout_step_as_cuda_graph_equals_eager_steps():
+    """PolicyRollout.capture(): one env step of the whole loop (history roll, normalisation update, network, draw,
+    planner, step, rollout buffer) replayed as a CUDA graph gives the same trajectory as eager steps -- same seeds, test
+    mode (arg-max actions) so both arms take identical actions."""
+    import torch
+    from hmp2g_b200.config import ScenarioConfig
+    from hmp2g_b200.policy import PolicyRollout
+    from hmp2g_b200.vec_env import DcaVecEnv
+    z = _fixture()
+    scfg = type('S', (ScenarioConfig,), dict(num_guards=50, num_attackers=55, size=5.0, random_jam_prob=0.05,
+                                             introduce_terrain=True, terrain_parameters=[0.15, 0.2], MaxEpisodeStep=40,
+                                             half_death_reward=True, REWARD_DEBUG=True, REWARD_DEBUG_Value=3))
+    arms = []
+    for graph in (False, True):
+        net = _net(z, torch).train()
+        env = DcaVecEnv(64, scfg=scfg, seed=5, empty_rows_nan=True)
+        roll = PolicyRollout(env, net, gamma_fwd=0.95, seed=1, test_mode=True)
+        step = roll.capture(warm=3) if graph else None
+        if not graph:
+            for _ in range(3):
+                roll.step()
+        n_fin = 0
+        for t in range(50):
+            fin = step() if graph else roll.step()
+            n_fin += int(fin.sum().item())
+        torch.cuda.synchronize()
+        arms.append((env.obs.clone(), env.reward.clone(), env.alive.clone(), roll.buf.reward.clone(), roll.buf.value.clone(),
+                     roll.buf.length.clone(), int(roll.episodes.item()), net._batch_norm.mean.clone(),
+                     int(net._batch_norm.n_sample.item()), n_fin))
+    a, b = arms
+    assert a[6] == b[6] and a[6] >= 64 and a[8] == b[8] and a[9] == b[9]
+    assert torch.equal(a[0].view(torch.int32), b[0].view(torch.int32))  # observations carry NaN rows: compare bits
+    for i in (1, 2, 3, 5):
+        assert torch.equal(a[i], b[i]), i
+    assert torch.allclose(a[4], b[4], rtol=1e-5, atol=1e-5) and torch.allclose(a[7], b[7], rtol=1e-6, atol=1e-7)
