@@ -206,7 +206,7 @@ class DcaSuperpoolEnv(object):
     """
 
     def __init__(self, process_pool=None, env_args_dict_list=None, spaces=None, n_env=None, scfg=None,
-                 device=None, seed=None, planner=None, env_gid0=0):
+                 device=None, seed=None, planner=None, env_gid0=0, reference_obs_dtype=False):
         scfg = scfg or GlobalConfig.ScenarioConfig
         if n_env is None:
             n_env = len(env_args_dict_list) if env_args_dict_list is not None else GlobalConfig.num_threads
@@ -216,6 +216,10 @@ class DcaSuperpoolEnv(object):
         seed = GlobalConfig.seed if seed is None else seed
         self.env = DcaVecEnv(n_env, scfg=scfg, device=device, seed=seed, env_gid0=env_gid0)
         self.planner = planner
+        # reference_obs_dtype: hand observations back as float64 once any guard of the batch is dead, as the reference
+        # does (a dead guard's observation is np.zeros(192), float64, and np.stack promotes the batch);
+        # the values are float32 numbers either way.  Default: always float32 (no 2x host copy).
+        self.reference_obs_dtype = bool(reference_obs_dtype)
         self.observation_space, self.action_space = [], []  # parallel_run.py:170-171
         E, G = self.env.E, self.env.G
         pin = dict(pin_memory=True)
@@ -325,7 +329,10 @@ class DcaSuperpoolEnv(object):
             for k, i in enumerate(idx_done):
                 info[i] = {'win': bool(win[i]), 'obs-echo': tobs[k], 'others': None}
         self._suffer_reset[stepped] = done[stepped]
-        return (self._h_obs.numpy(), self._h_rew.numpy().astype(np.float64), done, info.copy())
+        obs = self._h_obs.numpy()
+        if self.reference_obs_dtype and (obs[:, :, 0] == 0).any():  # a guard whose own record is empty is dead
+            obs = obs.astype(np.float64)
+        return (obs, self._h_rew.numpy().astype(np.float64), done, info.copy())
 
     def sleep(self):
         return None
