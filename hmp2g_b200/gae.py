@@ -39,6 +39,24 @@ def gae_return(reward, value, dead, traj_len=None, gamma=0.99, tau=0.95, threat_
     return (ret, threat, pushed) if want_pushed else (ret, threat)
 
 
+def gae_return_levels(reward, value_levels, dead, traj_len=None, gamma=0.99, tau=0.95, threat_limit=8, gamma_fwd=None):
+    """The policy-resonance variant of finalize (ALGORITHM/common/traj_gae.py:86-90, gae_finalize_return_pr :135-169):
+    the critic emits `distribution_precision` value levels per agent (value_levels f32 [T,E,G,P]); the reward is pushed
+    forward and the threat counted once per agent, then the same GAE scan runs on every level, fed by the agent's
+    pushed reward.  Two dca_gae launches: [T,E,G] for push-forward / threat, [T,E,G*P] (no dead frames) for the returns.
+    Returns (return_levels f32 [T,E,G,P], threat f32 [T,E,G], reward_pushed f32 [T,E,G])."""
+    T, E, G, P = value_levels.shape
+    assert reward.shape == (T, E, G)
+    v0 = value_levels[..., 0].contiguous()
+    _, threat, pushed = gae_return(reward, v0, dead, traj_len=traj_len, gamma=gamma, tau=tau, threat_limit=threat_limit,
+                                   want_pushed=True, gamma_fwd=gamma_fwd)
+    rep = pushed.unsqueeze(-1).expand(T, E, G, P).reshape(T, E, G * P).contiguous()
+    nodead = torch.zeros((T, E, G * P), dtype=torch.uint8, device=reward.device)
+    ret, _ = gae_return(rep, value_levels.reshape(T, E, G * P).contiguous(), nodead, traj_len=traj_len, gamma=gamma, tau=tau,
+                        threat_limit=threat_limit)
+    return ret.reshape(T, E, G, P), threat, pushed
+
+
 def allreduce_moments(stats, group=None):
     """stats f64[3] = (sum, sum of squares, count) of this rank's advantages -> the same over all ranks (in place)."""
     if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):

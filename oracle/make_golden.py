@@ -191,12 +191,52 @@ def run_gae_fwd():
     print('gae_conc4hist_fwd', '%.1f KB' % (os.path.getsize(path) / 1024))
 
 
+def run_gae_pr():
+    """Policy-resonance ('level') fixtures from ALGORITHM/common/traj_gae.py: finalize() with use_policy_resonance and
+    policy_resonance_method == 'level' (:86-90) -> gae_finalize_return_pr (:135-169): the GAE scan on every one of the
+    `distribution_precision` value levels of an agent, all fed by the agent's pushed-forward reward; SAFE_LIMIT 8."""
+    from ref_env import setup_reference
+    setup_reference()
+    import importlib
+    mod = importlib.import_module('ALGORITHM.common.traj_gae')
+
+    class Cfg:
+        gamma, tau = 0.99, 0.95
+        gamma_in_reward_forwarding, gamma_in_reward_forwarding_value = False, 0.99
+        use_policy_resonance, policy_resonance_method, distribution_precision = True, 'level', 5
+    rng = np.random.RandomState(21)
+    recs = {}
+    for idx, (T, G) in enumerate([(40, 6), (120, 20), (3, 7)]):
+        mod.trajectory.dead_mask_check = False
+        tr = mod.trajectory(traj_limit=T, env_id=0, alg_cfg=Cfg)
+        death = rng.randint(1, T + 15, size=G)
+        alive = np.arange(T)[:, None] < death[None]
+        reward = rng.choice([0.0, 1.0, -0.5, 0.5, 2.0], size=(T, G)).astype(np.float64)
+        levels = rng.randn(T, G, Cfg.distribution_precision).astype(np.float32)
+        tr.alive, tr.reward, tr.BAL_value_all_level = alive, reward.copy(), levels
+        tr.randl = rng.randint(0, Cfg.distribution_precision, size=T)
+        tr.key_dict = ['alive', 'reward', 'BAL_value_all_level']
+        tr.time_pointer = T
+        tr.finalize()
+        recs['c%d_reward' % idx] = reward
+        recs['c%d_levels' % idx] = levels
+        recs['c%d_dead' % idx] = ~alive
+        recs['c%d_return_levels' % idx] = tr.BAL_return_all_level
+        recs['c%d_threat' % idx] = tr.threat[..., 0].astype(np.float32)
+        recs['c%d_reward_pushed' % idx] = tr.reward
+    path = os.path.join(OUT, 'gae_common_pr.npz')
+    np.savez_compressed(path, **recs)
+    print('gae_common_pr', '%.1f KB' % (os.path.getsize(path) / 1024))
+
+
 if __name__ == '__main__':
-    which = sys.argv[1:] or (list(CASES) + ['gae', 'gae_fwd'])
+    which = sys.argv[1:] or (list(CASES) + ['gae', 'gae_fwd', 'gae_pr'])
     for n in which:
         if n == 'gae':
             run_gae()
         elif n == 'gae_fwd':
             run_gae_fwd()
+        elif n == 'gae_pr':
+            run_gae_pr()
         else:
             run_case(n, CASES[n])

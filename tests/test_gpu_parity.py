@@ -516,6 +516,22 @@ def test_cuda_pipelined_steps_are_bit_identical(planner):
     assert t >= 47 and n_done >= E // 4   # (at t = 40 the envs paused once are the ones that have just finished)
 
 
+def test_cuda_gae_policy_resonance_levels_match_reference():
+    """gae_return_levels against the reference's gae_finalize_return_pr fixtures (ALGORITHM/common/traj_gae.py:135-169):
+    returns of every value level bit-exact, threat (SAFE_LIMIT 8) and pushed reward exact."""
+    torch = _torch()
+    from hmp2g_b200.gae import gae_return_levels
+    z = np.load(gu.GOLDEN_DIR + '/gae_common_pr.npz')
+    for i in range(3):
+        r, lv, d = z['c%d_reward' % i], z['c%d_levels' % i], z['c%d_dead' % i]
+        ret, thr, push = gae_return_levels(torch.from_numpy(r[:, None].astype(np.float32)).cuda().contiguous(),
+                                           torch.from_numpy(lv[:, None]).cuda().contiguous(),
+                                           torch.from_numpy(d[:, None]).cuda(), threat_limit=8)
+        assert np.array_equal(push[:, 0].cpu().numpy().astype(np.float64), z['c%d_reward_pushed' % i])
+        assert np.array_equal(thr[:, 0].cpu().numpy(), z['c%d_threat' % i])
+        assert np.array_equal(ret[:, 0].cpu().numpy().view(np.uint32), z['c%d_return_levels' % i].view(np.uint32)), i
+
+
 def test_superpool_reference_obs_dtype_option():
     """reference_obs_dtype=True: float32 observations while every guard is alive, float64 (same values) once one is dead
     -- what np.stack over the reference's per-env observations yields."""

@@ -115,3 +115,17 @@ def test_gae_reward_forwarding_gamma_matches_reference():
             assert np.array_equal(pushed[:, 0], z['%s_c%d_reward_pushed' % (tag, i)])
             assert np.array_equal(threat[:, 0], z['%s_c%d_threat' % (tag, i)])
             assert np.array_equal(ret[:, 0].view(np.uint32), z['%s_c%d_return' % (tag, i)].view(np.uint32)), (tag, i)
+
+
+def test_gae_policy_resonance_levels_match_reference():
+    """gae_finalize_return_pr (ALGORITHM/common/traj_gae.py:135-169) = the plain scan on G x P columns fed by the pushed
+    reward of each agent: fixtures from the reference's common trajectory class with use_policy_resonance / 'level'."""
+    z = np.load(gu.GOLDEN_DIR + '/gae_common_pr.npz')
+    for i in range(3):
+        r, lv, d = z['c%d_reward' % i], z['c%d_levels' % i], z['c%d_dead' % i]
+        T, G, P = lv.shape
+        _, thr, push = gae(r[:, None], lv[:, None, :, 0], d[:, None], threat_limit=8)
+        assert np.array_equal(push[:, 0], z['c%d_reward_pushed' % i]) and np.array_equal(thr[:, 0], z['c%d_threat' % i])
+        ret, _, _ = gae(np.repeat(push[:, 0], P, axis=-1)[:, None], lv.reshape(T, 1, G * P), np.zeros((T, 1, G * P), bool),
+                        threat_limit=8)
+        assert np.array_equal(ret[:, 0].reshape(T, G, P).view(np.uint32), z['c%d_return_levels' % i].view(np.uint32)), i
