@@ -18,6 +18,9 @@ namespace dca {
 #ifndef DCA_CTAS_128
 #define DCA_CTAS_128 8  // resident CTAs per SM the 128-thread kernels are register-budgeted for
 #endif
+#ifndef DCA_CTAS_256
+#define DCA_CTAS_256 4  // ... and the 256-thread kernels (N > 128 entities per env): 64 registers like the 128-thread ones (3 CTAs / 80 registers: 100v100 7 % slower)
+#endif
 #ifdef DCA_DIAG_COUNT
 __device__ unsigned long long g_diag[8];  // diagnostics build only: kNN task / close-call counters
 #endif
@@ -826,7 +829,7 @@ __device__ __forceinline__ void push_shooter(const Smem &s, int i) {
 // ------------------------------------------------------------------ fused step kernel
 // collective_assaultGlobalEnv.step parallel_run.py:192-246 + EnvAutoReset.step UTIL/shm_env.py:33-74.
 template <int NT, int TG, int TA>
-__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
+__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : DCA_CTAS_256) k_step(
     const Params P, const int32_t *__restrict__ actions, const double *__restrict__ att_force,
     const uint8_t *__restrict__ skip, const uint32_t *__restrict__ rng_words, int autoreset, const Pipe pipe) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -1219,7 +1222,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_step(
 
 // reset kernel: SuperpoolEnv.reset -> collective_assaultGlobalEnv.reset parallel_run.py:248-270
 template <int NT, int TG, int TA>
-__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_reset(const Params P,
+__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : DCA_CTAS_256) k_reset(const Params P,
                                                                             const uint8_t *__restrict__ env_mask) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;
@@ -1238,7 +1241,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_reset(cons
 
 // observation-only kernel (the kNN gather kernel on the resident state)
 template <int NT, int TG, int TA>
-__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : 3) k_observe(const Params P,
+__global__ void __launch_bounds__(NT, NT == 128 ? DCA_CTAS_128 : DCA_CTAS_256) k_observe(const Params P,
                                                                               const uint32_t *__restrict__ rng_words) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int e = blockIdx.x;

@@ -192,3 +192,58 @@ def test_keyed_planner_episode_statistics_match_reference():
     assert abs(np.mean(wins) - ref['guard_win_rate']) <= 0.02
     se_a = np.sqrt(np.var(alive_end) / n + ref['std_guards_alive_at_end'] ** 2 / n_ref)
     assert abs(np.mean(alive_end) - ref['mean_guards_alive_at_end']) <= 4 * se_a + 0.05
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('G,A', [(50, 50), (40, 90), (100, 100)])
+def test_cuda_planner_every_team_size_path_matches_oracle(G, A):
+    """Injected team labels that force every member->slot path of k_plan on random states -- teams of 1..8 (subset DP),
+    9..16 (register assignment, precomputed costs), 17..32 (register assignment), more than 32 members (shared-memory
+    assignment), empty teams -- and, at 100v100, the workspaces that share one region of shared memory at their largest:
+    forces vs the C oracle (augmenting paths throughout) <= 1e-12."""
+    import torch
+    from test_gpu_parity import make_gpu_env
+    rng = np.random.RandomState(G * 1000 + A)
+    K = A // 5
+    E = 48
+    gpos = rng.uniform(-4, 4, size=(E, G, 2)); apos = rng.uniform(-4, 4, size=(E, A, 2))
+    galive = rng.rand(E, G) < 0.8; galive[:, 0] = True
+    aalive = rng.rand(E, A) < 0.85
+    label = np.zeros((E, A), np.int32)
+    for e in range(E):
+        mode = e % 6
+        if mode == 0:      # one team holds everybody (> 32 members when A > 32)
+            label[e] = 0
+        elif mode == 1:    # a team of 17..32, the rest spread
+            n_big = rng.randint(17, min(32, A - 1) + 1)
+            label[e, :n_big] = 1
+            label[e, n_big:] = rng.randint(2, K, size=A - n_big)
+        elif mode == 2:    # teams of 9..16
+            sizes = []
+            while sum(sizes) < A:
+                sizes.append(min(rng.randint(9, 17), A - sum(sizes)))
+            label[e] = np.repeat(np.arange(len(sizes)) % K, sizes)[:A]
+        elif mode == 3:    # small teams only (round robin): sizes about 5
+            label[e] = rng.permutation(A) % K
+        elif mode == 4:    # random sizes incl. singletons and empty teams
+            label[e] = rng.randint(0, max(2, K // 2), size=A)
+        else:              # one team of more than 32 and small ones
+            n_big = min(A - 3, 33 + rng.randint(0, 8))
+            label[e, :n_big] = K - 1
+            label[e, n_big:] = rng.randint(0, K - 1, size=A - n_big)
+        label[e] = label[e][rng.permutation(A)]
+    cent = np.zeros((E, K, 2))
+    for e in range(E):
+        for k in range(K):
+            m = label[e] == k
+            cent[e, k] = apos[e, m].mean(0) if m.any() else rng.uniform(-4, 4, size=2)
+    cfg = dict(num_guards=G, num_attackers=A)
+    env = make_gpu_env(cfg, E, seed=1, gid0=0, debug=False)
+    env.reset()
+    env.import_state(_blank_state(E, G, A, gpos, galive, apos, aalive))
+    got = env.plan(team_label=torch.from_numpy(label).to(env.device),
+                   team_centroid=torch.from_numpy(cent).to(env.device)).cpu().numpy()
+    for e in range(E):
+        want = orc.plan_core(gpos[e], galive[e], apos[e], aalive[e], label[e], cent[e], False)
+        np.testing.assert_allclose(got[e], want, rtol=0, atol=1e-12, err_msg='G=%d A=%d env %d (mode %d)' % (G, A, e, e % 6))
+    assert np.abs(got).max() > 0.1
