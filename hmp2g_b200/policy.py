@@ -61,7 +61,6 @@ class DynamicNormDevice(nn.Module):
     def update(self, x):
         """The training-mode half of DynamicNorm.forward (norm.py:47-63) from the batch statistics; with
         torch.distributed initialised the statistics of all ranks are summed first (one all-reduce of 49 doubles)."""
-        D = self.input_size
         stats = self.batch_stats(x)
         if torch.distributed.is_available() and torch.distributed.is_initialized():
             torch.distributed.all_reduce(stats, group=self.group)

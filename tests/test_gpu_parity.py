@@ -496,7 +496,8 @@ def test_cuda_pipelined_steps_are_bit_identical(planner):
     pool = [torch.randint(0, 7, (E, 50), generator=gen, device=piped.device, dtype=torch.int32) for _ in range(16)]
     t = 0
     n_done = 0
-    for burst in ([1, 2, 3, 7, 27, 5, 40] if planner == 'centroid' else [1, 2, 7, 30, 12]):  # t = 40: every env is done
+    # t = 40: every env is done; the long bursts at the end: any env handed over too early would fork for good
+    for burst in ([1, 2, 3, 7, 27, 5, 40, 600] if planner == 'centroid' else [1, 2, 7, 30, 12, 150]):
         for env in (piped, serial):
             for k in range(burst):   # nothing but plan + step on the stream inside a burst
                 force = env.plan_centroid() if planner == 'centroid' else env.plan()
