@@ -352,6 +352,63 @@ __device__ __forceinline__ void assign_dp8(const double *cost, int n, double *dp
     __syncwarp();
 }
 
+// The same DP for several small teams at once: the warp is split into groups of LANES lanes, group g works on its own
+// team (n members, list offset off; n = 0: nothing to do) with its own slab of shared memory -- n x 8 costs, 2^NMAX dp
+// values, 2^NMAX choices -- so four teams of up to 5 (LANES = 8) or two teams of 6 (LANES = 16) cost one pass instead of
+// four / two (a layer of a 5-member team has at most 10 subsets: a whole warp per team leaves two thirds of it idle).
+template <int LANES, int NMAX>
+__device__ __forceinline__ void assign_dp_groups(unsigned char *slabs, int n, int off, const double *ax, const double *ay,
+                                                 const double *sx, const double *sy, const int16_t *mem,
+                                                 int16_t *col_of_row) {
+    constexpr int kSlab = (NMAX * 8 * 8 + (1 << NMAX) * 8 + (1 << NMAX) + 15) / 16 * 16;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, gl = lane % LANES, grp = lane / LANES;
+    unsigned char *slab = slabs + grp * kSlab;
+    double *cost = (double *)slab, *dp = cost + NMAX * 8;
+    uint8_t *choice = (uint8_t *)(dp + (1 << NMAX));
+    for (int q = gl; q < n * 8; q += LANES) {
+        const int r = q >> 3, j = q & 7;
+        if (j < n) {
+            const int a = mem[off + r];
+            const double dx = ax[a] - sx[off + j], dy = ay[a] - sy[off + j];
+            cost[q] = sqrt(dx * dx + dy * dy);
+        }
+    }
+    if (gl == 0) dp[0] = 0.0;
+    int nmax = n;
+#pragma unroll
+    for (int o = LANES; o < 32; o <<= 1) nmax = max(nmax, __shfl_xor_sync(full, nmax, o));
+    __syncwarp();
+    for (int k = 1; k <= nmax; ++k) {  // warp-uniform trip count; groups with n < k idle
+        if (k <= n) {
+            const int cnt = kPlanBinom[n][k], first = kPlanPopOff[k];
+            const double *crow = cost + (k - 1) * 8;
+            for (int idx = gl; idx < cnt; idx += LANES) {
+                const unsigned mask = kPlanPopMask[first + idx];
+                double best = CUDART_INF;
+                int bj = 0;
+                for (unsigned m = mask; m; m &= m - 1) {
+                    const int j = __ffs(m) - 1;
+                    const double val = dp[mask ^ (1u << j)] + crow[j];
+                    if (val < best) { best = val; bj = j; }
+                }
+                dp[mask] = best;
+                choice[mask] = (uint8_t)bj;
+            }
+        }
+        __syncwarp();
+    }
+    if (gl == 0 && n > 0) {
+        unsigned mask = (1u << n) - 1u;
+        for (int r = n - 1; r >= 0; --r) {
+            const int j = choice[mask];
+            col_of_row[off + r] = (int16_t)j;
+            mask ^= 1u << j;
+        }
+    }
+    __syncwarp();
+}
+
 __device__ __forceinline__ double plan_sq2(double ax, double ay, double bx, double by) {
     const double dx = ax - bx, dy = ay - by;
     double d = 0;
@@ -690,10 +747,29 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
     // members entirely in registers, cost matrix precomputed up to 16)
     {
         const double *ax = s.ax, *ay = s.ay;
-        // small teams, one after the other: the n x n distances (two entries per lane), then the subset DP
+        // small teams by subset DP: up to 5 members four teams at a time (8 lanes each), 6 members two at a time
+        // (16 lanes each), 7 and 8 members one by one with the whole warp
+        for (int pass = 0; pass < 2; ++pass) {
+            const int groups = pass == 0 ? 4 : 2, lo = pass == 0 ? 1 : 6, hi = pass == 0 ? 5 : 6;
+            const int grp = lane / (32 / groups);
+            for (int kk = 0;;) {  // warp-uniform scan for the next `groups` teams of this size class
+                int myk = -1, c = 0;
+                for (; kk < K && c < groups; ++kk) {
+                    const int nm = s.cnt[kk];
+                    if (nm >= lo && nm <= hi) {
+                        if (c == grp) myk = kk;
+                        ++c;
+                    }
+                }
+                if (c == 0) break;
+                const int nm = myk >= 0 ? s.cnt[myk] : 0, off = myk >= 0 ? s.toff[myk] : 0;
+                if (pass == 0) assign_dp_groups<8, 5>((unsigned char *)s.cq, nm, off, ax, ay, s.sx, s.sy, s.mem, s.hcol);
+                else assign_dp_groups<16, 6>((unsigned char *)s.cq, nm, off, ax, ay, s.sx, s.sy, s.mem, s.hcol);
+            }
+        }
         for (int kk = 0; kk < K; ++kk) {  // warp-uniform
             const int nm = s.cnt[kk];
-            if (nm < 1 || nm > kPlanTeamPre) continue;
+            if (nm < 7 || nm > kPlanTeamPre) continue;
             const int off = s.toff[kk];
 #pragma unroll
             for (int q = lane; q < 64; q += 32) {
@@ -733,6 +809,17 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
     }
     __syncwarp();
     DCA_PROF(P, e, 8);
+    if (P.prof != nullptr && lane == 0) {  // diagnostics: team-size profile of this env (slots 10..13)
+        int mx = 0, n_big = 0, sum_big = 0, n_small = 0;
+        for (int kk = 0; kk < K; ++kk) {
+            const int nm = s.cnt[kk];
+            mx = max(mx, nm);
+            if (nm > kPlanTeamPre) { ++n_big; sum_big += nm; }
+            else if (nm > 0) ++n_small;
+        }
+        P.prof[(size_t)e * 16 + 10] = mx; P.prof[(size_t)e * 16 + 11] = n_big;
+        P.prof[(size_t)e * 16 + 12] = sum_big; P.prof[(size_t)e * 16 + 13] = n_small;
+    }
     // ---- forces (:175-188); dead attackers get zero
     for (int i = lane; i < A; i += 32) {
         const int a = s.mem[i];

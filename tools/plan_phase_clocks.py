@@ -46,7 +46,14 @@ def main(last=100, window=20, E=4096):
                 d = np.diff(c[:, :10], axis=1)
                 worst = np.argsort(-life[-1])[:5]
                 for w in worst:
-                    tail.append('env %4d lifetime %7.0f: ' % (w, life[-1][w]) + ' '.join('%6.0f' % x for x in d[w]))
+                    tail.append('env %4d lifetime %7.0f: ' % (w, life[-1][w]) + ' '.join('%6.0f' % x for x in d[w]) +
+                                ' | largest team %d, teams > 8: %d (members %d), small teams %d' % tuple(c[w, 10:14]))
+                ms_col = d[:, 7]
+                for lo_, hi_ in ((0, 8), (9, 12), (13, 16), (17, 22), (23, 32), (33, 999)):
+                    sel = (c[:, 10] >= lo_) & (c[:, 10] <= hi_)
+                    if sel.any():
+                        tail.append('largest team %2d..%3d: %4d envs, member->slot mean %7.0f cycles, lifetime mean %7.0f'
+                                    % (lo_, hi_, sel.sum(), ms_col[sel].mean(), life[-1][sel].mean()))
     acc /= window
     for n, v in zip(NAMES, acc):
         print('%-26s %9.0f cycles  %5.1f%%' % (n, v, 100 * v / acc.sum()))
