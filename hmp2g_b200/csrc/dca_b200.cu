@@ -236,6 +236,9 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
         if (e == cudaSuccess) e = cudaMemset(h->plan.label, 0, (size_t)n_env * A);
         if (e == cudaSuccess) e = cudaMalloc((void **)&h->plan.cent, (size_t)n_env * K * 16);
         if (e == cudaSuccess) e = cudaMemset(h->plan.cent, 0, (size_t)n_env * K * 16);
+        h->plan.big_n = A > kPlanTeamPre2 ? std::min(A, kPlanBigMax) : 0;  // cost-matrix scratch of the large teams
+        if (e == cudaSuccess && h->plan.big_n > 0)
+            e = cudaMalloc((void **)&h->plan.big, (size_t)n_env * h->plan.big_n * h->plan.big_n * sizeof(double));
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(k_plan<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      std::max(plan_smem_bytes(250, 250), plan_smem_bytes(kMaxN - 6, 6)));
@@ -258,6 +261,8 @@ int dca_create(const DcaConfig *cfg, int n_env, int device, DcaHandle **out) {
         if (h->P.blobs) cudaFree(h->P.blobs);
         if (h->epoch) cudaFree(h->epoch);
         cudaFree(h->plan.flags); cudaFree(h->plan.counter); cudaFree(h->plan.label); cudaFree(h->plan.cent);
+    cudaFree(h->plan.big);
+        cudaFree(h->plan.big);
         delete h;
         return rc;
     }

@@ -25,7 +25,10 @@ struct PlanState {
     uint32_t *counter;  // [E]    k-means calls so far (keyed RNG counter)
     uint8_t *label;     // [E,A]  team of every attacker
     double *cent;       // [E,K,2]
+    double *big;        // [E, big_n^2] cost matrices of teams with more than kPlanTeamPre2 members (L2-resident scratch)
+    int big_n;          // min(A, kPlanBigMax), 0 when A <= kPlanTeamPre2 (no such team can exist)
 };
+constexpr int kPlanBigMax = 64;
 
 // Shared-memory plan of one env.  The env is worked on by ONE warp phase after phase, so workspaces of different
 // phases share one region (`un`): k-means {d2, pre}, DBSCAN {gidx, adj, comp, csize, tsrc}, team->target {c1 (+ the
@@ -787,16 +790,45 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
             const int nm = s.cnt[kk];
             if (nm <= kPlanTeamPre) continue;
             const int off = s.toff[kk], ho = off + kk;
+            {   // a team whose members are all dead gets no forces (:175-188): its slot assignment is never read.  Late in
+                // an episode the pile of dead attackers often forms one team of 30-45 -- the most expensive assignment.
+                bool any_alive = false;
+                for (int i = lane; i < nm; i += 32) any_alive |= s.aalive[s.mem[off + i]] != 0;
+                if (!__any_sync(full, any_alive)) continue;
+            }
             const double *sx = s.sx + off, *sy = s.sy + off;
             const int16_t *mem = s.mem + off;
+            // Teams too large for the shared-memory cost matrix get theirs in the env's global scratch (it stays in L1 /
+            // L2): the square roots would otherwise sit inside the augmenting loop, once per visited (row, column) --
+            // a late-episode team of 33-45 attackers around the last guard took 0.9-1.2 M cycles that way.
+            double *big = (nm > kPlanTeamPre2 && nm <= ps.big_n) ? ps.big + (size_t)e * ps.big_n * ps.big_n : nullptr;
+            if (big != nullptr) {
+                for (int q = lane; q < nm * nm; q += 32) {
+                    const int r = q / nm, j = q - r * nm;
+                    const double dx = ax[mem[r]] - sx[j], dy = ay[mem[r]] - sy[j];
+                    big[q] = sqrt(dx * dx + dy * dy);
+                }
+                __syncwarp();
+            }
             if (nm <= 32) {
                 const double sxj = lane < nm ? sx[lane] : 0.0, syj = lane < nm ? sy[lane] : 0.0;
                 auto cost2 = [=](int i) {
                     const double dx = ax[mem[i]] - sxj, dy = ay[mem[i]] - syj;
                     return sqrt(dx * dx + dy * dy);
                 };
-                if (nm <= kPlanTeamPre2) assign_warp_reg_pre(cost2, nm, nm, s.cw, s.hcol + off);
-                else assign_warp_reg(cost2, nm, nm, s.hcol + off);
+                if (nm <= kPlanTeamPre2) {
+                    assign_warp_reg_pre(cost2, nm, nm, s.cw, s.hcol + off);
+                } else if (big != nullptr) {
+                    const double *col = big + (lane < nm ? lane : 0);
+                    auto cost_big = [=](int i) { return col[i * nm]; };
+                    assign_warp_reg(cost_big, nm, nm, s.hcol + off);
+                } else {
+                    assign_warp_reg(cost2, nm, nm, s.hcol + off);
+                }
+            } else if (big != nullptr) {
+                auto cost_big = [=](int i, int j) { return big[i * nm + j]; };
+                assign_warp(cost_big, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
+                            s.hcol + off);
             } else {
                 auto cost2 = [=](int i, int j) {
                     const double dx = ax[mem[i]] - sx[j], dy = ay[mem[i]] - sy[j];

@@ -15,12 +15,17 @@ NAMES = ['load', 'teams (labels / k-means)', 'guard list + adjacency', 'componen
          'ring slots', 'member->slot', 'forces']
 
 
-def main(last=100, window=20, E=4096):
+def main(last=100, window=20, E=4096, preroll=0):
     scfg = type('S', (ScenarioConfig,), dict(bench.WORKLOAD))
     env = DcaVecEnv(E, scfg=scfg, seed=1)
     env.reset()
     g = torch.Generator(device=env.device)
     g.manual_seed(0)
+    if preroll:  # the stationary episode-phase mix of bench.py: env e sits out the first preroll - offs[e] steps
+        offs = torch.randint(0, preroll, (E,), generator=g, device=env.device)
+        for s_ in range(preroll):
+            act = torch.randint(0, 7, (E, env.G), generator=g, device=env.device, dtype=torch.int32)
+            env.step(act, env.plan(), skip=(offs < (preroll - s_)).to(torch.uint8))
     prof = torch.zeros((E, 16), dtype=torch.int64, device=env.device)
     acc = np.zeros(9)
     life, span, tail = [], [], []
@@ -67,4 +72,4 @@ def main(last=100, window=20, E=4096):
 
 
 if __name__ == '__main__':
-    main(*(int(a) for a in sys.argv[1:3]))
+    main(*(int(a) for a in sys.argv[1:5]))
