@@ -275,6 +275,85 @@ __device__ __forceinline__ void assign_warp_reg(CostFn cost_col, int n, int m, i
     __syncwarp();
 }
 
+// The register routine for 33..64 columns: lane l owns columns l + 1 (slot 0) and l + 33 (slot 1).  Same arithmetic, same
+// order, ties -> lowest column (slot 0 before slot 1).  cost(i, j): 0-based row and column.
+template <typename CostFn>
+__device__ __forceinline__ void assign_warp_reg2(CostFn cost, int n, int m, int16_t *col_of_row) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const bool col0 = lane < m, col1 = lane + 32 < m;
+    double v0 = 0.0, v1 = 0.0, uc0 = 0.0, uc1 = 0.0;
+    int p0 = 0, p1 = 0;
+    unsigned free0 = m >= 32 ? full : ((1u << m) - 1u);
+    unsigned free1 = m >= 64 ? full : (m > 32 ? ((1u << (m - 32)) - 1u) : 0u);
+    for (int i = 1; i <= n; ++i) {
+        double u0 = 0.0, minv0 = CUDART_INF, minv1 = CUDART_INF, ui0 = 0.0;
+        int way0 = 0, way1 = 0, j0 = 0, i0 = i;
+        bool used0 = !col0, used1 = !col1;
+        for (;;) {
+            u64 key0 = ~0ull, key1 = ~0ull;
+            if (!used0) {
+                const double cur = (cost(i0 - 1, lane) - ui0) - v0;
+                if (cur < minv0) { minv0 = cur; way0 = j0; }
+                key0 = plan_dkey(minv0);
+            }
+            if (!used1) {
+                const double cur = (cost(i0 - 1, lane + 32) - ui0) - v1;
+                if (cur < minv1) { minv1 = cur; way1 = j0; }
+                key1 = plan_dkey(minv1);
+            }
+            unsigned holders;
+            const u64 kmin = plan_warp_min_key(key1 < key0 ? key1 : key0, &holders);
+            const unsigned h0 = __ballot_sync(full, key0 == kmin);  // used / missing columns hold ~0, never the minimum
+            int jn;
+            if (h0) {
+                jn = __ffs(h0);
+            } else {
+                const unsigned h1 = __ballot_sync(full, key1 == kmin);
+                jn = 32 + __ffs(h1);
+            }
+            const double delta = plan_dkey_inv(kmin);
+            if (col0) {
+                if (used0) { uc0 += delta; v0 -= delta; }
+                else minv0 -= delta;
+            }
+            if (col1) {
+                if (used1) { uc1 += delta; v1 -= delta; }
+                else minv1 -= delta;
+            }
+            u0 += delta;
+            j0 = jn;
+            const int sl = (j0 - 1) >> 5, src = (j0 - 1) & 31;
+            if (((sl ? free1 : free0) >> src) & 1u) break;
+            if (lane == src) {
+                if (sl) used1 = true;
+                else used0 = true;
+            }
+            i0 = __shfl_sync(full, sl ? p1 : p0, src);
+            ui0 = __shfl_sync(full, sl ? uc1 : uc0, src);
+        }
+        if ((j0 - 1) >> 5) free1 &= ~(1u << ((j0 - 1) & 31));
+        else free0 &= ~(1u << ((j0 - 1) & 31));
+        while (j0) {  // flip the augmenting path
+            const int sl = (j0 - 1) >> 5, src = (j0 - 1) & 31;
+            const int j1 = __shfl_sync(full, sl ? way1 : way0, src);
+            const int sl1 = j1 > 0 ? (j1 - 1) >> 5 : 0, s1 = j1 > 0 ? (j1 - 1) & 31 : 0;
+            const int pj1 = __shfl_sync(full, sl1 ? p1 : p0, s1);
+            const double uj1 = __shfl_sync(full, sl1 ? uc1 : uc0, s1);
+            if (lane == src) {
+                const int np = j1 == 0 ? i : pj1;
+                const double nu = j1 == 0 ? u0 : uj1;
+                if (sl) { p1 = np; uc1 = nu; }
+                else { p0 = np; uc0 = nu; }
+            }
+            j0 = j1;
+        }
+    }
+    if (col0 && p0) col_of_row[p0 - 1] = (int16_t)lane;
+    if (col1 && p1) col_of_row[p1 - 1] = (int16_t)(lane + 32);
+    __syncwarp();
+}
+
 // assign_warp_reg with the n x m costs evaluated up front into `scratch` (row-major): the square roots then run as
 // independent chains instead of sitting inside the augmenting loop's dependency chain.
 template <typename CostFn>
@@ -825,6 +904,9 @@ __global__ void __launch_bounds__(kPlanThreads, 32) k_plan(const Params P, const
                 } else {
                     assign_warp_reg(cost2, nm, nm, s.hcol + off);
                 }
+            } else if (big != nullptr && nm <= 64) {
+                auto cost_big = [=](int i, int j) { return big[i * nm + j]; };
+                assign_warp_reg2(cost_big, nm, nm, s.hcol + off);
             } else if (big != nullptr) {
                 auto cost_big = [=](int i, int j) { return big[i * nm + j]; };
                 assign_warp(cost_big, nm, nm, s.hu + ho, s.hv + ho, s.hminv + ho, s.hp + ho, s.hway + ho, s.hused + ho,
