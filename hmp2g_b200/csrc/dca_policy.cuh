@@ -205,8 +205,8 @@ __global__ void __launch_bounds__(256) k_conc_attend(const float *__restrict__ v
 // nn.Linear layout: w1 [48,16], w2 [48,48] (out, in).
 constexpr int kEncTile = 128, kEncThreads = 128;
 struct EncSmem {
-    float xs[kPolD][kEncTile];   // normalised observation rows, k-major
-    float hs[kPolH][kEncTile];   // hidden activations after the ReLU, k-major
+    float xs[kPolD][kEncTile + 4];   // normalised observation rows, k-major (+4: the transposing stores of a warp hit
+    float hs[kPolH][kEncTile + 4];   // hidden activations after the ReLU    2 banks' worth of rows instead of 8)
     float w1[kPolD][kPolH];      // w1^T
     float w2[kPolH][kPolH];      // w2^T
     float b1[kPolH], b2[kPolH];
