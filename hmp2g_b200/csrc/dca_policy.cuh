@@ -210,7 +210,12 @@ struct EncSmem {
     float w1[kPolD][kPolH];      // w1^T
     float w2[kPolH][kPolH];      // w2^T
     float b1[kPolH], b2[kPolH];
+    float4 stage[kEncTile * 4];      // the next tile's raw rows, fetched with cp.async while this tile is computed
 };
+__device__ __forceinline__ void enc_cp_async16(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
 
 __global__ void __launch_bounds__(kEncThreads) k_policy_encode(const float4 *__restrict__ x, const float *__restrict__ mean,
                                                                const float *__restrict__ var,
@@ -231,8 +236,25 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode(const float4 *__r
     const float mu[4] = {m.x, m.y, m.z, m.w};
     const int rg = tid >> 3, cg = tid & 7;  // this thread's 8 rows (rg*8 ..) and 6 columns (cg*6 ..)
     const size_t tiles = (rows + kEncTile - 1) / kEncTile;
+    auto prefetch = [&](size_t t) {  // every thread stages the four float4 it will read itself
+        if (t < tiles) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int i = tid + q * kEncThreads;
+                const size_t row = t * kEncTile + (i >> 2);
+                if (row < rows) enc_cp_async16(&s.stage[i], &x[row * 4 + quad]);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    prefetch(blockIdx.x);
     for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const size_t r0 = tile * kEncTile;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        float4 raw[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) raw[q] = s.stage[tid + q * kEncThreads];
+        prefetch(tile + gridDim.x);  // own slots only: they are in registers now
         __syncthreads();  // the previous tile's shared activations have been consumed; weights are in place
         // ---- load + normalise 128 rows (4 float4 per thread; a lane quad holds one row)
 #pragma unroll
@@ -242,7 +264,7 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode(const float4 *__r
             float e[4] = {0.f, 0.f, 0.f, 0.f};
             const bool in = row < rows;
             if (in) {
-                const float4 t = x[row * 4 + quad];
+                const float4 t = raw[q];
                 e[0] = t.x; e[1] = t.y; e[2] = t.z; e[3] = t.w;
             }
             bool bad = false;
