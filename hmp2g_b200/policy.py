@@ -208,16 +208,18 @@ class ConcNet4Hist(nn.Module):
                                          _ptr(xn), _ptr(dead), _ptr(v), stream))
         return xn.reshape(-1, 24, self.rawob_dim), dead.reshape(-1, 24), v.reshape(-1, 24, self.H)
 
-    def _tail(self, vf_c, vf_m, vh_c, vh_m):
+    def _tail(self, vf_c, vf_m, vh_c, vh_m, need_threat=True):
         logits = self.AT_get_logit_db(torch.cat((vf_c, vh_c), -1))
         vm = torch.cat((vf_m, vh_m), -1)
         value = self.CT_get_value(vm)[:, 0]
+        if not need_threat:  # Net.act returns (act, value, log-prob) only (net.py:231): the rollout never reads the threat
+            return logits, value, None
         t = self.CT_get_threat(vm)[:, 0]
         r = 0.5 * 11
         return logits, value, (torch.tanh(t / r) + 1.0) * r                   # re_scale, net.py:226-229
 
     @torch.no_grad()
-    def heads(self, obs_feed, chunk=1 << 18):
+    def heads(self, obs_feed, chunk=1 << 18, need_threat=True):
         """obs_feed f32 [..., 24, D] (empty rows NaN, a dead agent all NaN) -> (logits [..., n_action], value [...],
         threat [...]).  On the device with the fused kernels everything runs in one pass; the torch path processes
         `chunk` agents at a time."""
@@ -228,8 +230,9 @@ class ConcNet4Hist(nn.Module):
             x, dead_u8, v = self.encode_fused(obs_feed)
             vf_c, vf_m = self.MIX_conc_core_f.forward_fused(v, x, dead_u8, 1, 11)
             vh_c, vh_m = self.MIX_conc_core_h.forward_fused(v, x, dead_u8, 12, 12)
-            logits, value, threat = self._tail(vf_c, vf_m, vh_c, vh_m)
-            return logits.reshape(*lead, self.n_action), value.reshape(lead), threat.reshape(lead)
+            logits, value, threat = self._tail(vf_c, vf_m, vh_c, vh_m, need_threat)
+            return (logits.reshape(*lead, self.n_action), value.reshape(lead),
+                    threat.reshape(lead) if need_threat else None)
         x, dead = self._batch_norm(obs_feed)
         x = x.reshape(-1, 24, self.rawob_dim)
         dead = dead.reshape(-1, 24).bool()
@@ -249,7 +252,7 @@ class ConcNet4Hist(nn.Module):
     def act(self, obs_feed, test_mode=False, generator=None):
         """Net.act: (action int32 [...], value f32 [...], log-prob f32 [...]).  test_mode: arg-max (net.py:147), else one
         Categorical draw per agent (Gumbel arg-max of the logits, from `generator` on the device)."""
-        logits, value, _ = self.heads(obs_feed)
+        logits, value, _ = self.heads(obs_feed, need_threat=False)
         logp_all = torch.log_softmax(logits, -1)
         if test_mode:
             act = torch.argmax(logp_all, -1)
