@@ -205,3 +205,29 @@ def test_multiteam_jsonc_injection_and_chainvars():
             config.inject({'hmp2g_b200.multiteam.py->MtScenarioConfig': {'no_such_key': 1}})
     finally:
         config.reset_defaults(MtScenarioConfig, snap)
+
+
+def test_dynamic_norm_merge_matches_reference_moments_on_cpu():
+    """The host half of DynamicNormDevice -- merging batch statistics (sum, sum of squares, non-unit counts, rows) into
+    the running moments, ALGORITHM/common/norm.py:47-63 -- against the reference's DynamicNorm over three batches
+    (tests/golden/policy_net_4hist.npz); the statistics themselves are formed with numpy here (on the device:
+    dca_norm_moments), split in two halves and summed like an all-reduce over two ranks would."""
+    import torch
+    from hmp2g_b200.policy import DynamicNormDevice
+    z = np.load(os.path.join(REPO, 'tests', 'golden', 'policy_net_4hist.npz'))
+    bn = DynamicNormDevice(16)
+    bn.load_state_dict({k[len('sd/_batch_norm.'):]: torch.from_numpy(z[k]) for k in z.files if k.startswith('sd/_batch_norm.')})
+    x = z['obs_feed']
+
+    def stats_of(rows):
+        rows = rows.reshape(-1, 16)
+        r = rows[~np.isnan(rows).any(-1)].astype(np.float64)
+        return np.concatenate([r.sum(0), (r * r).sum(0), ((r != 0) & (r != 1) & (r != -1)).sum(0), [r.shape[0]]])
+    for i in range(3):
+        xb = x[i * 5:(i + 1) * 5]
+        stats = stats_of(xb[:2]) + stats_of(xb[2:])   # two "ranks"
+        bn.merge(torch.from_numpy(stats))
+        np.testing.assert_allclose(bn.mean.numpy(), z['norm%d_mean' % i], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(bn.var.numpy(), z['norm%d_var' % i], rtol=1e-5, atol=1e-6)
+        assert int(bn.n_sample.item()) == int(z['norm%d_n' % i][0])
+        assert np.array_equal(bn.one_hot_filter.numpy(), z['norm%d_filter' % i])
