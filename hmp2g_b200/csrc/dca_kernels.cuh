@@ -545,7 +545,10 @@ __device__ __forceinline__ void obs_pass(const Smem &s, const Params &P, const B
     if (!prebuilt) {
         init_pads(s, L, P);
         for (int i = tid; i < L.N; i += nt) build_row(s, L, i);
-        for (int t = tid; t < L.G * kObsRows; t += nt) s.sid[t] = -1;  // dead guards: zeros (:313-316), no RNG draws
+        {   // dead guards: zeros (:313-316), no RNG draws -- every row starts as "empty" (12 int16 = three 8-byte words)
+            uint2 *w = (uint2 *)s.sid;
+            for (int t = tid; t < L.G * (kObsRows / 4); t += nt) w[t] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
         __syncthreads();
         n_obs_guards = compact_alive(s, 0, L.G, s.glist);
     }
