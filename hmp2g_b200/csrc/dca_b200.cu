@@ -151,8 +151,20 @@ static cudaError_t allow_smem(K kernel, int bytes) {
 // Hand-over words for a planner launch: it waits per env for the step launched right before it on the same stream
 // (DCA_OPT_PIPELINE_STEPS) -- otherwise it is a normal launch behind everything earlier in the stream -- and always
 // publishes its own epoch.
+// A stream that is being captured into a CUDA graph gets ordinary launches: a replay would publish the captured epoch
+// values again, so nothing may wait on them.
+static bool stream_capturing(cudaStream_t st) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    return cudaStreamIsCapturing(st, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone;
+}
+
 static Pipe planner_pipe(DcaHandle *h, cudaStream_t st) {
     Pipe pipe;
+    if (h->pipeline_steps && stream_capturing(st)) {
+        pipe.epoch = nullptr; pipe.wait_step = pipe.wait_plan = pipe.publish = 0u;
+        h->last_was_step = false;
+        return pipe;
+    }
     pipe.epoch = h->pipeline_steps ? h->epoch : nullptr;
     pipe.wait_step = (h->pipeline_steps && h->last_was_step && h->last_step_stream == st) ? h->step_epoch : 0u;
     pipe.wait_plan = 0u;
@@ -325,17 +337,18 @@ int dca_step(DcaHandle *h, const int32_t *actions, const double *att_force, cons
     // DCA_OPT_PIPELINE_STEPS: the step takes its envs over one by one -- env e starts once the previous step launch has
     // published e (its blob; trivially true when the planner was a normal launch behind that step) and reads e's forces
     // once the planner warp of e has published them.  Every step / planner launch publishes, piped or not.
-    const bool piped = h->pipeline_steps && behind_planner && skip == nullptr;
+    const bool live = h->pipeline_steps && !stream_capturing(st_);  // captured launches neither wait nor publish
+    const bool piped = live && behind_planner && skip == nullptr;
     const bool pdl = piped || (h->overlap_planner && behind_planner);
     Pipe pipe;
-    pipe.epoch = h->pipeline_steps ? h->epoch : nullptr;  // epochs are published only while the option is on
+    pipe.epoch = live ? h->epoch : nullptr;  // epochs are published only while the option is on
     pipe.wait_step = piped ? h->step_epoch : 0u;  // 0 on the very first step: nothing to wait for
     pipe.wait_plan = piped ? h->plan_epoch : 0u;
-    pipe.publish = h->pipeline_steps ? ++h->step_epoch : 0u;
+    pipe.publish = live ? ++h->step_epoch : 0u;
     DCA_DISPATCH(h, pdl, k_step, h->P, actions, att_force, skip, rng_words, autoreset, pipe);
     CUDA_TRY(h, cudaGetLastError());
     h->planned_force = nullptr;
-    h->last_was_step = skip == nullptr;  // a pause mask orders the launch behind the whole previous kernel anyway
+    h->last_was_step = live && skip == nullptr;  // a pause mask orders the launch behind the whole previous kernel anyway
     h->last_step_stream = st_;
     h->launches += 1;
     return DCA_OK;

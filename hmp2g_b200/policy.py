@@ -304,7 +304,7 @@ class PolicyRollout(object):
         library's kernels through the C-ABI, torch's GEMMs, the Categorical draw) and return a callable that replays it
         -- one cudaGraphLaunch per env step instead of ~80 launches, which is what bounds a 4 ms step on the host.
         The replayed step writes the same tensors every time (`finished` below, env.obs / reward / done, the rollout
-        buffer).  DCA_OPT_PIPELINE_STEPS keeps host-side epoch counters and must stay off on a captured env."""
+        buffer).  (DCA_OPT_PIPELINE_STEPS keeps host-side epoch counters: the library launches normally while capturing.)"""
         for _ in range(warm):   # allocations, lazy module loads and per-function attributes happen outside the capture
             self.step(collect)
         torch.cuda.synchronize(self.env.device)

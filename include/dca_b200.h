@@ -298,8 +298,9 @@ int dca_mt_debug_phase_clocks(DcaMtHandle *h, uint64_t *clocks);
  * launched as programmatic dependents of each other, so the first CTAs of launch t+1 run in the SM slots the last,
  * partly filled wave of launch t leaves empty (a quarter of a 4096-env launch on 148 SMs).  Results are identical.
  * Anything else on the stream (a policy reading obs, dca_reset, a pause mask) is ordered behind the whole previous
- * launch as usual and restarts the pipeline.  The epoch counters live in the handle on the host: leave the option off
- * on a stream that is being captured into a CUDA graph (a replay would publish the captured epochs again).  Default 0. */
+ * launch as usual and restarts the pipeline.  The epoch counters live in the handle on the host, so launches on a
+ * stream that is being captured into a CUDA graph are ordinary ones (a replay would publish the captured epochs again).
+ * Default 0. */
 #define DCA_OPT_PIPELINE_STEPS 4
 int dca_set_option(DcaHandle *h, int option, int value);
 

@@ -214,7 +214,8 @@ def test_policy_rollout_step_as_cuda_graph_equals_eager_steps():
     arms = []
     for graph in (False, True):
         net = _net(z, torch).train()
-        env = DcaVecEnv(64, scfg=scfg, seed=5, empty_rows_nan=True)
+        # (the captured arm with DCA_OPT_PIPELINE_STEPS on: launches on a capturing stream fall back to ordinary ones)
+        env = DcaVecEnv(64, scfg=scfg, seed=5, empty_rows_nan=True, pipeline_steps=graph)
         roll = PolicyRollout(env, net, gamma_fwd=0.95, seed=1, test_mode=True)
         step = roll.capture(warm=3) if graph else None
         if not graph:
