@@ -109,6 +109,13 @@ class DynamicNormDevice(nn.Module):
         return self.apply_norm(x)
 
 
+def _linear_cat(lin, a, b):
+    """lin(cat((a, b), -1)) without materialising the concatenation: a W[:, :ka]^T + b W[:, ka:]^T + bias."""
+    ka = a.shape[-1]
+    y = torch.addmm(lin.bias, a, lin.weight[:, :ka].t())
+    return y.addmm_(b, lin.weight[:, ka:].t())
+
+
 class ConcCore(nn.Module):
     """Concentration(n_focus_on, h_dim, skip_connect=True, skip_connect_dim), ALGORITHM/common/conc.py:7-63."""
 
@@ -158,7 +165,7 @@ class ConcCore(nn.Module):
         stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
         _lib.check(lib.dca_conc_attend(_ptr(v), _ptr(x), _ptr(dead_u8), _ptr(qk), first, n, self.n_focus_on, B, _ptr(va),
                                        _ptr(stack), stream))
-        v_m = self.CT_motivate_mlp(torch.cat((vs, va @ self.CT_W_val), -1))
+        v_m = torch.relu_(_linear_cat(self.CT_motivate_mlp[0], vs, va @ self.CT_W_val))
         v_c = self.AT_forward_mlp(stack)
         return v_c, v_m
 
@@ -209,12 +216,12 @@ class ConcNet4Hist(nn.Module):
         return xn.reshape(-1, 24, self.rawob_dim), dead.reshape(-1, 24), v.reshape(-1, 24, self.H)
 
     def _tail(self, vf_c, vf_m, vh_c, vh_m, need_threat=True):
-        logits = self.AT_get_logit_db(torch.cat((vf_c, vh_c), -1))
-        vm = torch.cat((vf_m, vh_m), -1)
-        value = self.CT_get_value(vm)[:, 0]
+        db = self.AT_get_logit_db
+        logits = db[4](torch.relu_(db[2](torch.relu_(_linear_cat(db[0], vf_c, vh_c)))))
+        value = self.CT_get_value[2](torch.relu_(_linear_cat(self.CT_get_value[0], vf_m, vh_m)))[:, 0]
         if not need_threat:  # Net.act returns (act, value, log-prob) only (net.py:231): the rollout never reads the threat
             return logits, value, None
-        t = self.CT_get_threat(vm)[:, 0]
+        t = self.CT_get_threat[2](torch.relu_(_linear_cat(self.CT_get_threat[0], vf_m, vh_m)))[:, 0]
         r = 0.5 * 11
         return logits, value, (torch.tanh(t / r) + 1.0) * r                   # re_scale, net.py:226-229
 
