@@ -7,12 +7,12 @@ reference's Python interfaces.  No CPU fallback exists.
 from .config import ChainVar, GlobalConfig, ScenarioConfig, inject, load_jsonc  # noqa: F401
 
 __all__ = ['ChainVar', 'GlobalConfig', 'ScenarioConfig', 'inject', 'load_jsonc', 'DcaVecEnv', 'DcaSuperpoolEnv',
-           'make_parallel_envs', 'gae_return', 'DeviceRollout', 'DeviceRunner', 'MtScenarioConfig', 'DcaMultiTeamVecEnv',
+           'DcaEnvGroups', 'make_parallel_envs', 'gae_return', 'DeviceRollout', 'DeviceRunner', 'MtScenarioConfig', 'DcaMultiTeamVecEnv',
            'DcaMultiTeamSuperpoolEnv']
 
 
 def __getattr__(name):  # torch is imported lazily so that config-only users do not pay for it
-    if name in ('DcaVecEnv', 'DcaSuperpoolEnv', 'make_parallel_envs', 'pod_config'):
+    if name in ('DcaVecEnv', 'DcaSuperpoolEnv', 'DcaEnvGroups', 'make_parallel_envs', 'pod_config'):
         from . import vec_env
         return getattr(vec_env, name)
     if name in ('gae_return', 'normalized_advantage'):

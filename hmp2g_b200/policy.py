@@ -165,7 +165,10 @@ class ConcCore(nn.Module):
         stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
         _lib.check(lib.dca_conc_attend(_ptr(v), _ptr(x), _ptr(dead_u8), _ptr(qk), first, n, self.n_focus_on, B, _ptr(va),
                                        _ptr(stack), stream))
-        v_m = torch.relu_(_linear_cat(self.CT_motivate_mlp[0], vs, va @ self.CT_W_val))
+        # (va W_val) Wm2^T = va (W_val Wm2^T): the 48 x 48 product once per call instead of a [B,48] x [48,48] pass
+        lin = self.CT_motivate_mlp[0]
+        v_m = torch.addmm(lin.bias, vs, lin.weight[:, :self.h_dim].t())
+        v_m = torch.relu_(v_m.addmm_(va, self.CT_W_val @ lin.weight[:, self.h_dim:].t()))
         v_c = self.AT_forward_mlp(stack)
         return v_c, v_m
 

@@ -43,7 +43,7 @@ class DcaVecEnv(object):
     """n_env DCA envs resident on one GPU.  All tensors returned are views of buffers written in place."""
 
     def __init__(self, n_env, scfg=ScenarioConfig, device=None, seed=0, env_gid0=0, debug_outputs=False,
-                 empty_rows_nan=False, overlap_planner=True, pipeline_steps=False):
+                 empty_rows_nan=False, overlap_planner=True, pipeline_steps=False, buffers=None):
         if not torch.cuda.is_available():
             raise _lib.DcaError('hmp2g_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
         self.lib = _lib.load()
@@ -58,12 +58,17 @@ class DcaVecEnv(object):
         self.handle = C.c_void_p()
         _lib.check(self.lib.dca_create(C.byref(self.cfg), self.E, dev_index, C.byref(self.handle)))
         E, G, A, N, dev = self.E, self.G, self.A, self.N, self.device
-        self.obs = torch.zeros((E, G, OBS_ROWS, OBS_ROW), dtype=torch.float32, device=dev)
-        self.tobs = torch.zeros((E, G, OBS_ROWS, OBS_ROW), dtype=torch.float32, device=dev)
-        self.reward = torch.zeros((E, G), dtype=torch.float32, device=dev)
-        self.done = torch.zeros((E,), dtype=torch.uint8, device=dev)
-        self.win = torch.zeros((E,), dtype=torch.uint8, device=dev)
-        self.alive = torch.zeros((E, N), dtype=torch.uint8, device=dev)
+        def out(name, shape, dtype):  # `buffers`: caller-owned output tensors (DcaEnvGroups binds slices of its own)
+            if buffers is None or name not in buffers:
+                return torch.zeros(shape, dtype=dtype, device=dev)
+            self._check_tensor(buffers[name], dtype, shape, name)
+            return buffers[name]
+        self.obs = out('obs', (E, G, OBS_ROWS, OBS_ROW), torch.float32)
+        self.tobs = out('tobs', (E, G, OBS_ROWS, OBS_ROW), torch.float32)
+        self.reward = out('reward', (E, G), torch.float32)
+        self.done = out('done', (E,), torch.uint8)
+        self.win = out('win', (E,), torch.uint8)
+        self.alive = out('alive', (E, N), torch.uint8)
         self.slot_id = torch.full((E, G, OBS_ROWS), -1, dtype=torch.int16, device=dev) if debug_outputs else None
         self.nearest = torch.full((E, A), -1, dtype=torch.int32, device=dev) if debug_outputs else None
         bufs = _lib.DcaBuffers(_ptr(self.obs), _ptr(self.tobs), _ptr(self.reward), _ptr(self.done), _ptr(self.win),
@@ -192,6 +197,88 @@ class DcaVecEnv(object):
         s = _lib.DcaState(*[_ptr(st[n]) for n in _lib.STATE_FIELDS])
         _lib.check(self.lib.dca_import_state(self.handle, C.byref(s), self._stream()), self.handle)
         torch.cuda.current_stream(self.device).synchronize()
+
+
+class DcaEnvGroups(object):
+    """n_env envs as `groups` independent DcaVecEnv of n_env / groups envs each -- contiguous global env ids, so the
+    results are those of one DcaVecEnv(n_env) bit for bit (every draw is keyed by the global env id) -- issuing on their
+    own CUDA streams and writing their slices of shared [n_env, ...] output tensors.
+
+    Why: a launch of E envs ends in a tail (the last, partial wave of CTAs drains while nothing else may start); the
+    launch chains of the groups are independent, so one group's CTAs fill the slots the other group's launch boundary
+    leaves empty, and a latency-bound kernel of one group (the scripted planner) runs under the other group's work.
+    The classic double-buffered sampler: with a policy in the loop, group A's policy forward overlaps group B's env step.
+
+    step(..., sync=True) orders the launches behind the caller's current stream (fork) and the caller's stream behind
+    the results (join).  sync=False only launches: the caller brackets a burst of steps with fork() / join() itself
+    (actions that do not depend on the observations, e.g. a pre-generated pool)."""
+
+    def __init__(self, n_env, groups=2, env_gid0=0, device=None, **kw):
+        assert n_env % groups == 0, 'n_env must be a multiple of the group count'
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device('cuda', torch.cuda.current_device())
+        self.E, self.groups = int(n_env), int(groups)
+        self.Eg = self.E // self.groups
+        self.num_envs = self.E
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(self.groups)]
+        self.envs = []
+        first = DcaVecEnv(self.Eg, env_gid0=env_gid0, device=self.device, **kw)  # its own buffers: gives the shapes
+        self.G, self.A, self.N = first.G, first.A, first.N
+        full = lambda t: torch.zeros((self.E,) + tuple(t.shape[1:]), dtype=t.dtype, device=self.device)
+        self.obs, self.tobs, self.reward = full(first.obs), full(first.tobs), full(first.reward)
+        self.done, self.win, self.alive = full(first.done), full(first.win), full(first.alive)
+        first.close()
+        torch.cuda.synchronize(self.device)
+        for k in range(self.groups):
+            sl = slice(k * self.Eg, (k + 1) * self.Eg)
+            bufs = dict(obs=self.obs[sl], tobs=self.tobs[sl], reward=self.reward[sl], done=self.done[sl],
+                        win=self.win[sl], alive=self.alive[sl])
+            self.envs.append(DcaVecEnv(self.Eg, env_gid0=env_gid0 + k * self.Eg, device=self.device, buffers=bufs, **kw))
+        self._ev = [torch.cuda.Event() for _ in range(self.groups)]
+
+    def close(self):
+        for e in self.envs:
+            e.close()
+
+    def fork(self):
+        """Group streams wait for everything issued so far on the caller's current stream."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        for s in self.streams:
+            s.wait_event(ev)
+
+    def join(self):
+        """The caller's current stream waits for everything the groups have issued."""
+        cur = torch.cuda.current_stream(self.device)
+        for k, s in enumerate(self.streams):
+            self._ev[k].record(s)
+            cur.wait_event(self._ev[k])
+
+    def _each(self, fn, sync):
+        if sync:
+            self.fork()
+        for k, env in enumerate(self.envs):
+            with torch.cuda.stream(self.streams[k]):
+                fn(k, env, slice(k * self.Eg, (k + 1) * self.Eg))
+        if sync:
+            self.join()
+
+    def reset(self, sync=True):
+        self._each(lambda k, env, sl: env.reset(), sync)
+        return self.obs
+
+    def step(self, actions, att_force=None, planner='scripted', skip=None, autoreset=True, sync=True):
+        """actions int32 [E,G]; att_force f64 [E,A,2] or None -> planner 'scripted' (k_plan) / 'centroid' (stand-in) per
+        group on its stream.  Returns (obs, reward, done, win): the shared tensors."""
+        def one(k, env, sl):
+            f = att_force[sl] if att_force is not None else (env.plan() if planner == 'scripted' else env.plan_centroid())
+            env.step(actions[sl], f, skip=None if skip is None else skip[sl], autoreset=autoreset)
+        self._each(one, sync)
+        return self.obs, self.reward, self.done, self.win
+
+    def kernel_launches(self):
+        return sum(e.kernel_launches() for e in self.envs)
 
 
 class DcaSuperpoolEnv(object):

@@ -517,6 +517,48 @@ def test_cuda_pipelined_steps_are_bit_identical(planner):
     assert t >= 47 and n_done >= E // 4   # (at t = 40 the envs paused once are the ones that have just finished)
 
 
+@pytest.mark.parametrize('groups', [2, 4])
+def test_cuda_env_groups_are_bit_identical_to_one_env(groups):
+    """DcaEnvGroups: E envs as independent groups on their own streams (contiguous global env ids) must produce what one
+    DcaVecEnv(E) produces, bit for bit -- joined every step (sync=True), and in bursts of unjoined steps (sync=False,
+    the groups drifting apart by whole launches)."""
+    torch = _torch()
+    from hmp2g_b200.vec_env import DcaEnvGroups, DcaVecEnv
+    cfg = dict(num_guards=50, num_attackers=50, MaxEpisodeStep=40, random_jam_prob=0.05, introduce_terrain=True)
+    E = 2048
+    one = DcaVecEnv(E, scfg=scenario_from_dict(cfg), seed=11, env_gid0=64)
+    grp = DcaEnvGroups(E, groups=groups, scfg=scenario_from_dict(cfg), seed=11, env_gid0=64)
+    one.reset()
+    grp.reset()
+    gen = torch.Generator(device=one.device)
+    gen.manual_seed(3)
+    acts = [torch.randint(0, 7, (E, 50), generator=gen, device=one.device, dtype=torch.int32) for _ in range(8)]
+    torch.cuda.synchronize()
+
+    def same(t):
+        for name in ('obs', 'tobs', 'reward', 'done', 'win', 'alive'):
+            assert torch.equal(getattr(one, name), getattr(grp, name)), (t, name)
+
+    same(-1)
+    n_done = 0
+    for t in range(45):   # joined steps, scripted planner; episodes end and autoreset
+        one.step(acts[t % 8], one.plan())
+        grp.step(acts[t % 8], planner='scripted')
+        same(t)
+        n_done += int(one.done.sum().item())
+    assert n_done >= E
+    for burst in (3, 17, 40):   # unjoined bursts, centroid stand-in
+        for t in range(burst):
+            one.step(acts[t % 8], one.plan_centroid())
+        grp.fork()
+        for t in range(burst):
+            grp.step(acts[t % 8], planner='centroid', sync=False)
+        grp.join()
+        same(burst)
+    assert grp.kernel_launches() >= groups * (1 + 2 * (45 + 60))
+    grp.close()
+
+
 def test_cuda_gae_policy_resonance_levels_match_reference():
     """gae_return_levels against the reference's gae_finalize_return_pr fixtures (ALGORITHM/common/traj_gae.py:135-169):
     returns of every value level bit-exact, threat (SAFE_LIMIT 8) and pushed reward exact."""
