@@ -455,16 +455,72 @@ def run_ours(args):
             plan_call(h, fptr, sptr)
             assert lib.dca_step(h, aptrs[s % n_pool], fptr, C.c_void_p(skip.data_ptr()), None, 1, sptr) == 0
         torch.cuda.synchronize()
+    sampler = ClockSampler(physical_gpu_index(local_rank), period=0.002) if rank == 0 else None
+    # ---- the headline region with --env-groups n > 1: the E envs as n independent groups (DcaEnvGroups: E / n envs
+    # each, contiguous global env ids, own streams; same results as one group, tests/test_gpu_parity.py) -- one group's
+    # CTAs fill the slots the other group's launch boundary leaves empty.  Per-env pipelining is off in the groups.
+    n_groups = args.env_groups if args.env_groups > 0 else (2 if args.planner == 'centroid' else 1)
+    grouped = None
+    if n_groups > 1:
+        from hmp2g_b200.vec_env import DcaEnvGroups
+        grp = DcaEnvGroups(E, groups=n_groups, scfg=scfg, device=dev, seed=SEED, env_gid0=rank * E,
+                           overlap_planner=bool(overlap))
+        grp.reset()
+        Eg = grp.Eg
+        g_s = [C.c_void_p(s.cuda_stream) for s in grp.streams]
+        g_f = [C.c_void_p(ge._force.data_ptr()) for ge in grp.envs]
+        g_a = [[C.c_void_p(a[k * Eg:(k + 1) * Eg].data_ptr()) for a in act_pool] for k in range(n_groups)]
+
+        def group_step(i, skips=None):
+            for k, ge in enumerate(grp.envs):
+                plan_call(ge.handle, g_f[k], g_s[k])
+                lib.dca_step(ge.handle, g_a[k][i % n_pool], g_f[k],
+                             None if skips is None else C.c_void_p(skips.data_ptr() + k * Eg), None, 1, g_s[k])
+        if preroll:
+            all_skips = (offs[None, :] < (preroll - torch.arange(preroll, device=dev))[:, None]).to(torch.uint8)
+            torch.cuda.synchronize()
+            for s in range(preroll):
+                group_step(s, all_skips[s])
+            torch.cuda.synchronize()
+            del all_skips
+        for i in range(W):
+            group_step(i)
+        gt0, gt1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if sampler:
+            sampler.start()
+        gl0 = grp.kernel_launches()
+        gt0.record(stream)
+        for s_ in grp.streams:
+            s_.wait_event(gt0)
+        for i in range(K):
+            group_step(W + i)
+        grp.join()
+        gt1.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        tg = torch.tensor([gt0.elapsed_time(gt1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+        grouped = {'ms_total': float(tg.item()), 'gpu_launches': grp.kernel_launches() - gl0,
+                   'alive_frac': float(grp.alive.float().mean().item()), 'done_frac': float(grp.done.float().mean().item())}
+        grp.close()
+        del grp
+        torch.cuda.empty_cache()
     launches0 = env.kernel_launches()
     for i in range(W):
         assert one_step(i) == 0
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(physical_gpu_index(local_rank), period=0.002) if rank == 0 else None
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    if sampler:
+    if sampler and grouped is None:
         sampler.start()
     launches_before = env.kernel_launches()
     # timed region: K steps back to back, nothing else on the stream (the step kernel is a programmatic dependent of
@@ -554,6 +610,14 @@ def run_ours(args):
     value = world * E * N * K / (ms_total * 1e-3)
     alive_frac = float(env.alive.float().mean().item())
     done_frac = float(env.done.float().mean().item())
+    one_group = {'value': value, 'unit': 'agent-steps/s', 'ms_per_step': ms_total / K, 'gpu_launches': gpu_launches,
+                 'pipeline_steps': bool(piped),
+                 'what': 'the same K steps with all %d envs in one DcaVecEnv on one stream (launch t+1 handed its envs '
+                         'one by one, DCA_OPT_PIPELINE_STEPS)' % E}
+    if grouped is not None:  # the headline is the grouped region
+        ms_total, gpu_launches = grouped['ms_total'], grouped['gpu_launches']
+        value = world * E * N * K / (ms_total * 1e-3)
+        alive_frac, done_frac = grouped['alive_frac'], grouped['done_frac']
 
     # ---- the gather kernel alone (k_observe: kNN + obs gather on the resident state), north_star's ">= 60 % of HBM
     # roofline on the gather kernel" line
@@ -700,7 +764,11 @@ def run_ours(args):
     ncu = ncu_traffic()
     traffic = args.traffic if args.traffic is not None else (
         ncu.get('k_step_dram_bytes_per_launch') if (E == ncu.get('envs_per_gpu') and args.scenario == '50v50') else None)
-    achieved = algo_bytes / (ms_step_kernel * 1e-3) / 1e9
+    achieved_alone = algo_bytes / (ms_step_kernel * 1e-3) / 1e9
+    # roofline.achieved: the algorithmic bytes of the k_step launches of the timed region / the region's time (CUDA events
+    # on the launch stream).  Launches overlap there (env groups / per-env hand-over), so this is the only launch
+    # duration the region defines; the stand-alone duration of one launch over all E envs is reported next to it.
+    achieved = algo_bytes / (ms_total / K * 1e-3) / 1e9
     line = {
         'metric': 'agent_steps_per_sec', 'value': value, 'unit': 'agent-steps/s', 'n_gpus': world, 'steps': K,
         'warmup': W, 'ms_per_step': ms_total / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
@@ -710,7 +778,12 @@ def run_ours(args):
                                % (G, A, E, 'centroid planner stand-in' if args.planner == 'centroid' else
                                   'scripted formation planner k_plan in the timed region',
                                   '' if args.scenario == '50v50' else ' at another team size'),
-                   'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD, 'overlap_planner': bool(overlap), 'pipeline_steps': bool(piped),
+                   'envs_per_gpu': E, 'entities_per_env': N, 'scenario': WORKLOAD, 'overlap_planner': bool(overlap),
+                   'env_groups': n_groups,
+                   'env_groups_note': ('the %d envs step as %d independent groups of %d (DcaEnvGroups: own streams, '
+                                       'contiguous global env ids, results identical to one group)' % (E, n_groups, E // n_groups))
+                   if grouped is not None else 'one group',
+                   'pipeline_steps': bool(piped) if grouped is None else False,
                    'pre_roll': ('each env advanced by a random number of steps in [0, %d) before warm-up (untimed set-up): '
                                 'stationary mix of episode phases' % preroll) if preroll else 'none: synchronised reset',
                    'l2': 'no explicit flush: per-step working set %.0f MB (obs %.0f MB written + state %.0f MB r/w) '
@@ -719,17 +792,25 @@ def run_ours(args):
                    'alive_fraction_at_end': alive_frac, 'done_fraction_last_step': done_frac},
         'roofline': {'bound': 'hbm', 'kernel': 'k_step', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
-                     'algorithmic_bytes_per_launch': algo_bytes, 'kernel_ms': ms_step_kernel,
+                     'algorithmic_bytes_per_launch': algo_bytes,
+                     'achieved_source': 'timed region: %d k_step launches x %d envs, algorithmic bytes / region time '
+                                        '(planner stand-in launches inside that time)' % (K * n_groups, E // n_groups),
+                     'achieved_standalone': achieved_alone, 'frac_standalone': achieved_alone / peak,
+                     'kernel_ms': ms_step_kernel,
                      'kernel_ms_source': 'CUDA events around each k_step launch over the %d steps that follow the '
                                          'timed region (same episodes; launched stand-alone: in the timed region the '
                                          'kernel starts under the planner stand-in, DCA_OPT_OVERLAP_PLANNER)' % Kfirst,
                      'kernel_ms_episode_avg': ms_step_kernel_episode, 'episode_avg_steps': Kk,
-                     'pipelined_ms_per_step': ms_total / K,
-                     'frac_pipelined': algo_bytes / (ms_total / K * 1e-3) / 1e9 / peak,
-                     'pipelined_note': 'in the timed region launch t+1 starts inside the last wave of launch t '
-                                       '(DCA_OPT_PIPELINE_STEPS), so a launch has no duration of its own there: this is '
-                                       'algorithmic bytes / (region time / K); kernel_ms is the same kernel launched '
-                                       'stand-alone',
+                     'timed_region_ms_per_step': ms_total / K,
+                     'frac_timed_region': algo_bytes / (ms_total / K * 1e-3) / 1e9 / peak,
+                     'timed_region_note': 'in the timed region launches overlap (env groups on their own streams / '
+                                          'launch t+1 starting inside the last wave of launch t), so a launch has no '
+                                          'duration of its own there: this is the algorithmic bytes of all k_step '
+                                          'launches of the region / region time (the planner stand-in launches are '
+                                          'inside that time); kernel_ms and frac are the same kernel launched '
+                                          'stand-alone over all %d envs' % E,
+                     'pipelined_ms_per_step': one_group['ms_per_step'],
+                     'frac_pipelined': algo_bytes / (one_group['ms_per_step'] * 1e-3) / 1e9 / peak,
                      'kernel_ms_synchronised_start': ms_step_sync_start,
                      'frac_synchronised_start': algo_bytes / (ms_step_sync_start * 1e-3) / 1e9 / peak,
                      'frac_episode_avg': algo_bytes / (ms_step_kernel_episode * 1e-3) / 1e9 / peak,
@@ -758,6 +839,7 @@ def run_ours(args):
         'e2e': {'value': e2e_value, 'unit': 'agent-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'steps': Ke, 'api': 'DcaSuperpoolEnv.step (numpy actions in; planner + step on device; numpy '
                                     'obs/reward/done/info out)'},
+        'one_group': one_group if grouped is not None else None,
         'with_scripted_planner': scripted,
         'other_configs': other,
         'policy_rollout_50v55': policy_line,
@@ -805,6 +887,9 @@ def main():
     ap.add_argument('--no-other-configs', action='store_true', help='skip the 100v100 / 50v55 report lines')
     ap.add_argument('--planner', default='centroid', choices=['centroid', 'scripted'],
                     help='attacker forces: the centroid stand-in of configs[1] (default) or the scripted formation planner k_plan')
+    ap.add_argument('--env-groups', type=int, default=0,
+                    help='step the envs as this many independent groups on their own streams (DcaEnvGroups); '
+                         '0 = 2 with the centroid stand-in, 1 with --planner scripted')
     ap.add_argument('--no-preroll', action='store_true',
                     help='time from a synchronised reset of all envs instead of the stationary episode-phase mix')
     ap.add_argument('--no-pipeline', action='store_true',

@@ -12,14 +12,14 @@ from hmp2g_b200.config import ScenarioConfig  # noqa: E402
 from hmp2g_b200.vec_env import DcaVecEnv  # noqa: E402
 
 
-def run(groups, piped, E=4096, steps=720, preroll=True):
+def run(groups, piped, E=4096, steps=720, preroll=True, overlap=True, scripted=False):
     scfg = type('S', (ScenarioConfig,), dict(bench.WORKLOAD))
     Eg = E // groups
     streams = [torch.cuda.Stream() for _ in range(groups)]
     envs = []
     for k in range(groups):
         with torch.cuda.stream(streams[k]):
-            env = DcaVecEnv(Eg, scfg=scfg, seed=1, env_gid0=k * Eg, overlap_planner=True, pipeline_steps=piped)
+            env = DcaVecEnv(Eg, scfg=scfg, seed=1, env_gid0=k * Eg, overlap_planner=overlap, pipeline_steps=piped)
             env.reset()
             envs.append(env)
     g = torch.Generator(device=envs[0].device)
@@ -28,10 +28,19 @@ def run(groups, piped, E=4096, steps=720, preroll=True):
     pools = [[p[k * Eg:(k + 1) * Eg].contiguous() for p in pool] for k in range(groups)]
     torch.cuda.synchronize()
 
-    def step_all(i):
+    import ctypes as C
+    lib = envs[0].lib
+    sp = [C.c_void_p(s.cuda_stream) for s in streams]
+    fp = [C.c_void_p(e._force.data_ptr()) for e in envs]
+    ap = [[C.c_void_p(a.data_ptr()) for a in pools[k]] for k in range(groups)]
+
+    def step_all(i):   # raw C-ABI calls, as bench.py's timed loop
         for k in range(groups):
-            with torch.cuda.stream(streams[k]):
-                envs[k].step(pools[k][i % 16], envs[k].plan_centroid())
+            if scripted:
+                lib.dca_plan(envs[k].handle, fp[k], None, None, sp[k])
+            else:
+                lib.dca_plan_centroid(envs[k].handle, fp[k], sp[k])
+            lib.dca_step(envs[k].handle, ap[k][i % 16], fp[k], None, None, 1, sp[k])
 
     if preroll:   # stationary episode-phase mix, as bench.py
         for k in range(groups):
@@ -41,7 +50,7 @@ def run(groups, piped, E=4096, steps=720, preroll=True):
                 offs = torch.randint(0, 180, (Eg,), generator=gk, device=envs[k].device)
                 for s_ in range(180):
                     skip = (offs < (180 - s_)).to(torch.uint8)
-                    envs[k].step(pools[k][s_ % 16], envs[k].plan_centroid(), skip=skip)
+                    envs[k].step(pools[k][s_ % 16], envs[k].plan() if scripted else envs[k].plan_centroid(), skip=skip)
     for i in range(200):
         step_all(i)
     torch.cuda.synchronize()
@@ -61,11 +70,20 @@ def run(groups, piped, E=4096, steps=720, preroll=True):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
-    print('groups=%d piped=%d E=%d: %.4f ms per step of all groups, %.3f G agent-steps/s' % (
-        groups, piped, E, ms, E * envs[0].N / ms / 1e6), flush=True)
+    print('%s groups=%d piped=%d overlap=%d E=%d: %.4f ms per step of all groups, %.3f G agent-steps/s' % (
+        'scripted' if scripted else 'centroid', groups, piped, overlap, E, ms, E * envs[0].N / ms / 1e6), flush=True)
 
 
 if __name__ == '__main__':
-    for groups in (1, 2, 4):
-        for piped in (True, False):
-            run(groups, piped)
+    run(1, True)
+    for groups in (2, 4, 8):
+        run(groups, False)
+        run(groups, False, overlap=False)
+    run(2, True)
+    run(1, True, steps=360, scripted=True)
+    for groups in (2, 4):
+        run(groups, True, steps=360, scripted=True)
+        run(groups, False, steps=360, scripted=True)
+    for E in (2048, 8192):
+        run(1, True, E=E)
+        run(2, False, E=E)
