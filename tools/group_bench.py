@@ -12,7 +12,7 @@ from hmp2g_b200.config import ScenarioConfig  # noqa: E402
 from hmp2g_b200.vec_env import DcaVecEnv  # noqa: E402
 
 
-def run(groups, piped, E=4096, steps=720, preroll=True, overlap=True, scripted=False):
+def run(groups, piped, E=4096, steps=720, preroll=True, overlap=True, scripted=False, noplan=False):
     scfg = type('S', (ScenarioConfig,), dict(bench.WORKLOAD))
     Eg = E // groups
     streams = [torch.cuda.Stream() for _ in range(groups)]
@@ -36,7 +36,9 @@ def run(groups, piped, E=4096, steps=720, preroll=True, overlap=True, scripted=F
 
     def step_all(i):   # raw C-ABI calls, as bench.py's timed loop
         for k in range(groups):
-            if scripted:
+            if noplan:   # forces left as they are: what the step costs with no planner launch in the chain at all
+                pass
+            elif scripted:
                 lib.dca_plan(envs[k].handle, fp[k], None, None, sp[k])
             else:
                 lib.dca_plan_centroid(envs[k].handle, fp[k], sp[k])
@@ -71,10 +73,16 @@ def run(groups, piped, E=4096, steps=720, preroll=True, overlap=True, scripted=F
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     print('%s groups=%d piped=%d overlap=%d E=%d: %.4f ms per step of all groups, %.3f G agent-steps/s' % (
-        'scripted' if scripted else 'centroid', groups, piped, overlap, E, ms, E * envs[0].N / ms / 1e6), flush=True)
+        'no planner launch' if noplan else ('scripted' if scripted else 'centroid'), groups, piped, overlap, E, ms,
+        E * envs[0].N / ms / 1e6), flush=True)
 
 
 if __name__ == '__main__':
+    if len(sys.argv) > 1 and sys.argv[1] == 'noplan':
+        run(2, False)
+        for groups in (2, 3, 4):
+            run(groups, False, E=4096 // groups * groups, noplan=True)
+        sys.exit(0)
     run(1, True)
     for groups in (2, 4, 8):
         run(groups, False)
