@@ -278,9 +278,14 @@ class PolicyRollout(object):
     step (k_step) + history pool (k_histpool) + conc_4hist policy + rollout buffer + GAE (k_gae), no host hop.
     env: DcaVecEnv(empty_rows_nan=True) whose guards the policy drives."""
 
-    def __init__(self, env, net, gamma=0.99, tau=0.95, gamma_fwd=None, seed=0, test_mode=False):
+    def __init__(self, env, net, gamma=0.99, tau=0.95, gamma_fwd=None, seed=0, test_mode=False, plan_ahead=True):
         from .rollout import DeviceRollout, HistoryPool
         self.env, self.net, self.test_mode = env, net, test_mode
+        # plan_ahead: the scripted attackers' planner (k_plan) needs the env state, not the guards' actions -- it runs on
+        # a side stream under the policy forward (one warp per env chasing dependent chains: it leaves the SMs' issue
+        # slots to the policy's GEMMs) and the step joins both.  Same launches, same results; also inside a CUDA graph
+        # (fork / join by events = parallel branches of the captured graph).
+        self._side = torch.cuda.Stream(device=env.device) if plan_ahead else None
         self.hist = HistoryPool(env.E, env.G, device=env.device)
         self.buf = DeviceRollout(env, gamma=gamma, tau=tau, gamma_fwd=gamma_fwd)
         self.gen = torch.Generator(device=env.device)
@@ -295,11 +300,22 @@ class PolicyRollout(object):
         """One env step of every env: history roll -> policy -> plan -> step -> rollout buffer.  Returns the mask of
         finished envs (device bool [E])."""
         env = self.env
+        force = None
+        if self._side is not None:
+            cur = torch.cuda.current_stream(env.device)
+            fork, join = torch.cuda.Event(), torch.cuda.Event()
+            fork.record(cur)
+            self._side.wait_event(fork)
+            with torch.cuda.stream(self._side):
+                force = env.plan()
+                join.record(self._side)
         feed = self.hist.roll(self.obs, suffered_reset=self.suffered)
         act, value, _ = self.net.act(feed, test_mode=self.test_mode, generator=self.gen)
         alive_before = self.buf.alive_guards().clone() if collect else None
         lens_before = self.buf.length.clone() if collect else None
-        self.obs, reward, done, win = env.step(act)   # plan() inside: the scripted attackers of World.step
+        if force is not None:
+            cur.wait_event(join)
+        self.obs, reward, done, win = env.step(act, force)   # force None: plan() inside, the scripted attackers of World.step
         fin = done != 0
         if collect:
             self.buf.add(alive_before, value, reward, done)

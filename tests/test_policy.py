@@ -202,7 +202,9 @@ def test_policy_rollout_50v55_statistics_match_reference_run():
 def test_policy_rollout_step_as_cuda_graph_equals_eager_steps():
     """PolicyRollout.capture(): one env step of the whole loop (history roll, normalisation update, network, draw,
     planner, step, rollout buffer) replayed as a CUDA graph gives the same trajectory as eager steps -- same seeds, test
-    mode (arg-max actions) so both arms take identical actions."""
+    mode (arg-max actions) so both arms take identical actions.  The eager arm plans inside env.step on the one stream;
+    the captured arm runs the planner on its side stream under the policy forward (plan_ahead), so the test also pins
+    that fork / join."""
     import torch
     from hmp2g_b200.config import ScenarioConfig
     from hmp2g_b200.policy import PolicyRollout
@@ -216,7 +218,7 @@ def test_policy_rollout_step_as_cuda_graph_equals_eager_steps():
         net = _net(z, torch).train()
         # (the captured arm with DCA_OPT_PIPELINE_STEPS on: launches on a capturing stream fall back to ordinary ones)
         env = DcaVecEnv(64, scfg=scfg, seed=5, empty_rows_nan=True, pipeline_steps=graph)
-        roll = PolicyRollout(env, net, gamma_fwd=0.95, seed=1, test_mode=True)
+        roll = PolicyRollout(env, net, gamma_fwd=0.95, seed=1, test_mode=True, plan_ahead=graph)
         step = roll.capture(warm=3) if graph else None
         if not graph:
             for _ in range(3):
