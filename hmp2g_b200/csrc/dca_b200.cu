@@ -603,6 +603,29 @@ int dca_policy_encode(const float *x, const float *mean, const float *var, const
     return DCA_OK;
 }
 
+int dca_policy_linear(const float *a, int lda, int ka, const float *wa, int wa_sn, int wa_sk, const float *b, int ldb, int kb,
+                      const float *wb, int wb_sn, int wb_sk, const float *bias, int n, int relu, uint64_t rows, float *out,
+                      int ldo, dca_stream_t stream) {
+    if (!a || !wa || !out || rows == 0 || ka <= 0 || n <= 0 || (kb > 0 && (!b || !wb)))
+        return fail(nullptr, DCA_E_INVALID, "dca_policy_linear: null buffer or empty batch");
+    if (n > 48 || (ka & 3) || (kb & 3) || kb < 0 || (lda & 3) || (kb > 0 && (ldb & 3)) || ldo < n)
+        return fail(nullptr, DCA_E_INVALID, "dca_policy_linear: n <= 48, ka / kb / lda / ldb multiples of 4, ldo >= n");
+    if (((uintptr_t)a & 15) || (kb > 0 && ((uintptr_t)b & 15)))
+        return fail(nullptr, DCA_E_INVALID, "dca_policy_linear: inputs must be 16-byte aligned");
+    PtrDeviceGuard guard(a);
+    const LinSrc sa{a, wa, lda, ka, wa_sn, wa_sk};
+    const LinSrc sb{b, wb, ldb, kb > 0 ? kb : 0, wb_sn, wb_sk};
+    const size_t tiles = (rows + kLinTile - 1) / kLinTile;
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, 148 * 4);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n > 24) k_policy_linear<6><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, relu, (size_t)rows, out, ldo);
+    else if (n > 8) k_policy_linear<3><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, relu, (size_t)rows, out, ldo);
+    else k_policy_linear<1><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, relu, (size_t)rows, out, ldo);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_linear: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
 // ---- dca_adv_moments_static: the same two kernels with the per-CTA partials in a library-owned array ---------------
 // No counterpart in the reference; added for callers that cannot call cudaMalloc
 // (graph capture, serving loops).  The array lives in every GPU context that loads the library until exit.

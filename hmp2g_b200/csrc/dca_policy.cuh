@@ -342,4 +342,101 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode(const float4 *__r
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// One dense layer of the conc / conc_4hist policy on every agent row: out = act(a Wa^T + b Wb^T + bias), N <= 48 output
+// features, for the layers behind the attention (Concentration's query / key / value / motivate / forward layers
+// ALGORITHM/common/conc.py:30-62, the logit / value / threat heads ALGORITHM/conc_4hist/net.py:213-229).  The second
+// input replaces the reference's torch.cat((a, b), -1) in front of a Linear.  Why not cuBLAS: its float32 SIMT tiles
+// are 64 x 128 and N is 48 (24, 7, 1 in the heads), so 62 % of every tile is padding, and bias and ReLU are separate
+// passes over the activation.  Here a CTA owns 128 rows x all N columns, register-blocked like k_policy_encode (a
+// thread accumulates 8 rows x NC columns, N <= 8 NC), the inputs come through shared memory k-major in chunks of up to
+// 64 features, float32 FFMA in ascending k.
+// a: [rows, Ka] with row stride lda (a column slice of a wider tensor is fine), b likewise (Kb = 0: none); weights are
+// addressed W[n * sn + k * sk], so nn.Linear weights, their column halves and transposed matrices need no copies.
+constexpr int kLinTile = 128, kLinThreads = 128, kLinKC = 64;
+struct LinSmem {
+    float xs[kLinKC][kLinTile + 4];
+    float ws[kLinKC][48];
+};
+struct LinSrc {
+    const float *x;
+    const float *w;
+    int ld, K, sn, sk;
+};
+
+template <int NC>
+__global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, const LinSrc sb, const float *__restrict__ bias,
+                                                               int N, int relu, size_t rows, float *__restrict__ out, int ldo) {
+    __shared__ __align__(16) LinSmem s;
+    constexpr int NP = 8 * NC;  // padded width
+    const int tid = threadIdx.x;
+    const int rg = tid >> 3, cg = tid & 7;
+    const size_t tiles = (rows + kLinTile - 1) / kLinTile;
+    float bs[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) bs[c] = (bias != nullptr && cg * NC + c < N) ? bias[cg * NC + c] : 0.f;
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const size_t r0 = tile * kLinTile;
+        float acc[8][NC];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[r][c] = bs[c];
+        for (int src = 0; src < 2; ++src) {
+            const LinSrc &S = src == 0 ? sa : sb;
+            for (int k0 = 0; k0 < S.K; k0 += kLinKC) {
+                const int kc = min(kLinKC, S.K - k0);  // a multiple of 4 (checked by the host)
+                __syncthreads();  // the previous chunk has been consumed
+                // inputs: a lane quad reads 16 consecutive floats of one row; transposed into xs[k][row]
+                for (int kb = 0; kb < kc; kb += 16) {
+                    const int quad = tid & 3, kq = kb + quad * 4;
+#pragma unroll
+                    for (int pass = 0; pass < 4; ++pass) {
+                        const int lr = pass * 32 + (tid >> 2);
+                        const size_t row = r0 + lr;
+                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (row < rows && kq < kc) v = *(const float4 *)(S.x + row * (size_t)S.ld + k0 + kq);
+                        if (kq < kc) { s.xs[kq][lr] = v.x; s.xs[kq + 1][lr] = v.y; s.xs[kq + 2][lr] = v.z; s.xs[kq + 3][lr] = v.w; }
+                    }
+                }
+                // weights of this chunk, k-major, zero beyond N
+                for (int i = tid; i < kc * NP; i += kLinThreads) {
+                    const int k = i / NP, n = i - k * NP;
+                    s.ws[k][n] = n < N ? S.w[(size_t)n * S.sn + (size_t)(k0 + k) * S.sk] : 0.f;
+                }
+                __syncthreads();
+#pragma unroll 4
+                for (int k = 0; k < kc; ++k) {
+                    const float4 a0 = *(const float4 *)&s.xs[k][rg * 8], a1 = *(const float4 *)&s.xs[k][rg * 8 + 4];
+                    const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                    float w[NC];
+                    if constexpr (NC == 6) {
+                        const float2 w01 = *(const float2 *)&s.ws[k][cg * 6], w23 = *(const float2 *)&s.ws[k][cg * 6 + 2],
+                                     w45 = *(const float2 *)&s.ws[k][cg * 6 + 4];
+                        w[0] = w01.x; w[1] = w01.y; w[2] = w23.x; w[3] = w23.y; w[4] = w45.x; w[5] = w45.y;
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < NC; ++c) w[c] = s.ws[k][cg * NC + c];
+                    }
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+#pragma unroll
+                        for (int c = 0; c < NC; ++c) acc[r][c] = fmaf(a[r], w[c], acc[r][c]);
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const size_t row = r0 + rg * 8 + r;
+            if (row < rows) {
+#pragma unroll
+                for (int c = 0; c < NC; ++c) {
+                    const int n = cg * NC + c;
+                    if (n < N) out[row * (size_t)ldo + n] = relu ? fmaxf(acc[r][c], 0.f) : acc[r][c];
+                }
+            }
+        }
+    }
+}
+
 }  // namespace dca

@@ -116,6 +116,24 @@ def _linear_cat(lin, a, b):
     return y.addmm_(b, lin.weight[:, ka:].t())
 
 
+def _plin(a, wa, b=None, wb=None, bias=None, relu=False):
+    """act(a wa^T + b wb^T + bias) on the device in one kernel (dca_policy_linear): a [B,ka] / b [B,kb] float32 with unit
+    inner stride (column slices of wider tensors are fine), wa [n,ka] / wb [n,kb] any 2-D views (x @ M: pass M.t())."""
+    lib = _lib.load()
+    B, n = a.shape[0], wa.shape[0]
+    assert a.dtype == torch.float32 and a.stride(1) == 1 and wa.shape[1] == a.shape[1]
+    out = torch.empty((B, n), dtype=torch.float32, device=a.device)
+    if b is not None:
+        assert b.dtype == torch.float32 and b.stride(1) == 1 and wb.shape == (n, b.shape[1]) and b.shape[0] == B
+    stream = C.c_void_p(torch.cuda.current_stream(a.device).cuda_stream)
+    _lib.check(lib.dca_policy_linear(
+        _ptr(a), a.stride(0), a.shape[1], _ptr(wa), wa.stride(0), wa.stride(1),
+        None if b is None else _ptr(b), 0 if b is None else b.stride(0), 0 if b is None else b.shape[1],
+        None if b is None else _ptr(wb), 0 if b is None else wb.stride(0), 0 if b is None else wb.stride(1),
+        None if bias is None else _ptr(bias), n, int(bool(relu)), B, _ptr(out), out.stride(0), stream))
+    return out
+
+
 class ConcCore(nn.Module):
     """Concentration(n_focus_on, h_dim, skip_connect=True, skip_connect_dim), ALGORITHM/common/conc.py:7-63."""
 
@@ -159,17 +177,17 @@ class ConcCore(nn.Module):
         lib = _lib.load()
         B = v.shape[0]
         vs = v[:, 0]
-        qk = ((vs @ self.CT_W_query) @ self.CT_W_key.t()).contiguous()
+        qk = _plin(_plin(vs, self.CT_W_query.t()), self.CT_W_key)   # (vs W_query) W_key^T
         va = torch.empty((B, self.h_dim), dtype=torch.float32, device=v.device)
         stack = torch.empty((B, (self.n_focus_on + 1) * (self.h_dim + x.shape[-1])), dtype=torch.float32, device=v.device)
         stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
         _lib.check(lib.dca_conc_attend(_ptr(v), _ptr(x), _ptr(dead_u8), _ptr(qk), first, n, self.n_focus_on, B, _ptr(va),
                                        _ptr(stack), stream))
         # (va W_val) Wm2^T = va (W_val Wm2^T): the 48 x 48 product once per call instead of a [B,48] x [48,48] pass
-        lin = self.CT_motivate_mlp[0]
-        v_m = torch.addmm(lin.bias, vs, lin.weight[:, :self.h_dim].t())
-        v_m = torch.relu_(v_m.addmm_(va, self.CT_W_val @ lin.weight[:, self.h_dim:].t()))
-        v_c = self.AT_forward_mlp(stack)
+        lin, fwd = self.CT_motivate_mlp[0], self.AT_forward_mlp[0]
+        fold = self.CT_W_val @ lin.weight[:, self.h_dim:].t()
+        v_m = _plin(vs, lin.weight[:, :self.h_dim], va, fold.t(), lin.bias, relu=True)
+        v_c = _plin(stack, fwd.weight, bias=fwd.bias, relu=True)
         return v_c, v_m
 
 
@@ -218,6 +236,21 @@ class ConcNet4Hist(nn.Module):
                                          _ptr(xn), _ptr(dead), _ptr(v), stream))
         return xn.reshape(-1, 24, self.rawob_dim), dead.reshape(-1, 24), v.reshape(-1, 24, self.H)
 
+    def _tail_fused(self, vf_c, vf_m, vh_c, vh_m, need_threat=True):
+        """_tail with every layer as one dca_policy_linear launch (the concatenations become second inputs)."""
+        h = self.H
+        db, cv, ct = self.AT_get_logit_db, self.CT_get_value, self.CT_get_threat
+        a1 = _plin(vf_c, db[0].weight[:, :h], vh_c, db[0].weight[:, h:], db[0].bias, relu=True)
+        logits = _plin(_plin(a1, db[2].weight, bias=db[2].bias, relu=True), db[4].weight, bias=db[4].bias)
+        c1 = _plin(vf_m, cv[0].weight[:, :h], vh_m, cv[0].weight[:, h:], cv[0].bias, relu=True)
+        value = _plin(c1, cv[2].weight, bias=cv[2].bias)[:, 0]
+        if not need_threat:
+            return logits, value, None
+        t1 = _plin(vf_m, ct[0].weight[:, :h], vh_m, ct[0].weight[:, h:], ct[0].bias, relu=True)
+        t = _plin(t1, ct[2].weight, bias=ct[2].bias)[:, 0]
+        r = 0.5 * 11
+        return logits, value, (torch.tanh(t / r) + 1.0) * r
+
     def _tail(self, vf_c, vf_m, vh_c, vh_m, need_threat=True):
         db = self.AT_get_logit_db
         logits = db[4](torch.relu_(db[2](torch.relu_(_linear_cat(db[0], vf_c, vh_c)))))
@@ -240,7 +273,7 @@ class ConcNet4Hist(nn.Module):
             x, dead_u8, v = self.encode_fused(obs_feed)
             vf_c, vf_m = self.MIX_conc_core_f.forward_fused(v, x, dead_u8, 1, 11)
             vh_c, vh_m = self.MIX_conc_core_h.forward_fused(v, x, dead_u8, 12, 12)
-            logits, value, threat = self._tail(vf_c, vf_m, vh_c, vh_m, need_threat)
+            logits, value, threat = self._tail_fused(vf_c, vf_m, vh_c, vh_m, need_threat)
             return (logits.reshape(*lead, self.n_action), value.reshape(lead),
                     threat.reshape(lead) if need_threat else None)
         x, dead = self._batch_norm(obs_feed)

@@ -217,6 +217,17 @@ int dca_policy_encode(const float *x, const float *mean, const float *var, const
                       const float *w2, const float *b2, uint64_t rows, float *x_norm, uint8_t *row_nan, float *v,
                       dca_stream_t stream);
 
+/* replaces: one nn.Linear (+ the torch.cat in front of it, + ReLU) of the conc / conc_4hist policy behind the encoder --
+ * Concentration's query / key / value / motivate / forward layers (ALGORITHM/common/conc.py:30-62) and the logit /
+ * value / threat heads (ALGORITHM/conc_4hist/net.py:213-229): out = act(a Wa^T + b Wb^T + bias), float32 FFMA.
+ *   a f32 [rows,ka] with row stride lda, b f32 [rows,kb] with row stride ldb (kb = 0: no second input); weights are read
+ *   as W[n * sn + k * sk] (nn.Linear weight: sn = in_features, sk = 1; a transposed matrix: sn = 1, sk = row length);
+ *   bias f32 [n] or NULL; n <= 48; relu 0/1; out f32 [rows,n] with row stride ldo.  ka, kb, lda, ldb multiples of 4,
+ *   a and b 16-byte aligned. */
+int dca_policy_linear(const float *a, int lda, int ka, const float *wa, int wa_sn, int wa_sk, const float *b, int ldb, int kb,
+                      const float *wb, int wb_sn, int wb_sk, const float *bias, int n, int relu, uint64_t rows, float *out,
+                      int ldo, dca_stream_t stream);
+
 /* replaces: the part of Concentration.forward between its matrix products, ALGORITHM/common/conc.py:30-58 (masked
  * softmax attention of the agent's own encoding over one entity list, attended encoding, top-n_focus gather with the
  * skip connection), for the conc / conc_4hist policy (ALGORITHM/conc_4hist/net.py:205-207).  One warp per agent.

@@ -110,6 +110,40 @@ def test_net_matches_reference_net_on_reference_observations():
     assert np.abs(freq - probs[0, 0]).max() < 0.02
 
 
+def test_policy_linear_kernel_matches_float64_reference():
+    """dca_policy_linear: act(a Wa^T + b Wb^T + bias) for the layer shapes of the policy -- ragged row counts, inputs
+    that are column slices of wider tensors, weight halves and transposed weights, N = 48 / 24 / 7 / 1."""
+    import torch
+    from hmp2g_b200.policy import _plin
+    g = torch.Generator(device='cuda')
+    g.manual_seed(7)
+    rnd = lambda *s: torch.randn(*s, generator=g, device='cuda', dtype=torch.float32)
+    for B in (1, 127, 1000, 4133):
+        wide = rnd(B, 256)
+        va = rnd(B, 48)
+        cases = [
+            (wide[:, :48], rnd(48, 48).t(), None, None, None, False),                       # x @ M
+            (wide[:, 64:112], rnd(48, 96)[:, :48], va, rnd(48, 96)[:, 48:], rnd(48), True),  # cat((a, b)) -> Linear, ReLU
+            (wide, rnd(48, 256), None, None, rnd(48), True),                                # forward layer, K = 256
+            (wide[:, :192], rnd(48, 192), None, None, rnd(48), True),                       # K = 192
+            (va, rnd(24, 48), None, None, rnd(24), True),                                   # 48 -> 24
+            (wide[:, 8:32], rnd(7, 24), None, None, rnd(7), False),                         # 24 -> 7
+            (va, rnd(1, 48), None, None, rnd(1), False),                                    # 48 -> 1
+        ]
+        for i, (a, wa, b, wb, bias, relu) in enumerate(cases):
+            got = _plin(a, wa, b, wb, bias, relu)
+            want = a.double() @ wa.double().t()
+            if b is not None:
+                want = want + b.double() @ wb.double().t()
+            if bias is not None:
+                want = want + bias.double()
+            if relu:
+                want = want.clamp_min(0)
+            scale = float(want.abs().max()) + 1.0
+            assert got.shape == want.shape
+            assert float((got.double() - want).abs().max()) < 2e-5 * scale, (B, i)
+
+
 def test_fused_attention_kernel_matches_the_torch_path():
     """dca_conc_attend (scores, masked softmax, attended encoding, stable top-k gather in one kernel) against the same
     steps written with torch ops (bmm / softmax / stable argsort / gather / cat): identical picks, values to float32
