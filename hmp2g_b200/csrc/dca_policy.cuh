@@ -375,6 +375,7 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
     float bs[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) bs[c] = (bias != nullptr && cg * NC + c < N) ? bias[cg * NC + c] : 0.f;
+    const bool vec2 = (ldo & 1) == 0 && ((uintptr_t)out & 7) == 0;
     for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const size_t r0 = tile * kLinTile;
         float acc[8][NC];
@@ -429,10 +430,18 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
         for (int r = 0; r < 8; ++r) {
             const size_t row = r0 + rg * 8 + r;
             if (row < rows) {
+                float *o = out + row * (size_t)ldo + cg * NC;
+                if (NC == 6 && N == 48 && vec2) {  // full-width layer, 8-byte aligned rows: three 8-byte stores
 #pragma unroll
-                for (int c = 0; c < NC; ++c) {
-                    const int n = cg * NC + c;
-                    if (n < N) out[row * (size_t)ldo + n] = relu ? fmaxf(acc[r][c], 0.f) : acc[r][c];
+                    for (int c = 0; c < NC; c += 2) {
+                        float2 v2 = make_float2(acc[r][c], acc[r][c + 1]);
+                        if (relu) { v2.x = fmaxf(v2.x, 0.f); v2.y = fmaxf(v2.y, 0.f); }
+                        *(float2 *)(o + c) = v2;
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < NC; ++c)
+                        if (cg * NC + c < N) o[c] = relu ? fmaxf(acc[r][c], 0.f) : acc[r][c];
                 }
             }
         }

@@ -177,7 +177,8 @@ class ConcCore(nn.Module):
         lib = _lib.load()
         B = v.shape[0]
         vs = v[:, 0]
-        qk = _plin(_plin(vs, self.CT_W_query.t()), self.CT_W_key)   # (vs W_query) W_key^T
+        # (vs W_query) W_key^T = vs (W_query W_key^T): the 48 x 48 product once per call instead of a second [B,48] pass
+        qk = _plin(vs, (self.CT_W_query @ self.CT_W_key.t()).t())
         va = torch.empty((B, self.h_dim), dtype=torch.float32, device=v.device)
         stack = torch.empty((B, (self.n_focus_on + 1) * (self.h_dim + x.shape[-1])), dtype=torch.float32, device=v.device)
         stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
