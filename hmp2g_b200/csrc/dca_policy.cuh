@@ -349,20 +349,24 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode(const float4 *__r
 // input replaces the reference's torch.cat((a, b), -1) in front of a Linear.  Why not cuBLAS: its float32 SIMT tiles
 // are 64 x 128 and N is 48 (24, 7, 1 in the heads), so 62 % of every tile is padding, and bias and ReLU are separate
 // passes over the activation.  Here a CTA owns 128 rows x all N columns, register-blocked like k_policy_encode (a
-// thread accumulates 8 rows x NC columns, N <= 8 NC), the inputs come through shared memory k-major in chunks of up to
-// 64 features, float32 FFMA in ascending k.
+// thread accumulates 8 rows x NC columns, N <= 8 NC); inputs and weights come through shared memory in chunks of 32
+// features, two stages deep (cp.async: chunk c + 1 is in flight while chunk c is multiplied); float32 FFMA in ascending k.
 // a: [rows, Ka] with row stride lda (a column slice of a wider tensor is fine), b likewise (Kb = 0: none); weights are
 // addressed W[n * sn + k * sk], so nn.Linear weights, their column halves and transposed matrices need no copies.
-constexpr int kLinTile = 128, kLinThreads = 128, kLinKC = 64;
-struct LinSmem {
-    float xs[kLinKC][kLinTile + 4];
-    float ws[kLinKC][48];
+constexpr int kLinTile = 128, kLinThreads = 128, kLinKC = 32, kLinStride = kLinKC + 4;
+struct LinSmem {                              // 48 KB: two stages of {128 input rows x 32 features, 32 x 48 weights}
+    float xs[2][kLinTile][kLinStride];        // row-major as in global memory (cp.async, no transposition); a thread's
+    float ws[2][kLinKC][48];                  // rows are rg, rg + 16, ..: the 4 row groups of a warp sit 144 B apart
 };
 struct LinSrc {
     const float *x;
     const float *w;
     int ld, K, sn, sk;
 };
+__device__ __forceinline__ void lin_cp_async4(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
 
 template <int NC>
 __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, const LinSrc sb, const float *__restrict__ bias,
@@ -372,10 +376,32 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
     const int tid = threadIdx.x;
     const int rg = tid >> 3, cg = tid & 7;
     const size_t tiles = (rows + kLinTile - 1) / kLinTile;
+    const int chunks_a = (sa.K + kLinKC - 1) / kLinKC, chunks = chunks_a + (sb.K + kLinKC - 1) / kLinKC;
     float bs[NC];
 #pragma unroll
     for (int c = 0; c < NC; ++c) bs[c] = (bias != nullptr && cg * NC + c < N) ? bias[cg * NC + c] : 0.f;
     const bool vec2 = (ldo & 1) == 0 && ((uintptr_t)out & 7) == 0;
+    // stage chunk c of tile t into buffer b (asynchronous; rows past the end repeat the last row, never stored)
+    auto stage = [&](size_t t, int c, int b) {
+        if (t < tiles) {
+            const LinSrc &S = c < chunks_a ? sa : sb;
+            const int k0 = (c < chunks_a ? c : c - chunks_a) * kLinKC, kc = min(kLinKC, S.K - k0), q4 = kc >> 2;
+            const size_t r0 = t * kLinTile;
+            for (int i = tid; i < kLinTile * q4; i += kLinThreads) {
+                const int lr = i / q4, q = i - lr * q4;
+                const size_t row = min(r0 + lr, rows - 1);
+                enc_cp_async16(&s.xs[b][lr][q * 4], S.x + row * (size_t)S.ld + k0 + q * 4);
+            }
+            for (int i = tid; i < kc * NP; i += kLinThreads) {
+                const int k = i / NP, n = i - k * NP;
+                if (n < N) lin_cp_async4(&s.ws[b][k][n], S.w + (size_t)n * S.sn + (size_t)(k0 + k) * S.sk);
+                else s.ws[b][k][n] = 0.f;
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int buf = 0;
+    stage(blockIdx.x, 0, 0);
     for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const size_t r0 = tile * kLinTile;
         float acc[8][NC];
@@ -383,52 +409,43 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
         for (int r = 0; r < 8; ++r)
 #pragma unroll
             for (int c = 0; c < NC; ++c) acc[r][c] = bs[c];
-        for (int src = 0; src < 2; ++src) {
-            const LinSrc &S = src == 0 ? sa : sb;
-            for (int k0 = 0; k0 < S.K; k0 += kLinKC) {
-                const int kc = min(kLinKC, S.K - k0);  // a multiple of 4 (checked by the host)
-                __syncthreads();  // the previous chunk has been consumed
-                // inputs: a lane quad reads 16 consecutive floats of one row; transposed into xs[k][row]
-                for (int kb = 0; kb < kc; kb += 16) {
-                    const int quad = tid & 3, kq = kb + quad * 4;
+        for (int c = 0; c < chunks; ++c) {
+            if (c + 1 < chunks) stage(tile, c + 1, buf ^ 1);
+            else stage(tile + gridDim.x, 0, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+            __syncthreads();  // chunk c has landed for every thread
+            const LinSrc &S = c < chunks_a ? sa : sb;
+            const int k0 = (c < chunks_a ? c : c - chunks_a) * kLinKC, kc = min(kLinKC, S.K - k0);
+            for (int k4 = 0; k4 < kc; k4 += 4) {
+                float4 a[8];
 #pragma unroll
-                    for (int pass = 0; pass < 4; ++pass) {
-                        const int lr = pass * 32 + (tid >> 2);
-                        const size_t row = r0 + lr;
-                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (row < rows && kq < kc) v = *(const float4 *)(S.x + row * (size_t)S.ld + k0 + kq);
-                        if (kq < kc) { s.xs[kq][lr] = v.x; s.xs[kq + 1][lr] = v.y; s.xs[kq + 2][lr] = v.z; s.xs[kq + 3][lr] = v.w; }
-                    }
-                }
-                // weights of this chunk, k-major, zero beyond N
-                for (int i = tid; i < kc * NP; i += kLinThreads) {
-                    const int k = i / NP, n = i - k * NP;
-                    s.ws[k][n] = n < N ? S.w[(size_t)n * S.sn + (size_t)(k0 + k) * S.sk] : 0.f;
-                }
-                __syncthreads();
-#pragma unroll 4
-                for (int k = 0; k < kc; ++k) {
-                    const float4 a0 = *(const float4 *)&s.xs[k][rg * 8], a1 = *(const float4 *)&s.xs[k][rg * 8 + 4];
-                    const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                for (int r = 0; r < 8; ++r) a[r] = *(const float4 *)&s.xs[buf][rg + 16 * r][k4];
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
                     float w[NC];
                     if constexpr (NC == 6) {
-                        const float2 w01 = *(const float2 *)&s.ws[k][cg * 6], w23 = *(const float2 *)&s.ws[k][cg * 6 + 2],
-                                     w45 = *(const float2 *)&s.ws[k][cg * 6 + 4];
+                        const float2 w01 = *(const float2 *)&s.ws[buf][k4 + kk][cg * 6],
+                                     w23 = *(const float2 *)&s.ws[buf][k4 + kk][cg * 6 + 2],
+                                     w45 = *(const float2 *)&s.ws[buf][k4 + kk][cg * 6 + 4];
                         w[0] = w01.x; w[1] = w01.y; w[2] = w23.x; w[3] = w23.y; w[4] = w45.x; w[5] = w45.y;
                     } else {
 #pragma unroll
-                        for (int c = 0; c < NC; ++c) w[c] = s.ws[k][cg * NC + c];
+                        for (int cc = 0; cc < NC; ++cc) w[cc] = s.ws[buf][k4 + kk][cg * NC + cc];
                     }
 #pragma unroll
-                    for (int r = 0; r < 8; ++r)
+                    for (int r = 0; r < 8; ++r) {
+                        const float ar = kk == 0 ? a[r].x : (kk == 1 ? a[r].y : (kk == 2 ? a[r].z : a[r].w));
 #pragma unroll
-                        for (int c = 0; c < NC; ++c) acc[r][c] = fmaf(a[r], w[c], acc[r][c]);
+                        for (int cc = 0; cc < NC; ++cc) acc[r][cc] = fmaf(ar, w[cc], acc[r][cc]);
+                    }
                 }
             }
+            __syncthreads();  // buffer `buf` is free for the chunk after next
+            buf ^= 1;
         }
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-            const size_t row = r0 + rg * 8 + r;
+            const size_t row = r0 + rg + 16 * r;
             if (row < rows) {
                 float *o = out + row * (size_t)ldo + cg * NC;
                 if (NC == 6 && N == 48 && vec2) {  // full-width layer, 8-byte aligned rows: three 8-byte stores
@@ -446,6 +463,7 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
             }
         }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 }  // namespace dca
