@@ -618,9 +618,27 @@ int dca_policy_linear(const float *a, int lda, int ka, const float *wa, int wa_s
     const size_t tiles = (rows + kLinTile - 1) / kLinTile;
     const unsigned grid = (unsigned)std::min<size_t>(tiles, 148 * 4);
     cudaStream_t st = (cudaStream_t)stream;
-    if (n > 24) k_policy_linear<6><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, relu, (size_t)rows, out, ldo);
-    else if (n > 8) k_policy_linear<3><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, relu, (size_t)rows, out, ldo);
-    else k_policy_linear<1><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, relu, (size_t)rows, out, ldo);
+    const int act = relu & 1;
+    if ((relu & 2) || (ka & 7) || (kb & 7)) {  // float32 FFMA path (asked for, or a k that is not a multiple of 8)
+        if (n > 24) k_policy_linear<6><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, act, (size_t)rows, out, ldo);
+        else if (n > 8) k_policy_linear<3><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, act, (size_t)rows, out, ldo);
+        else k_policy_linear<1><<<grid, kLinThreads, 0, st>>>(sa, sb, bias, n, act, (size_t)rows, out, ldo);
+    } else {                                  // 3xTF32 on the tensor cores
+        static bool attr_set[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+            cudaError_t ea = cudaFuncSetAttribute(k_policy_linear_tc<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LinSmemTc));
+            if (ea == cudaSuccess) ea = cudaFuncSetAttribute(k_policy_linear_tc<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LinSmemTc));
+            if (ea == cudaSuccess) ea = cudaFuncSetAttribute(k_policy_linear_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LinSmemTc));
+            if (ea != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_linear: ") + cudaGetErrorString(ea));
+            attr_set[dev] = true;
+        }
+        const size_t sm = sizeof(LinSmemTc);
+        if (n > 24) k_policy_linear_tc<6><<<grid, kLinThreads, sm, st>>>(sa, sb, bias, n, act, (size_t)rows, out, ldo);
+        else if (n > 8) k_policy_linear_tc<3><<<grid, kLinThreads, sm, st>>>(sa, sb, bias, n, act, (size_t)rows, out, ldo);
+        else k_policy_linear_tc<1><<<grid, kLinThreads, sm, st>>>(sa, sb, bias, n, act, (size_t)rows, out, ldo);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_linear: ") + cudaGetErrorString(e));
     return DCA_OK;

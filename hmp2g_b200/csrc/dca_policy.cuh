@@ -466,4 +466,130 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
     asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
+// The same layer on the tensor cores with float32-class accuracy ("3xTF32"): every operand is split into a tf32 head
+// and a tf32 tail (x = hi + lo exactly to 2^-22 |x|), and a product is three mma.sync.m16n8k8 tf32 instructions --
+// lo*hi + hi*lo + hi*hi, small terms first, float32 accumulators; the dropped lo*lo term is 2^-22 of the product, the
+// size of float32 rounding itself (a single tf32 pass, 2^-11, would move the attention's picks: its logits reach the
+// hundreds).  The FFMA kernel above is bound by shared-memory operand bandwidth (14 floats per 48 FFMA per thread) at a
+// third of the FP32 peak; here a warp owns 32 rows x all N columns (2 x NT accumulator tiles) and loads 20 words per
+// 8 k-steps.  Staging as above (row-major rows with a 36-float stride and k-major weights with a 56-float stride make
+// every fragment load conflict-free).  Needs ka, kb multiples of 8.
+constexpr int kLinWStride = 56;
+struct LinSmemTc {
+    float xs[2][kLinTile][kLinStride];
+    float ws[2][kLinKC][kLinWStride];
+};
+__device__ __forceinline__ void tf32_split(float x, uint32_t &hi, uint32_t &lo) {
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+    const float rest = x - __uint_as_float(hi);
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(rest));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <int NT>
+__global__ void __launch_bounds__(kLinThreads) k_policy_linear_tc(const LinSrc sa, const LinSrc sb,
+                                                                  const float *__restrict__ bias, int N, int relu, size_t rows,
+                                                                  float *__restrict__ out, int ldo) {
+    extern __shared__ __align__(16) unsigned char lin_raw[];
+    LinSmemTc &s = *reinterpret_cast<LinSmemTc *>(lin_raw);
+    constexpr int NP = 8 * NT;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const size_t tiles = (rows + kLinTile - 1) / kLinTile;
+    const int chunks_a = (sa.K + kLinKC - 1) / kLinKC, chunks = chunks_a + (sb.K + kLinKC - 1) / kLinKC;
+    float bs[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) bs[nt][j] = (bias != nullptr && nt * 8 + 2 * t + j < N) ? bias[nt * 8 + 2 * t + j] : 0.f;
+    const bool vec2 = (ldo & 1) == 0 && ((uintptr_t)out & 7) == 0;
+    auto stage = [&](size_t tl, int c, int b) {
+        if (tl < tiles) {
+            const LinSrc &S = c < chunks_a ? sa : sb;
+            const int k0 = (c < chunks_a ? c : c - chunks_a) * kLinKC, kc = min(kLinKC, S.K - k0), q4 = kc >> 2;
+            const size_t r0 = tl * kLinTile;
+            for (int i = tid; i < kLinTile * q4; i += kLinThreads) {
+                const int lr = i / q4, q = i - lr * q4;
+                const size_t row = min(r0 + lr, rows - 1);
+                enc_cp_async16(&s.xs[b][lr][q * 4], S.x + row * (size_t)S.ld + k0 + q * 4);
+            }
+            for (int i = tid; i < kc * NP; i += kLinThreads) {
+                const int k = i / NP, n = i - k * NP;
+                if (n < N) lin_cp_async4(&s.ws[b][k][n], S.w + (size_t)n * S.sn + (size_t)(k0 + k) * S.sk);
+                else s.ws[b][k][n] = 0.f;
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int buf = 0;
+    stage(blockIdx.x, 0, 0);
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const size_t r0 = tile * kLinTile;
+        float acc[2][NT][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                acc[mt][nt][0] = acc[mt][nt][2] = bs[nt][0];
+                acc[mt][nt][1] = acc[mt][nt][3] = bs[nt][1];
+            }
+        for (int c = 0; c < chunks; ++c) {
+            if (c + 1 < chunks) stage(tile, c + 1, buf ^ 1);
+            else stage(tile + gridDim.x, 0, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+            __syncthreads();
+            const LinSrc &S = c < chunks_a ? sa : sb;
+            const int k0 = (c < chunks_a ? c : c - chunks_a) * kLinKC, kc = min(kLinKC, S.K - k0);
+            for (int ks = 0; ks < kc; ks += 8) {
+                uint32_t bh[NT][2], bl[NT][2];
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) tf32_split(s.ws[buf][ks + t + 4 * j][nt * 8 + g], bh[nt][j], bl[nt][j]);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    const int row = warp * 32 + mt * 16 + g;
+                    uint32_t ah[4], al[4];
+                    tf32_split(s.xs[buf][row][ks + t], ah[0], al[0]);
+                    tf32_split(s.xs[buf][row + 8][ks + t], ah[1], al[1]);
+                    tf32_split(s.xs[buf][row][ks + t + 4], ah[2], al[2]);
+                    tf32_split(s.xs[buf][row + 8][ks + t + 4], ah[3], al[3]);
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        mma_tf32(acc[mt][nt], al, bh[nt]);
+                        mma_tf32(acc[mt][nt], ah, bl[nt]);
+                        mma_tf32(acc[mt][nt], ah, bh[nt]);
+                    }
+                }
+            }
+            __syncthreads();
+            buf ^= 1;
+        }
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const size_t row = r0 + warp * 32 + mt * 16 + g + 8 * h;
+                if (row >= rows) continue;
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    const int n = nt * 8 + 2 * t;
+                    float v0 = acc[mt][nt][2 * h], v1 = acc[mt][nt][2 * h + 1];
+                    if (relu) { v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); }
+                    float *o = out + row * (size_t)ldo + n;
+                    if (vec2 && n + 1 < N) {
+                        *(float2 *)o = make_float2(v0, v1);
+                    } else {
+                        if (n < N) o[0] = v0;
+                        if (n + 1 < N) o[1] = v1;
+                    }
+                }
+            }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
 }  // namespace dca

@@ -116,9 +116,11 @@ def _linear_cat(lin, a, b):
     return y.addmm_(b, lin.weight[:, ka:].t())
 
 
-def _plin(a, wa, b=None, wb=None, bias=None, relu=False):
+def _plin(a, wa, b=None, wb=None, bias=None, relu=False, ffma=False):
     """act(a wa^T + b wb^T + bias) on the device in one kernel (dca_policy_linear): a [B,ka] / b [B,kb] float32 with unit
-    inner stride (column slices of wider tensors are fine), wa [n,ka] / wb [n,kb] any 2-D views (x @ M: pass M.t())."""
+    inner stride (column slices of wider tensors are fine), wa [n,ka] / wb [n,kb] any 2-D views (x @ M: pass M.t()).
+    Arithmetic: three tf32 tensor-core products per multiply on head + tail splits of the operands (float32-class
+    accuracy); ffma=True: plain float32 FFMA."""
     lib = _lib.load()
     B, n = a.shape[0], wa.shape[0]
     assert a.dtype == torch.float32 and a.stride(1) == 1 and wa.shape[1] == a.shape[1]
@@ -130,7 +132,7 @@ def _plin(a, wa, b=None, wb=None, bias=None, relu=False):
         _ptr(a), a.stride(0), a.shape[1], _ptr(wa), wa.stride(0), wa.stride(1),
         None if b is None else _ptr(b), 0 if b is None else b.stride(0), 0 if b is None else b.shape[1],
         None if b is None else _ptr(wb), 0 if b is None else wb.stride(0), 0 if b is None else wb.stride(1),
-        None if bias is None else _ptr(bias), n, int(bool(relu)), B, _ptr(out), out.stride(0), stream))
+        None if bias is None else _ptr(bias), n, int(bool(relu)) | (2 if ffma else 0), B, _ptr(out), out.stride(0), stream))
     return out
 
 

@@ -222,8 +222,10 @@ int dca_policy_encode(const float *x, const float *mean, const float *var, const
  * value / threat heads (ALGORITHM/conc_4hist/net.py:213-229): out = act(a Wa^T + b Wb^T + bias), float32 FFMA.
  *   a f32 [rows,ka] with row stride lda, b f32 [rows,kb] with row stride ldb (kb = 0: no second input); weights are read
  *   as W[n * sn + k * sk] (nn.Linear weight: sn = in_features, sk = 1; a transposed matrix: sn = 1, sk = row length);
- *   bias f32 [n] or NULL; n <= 48; relu 0/1; out f32 [rows,n] with row stride ldo.  ka, kb, lda, ldb multiples of 4,
- *   a and b 16-byte aligned. */
+ *   bias f32 [n] or NULL; n <= 48; relu: bit 0 = ReLU, bit 1 = float32 FFMA arithmetic instead of the default, three tf32
+ *   tensor-core products per multiply with the operands split into head + tail (float32-class accuracy, error 2^-22 of
+ *   a product; taken anyway when ka or kb is not a multiple of 8); out f32 [rows,n] with row stride ldo.  ka, kb, lda,
+ *   ldb multiples of 4, a and b 16-byte aligned. */
 int dca_policy_linear(const float *a, int lda, int ka, const float *wa, int wa_sn, int wa_sk, const float *b, int ldb, int kb,
                       const float *wb, int wb_sn, int wb_sk, const float *bias, int n, int relu, uint64_t rows, float *out,
                       int ldo, dca_stream_t stream);
