@@ -387,10 +387,19 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear(const LinSrc sa, 
             const LinSrc &S = c < chunks_a ? sa : sb;
             const int k0 = (c < chunks_a ? c : c - chunks_a) * kLinKC, kc = min(kLinKC, S.K - k0), q4 = kc >> 2;
             const size_t r0 = t * kLinTile;
-            for (int i = tid; i < kLinTile * q4; i += kLinThreads) {
-                const int lr = i / q4, q = i - lr * q4;
-                const size_t row = min(r0 + lr, rows - 1);
-                enc_cp_async16(&s.xs[b][lr][q * 4], S.x + row * (size_t)S.ld + k0 + q * 4);
+            if ((q4 & (q4 - 1)) == 0) {  // 8 / 4 / 2 pieces of 16 bytes per row (chunks of 32 / 16 / 8 features): shifts
+                const int sh = __ffs(q4) - 1, q = tid & (q4 - 1), step = kLinThreads >> sh;
+                const float *src = S.x + k0 + q * 4;
+                for (int lr = tid >> sh; lr < kLinTile; lr += step) {
+                    const size_t row = min(r0 + lr, rows - 1);
+                    enc_cp_async16(&s.xs[b][lr][q * 4], src + row * (size_t)S.ld);
+                }
+            } else {
+                for (int i = tid; i < kLinTile * q4; i += kLinThreads) {
+                    const int lr = i / q4, q = i - lr * q4;
+                    const size_t row = min(r0 + lr, rows - 1);
+                    enc_cp_async16(&s.xs[b][lr][q * 4], S.x + row * (size_t)S.ld + k0 + q * 4);
+                }
             }
             for (int i = tid; i < kc * NP; i += kLinThreads) {
                 const int k = i / NP, n = i - k * NP;
@@ -479,10 +488,14 @@ struct LinSmemTc {
     float xs[2][kLinTile][kLinStride];
     float ws[2][kLinKC][kLinWStride];
 };
+// head: x rounded to tf32's 10 mantissa bits, nearest with ties away from zero -- what cvt.rna.tf32.f32 computes, done
+// with two integer instructions (cvt runs on the quarter-rate conversion pipe, which bound the first version of this
+// kernel at 54 % busy with the tensor pipe at 5 %); tail: x - head (exact), rounded the same way (left to the tensor
+// core's truncation, 2^-21 |x| instead of 2^-22, two of the 1000 reference agents took another pick).
+__device__ __forceinline__ uint32_t tf32_rna(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
 __device__ __forceinline__ void tf32_split(float x, uint32_t &hi, uint32_t &lo) {
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-    const float rest = x - __uint_as_float(hi);
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(rest));
+    hi = tf32_rna(x);
+    lo = tf32_rna(x - __uint_as_float(hi));
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
     asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -511,10 +524,19 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear_tc(const LinSrc s
             const LinSrc &S = c < chunks_a ? sa : sb;
             const int k0 = (c < chunks_a ? c : c - chunks_a) * kLinKC, kc = min(kLinKC, S.K - k0), q4 = kc >> 2;
             const size_t r0 = tl * kLinTile;
-            for (int i = tid; i < kLinTile * q4; i += kLinThreads) {
-                const int lr = i / q4, q = i - lr * q4;
-                const size_t row = min(r0 + lr, rows - 1);
-                enc_cp_async16(&s.xs[b][lr][q * 4], S.x + row * (size_t)S.ld + k0 + q * 4);
+            if ((q4 & (q4 - 1)) == 0) {  // 8 / 4 / 2 pieces of 16 bytes per row (chunks of 32 / 16 / 8 features): shifts
+                const int sh = __ffs(q4) - 1, q = tid & (q4 - 1), step = kLinThreads >> sh;
+                const float *src = S.x + k0 + q * 4;
+                for (int lr = tid >> sh; lr < kLinTile; lr += step) {
+                    const size_t row = min(r0 + lr, rows - 1);
+                    enc_cp_async16(&s.xs[b][lr][q * 4], src + row * (size_t)S.ld);
+                }
+            } else {
+                for (int i = tid; i < kLinTile * q4; i += kLinThreads) {
+                    const int lr = i / q4, q = i - lr * q4;
+                    const size_t row = min(r0 + lr, rows - 1);
+                    enc_cp_async16(&s.xs[b][lr][q * 4], S.x + row * (size_t)S.ld + k0 + q * 4);
+                }
             }
             for (int i = tid; i < kc * NP; i += kLinThreads) {
                 const int k = i / NP, n = i - k * NP;
