@@ -591,13 +591,21 @@ int dca_policy_encode(const float *x, const float *mean, const float *var, const
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
         cudaError_t ea = cudaFuncSetAttribute(k_policy_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+        if (ea == cudaSuccess)
+            ea = cudaFuncSetAttribute(k_policy_encode_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncTcSmem));
         if (ea != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_encode: ") + cudaGetErrorString(ea));
         attr_set[dev] = true;
     }
     const size_t tiles = (rows + kEncTile - 1) / kEncTile;
+#ifdef DCA_ENCODE_FFMA  // the float32 FFMA encoder (before the tensor-core one existed); kept for A/B builds
     const unsigned grid = (unsigned)std::min<size_t>(tiles, 148 * 4);
     k_policy_encode<<<grid, kEncThreads, sizeof(EncSmem), (cudaStream_t)stream>>>(
         (const float4 *)x, mean, var, w1, b1, w2, b2, (size_t)rows, (float4 *)x_norm, row_nan, v);
+#else
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, 148 * 3);
+    k_policy_encode_tc<<<grid, kEncThreads, sizeof(EncTcSmem), (cudaStream_t)stream>>>(
+        (const float4 *)x, mean, var, w1, b1, w2, b2, (size_t)rows, (float4 *)x_norm, row_nan, v);
+#endif
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_policy_encode: ") + cudaGetErrorString(e));
     return DCA_OK;
