@@ -622,31 +622,31 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear_tc(const LinSrc s
 // the A layout of the next) and runs layer 2 from there; only __syncwarp between the phases.  The weights are split
 // into tf32 head / tail once per CTA and stay in shared memory k-major (stride 56: conflict-free B fragment loads).
 constexpr int kEncXs = 20, kEncHs = 52;  // row strides (floats): g * stride + t hits 32 distinct banks for g < 8, t < 4
-struct EncTcSmem {
+constexpr int kEncTcThreads = 256, kEncTcWarps = kEncTcThreads / 32, kEncTcTile = kEncTcWarps * 32;
+struct EncTcSmem {  // 66 KB: three CTAs = 24 warps per SM (a first version with 128 rows of hs per 128 threads: 12)
     float w1h[kPolD][kLinWStride], w1l[kPolD][kLinWStride];
     float w2h[kPolH][kLinWStride], w2l[kPolH][kLinWStride];
     float b1[kPolH], b2[kPolH];
-    float xs[kEncTile][kEncXs];
-    float hs[kEncTile][kEncHs];
-    float4 stage[kEncTile * 4];
+    float xs[kEncTcWarps][16][kEncXs];  // per warp: the 16 rows of the half tile in work
+    float hs[kEncTcWarps][16][kEncHs];
 };
 
-__global__ void __launch_bounds__(kEncThreads) k_policy_encode_tc(const float4 *__restrict__ x, const float *__restrict__ mean,
-                                                                  const float *__restrict__ var,
-                                                                  const float *__restrict__ w1, const float *__restrict__ b1,
-                                                                  const float *__restrict__ w2, const float *__restrict__ b2,
-                                                                  size_t rows, float4 *__restrict__ x_norm,
-                                                                  uint8_t *__restrict__ row_nan, float *__restrict__ v) {
+__global__ void __launch_bounds__(kEncTcThreads, 3) k_policy_encode_tc(const float4 *__restrict__ x, const float *__restrict__ mean,
+                                                                    const float *__restrict__ var,
+                                                                    const float *__restrict__ w1, const float *__restrict__ b1,
+                                                                    const float *__restrict__ w2, const float *__restrict__ b2,
+                                                                    size_t rows, float4 *__restrict__ x_norm,
+                                                                    uint8_t *__restrict__ row_nan, float *__restrict__ v) {
     extern __shared__ __align__(16) unsigned char enc_tc_raw[];
     EncTcSmem &s = *reinterpret_cast<EncTcSmem *>(enc_tc_raw);
     const unsigned full = 0xffffffffu;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, quad = lane & 3, g = lane >> 2, t = lane & 3;
-    for (int i = tid; i < kPolD * kPolH; i += kEncThreads) {  // w1[j][k] -> w1h / w1l[k][j]
+    for (int i = tid; i < kPolD * kPolH; i += kEncTcThreads) {  // w1[j][k] -> w1h / w1l[k][j]
         uint32_t hi, lo;
         tf32_split(w1[i], hi, lo);
         s.w1h[i % kPolD][i / kPolD] = __uint_as_float(hi); s.w1l[i % kPolD][i / kPolD] = __uint_as_float(lo);
     }
-    for (int i = tid; i < kPolH * kPolH; i += kEncThreads) {
+    for (int i = tid; i < kPolH * kPolH; i += kEncTcThreads) {
         uint32_t hi, lo;
         tf32_split(w2[i], hi, lo);
         s.w2h[i % kPolH][i / kPolH] = __uint_as_float(hi); s.w2l[i % kPolH][i / kPolH] = __uint_as_float(lo);
@@ -656,36 +656,32 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode_tc(const float4 *
     const float sd[4] = {__fsqrt_rn(__fadd_rn(vv.x, 1e-8f)), __fsqrt_rn(__fadd_rn(vv.y, 1e-8f)),
                          __fsqrt_rn(__fadd_rn(vv.z, 1e-8f)), __fsqrt_rn(__fadd_rn(vv.w, 1e-8f))};
     const float mu[4] = {m.x, m.y, m.z, m.w};
-    const size_t tiles = (rows + kEncTile - 1) / kEncTile;
-    // slot q of this lane: local row warp * 32 + g + 8 q, float4 `quad` of it
-    auto prefetch = [&](size_t tl) {
-        if (tl < tiles) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const size_t row = tl * kEncTile + warp * 32 + g + 8 * q;
-                if (row < rows) enc_cp_async16(&s.stage[tid + q * kEncThreads], &x[row * 4 + quad]);
-            }
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    prefetch(blockIdx.x);
-    __syncthreads();  // weights in place
-    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const size_t r0 = tile * kEncTile + warp * 32;  // this warp's first row
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        float4 raw[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) raw[q] = s.stage[tid + q * kEncThreads];
-        prefetch(tile + gridDim.x);  // own slots only: they are in registers now
-        __syncwarp();                // the previous tile's xs / hs rows of this warp have been consumed
-        // ---- normalise this warp's 32 rows (4 per lane quad)
+    const size_t tiles = (rows + kEncTcTile - 1) / kEncTcTile;
+    float (*xs)[kEncXs] = s.xs[warp];
+    float (*hs)[kEncHs] = s.hs[warp];
+    // slot q of this lane: row (warp's first row) + g + 8 q, float4 `quad` of it; the next tile's slots travel in registers
+    float4 nxt[4];
+    auto fetch = [&](size_t tl) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const int lr = g + 8 * q;
-            const size_t row = r0 + lr;
-            float e[4] = {0.f, 0.f, 0.f, 0.f};
+            const size_t row = tl * kEncTcTile + warp * 32 + g + 8 * q;
+            nxt[q] = (tl < tiles && row < rows) ? x[row * 4 + quad] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+    fetch(blockIdx.x);
+    __syncthreads();  // weights in place
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const size_t r0 = tile * kEncTcTile + warp * 32;  // this warp's first row
+        float4 raw[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) raw[q] = nxt[q];
+        fetch(tile + gridDim.x);
+        // ---- normalise this warp's 32 rows (4 per lane quad); the values stay in raw[]
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const size_t row = r0 + g + 8 * q;
+            float e[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
             const bool in = row < rows;
-            if (in) { e[0] = raw[q].x; e[1] = raw[q].y; e[2] = raw[q].z; e[3] = raw[q].w; }
             bool bad = false;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -693,30 +689,32 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode_tc(const float4 *
                 else e[k] = fminf(fmaxf(__fdiv_rn(__fsub_rn(e[k], mu[k]), sd[k]), -10.f), 10.f);
             }
             const unsigned bb = __ballot_sync(full, bad);
+            raw[q] = make_float4(e[0], e[1], e[2], e[3]);
             if (in) {
-                x_norm[row * 4 + quad] = make_float4(e[0], e[1], e[2], e[3]);
+                x_norm[row * 4 + quad] = raw[q];
                 if (quad == 0) row_nan[row] = ((bb >> lane) & 0xfu) != 0;
             }
-            *(float4 *)&s.xs[warp * 32 + lr][quad * 4] = make_float4(e[0], e[1], e[2], e[3]);
         }
-        __syncwarp();
-        // ---- layer 1: h = relu(x w1^T + b1), 32 rows x 48 columns per warp, K = 16
 #pragma unroll
-        for (int mt = 0; mt < 2; ++mt) {
+        for (int mt = 0; mt < 2; ++mt) {  // half tiles of 16 rows: slots 2 mt and 2 mt + 1
+            __syncwarp();  // the previous half's xs / hs have been consumed
+            *(float4 *)&xs[g][quad * 4] = raw[2 * mt];
+            *(float4 *)&xs[g + 8][quad * 4] = raw[2 * mt + 1];
+            __syncwarp();
             float acc[6][4];
+            // ---- layer 1: h = relu(x w1^T + b1), 16 rows x 48 columns, K = 16
 #pragma unroll
             for (int nt = 0; nt < 6; ++nt) {
                 acc[nt][0] = acc[nt][2] = s.b1[nt * 8 + 2 * t];
                 acc[nt][1] = acc[nt][3] = s.b1[nt * 8 + 2 * t + 1];
             }
-            const int row = warp * 32 + mt * 16 + g;
 #pragma unroll
             for (int ks = 0; ks < kPolD; ks += 8) {
                 uint32_t ah[4], al[4];
-                tf32_split(s.xs[row][ks + t], ah[0], al[0]);
-                tf32_split(s.xs[row + 8][ks + t], ah[1], al[1]);
-                tf32_split(s.xs[row][ks + t + 4], ah[2], al[2]);
-                tf32_split(s.xs[row + 8][ks + t + 4], ah[3], al[3]);
+                tf32_split(xs[g][ks + t], ah[0], al[0]);
+                tf32_split(xs[g + 8][ks + t], ah[1], al[1]);
+                tf32_split(xs[g][ks + t + 4], ah[2], al[2]);
+                tf32_split(xs[g + 8][ks + t + 4], ah[3], al[3]);
 #pragma unroll
                 for (int nt = 0; nt < 6; ++nt) {
                     const uint32_t bh[2] = {__float_as_uint(s.w1h[ks + t][nt * 8 + g]), __float_as_uint(s.w1h[ks + t + 4][nt * 8 + g])};
@@ -728,28 +726,23 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode_tc(const float4 *
             }
 #pragma unroll
             for (int nt = 0; nt < 6; ++nt) {
-                *(float2 *)&s.hs[row][nt * 8 + 2 * t] = make_float2(fmaxf(acc[nt][0], 0.f), fmaxf(acc[nt][1], 0.f));
-                *(float2 *)&s.hs[row + 8][nt * 8 + 2 * t] = make_float2(fmaxf(acc[nt][2], 0.f), fmaxf(acc[nt][3], 0.f));
+                *(float2 *)&hs[g][nt * 8 + 2 * t] = make_float2(fmaxf(acc[nt][0], 0.f), fmaxf(acc[nt][1], 0.f));
+                *(float2 *)&hs[g + 8][nt * 8 + 2 * t] = make_float2(fmaxf(acc[nt][2], 0.f), fmaxf(acc[nt][3], 0.f));
             }
-        }
-        __syncwarp();
-        // ---- layer 2: v = h w2^T + b2, K = 48
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt) {
-            float acc[6][4];
+            __syncwarp();
+            // ---- layer 2: v = h w2^T + b2, K = 48
 #pragma unroll
             for (int nt = 0; nt < 6; ++nt) {
                 acc[nt][0] = acc[nt][2] = s.b2[nt * 8 + 2 * t];
                 acc[nt][1] = acc[nt][3] = s.b2[nt * 8 + 2 * t + 1];
             }
-            const int row = warp * 32 + mt * 16 + g;
 #pragma unroll 2
             for (int ks = 0; ks < kPolH; ks += 8) {
                 uint32_t ah[4], al[4];
-                tf32_split(s.hs[row][ks + t], ah[0], al[0]);
-                tf32_split(s.hs[row + 8][ks + t], ah[1], al[1]);
-                tf32_split(s.hs[row][ks + t + 4], ah[2], al[2]);
-                tf32_split(s.hs[row + 8][ks + t + 4], ah[3], al[3]);
+                tf32_split(hs[g][ks + t], ah[0], al[0]);
+                tf32_split(hs[g + 8][ks + t], ah[1], al[1]);
+                tf32_split(hs[g][ks + t + 4], ah[2], al[2]);
+                tf32_split(hs[g + 8][ks + t + 4], ah[3], al[3]);
 #pragma unroll
                 for (int nt = 0; nt < 6; ++nt) {
                     const uint32_t bh[2] = {__float_as_uint(s.w2h[ks + t][nt * 8 + g]), __float_as_uint(s.w2h[ks + t + 4][nt * 8 + g])};
@@ -761,7 +754,7 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode_tc(const float4 *
             }
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const size_t grow = tile * kEncTile + row + 8 * h;
+                const size_t grow = r0 + mt * 16 + g + 8 * h;
                 if (grow < rows) {
 #pragma unroll
                     for (int nt = 0; nt < 6; ++nt)
@@ -770,7 +763,6 @@ __global__ void __launch_bounds__(kEncThreads) k_policy_encode_tc(const float4 *
             }
         }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 }  // namespace dca
