@@ -285,8 +285,9 @@ def policy_rollout_run(E, dev, rank, world, steps=60, warm=10):
            'gae_and_advantage_ms': g0.elapsed_time(g1), 'rollout_buffer_TEG': list(roll.buf.reward.shape),
            'episodes_finished': int(roll.episodes.item()), 'wins': int(roll.wins.item()),
            'policy': 'ConcNet4Hist (hmp2g_b200/policy.py): encoder + normalisation (k_policy_encode), attention / top-k '
-                     '(k_conc_attend), moments, history roll, planner, step, GAE: this library; the remaining [agents, '
-                     '48..256] x [.., 48] products: torch fp32 (cuBLAS)',
+                     '(k_conc_attend), every dense layer behind them (dca_policy_linear, 3xTF32 on the tensor cores), '
+                     'moments, history roll, planner, step, GAE: this library; torch: two 48 x 48 weight folds, the '
+                     'Categorical draw and the rollout-buffer bookkeeping',
            'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}
     del roll, env, net
     torch.cuda.empty_cache()
