@@ -277,6 +277,11 @@ class DcaEnvGroups(object):
         self._each(one, sync)
         return self.obs, self.reward, self.done, self.win
 
+    def observe(self, sync=True):
+        """The observation pass alone on the resident state (DcaVecEnv.observe) for every group."""
+        self._each(lambda k, env, sl: env.observe(), sync)
+        return self.obs
+
     def kernel_launches(self):
         return sum(e.kernel_launches() for e in self.envs)
 

@@ -27,13 +27,65 @@ from hmp2g_b200.config import ScenarioConfig  # noqa: E402
 from hmp2g_b200.vec_env import DcaVecEnv  # noqa: E402
 
 
+def main_groups(args):
+    dev = torch.device('cuda', 0)
+    torch.cuda.set_device(dev)
+    scfg = type('BenchScenarioConfig', (ScenarioConfig,), dict(WORKLOAD))
+    n, Eg = args.groups, args.envs // args.groups
+    streams = [torch.cuda.Stream(device=dev) for _ in range(n)]
+    envs = []
+    for k in range(n):
+        with torch.cuda.stream(streams[k]):
+            env = DcaVecEnv(Eg, scfg=scfg, device=dev, seed=SEED, env_gid0=k * Eg)
+            env.lib.dca_set_option(env.handle, 2, 0)
+            env.reset()
+            envs.append(env)
+    lib = envs[0].lib
+    sp = [C.c_void_p(s.cuda_stream) for s in streams]
+    fp = [C.c_void_p(e._force.data_ptr()) for e in envs]
+    pool = [torch.randint(0, 7, (Eg, envs[0].G), device=dev, dtype=torch.int32) for _ in range(8)]
+    ap_ = [C.c_void_p(a.data_ptr()) for a in pool]
+    torch.cuda.synchronize()
+    for i in range(args.warm_steps):
+        for k in range(n):
+            lib.dca_plan_centroid(envs[k].handle, fp[k], sp[k])
+            lib.dca_step(envs[k].handle, ap_[i % 8], fp[k], None, None, 1, sp[k])
+
+    def launch(i):
+        for k in range(n):
+            if args.kernel == 'observe':
+                lib.dca_observe(envs[k].handle, None, sp[k])
+            else:
+                lib.dca_step(envs[k].handle, ap_[i % 8], fp[k], None, None, 1, sp[k])
+
+    for i in range(5):
+        launch(i)
+    torch.cuda.synchronize()
+    import time
+    rt = torch.cuda.cudart()
+    t0 = time.perf_counter()
+    rt.cudaProfilerStart()
+    for i in range(args.launches):
+        launch(i)
+    rt.cudaProfilerStop()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / args.launches
+    print('RANGE kernel=%s groups=%d passes=%d envs=%d ms_per_pass=%.5f (host clock around the synchronised range; not a '
+          'bench value under ncu)' % (args.kernel, n, args.launches, n * Eg, ms))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--kernel', default='observe', choices=['observe', 'step'])
     ap.add_argument('--launches', type=int, default=64)
     ap.add_argument('--envs', type=int, default=ENVS_PER_GPU)
     ap.add_argument('--warm-steps', type=int, default=60, help='env steps before the range (mid-episode state)')
+    ap.add_argument('--groups', type=int, default=1,
+                    help='the envs as this many independent groups on their own streams (DcaEnvGroups arrangement); '
+                         '--launches then counts launches PER GROUP, i.e. passes over all envs')
     args = ap.parse_args()
+    if args.groups > 1:
+        return main_groups(args)
     dev = torch.device('cuda', 0)
     torch.cuda.set_device(dev)
     scfg = type('BenchScenarioConfig', (ScenarioConfig,), dict(WORKLOAD))

@@ -38,8 +38,12 @@ def main():
         d['k_%s_range_seconds_per_launch_under_ncu' % k] = m.get('gpu__time_duration.sum', 0) / launches
         notes.append('k_%s: %.1f MB read + %.1f MB written per launch' % (
             k, m.get('dram__bytes_read.sum', 0) / launches / 1e6, m.get('dram__bytes_write.sum', 0) / launches / 1e6))
-    d['range_source'] = ('profiles/%s ncu --replay-mode range --cache-control none over %d back-to-back launches '
-                         '(tools/dram_range.py): ' % (tag, launches)) + '; '.join(notes)
+    key = 'range_source_two_groups' if any('two_groups' in s_ for s_ in sys.argv[3:]) else 'range_source'
+    d[key] = ('profiles/%s ncu --replay-mode range --cache-control none over %d back-to-back launches '
+              '(tools/dram_range.py): ' % (tag, launches)) + '; '.join(notes)
+    json.dump(d, open(p, 'w'), indent=1)
+    print(d[key])
+    return
     json.dump(d, open(p, 'w'), indent=1)
     print(d['range_source'])
 
