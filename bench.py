@@ -855,6 +855,9 @@ def run_ours(args):
                      'frac_synchronised_start': algo_bytes / (ms_step_sync_start * 1e-3) / 1e9 / peak,
                      'frac_episode_avg': algo_bytes / (ms_step_kernel_episode * 1e-3) / 1e9 / peak,
                      'dram_frac': dram_frac(ncu, 'k_step', ms_step_kernel_episode, peak, E, args.scenario),
+                     'dram_frac_timed_region': (dram_frac(ncu, 'k_step_two_groups', ms_total / K, peak, E, args.scenario)
+                                                if n_groups == 2 else None),
+                     'dram_frac_timed_region_source': ncu.get('range_source_two_groups') if n_groups == 2 else None,
                      'traffic_source': ncu.get('source')},
         'roofline_gather_kernel': {'bound': 'hbm', 'kernel': 'k_observe', 'unit': 'GB/s', 'peak': peak,
                                    'achieved': gather_bytes / (ms_gather * 1e-3) / 1e9,
