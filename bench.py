@@ -903,11 +903,11 @@ def run_ours(args):
         v, dt = cpu_port_run(n_cpu_env, cpu_steps, 5, cores)
         v0, _ = cpu_port_run(n_cpu_env, cpu_steps, 5, cores, full_planner=False)
         v1, dt1 = cpu_port_run(128, 40, 3, 1)
-        ref = reference_pool_run(args.scenario, 40, 5, procs=cores, fold=2)
+        ref = reference_pool_run(args.scenario, 360, 5, procs=cores, fold=2)  # two whole episodes, ~10 s
         if ref is not None:  # the reference's own path (SmartPool + SuperpoolEnv + MISSION/dca), staged in oracle/_ref
             line['cpu_baseline'] = {
                 'value': ref['agent_steps_per_sec'], 'unit': 'agent-steps/s', 'cores': cores, 'kind': 'reference',
-                'sample': '%d envs (%d worker processes x fold %d) x 40 steps of the same %s workload through the '
+                'sample': '%d envs (%d worker processes x fold %d) x 360 steps (two whole episodes) of the same %s workload through the '
                           'unmodified SuperpoolEnv.step, scripted attacker planner inside World.step (%.1f s)'
                           % (ref['envs'], ref['procs'], ref['fold'], args.scenario, ref['seconds']),
                 'port_value': v, 'port_value_without_planner': v0, 'port_single_core_value': v1,
