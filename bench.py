@@ -729,7 +729,38 @@ def run_ours(args):
     mt_bytes = E * mt.N * (12 * 17 * 4 + 2 * (6 * 8 + 5) + 4 + 4 + 1)
     mt_alive = float(mt.alive.float().mean().item())
     mt_N = mt.N
-    del mt, mt_pool
+    del mt
+    # the same envs as two groups of E / 2 on their own streams (contiguous global env ids: the same episodes)
+    mt_streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+    mt_g, mt_gp = [], []
+    for k in range(2):
+        with torch.cuda.stream(mt_streams[k]):
+            m_ = DcaMultiTeamVecEnv(E // 2, scfg=mt_cfg, device=dev, seed=SEED, env_gid0=rank * E + k * (E // 2))
+            m_.reset()
+            mt_g.append(m_)
+            mt_gp.append([p[k * (E // 2):(k + 1) * (E // 2)].contiguous() for p in mt_pool])
+    torch.cuda.synchronize()
+
+    def mt_group_step(i):
+        for k in range(2):
+            with torch.cuda.stream(mt_streams[k]):
+                mt_g[k].step(mt_gp[k][i % 8])
+    for i in range(20):
+        mt_group_step(i)
+    torch.cuda.synchronize()
+    g0.record(stream)
+    for s_ in mt_streams:
+        s_.wait_event(g0)
+    for i in range(Km):
+        mt_group_step(i)
+    for s_ in mt_streams:
+        ev_ = torch.cuda.Event()
+        ev_.record(s_)
+        stream.wait_event(ev_)
+    g1.record(stream)
+    torch.cuda.synchronize()
+    ms_mt_groups = g0.elapsed_time(g1) / Km
+    del mt_g, mt_gp, mt_pool
     # ---- BASELINE.json configs[2] / [3] at the same env count (extra report lines; not the headline)
     other = {}
     if args.scenario == '50v50' and not args.no_other_configs:
@@ -882,6 +913,10 @@ def run_ours(args):
                              'achieved': mt_bytes / (ms_mt * 1e-3) / 1e9, 'peak': peak,
                              'frac': mt_bytes / (ms_mt * 1e-3) / 1e9 / peak, 'alive_fraction_at_end': mt_alive,
                              'algorithmic_bytes_per_launch': mt_bytes,
+                             'two_groups': {'ms_per_step': ms_mt_groups,
+                                            'agent_steps_per_sec': E * mt_N / (ms_mt_groups * 1e-3),
+                                            'frac': mt_bytes / (ms_mt_groups * 1e-3) / 1e9 / peak,
+                                            'what': 'the same envs stepped as two groups of %d on their own streams' % (E // 2)},
                              'traffic': ncu.get('k_mt_step_dram_bytes_per_launch') if E == ncu.get('envs_per_gpu') else None},
         'gae_kernel': {'bound': 'hbm', 'kernel': 'k_gae', 'unit': 'GB/s',
                        'shape_TEG': [T, E, G], 'kernel_ms': ms_gae, 'achieved': gae_bytes / (ms_gae * 1e-3) / 1e9,
