@@ -555,6 +555,16 @@ def test_cuda_env_groups_are_bit_identical_to_one_env(groups):
             grp.step(acts[t % 8], planner='centroid', sync=False)
         grp.join()
         same(burst)
+    # ENV-PAUSE mask and injected attacker forces are handed to the groups as slices
+    force = torch.randn((E, 50, 2), generator=gen, device=one.device, dtype=torch.float64)
+    for t in range(6):
+        skip = (torch.rand((E,), generator=gen, device=one.device) < 0.3).to(torch.uint8)
+        one.step(acts[t % 8], force, skip=skip)
+        grp.step(acts[t % 8], att_force=force, skip=skip)
+        same(100 + t)
+    grp.observe()
+    one.observe()
+    same(200)
     assert grp.kernel_launches() >= groups * (1 + 2 * (45 + 60))
     grp.close()
 
