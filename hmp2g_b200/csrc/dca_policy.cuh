@@ -27,24 +27,31 @@ __global__ void __launch_bounds__(kNormThreads) k_norm_partial(const float4 *__r
     double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0}, nu[4] = {0, 0, 0, 0}, cnt = 0;
     const size_t rows_per_pass = (size_t)kNormBlocks * kNormThreads / 4;
     const size_t first = ((size_t)blockIdx.x * kNormThreads + (tid & ~31)) / 4;  // first row of this warp
-    for (size_t base = first; base < rows; base += rows_per_pass) {               // warp-uniform
-        const size_t row = base + (lane >> 2);
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        bool bad = true;
-        if (row < rows) {
-            v = x[row * 4 + quad];
-            bad = (v.x != v.x) || (v.y != v.y) || (v.z != v.z) || (v.w != v.w);
-        }
-        const unsigned b = __ballot_sync(full, bad);
-        if ((b >> (lane & ~3)) & 0xfu) continue;  // exclude_nan: a row with any NaN contributes nothing
-        const float e[4] = {v.x, v.y, v.z, v.w};
+    constexpr int U = 4;  // rows in flight per lane quad (one float4 per thread and pass kept HBM at 3 TB/s); the sums
+                          // take the rows in the same order as a one-row loop
+    for (size_t base = first; base < rows; base += U * rows_per_pass) {           // warp-uniform
+        float4 v[U];
+        bool in[U];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const double d = (double)e[k];
-            s[k] += d; q[k] += d * d;
-            if (!norm_unit(e[k])) nu[k] += 1.0;
+        for (int u = 0; u < U; ++u) {
+            const size_t row = base + u * rows_per_pass + (lane >> 2);
+            in[u] = row < rows;
+            v[u] = in[u] ? x[row * 4 + quad] : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        if (quad == 0) cnt += 1.0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const bool bad = !in[u] || (v[u].x != v[u].x) || (v[u].y != v[u].y) || (v[u].z != v[u].z) || (v[u].w != v[u].w);
+            const unsigned b = __ballot_sync(full, bad);
+            if ((b >> (lane & ~3)) & 0xfu) continue;  // exclude_nan: a row with any NaN contributes nothing
+            const float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const double d = (double)e[k];
+                s[k] += d; q[k] += d * d;
+                if (!norm_unit(e[k])) nu[k] += 1.0;
+            }
+            if (quad == 0) cnt += 1.0;
+        }
     }
     // lanes with the same quad hold the same four features: fold lane bits 2..4
 #pragma unroll
