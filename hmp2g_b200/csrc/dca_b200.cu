@@ -540,7 +540,7 @@ int dca_norm_moments(const float *x, uint64_t rows, int dim, double *scratch, do
     PtrDeviceGuard guard(x);
     cudaStream_t st = (cudaStream_t)stream;
     k_norm_partial<<<kNormBlocks, kNormThreads, 0, st>>>((const float4 *)x, (size_t)rows, scratch);
-    k_norm_final<<<1, 64, 0, st>>>(scratch, stats);
+    k_norm_final<<<1, kNormFinalThreads, 0, st>>>(scratch, stats);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_norm_moments: ") + cudaGetErrorString(e));
     return DCA_OK;
