@@ -121,6 +121,28 @@ def test_no_gpu_means_loud_failure_not_fallback():
     assert b'no CPU fallback' in lib.dca_last_error(None)
 
 
+def test_policy_entry_points_reject_bad_arguments_before_any_launch():
+    """Argument validation of the policy kernels' entry points happens on the host, before a device is touched: null
+    buffers, empty batches, widths the kernels do not cover, misaligned inputs -> DCA_E_INVALID with a message."""
+    from hmp2g_b200 import _lib
+    lib = _lib.load()
+    P = ctypes.c_void_p
+    buf = (ctypes.c_float * 64)()
+    a = P(ctypes.addressof(buf))
+    inv = -1  # DCA_E_INVALID
+    lin = lambda **kw: lib.dca_policy_linear(kw.get('a', a), kw.get('lda', 48), kw.get('ka', 48), kw.get('wa', a), 48, 1,
+                                             kw.get('b', None), kw.get('ldb', 0), kw.get('kb', 0), kw.get('wb', None), 0, 0,
+                                             None, kw.get('n', 48), 1, kw.get('rows', 1), kw.get('out', a), kw.get('ldo', 48), None)
+    assert lin(a=None) == inv and lin(out=None) == inv and lin(rows=0) == inv
+    assert lin(n=49) == inv and lin(ka=46) == inv and lin(lda=50) == inv and lin(ldo=40) == inv
+    assert lin(kb=48) == inv                       # a second input without its buffers
+    assert lin(a=P(ctypes.addressof(buf) + 4)) == inv   # inputs are read 16 bytes at a time
+    assert b'dca_policy_linear' in lib.dca_last_error(None)
+    assert lib.dca_policy_encode(None, a, a, a, a, a, a, 1, a, a, a, None) == inv
+    assert lib.dca_conc_attend(a, a, a, a, 0, 11, 2, 1, a, a, None) == inv   # entity 0 is the agent itself
+    assert lib.dca_norm_moments(None, 1, 16, a, a, None) == inv
+
+
 def test_product_never_touches_the_oracle():
     """Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may use oracle/."""
     pat = re.compile(r'(import|from)\s+\S*oracle|dca_oracle|oracle/|libdca_oracle|\borc_[a-z]+')
