@@ -59,7 +59,7 @@ class DcaMtState(C.Structure):
 EXPORTS = ('dca_abi_version', 'dca_last_error', 'dca_create', 'dca_destroy', 'dca_bind_buffers', 'dca_reset',
            'dca_step', 'dca_observe', 'dca_plan', 'dca_plan_centroid', 'dca_export_state', 'dca_import_state', 'dca_gae',
            'dca_kernel_launches', 'dca_debug_phase_clocks', 'dca_set_option', 'dca_runner_init', 'dca_runner_update',
-           'dca_runner_report', 'dca_histpool_roll', 'dca_adv_moments', 'dca_adv_normalize', 'dca_adv_moments_static', 'dca_norm_moments', 'dca_norm_apply', 'dca_conc_attend', 'dca_policy_encode', 'dca_policy_linear',
+           'dca_runner_report', 'dca_histpool_roll', 'dca_adv_moments', 'dca_adv_normalize', 'dca_adv_moments_static', 'dca_norm_moments', 'dca_norm_apply', 'dca_conc_attend', 'dca_conc_attend2', 'dca_policy_encode', 'dca_policy_linear',
            'dca_mt_create', 'dca_mt_destroy',
            'dca_mt_bind_buffers', 'dca_mt_reset', 'dca_mt_step', 'dca_mt_export_state', 'dca_mt_import_state', 'dca_mt_debug_phase_clocks')
 
@@ -109,6 +109,7 @@ def load(build_if_missing=False):
     lib.dca_norm_apply.argtypes = [_P, _P, _P, C.c_uint64, C.c_int, _P, _P, _P]
     lib.dca_policy_encode.argtypes = [_P, _P, _P, _P, _P, _P, _P, C.c_uint64, _P, _P, _P, _P]
     lib.dca_conc_attend.argtypes = [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, _P, _P, _P]
+    lib.dca_conc_attend2.argtypes = [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, _P, _P, _P, _P, _P]
     lib.dca_policy_linear.argtypes = [_P, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P, C.c_int, C.c_int,
                                       _P, C.c_int, C.c_int, C.c_uint64, _P, C.c_int, _P]
     lib.dca_mt_create.argtypes = [C.POINTER(DcaMtConfig), C.c_int, C.c_int, C.POINTER(_P)]

@@ -578,6 +578,34 @@ int dca_conc_attend(const float *v, const float *x, const uint8_t *dead, const f
     return DCA_OK;
 }
 
+int dca_conc_attend2(const float *v, const float *x, const uint8_t *dead, const float *qk_a, const float *qk_b, int first_a,
+                     int n_a, int focus_a, int n_b, int focus_b, uint64_t n_agent, float *va_a, float *stack_a, float *va_b,
+                     float *stack_b, dca_stream_t stream) {
+    if (!v || !x || !dead || !qk_a || !qk_b || !va_a || !stack_a || !va_b || !stack_b || n_agent == 0)
+        return fail(nullptr, DCA_E_INVALID, "dca_conc_attend2: null buffer or empty batch");
+    if (first_a < 1 || n_a < 1 || n_b < 1 || first_a + n_a + n_b > 24 || focus_a < 1 || focus_a > n_a || focus_b < 1 || focus_b > n_b)
+        return fail(nullptr, DCA_E_INVALID, "dca_conc_attend2: the two adjacent entity lists must lie in [1, 24), 1 <= n_focus <= n");
+    if (((uintptr_t)v | (uintptr_t)x | (uintptr_t)qk_a | (uintptr_t)qk_b) & 15)
+        return fail(nullptr, DCA_E_INVALID, "dca_conc_attend2: v, x and qk must be 16-byte aligned");
+    PtrDeviceGuard guard(v);
+    const int threads = 256, warps = threads / 32;
+    const size_t smem = sizeof(AttWarpSmem) * warps;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaError_t ea = cudaFuncSetAttribute(k_conc_attend2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (ea != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_conc_attend2: ") + cudaGetErrorString(ea));
+        attr_set[dev] = true;
+    }
+    const unsigned grid = (unsigned)((n_agent + warps - 1) / warps);
+    k_conc_attend2<<<grid, threads, smem, (cudaStream_t)stream>>>(v, x, dead, qk_a, qk_b, first_a, n_a, focus_a, n_b, focus_b,
+                                                                  (size_t)n_agent, va_a, stack_a, va_b, stack_b);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, DCA_E_CUDA, std::string("dca_conc_attend2: ") + cudaGetErrorString(e));
+    return DCA_OK;
+}
+
 int dca_policy_encode(const float *x, const float *mean, const float *var, const float *w1, const float *b1,
                       const float *w2, const float *b2, uint64_t rows, float *x_norm, uint8_t *row_nan, float *v,
                       dca_stream_t stream) {

@@ -208,6 +208,107 @@ __global__ void __launch_bounds__(256) k_conc_attend(const float *__restrict__ v
     }
 }
 
+// Both entity lists of an agent in one pass (conc_4hist: "current" then "history", adjacent in the 24 rows): the warp
+// first pulls the agent's whole block -- 24 encodings (4.6 KB, contiguous) and 24 observation rows (1.5 KB) -- into its
+// slice of shared memory with 16-byte cp.async copies, all in flight at once and fully coalesced (k_conc_attend's lanes
+// each walk their own 192-byte row: 12 dependent, uncoalesced loads per lane, DRAM at 44 % of peak), then does exactly
+// k_conc_attend's arithmetic in k_conc_attend's order for list a and for list b (same butterflies over the same lanes:
+// the results are bit-identical), reading rows from shared memory (row stride 52 floats: conflict-free 16-byte reads).
+// Lists: entities first_a .. first_a+n_a-1 and first_a+n_a .. first_a+n_a+n_b-1; n_a + n_b <= 32.
+__device__ __forceinline__ void enc_cp_async16(void *smem_dst, const void *gsrc);
+constexpr int kAttVs = 52;
+struct AttWarpSmem {
+    float v[kPolEnt][kAttVs];
+    float x[kPolEnt][kPolD];
+};
+__global__ void __launch_bounds__(256) k_conc_attend2(const float *__restrict__ v, const float *__restrict__ x,
+                                                       const uint8_t *__restrict__ dead, const float *__restrict__ qk_a,
+                                                       const float *__restrict__ qk_b, int first_a, int n_a, int focus_a,
+                                                       int n_b, int focus_b, size_t B, float *__restrict__ va_a,
+                                                       float *__restrict__ stack_a, float *__restrict__ va_b,
+                                                       float *__restrict__ stack_b) {
+    extern __shared__ __align__(16) unsigned char att_raw[];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t b = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= B) return;  // warp-uniform
+    AttWarpSmem &s = reinterpret_cast<AttWarpSmem *>(att_raw)[warp];
+    {
+        const float *vb = v + b * kPolEnt * kPolH, *xb = x + b * kPolEnt * kPolD;
+        for (int i = lane; i < kPolEnt * (kPolH / 4); i += 32) {
+            const int r = i / (kPolH / 4), q = i - r * (kPolH / 4);
+            enc_cp_async16(&s.v[r][q * 4], vb + i * 4);
+        }
+        for (int i = lane; i < kPolEnt * (kPolD / 4); i += 32) enc_cp_async16(&s.x[0][0] + i * 4, xb + i * 4);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    // dot products: lane L < n_a + n_b owns entity first_a + L (list a, then list b)
+    const int n_ab = n_a + n_b;
+    const bool mine = lane < n_ab && !dead[b * kPolEnt + first_a + lane];
+    const float4 *q4 = (const float4 *)((lane < n_a ? qk_a : qk_b) + b * kPolH);
+    float4 qv[kPolH / 4];
+#pragma unroll
+    for (int k = 0; k < kPolH / 4; ++k) qv[k] = q4[k];
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    float dot = -CUDART_INF_F;
+    if (mine) {
+        const float4 *row = (const float4 *)&s.v[first_a + lane][0];
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < kPolH / 4; ++k) {
+            const float4 a = row[k], q = qv[k];
+            acc = fmaf(a.x, q.x, acc); acc = fmaf(a.y, q.y, acc); acc = fmaf(a.z, q.z, acc); acc = fmaf(a.w, q.w, acc);
+        }
+        dot = acc * 0.14433756729740643f;  // 1 / sqrt(48)
+    }
+    const float dot_b = __shfl_sync(full, dot, (lane + n_a) & 31);  // list b's scores moved to lanes 0 .. n_b-1
+#pragma unroll 1
+    for (int list = 0; list < 2; ++list) {
+        const int first = list == 0 ? first_a : first_a + n_a, n = list == 0 ? n_a : n_b, n_focus = list == 0 ? focus_a : focus_b;
+        float *va = list == 0 ? va_a : va_b, *stack = list == 0 ? stack_a : stack_b;
+        const float compat = lane < n ? (list == 0 ? dot : dot_b) : -CUDART_INF_F;
+        float mx = compat;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(full, mx, o));
+        const float ex = (lane < n && compat > -CUDART_INF_F) ? expf(compat - mx) : 0.f;
+        float sum = ex;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(full, sum, o);
+        const float score = sum > 0.f ? __fdiv_rn(ex, sum) : 0.f;
+        {
+            float a0 = 0.f, a1 = 0.f;
+            for (int j = 0; j < n; ++j) {
+                const float sj = __shfl_sync(full, score, j);
+                const float *row = s.v[first + j];
+                a0 = fmaf(sj, row[lane], a0);
+                if (lane < kPolH - 32) a1 = fmaf(sj, row[32 + lane], a1);
+            }
+            va[b * kPolH + lane] = a0;
+            if (lane < kPolH - 32) va[b * kPolH + 32 + lane] = a1;
+        }
+        const int row_len = kPolH + kPolD;  // 64
+        float *sb = stack + b * (size_t)(n_focus + 1) * row_len;
+        {
+            sb[lane] = s.v[0][lane];
+            if (lane < kPolH - 32) sb[32 + lane] = s.v[0][32 + lane];
+            else sb[32 + lane] = s.x[0][lane - (kPolH - 32)];
+        }
+        unsigned taken = 0;
+        for (int r = 1; r <= n_focus; ++r) {
+            const unsigned key = (lane < n && !((taken >> lane) & 1u)) ? __float_as_uint(score) + 1u : 0u;
+            const unsigned best = __reduce_max_sync(full, key);
+            const int j = __ffs(__ballot_sync(full, key == best && key != 0u)) - 1;
+            taken |= 1u << j;
+            const float *vr = s.v[first + j], *xr = s.x[first + j];
+            float *o = sb + r * row_len;
+            o[lane] = vr[lane];
+            if (lane < kPolH - 32) o[32 + lane] = vr[32 + lane];
+            else o[32 + lane] = xr[lane - (kPolH - 32)];
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // The observation encoder of the conc / conc_4hist policy on every entity row (Net._act ALGORITHM/conc_4hist/net.py:
 // 194-199): DynamicNorm apply + mask + nan_to_num (as k_norm_apply) + AT_obs_encoder = Linear(16,48), ReLU,

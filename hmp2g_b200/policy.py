@@ -172,6 +172,18 @@ class ConcCore(nn.Module):
         v_c = self.AT_forward_mlp(stack.reshape(stack.shape[0], -1))
         return v_c, v_m
 
+    def qk_fused(self, vs):
+        """(vs W_query) W_key^T = vs (W_query W_key^T): the 48 x 48 product once per call instead of a second [B,48] pass."""
+        return _plin(vs, (self.CT_W_query @ self.CT_W_key.t()).t())
+
+    def post_fused(self, vs, va, stack):
+        """The layers behind the attention kernel: -> (v_C, v_M)."""
+        lin, fwd = self.CT_motivate_mlp[0], self.AT_forward_mlp[0]
+        fold = self.CT_W_val @ lin.weight[:, self.h_dim:].t()   # (va W_val) Wm2^T = va (W_val Wm2^T)
+        v_m = _plin(vs, lin.weight[:, :self.h_dim], va, fold.t(), lin.bias, relu=True)
+        v_c = _plin(stack, fwd.weight, bias=fwd.bias, relu=True)
+        return v_c, v_m
+
     def forward_fused(self, v, x, dead_u8, first, n):
         """The same on the whole [B,24,*] tensors with the part between the matrix products in one kernel
         (dca_conc_attend: scores, masked softmax, attended encoding, stable top-n_focus gather): v f32 [B,24,h] entity
@@ -179,19 +191,13 @@ class ConcCore(nn.Module):
         lib = _lib.load()
         B = v.shape[0]
         vs = v[:, 0]
-        # (vs W_query) W_key^T = vs (W_query W_key^T): the 48 x 48 product once per call instead of a second [B,48] pass
-        qk = _plin(vs, (self.CT_W_query @ self.CT_W_key.t()).t())
+        qk = self.qk_fused(vs)
         va = torch.empty((B, self.h_dim), dtype=torch.float32, device=v.device)
         stack = torch.empty((B, (self.n_focus_on + 1) * (self.h_dim + x.shape[-1])), dtype=torch.float32, device=v.device)
         stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
         _lib.check(lib.dca_conc_attend(_ptr(v), _ptr(x), _ptr(dead_u8), _ptr(qk), first, n, self.n_focus_on, B, _ptr(va),
                                        _ptr(stack), stream))
-        # (va W_val) Wm2^T = va (W_val Wm2^T): the 48 x 48 product once per call instead of a [B,48] x [48,48] pass
-        lin, fwd = self.CT_motivate_mlp[0], self.AT_forward_mlp[0]
-        fold = self.CT_W_val @ lin.weight[:, self.h_dim:].t()
-        v_m = _plin(vs, lin.weight[:, :self.h_dim], va, fold.t(), lin.bias, relu=True)
-        v_c = _plin(stack, fwd.weight, bias=fwd.bias, relu=True)
-        return v_c, v_m
+        return self.post_fused(vs, va, stack)
 
 
 class ConcNet4Hist(nn.Module):
@@ -222,6 +228,7 @@ class ConcNet4Hist(nn.Module):
         return net.to(device)
 
     fused = True  # dca_policy_encode / dca_conc_attend instead of torch elementwise + GEMM + bmm / sort / gather passes
+    attend_both = True  # fused path: dca_conc_attend2 (both entity lists in one kernel) instead of two dca_conc_attend
 
     def encode_fused(self, obs_feed):
         """DynamicNorm apply + mask + AT_obs_encoder in one kernel: -> (x f32 [B,24,D], dead u8 [B,24], v f32 [B,24,H])."""
@@ -274,8 +281,22 @@ class ConcNet4Hist(nn.Module):
             if self._batch_norm.training:
                 self._batch_norm.update(obs_feed)
             x, dead_u8, v = self.encode_fused(obs_feed)
-            vf_c, vf_m = self.MIX_conc_core_f.forward_fused(v, x, dead_u8, 1, 11)
-            vh_c, vh_m = self.MIX_conc_core_h.forward_fused(v, x, dead_u8, 12, 12)
+            cf, ch = self.MIX_conc_core_f, self.MIX_conc_core_h
+            if self.attend_both:   # both entity lists in one attention kernel (dca_conc_attend2)
+                vs, B, h, d = v[:, 0], v.shape[0], self.H, self.rawob_dim
+                qk_f, qk_h = cf.qk_fused(vs), ch.qk_fused(vs)
+                new = lambda n: torch.empty((B, n), dtype=torch.float32, device=v.device)
+                va_f, va_h = new(h), new(h)
+                st_f, st_h = new((cf.n_focus_on + 1) * (h + d)), new((ch.n_focus_on + 1) * (h + d))
+                stream = C.c_void_p(torch.cuda.current_stream(v.device).cuda_stream)
+                _lib.check(_lib.load().dca_conc_attend2(_ptr(v), _ptr(x), _ptr(dead_u8), _ptr(qk_f), _ptr(qk_h), 1, 11,
+                                                        cf.n_focus_on, 12, ch.n_focus_on, B, _ptr(va_f), _ptr(st_f),
+                                                        _ptr(va_h), _ptr(st_h), stream))
+                vf_c, vf_m = cf.post_fused(vs, va_f, st_f)
+                vh_c, vh_m = ch.post_fused(vs, va_h, st_h)
+            else:
+                vf_c, vf_m = cf.forward_fused(v, x, dead_u8, 1, 11)
+                vh_c, vh_m = ch.forward_fused(v, x, dead_u8, 12, 12)
             logits, value, threat = self._tail_fused(vf_c, vf_m, vh_c, vh_m, need_threat)
             return (logits.reshape(*lead, self.n_action), value.reshape(lead),
                     threat.reshape(lead) if need_threat else None)

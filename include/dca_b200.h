@@ -240,6 +240,13 @@ int dca_policy_linear(const float *a, int lda, int ka, const float *wa, int wa_s
 int dca_conc_attend(const float *v, const float *x, const uint8_t *dead, const float *qk, int first, int n, int n_focus,
                     uint64_t n_agent, float *va, float *stack, dca_stream_t stream);
 
+/* dca_conc_attend for two adjacent entity lists of every agent in one pass (conc_4hist: entities 1..11 and 12..23,
+ * ALGORITHM/conc_4hist/net.py:170-181,205-207): list a = entities first_a .. first_a+n_a-1 with qk_a / focus_a, list b the
+ * n_b entities behind it with qk_b / focus_b.  Outputs as two dca_conc_attend calls, bit for bit. */
+int dca_conc_attend2(const float *v, const float *x, const uint8_t *dead, const float *qk_a, const float *qk_b, int first_a,
+                     int n_a, int focus_a, int n_b, int focus_b, uint64_t n_agent, float *va_a, float *stack_a, float *va_b,
+                     float *stack_b, dca_stream_t stream);
+
 /* ---- dca_multiteam -------------------------------------------------------------------------------------------------
  * The sibling env MISSION/dca_multiteam (N teams, every agent policy-controlled, per-hit success draw, shrinking kill
  * circle, team ranking).  Same conventions as the dca_* calls above. */

@@ -174,6 +174,12 @@ def test_fused_attention_kernel_matches_the_torch_path():
             lt, vt, tt = net.heads(x)
         finally:
             ConcNet4Hist.fused = True
+        ConcNet4Hist.attend_both = False   # the one-list attention kernel, twice: bit-identical to the two-list kernel
+        try:
+            l1, v1, t1 = net.heads(x)
+        finally:
+            ConcNet4Hist.attend_both = True
+        assert torch.equal(l1, lf) and torch.equal(v1, vf) and torch.equal(t1, tf)
         # picks can only differ where the two softmax implementations disagree on whether a score underflows to exactly 0
         bad = ((lf - lt).abs() > 1e-4 + 1e-4 * lt.abs()).any(-1).float().mean().item()
         print('fused vs torch: %.5f%% of agents with a different pick' % (100 * bad))
