@@ -110,6 +110,32 @@ def test_net_matches_reference_net_on_reference_observations():
     assert np.abs(freq - probs[0, 0]).max() < 0.02
 
 
+def test_encoder_normalisation_is_bit_identical_to_the_division_kernel():
+    """The normalised rows and row masks that dca_policy_encode writes next to the encodings must agree bit for bit with
+    dca_norm_apply (the stand-alone DynamicNorm apply kernel, pinned against the reference's fixtures): on the reference
+    observations and on random rows / random moments (tiny and huge spreads, NaN rows, a constant feature)."""
+    import torch
+    from hmp2g_b200.policy import ConcNet4Hist
+    z = _fixture()
+    net = _net(z, torch).eval()
+    g = torch.Generator(device='cuda'); g.manual_seed(11)
+    feeds = [torch.from_numpy(z['obs_feed']).cuda()]
+    for scale in (1e-3, 1.0, 37.0):
+        xb = torch.randn((64, 50, 24, 16), device='cuda', generator=g) * scale
+        xb[torch.rand((64, 50, 24), device='cuda', generator=g) < 0.3] = float('nan')
+        xb[..., 5] = 0.0   # a constant feature: (0 - mean) / sd and exact zeros
+        feeds.append(xb)
+    bn = net._batch_norm
+    for i, x in enumerate(feeds):
+        if i:
+            bn.mean.copy_(torch.randn(16, device='cuda', generator=g) * (10.0 ** (i - 2)))
+            bn.var.copy_(torch.rand(16, device='cuda', generator=g) * (10.0 ** (2 * i - 4)) + 1e-12)
+        xn, dead, _ = net.encode_fused(x.contiguous())
+        want, mask = bn.apply_norm(x.contiguous())
+        assert torch.equal(xn.reshape(-1).view(torch.int32), want.reshape(-1).view(torch.int32)), i
+        assert torch.equal(dead.reshape(-1), mask.reshape(-1)), i
+
+
 def test_policy_linear_kernel_matches_float64_reference():
     """dca_policy_linear: act(a Wa^T + b Wb^T + bias) for the layer shapes of the policy -- ragged row counts, inputs
     that are column slices of wider tensors, weight halves and transposed weights, N = 48 / 24 / 7 / 1."""
