@@ -78,6 +78,11 @@ def run(groups, piped, E=4096, steps=720, preroll=True, overlap=True, scripted=F
 
 
 if __name__ == '__main__':
+    if len(sys.argv) > 1 and sys.argv[1] == 'sweep':   # SURVEY.md 8(d) E sweep, one pipelined group against two groups
+        for E in (1024, 2048, 4096, 8192, 16384, 32768):
+            run(1, True, E=E, steps=360 if E <= 8192 else 180)
+            run(2, False, E=E, steps=360 if E <= 8192 else 180)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == 'noplan':
         run(2, False)
         for groups in (2, 3, 4):
