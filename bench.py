@@ -479,7 +479,8 @@ def run_ours(args):
     # ---- the headline region with --env-groups n > 1: the E envs as n independent groups (DcaEnvGroups: E / n envs
     # each, contiguous global env ids, own streams; same results as one group, tests/test_gpu_parity.py) -- one group's
     # CTAs fill the slots the other group's launch boundary leaves empty.  Per-env pipelining is off in the groups.
-    n_groups = args.env_groups if args.env_groups > 0 else (2 if args.planner == 'centroid' else 1)
+    # (auto: two groups from one full wave of CTAs per group upwards -- profiles/r2_cn_E_sweep_groups.txt)
+    n_groups = args.env_groups if args.env_groups > 0 else (2 if args.planner == 'centroid' and E >= 4096 else 1)
     grouped = None
     if n_groups > 1:
         from hmp2g_b200.vec_env import DcaEnvGroups
@@ -974,7 +975,7 @@ def main():
                     help='attacker forces: the centroid stand-in of configs[1] (default) or the scripted formation planner k_plan')
     ap.add_argument('--env-groups', type=int, default=0,
                     help='step the envs as this many independent groups on their own streams (DcaEnvGroups); '
-                         '0 = 2 with the centroid stand-in, 1 with --planner scripted')
+                         '0 = 2 with the centroid stand-in at 4096 envs per GPU or more, else 1')
     ap.add_argument('--no-preroll', action='store_true',
                     help='time from a synchronised reset of all envs instead of the stationary episode-phase mix')
     ap.add_argument('--no-pipeline', action='store_true',
