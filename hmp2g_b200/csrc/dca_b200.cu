@@ -630,7 +630,7 @@ int dca_policy_encode(const float *x, const float *mean, const float *var, const
     k_policy_encode<<<grid, kEncThreads, sizeof(EncSmem), (cudaStream_t)stream>>>(
         (const float4 *)x, mean, var, w1, b1, w2, b2, (size_t)rows, (float4 *)x_norm, row_nan, v);
 #else
-    const unsigned grid = (unsigned)std::min<size_t>((rows + kEncTcTile - 1) / kEncTcTile, 148 * 3);
+    const unsigned grid = (unsigned)std::min<size_t>((rows + kEncTcTile - 1) / kEncTcTile, 148 * 2);
     k_policy_encode_tc<<<grid, kEncTcThreads, sizeof(EncTcSmem), (cudaStream_t)stream>>>(
         (const float4 *)x, mean, var, w1, b1, w2, b2, (size_t)rows, (float4 *)x_norm, row_nan, v);
 #endif

@@ -738,15 +738,15 @@ __global__ void __launch_bounds__(kLinThreads) k_policy_linear_tc(const LinSrc s
 // into tf32 head / tail once per CTA and stay in shared memory k-major (stride 56: conflict-free B fragment loads).
 constexpr int kEncXs = 20, kEncHs = 52;  // row strides (floats): g * stride + t hits 32 distinct banks for g < 8, t < 4
 constexpr int kEncTcThreads = 256, kEncTcWarps = kEncTcThreads / 32, kEncTcTile = kEncTcWarps * 32;
-struct EncTcSmem {  // 66 KB: three CTAs = 24 warps per SM (a first version with 128 rows of hs per 128 threads: 12)
+struct EncTcSmem {  // 102 KB: two CTAs = 16 warps per SM
     float w1h[kPolD][kLinWStride], w1l[kPolD][kLinWStride];
     float w2h[kPolH][kLinWStride], w2l[kPolH][kLinWStride];
     float b1[kPolH], b2[kPolH];
-    float xs[kEncTcWarps][16][kEncXs];  // per warp: the 16 rows of the half tile in work
-    float hs[kEncTcWarps][16][kEncHs];
+    float xs[kEncTcWarps][32][kEncXs];  // per warp: its 32 rows of the tile in work
+    float hs[kEncTcWarps][32][kEncHs];
 };
 
-__global__ void __launch_bounds__(kEncTcThreads, 3) k_policy_encode_tc(const float4 *__restrict__ x, const float *__restrict__ mean,
+__global__ void __launch_bounds__(kEncTcThreads, 2) k_policy_encode_tc(const float4 *__restrict__ x, const float *__restrict__ mean,
                                                                     const float *__restrict__ var,
                                                                     const float *__restrict__ w1, const float *__restrict__ b1,
                                                                     const float *__restrict__ w2, const float *__restrict__ b2,
@@ -810,73 +810,96 @@ __global__ void __launch_bounds__(kEncTcThreads, 3) k_policy_encode_tc(const flo
                 if (quad == 0) row_nan[row] = ((bb >> lane) & 0xfu) != 0;
             }
         }
+        __syncwarp();  // the previous tile's xs / hs have been consumed
 #pragma unroll
-        for (int mt = 0; mt < 2; ++mt) {  // half tiles of 16 rows: slots 2 mt and 2 mt + 1
-            __syncwarp();  // the previous half's xs / hs have been consumed
-            *(float4 *)&xs[g][quad * 4] = raw[2 * mt];
-            *(float4 *)&xs[g + 8][quad * 4] = raw[2 * mt + 1];
-            __syncwarp();
-            float acc[6][4];
-            // ---- layer 1: h = relu(x w1^T + b1), 16 rows x 48 columns, K = 16
+        for (int q = 0; q < 4; ++q) *(float4 *)&xs[g + 8 * q][quad * 4] = raw[q];
+        __syncwarp();
+        // Both 16-row halves go through a k-step together, so a B fragment (weights) is read from shared memory once
+        // per 32 rows: with one half at a time the kernel sat at 73 % of the shared-memory throughput.
+        float acc[2][6][4];
+        // ---- layer 1: h = relu(x w1^T + b1), 32 rows x 48 columns, K = 16
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < 6; ++nt) {
-                acc[nt][0] = acc[nt][2] = s.b1[nt * 8 + 2 * t];
-                acc[nt][1] = acc[nt][3] = s.b1[nt * 8 + 2 * t + 1];
+                acc[mt][nt][0] = acc[mt][nt][2] = s.b1[nt * 8 + 2 * t];
+                acc[mt][nt][1] = acc[mt][nt][3] = s.b1[nt * 8 + 2 * t + 1];
             }
 #pragma unroll
-            for (int ks = 0; ks < kPolD; ks += 8) {
+        for (int ks = 0; ks < kPolD; ks += 8) {
+            uint32_t bh[6][2], bl[6][2];
+#pragma unroll
+            for (int nt = 0; nt < 6; ++nt) {
+                bh[nt][0] = __float_as_uint(s.w1h[ks + t][nt * 8 + g]); bh[nt][1] = __float_as_uint(s.w1h[ks + t + 4][nt * 8 + g]);
+                bl[nt][0] = __float_as_uint(s.w1l[ks + t][nt * 8 + g]); bl[nt][1] = __float_as_uint(s.w1l[ks + t + 4][nt * 8 + g]);
+            }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                const int row = mt * 16 + g;
                 uint32_t ah[4], al[4];
-                tf32_split(xs[g][ks + t], ah[0], al[0]);
-                tf32_split(xs[g + 8][ks + t], ah[1], al[1]);
-                tf32_split(xs[g][ks + t + 4], ah[2], al[2]);
-                tf32_split(xs[g + 8][ks + t + 4], ah[3], al[3]);
+                tf32_split(xs[row][ks + t], ah[0], al[0]);
+                tf32_split(xs[row + 8][ks + t], ah[1], al[1]);
+                tf32_split(xs[row][ks + t + 4], ah[2], al[2]);
+                tf32_split(xs[row + 8][ks + t + 4], ah[3], al[3]);
 #pragma unroll
                 for (int nt = 0; nt < 6; ++nt) {
-                    const uint32_t bh[2] = {__float_as_uint(s.w1h[ks + t][nt * 8 + g]), __float_as_uint(s.w1h[ks + t + 4][nt * 8 + g])};
-                    const uint32_t bl[2] = {__float_as_uint(s.w1l[ks + t][nt * 8 + g]), __float_as_uint(s.w1l[ks + t + 4][nt * 8 + g])};
-                    mma_tf32(acc[nt], al, bh);
-                    mma_tf32(acc[nt], ah, bl);
-                    mma_tf32(acc[nt], ah, bh);
+                    mma_tf32(acc[mt][nt], al, bh[nt]);
+                    mma_tf32(acc[mt][nt], ah, bl[nt]);
+                    mma_tf32(acc[mt][nt], ah, bh[nt]);
                 }
             }
+        }
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < 6; ++nt) {
-                *(float2 *)&hs[g][nt * 8 + 2 * t] = make_float2(fmaxf(acc[nt][0], 0.f), fmaxf(acc[nt][1], 0.f));
-                *(float2 *)&hs[g + 8][nt * 8 + 2 * t] = make_float2(fmaxf(acc[nt][2], 0.f), fmaxf(acc[nt][3], 0.f));
+                *(float2 *)&hs[mt * 16 + g][nt * 8 + 2 * t] = make_float2(fmaxf(acc[mt][nt][0], 0.f), fmaxf(acc[mt][nt][1], 0.f));
+                *(float2 *)&hs[mt * 16 + g + 8][nt * 8 + 2 * t] = make_float2(fmaxf(acc[mt][nt][2], 0.f), fmaxf(acc[mt][nt][3], 0.f));
             }
-            __syncwarp();
-            // ---- layer 2: v = h w2^T + b2, K = 48
+        __syncwarp();
+        // ---- layer 2: v = h w2^T + b2, K = 48
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < 6; ++nt) {
-                acc[nt][0] = acc[nt][2] = s.b2[nt * 8 + 2 * t];
-                acc[nt][1] = acc[nt][3] = s.b2[nt * 8 + 2 * t + 1];
+                acc[mt][nt][0] = acc[mt][nt][2] = s.b2[nt * 8 + 2 * t];
+                acc[mt][nt][1] = acc[mt][nt][3] = s.b2[nt * 8 + 2 * t + 1];
             }
-#pragma unroll 2
-            for (int ks = 0; ks < kPolH; ks += 8) {
+#pragma unroll 1
+        for (int ks = 0; ks < kPolH; ks += 8) {
+            uint32_t bh[6][2], bl[6][2];
+#pragma unroll
+            for (int nt = 0; nt < 6; ++nt) {
+                bh[nt][0] = __float_as_uint(s.w2h[ks + t][nt * 8 + g]); bh[nt][1] = __float_as_uint(s.w2h[ks + t + 4][nt * 8 + g]);
+                bl[nt][0] = __float_as_uint(s.w2l[ks + t][nt * 8 + g]); bl[nt][1] = __float_as_uint(s.w2l[ks + t + 4][nt * 8 + g]);
+            }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                const int row = mt * 16 + g;
                 uint32_t ah[4], al[4];
-                tf32_split(hs[g][ks + t], ah[0], al[0]);
-                tf32_split(hs[g + 8][ks + t], ah[1], al[1]);
-                tf32_split(hs[g][ks + t + 4], ah[2], al[2]);
-                tf32_split(hs[g + 8][ks + t + 4], ah[3], al[3]);
+                tf32_split(hs[row][ks + t], ah[0], al[0]);
+                tf32_split(hs[row + 8][ks + t], ah[1], al[1]);
+                tf32_split(hs[row][ks + t + 4], ah[2], al[2]);
+                tf32_split(hs[row + 8][ks + t + 4], ah[3], al[3]);
 #pragma unroll
                 for (int nt = 0; nt < 6; ++nt) {
-                    const uint32_t bh[2] = {__float_as_uint(s.w2h[ks + t][nt * 8 + g]), __float_as_uint(s.w2h[ks + t + 4][nt * 8 + g])};
-                    const uint32_t bl[2] = {__float_as_uint(s.w2l[ks + t][nt * 8 + g]), __float_as_uint(s.w2l[ks + t + 4][nt * 8 + g])};
-                    mma_tf32(acc[nt], al, bh);
-                    mma_tf32(acc[nt], ah, bl);
-                    mma_tf32(acc[nt], ah, bh);
+                    mma_tf32(acc[mt][nt], al, bh[nt]);
+                    mma_tf32(acc[mt][nt], ah, bl[nt]);
+                    mma_tf32(acc[mt][nt], ah, bh[nt]);
                 }
             }
+        }
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const size_t grow = r0 + mt * 16 + g + 8 * h;
                 if (grow < rows) {
 #pragma unroll
                     for (int nt = 0; nt < 6; ++nt)
-                        *(float2 *)(v + grow * kPolH + nt * 8 + 2 * t) = make_float2(acc[nt][2 * h], acc[nt][2 * h + 1]);
+                        *(float2 *)(v + grow * kPolH + nt * 8 + 2 * t) = make_float2(acc[mt][nt][2 * h], acc[mt][nt][2 * h + 1]);
                 }
             }
-        }
     }
 }
 
